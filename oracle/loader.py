@@ -1,0 +1,133 @@
+"""ctypes loaders for the checker libraries.  TEST INFRASTRUCTURE ONLY.
+
+Only tests/, __graft_entry__.smoke() and bench.py (cpu_baseline leg,
+--impl reference, and synthetic-input generation with the reference's own
+generator) may import this module.  The product (spmm-research_b200/) never does.
+
+  oracle()   -> oracle/liboracle.so        our C restatement (oracle/spmm_oracle.c)
+  ref()      -> oracle/_ref/libspmm_ref.so the reference's compute_csr + partitioner macros
+  merge_ref()-> oracle/_ref/libmerge_ref.so the reference's CPU merge-path code
+  amg()      -> oracle/_ref/libamg_ref.so  the reference's artificial-matrix-generator
+"""
+import ctypes as C
+import os
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+_i32p = np.ctypeslib.ndpointer(np.int32, flags="C_CONTIGUOUS")
+_i64p = np.ctypeslib.ndpointer(np.int64, flags="C_CONTIGUOUS")
+_f64p = np.ctypeslib.ndpointer(np.float64, flags="C_CONTIGUOUS")
+_cache = {}
+
+
+def _load(path):
+    if path not in _cache:
+        if not os.path.exists(path):
+            raise FileNotFoundError(
+                f"{path} missing: run `make -C oracle oracle ref` (ref needs /root/reference)")
+        _cache[path] = C.CDLL(path)
+    return _cache[path]
+
+
+def have_ref():
+    return all(os.path.exists(os.path.join(HERE, "_ref", f))
+               for f in ("libspmm_ref.so", "libamg_ref.so", "libmerge_ref.so"))
+
+
+def oracle():
+    lib = _load(os.path.join(HERE, "liboracle.so"))
+    if not hasattr(lib, "_typed"):
+        lib.oracle_spmm_csr.argtypes = [_i32p, _i32p, _f64p, C.c_long, C.c_long, _f64p, _f64p, C.c_int]
+        lib.oracle_spmm_csr.restype = None
+        lib.oracle_spmm_merge.argtypes = [_i32p, _i32p, _f64p, C.c_long, C.c_long, _f64p, _f64p, C.c_int, C.c_int]
+        lib.oracle_spmm_merge.restype = None
+        lib.oracle_balance_prefix_sums.argtypes = [_i32p, C.c_long, C.c_long, C.c_long, _i64p]
+        lib.oracle_balance_iterations.argtypes = [C.c_long, C.c_long, C.c_long, _i64p]
+        lib.oracle_merge_partition.argtypes = [_i32p, C.c_long, C.c_long, C.c_long, _i64p]
+        lib.oracle_fnv1a64.argtypes = [C.c_void_p, C.c_size_t]
+        lib.oracle_fnv1a64.restype = C.c_uint64
+        lib.oracle_num_threads.restype = C.c_int
+        lib._typed = True
+    return lib
+
+
+def ref():
+    lib = _load(os.path.join(HERE, "_ref", "libspmm_ref.so"))
+    if not hasattr(lib, "_typed"):
+        lib.ref_spmm_csr.argtypes = [_i32p, _i32p, _f64p, C.c_long, C.c_long, C.c_long, _f64p, _f64p, C.c_int]
+        lib.ref_spmm_csr.restype = None
+        lib.ref_spmm_csr_nocopy.argtypes = lib.ref_spmm_csr.argtypes
+        lib.ref_spmm_csr_nocopy.restype = None
+        lib.ref_balance_prefix_sums.argtypes = [_i32p, C.c_long, C.c_long, C.c_long, _i64p]
+        lib.ref_balance_prefix_sums_pairs.argtypes = [_i32p, C.c_long, C.c_long, C.c_long, _i64p]
+        lib.ref_balance_iterations.argtypes = [C.c_long, C.c_long, C.c_long, _i64p]
+        lib.ref_num_threads.restype = C.c_int
+        lib._typed = True
+    return lib
+
+
+def merge_ref():
+    lib = _load(os.path.join(HERE, "_ref", "libmerge_ref.so"))
+    if not hasattr(lib, "_typed"):
+        lib.ref_merge_partition.argtypes = [_i32p, C.c_long, C.c_long, C.c_long, _i64p]
+        lib.ref_spmv_merge.argtypes = [_i32p, _i32p, _f64p, C.c_long, C.c_long, _f64p, _f64p, C.c_int]
+        lib.ref_spmv_merge.restype = None
+        lib._typed = True
+    return lib
+
+
+class _CsrHead(C.Structure):
+    # leading fields of struct csr_matrix (artificial_matrix_generation.h:10-17)
+    _fields_ = [("row_ptr", C.POINTER(C.c_int)), ("col_ind", C.POINTER(C.c_int)),
+                ("values", C.POINTER(C.c_double)),
+                ("nr_rows", C.c_uint), ("nr_cols", C.c_uint), ("nr_nzeros", C.c_uint)]
+
+
+def amg():
+    lib = _load(os.path.join(HERE, "_ref", "libamg_ref.so"))
+    if not hasattr(lib, "_typed"):
+        lib.artificial_matrix_generation.argtypes = [
+            C.c_long, C.c_long, C.c_double, C.c_double, C.c_char_p, C.c_uint, C.c_char_p,
+            C.c_double, C.c_double, C.c_double, C.c_double]
+        lib.artificial_matrix_generation.restype = C.POINTER(_CsrHead)
+        lib.free_csr_matrix.argtypes = [C.POINTER(_CsrHead)]
+        lib._typed = True
+    return lib
+
+
+def generate(args):
+    """Run the reference generator.  `args` is the harness's positional order
+    (spmv_bench.cpp:851-862): rows cols avg std distribution placement bw skew
+    neighbours cross_row_similarity seed -- a string or a sequence.
+    Returns (row_ptr int32[m+1], col_ind int32[nnz], values f64[nnz], m, c)."""
+    if isinstance(args, str):
+        args = args.split()
+    rows, cols, avg, std, distr, place, bw, skew, neigh, crs, seed = args[:11]
+    lib = amg()
+    p = lib.artificial_matrix_generation(
+        int(rows), int(cols), float(avg), float(std), str(distr).encode(), int(seed),
+        str(place).encode(), float(bw), float(skew), float(neigh), float(crs))
+    h = p.contents
+    m, c, nnz = int(h.nr_rows), int(h.nr_cols), int(h.nr_nzeros)
+    ia = np.ctypeslib.as_array(h.row_ptr, shape=(m + 1,)).astype(np.int32, copy=True)
+    ja = np.ctypeslib.as_array(h.col_ind, shape=(max(nnz, 1),))[:nnz].astype(np.int32, copy=True)
+    a = np.ctypeslib.as_array(h.values, shape=(max(nnz, 1),))[:nnz].astype(np.float64, copy=True)
+    lib.free_csr_matrix(p)
+    return ia, ja, a, m, c
+
+
+def fnv(arr):
+    arr = np.ascontiguousarray(arr)
+    return "%016x" % oracle().oracle_fnv1a64(arr.ctypes.data, arr.nbytes)
+
+
+def spmm_oracle(ia, ja, a, m, c, x, k):
+    y = np.empty(m * k, dtype=np.float64)
+    oracle().oracle_spmm_csr(ia, ja, a, m, c, x, y, k)
+    return y
+
+
+def spmm_ref(ia, ja, a, m, c, x, k):
+    y = np.empty(m * k, dtype=np.float64)
+    ref().ref_spmm_csr(ia, ja, a, m, c, len(ja), x, y, k)
+    return y

@@ -1,0 +1,229 @@
+/*
+ * spmm_oracle.c -- CPU restatement of the reference's SpMM hot path.
+ *
+ * TEST INFRASTRUCTURE ONLY.  Nothing under spmm-research_b200/ (the product) may
+ * link, import or execute this file; only tests/, __graft_entry__.smoke() and
+ * bench.py's cpu_baseline / --impl reference legs use it, and there only as
+ * the checker / the timed CPU baseline.
+ *
+ * Parity status: PINNED.  Every function here is checked in tests/ against
+ *   (1) the golden vectors of SURVEY.md section 8(c) (generator FNV hashes,
+ *       partition row starts, merge-path coordinates), and
+ *   (2) the reference's own code compiled from /root/reference into
+ *       oracle/_ref/libspmm_ref.so (see oracle/Makefile, oracle/ref_shim.cpp).
+ *
+ * All "ref:" citations are relative to /root/reference.
+ */
+#include <stdint.h>
+#include <stddef.h>
+#include <stdlib.h>
+#include <string.h>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+
+/* ---------------------------------------------------------------------------
+ * a3: naive CSR SpMM  ("Naive_CSR_CPU")
+ * ref: benchmark_code/CPU/AMD/spmv_code_bench/spmm_kernel_csr.cpp:69-97
+ *
+ *   for n < k:  for i < m (omp for):  sum = 0
+ *       for j in [ia[i], ia[i+1]):  sum += a[j] * x[n*c + ja[j]]
+ *       y[i*k + n] = sum
+ *
+ * x = k contiguous vectors of length c (column-major, ld = c);
+ * y = row-major m x k (ld = k), fully overwritten.  Left-to-right fp64 sum.
+ * ------------------------------------------------------------------------- */
+void oracle_spmm_csr(const int32_t *ia, const int32_t *ja, const double *a,
+                     long m, long c, const double *x, double *y, int k)
+{
+	#pragma omp parallel
+	{
+		for (long n = 0; n < k; n++) {
+			#pragma omp for
+			for (long i = 0; i < m; i++) {
+				double sum = 0;
+				for (long j = ia[i]; j < ia[i + 1]; j++)
+					sum += a[j] * x[n * c + ja[j]];
+				y[i * (long) k + n] = sum;
+			}
+		}
+	}
+}
+
+int oracle_num_threads(void)
+{
+#ifdef _OPENMP
+	return omp_get_max_threads();
+#else
+	return 1;
+#endif
+}
+
+/* ---------------------------------------------------------------------------
+ * binary_search with the reference's "nearest value" semantics.
+ * ref: lib/macros/macrolib.h:471-515 (__binary_search, default cmp/dist).
+ *
+ * Inclusive index range [lo, hi].  T < A[lo] -> lo;  T > A[hi] -> hi;
+ * otherwise bisect keeping A[s] <= T <= A[e] (s moves only when T > A[mid]);
+ * exact hit on s, then on e; else the nearer of the two, tie -> e.
+ * ------------------------------------------------------------------------- */
+static long nearest_search(const int32_t *A, long lo, long hi, long T)
+{
+	long s = lo, e = hi, mid;
+	if (T < A[s])
+		return s;
+	if (T > A[e])
+		return e;
+	for (;;) {
+		mid = (s + e) / 2;
+		if (mid == s || mid == e)
+			break;
+		if (T > A[mid])
+			s = mid;
+		else
+			e = mid;
+	}
+	if (T == A[s])
+		return s;
+	if (T == A[e])
+		return e;
+	long ds = T - A[s]; if (ds < 0) ds = -ds;
+	long de = T - A[e]; if (de < 0) de = -de;
+	return (ds < de) ? s : e;
+}
+
+/* ---------------------------------------------------------------------------
+ * a5: nnz-balanced row split.
+ * ref: lib/parallel_util.h:141-165 (loop_partitioner_balance_prefix_sums),
+ *      call site spmv_kernel_csr.cpp:112 (Sums = ia, N = m, total_sum = nnz).
+ *
+ * out[t] = first row of worker t, out[P] = m.  Target T_t = (nnz*t)/P in long
+ * integer division; the search range is ia[0..m-1] (N-1), never m.
+ * Worker t's end is worker t+1's start (same target), last end forced to m.
+ * ------------------------------------------------------------------------- */
+void oracle_balance_prefix_sums(const int32_t *ia, long m, long nnz, long P, int64_t *out)
+{
+	out[0] = 0;
+	for (long t = 1; t < P; t++) {
+		long T = (nnz * t) / P;
+		out[t] = (m > 0) ? nearest_search(ia, 0, m - 1, T) : 0;
+	}
+	out[P] = m;
+}
+
+/* ---------------------------------------------------------------------------
+ * a5': equal-iterations split of [start, end), increment 1.
+ * ref: lib/parallel_util.h:47-93 (loop_partitioner_balance_iterations_base).
+ * out[2t], out[2t+1] = [local_start, local_end) of worker t.
+ * ------------------------------------------------------------------------- */
+void oracle_balance_iterations(long start, long end, long P, int64_t *out)
+{
+	long len = end - start;
+	for (long t = 0; t < P; t++) {
+		long s, e;
+		if (1 > len) {                /* |incr| > len: worker 0 gets all */
+			s = (t == 0) ? start : end;
+			e = end;
+		} else {
+			long per = len / P, rem = len % P;
+			if (rem != 0 && t < rem) {
+				per += 1;
+				rem = 0;
+			}
+			s = start + per * t + rem;
+			e = s + per;
+			if (t == P - 1)
+				e = end;
+		}
+		out[2 * t] = s;
+		out[2 * t + 1] = e;
+	}
+}
+
+/* ---------------------------------------------------------------------------
+ * a7: merge-path diagonal search.
+ * ref: benchmark_code/CPU/ARM/spmv_code_bench/spmv_kernel_merge.cpp:214-234
+ *      (MergePathSearch), list A = row_end_offsets = ia+1 (length m),
+ *      list B = counting iterator 0..nnz-1.
+ * ------------------------------------------------------------------------- */
+void oracle_merge_path_search(long diagonal, const int32_t *row_end, long m, long nnz,
+                              int64_t *row_out, int64_t *nz_out)
+{
+	long x_min = diagonal - nnz; if (x_min < 0) x_min = 0;
+	long x_max = (diagonal < m) ? diagonal : m;
+	while (x_min < x_max) {
+		long p = (x_min + x_max) >> 1;
+		if (row_end[p] <= diagonal - p - 1)
+			x_min = p + 1;
+		else
+			x_max = p;
+	}
+	*row_out = (x_min < m) ? x_min : m;
+	*nz_out = diagonal - x_min;
+}
+
+/* P+1 coordinates at diagonals min(items*t, m+nnz), items = ceil((m+nnz)/P).
+ * ref: spmv_kernel_merge.cpp:262-272.  out[2t] = row, out[2t+1] = nnz index. */
+void oracle_merge_partition(const int32_t *ia, long m, long nnz, long P, int64_t *out)
+{
+	long L = m + nnz;
+	long items = (L + P - 1) / P;
+	for (long t = 0; t <= P; t++) {
+		long d = items * t; if (d > L) d = L;
+		oracle_merge_path_search(d, ia + 1, m, nnz, &out[2 * t], &out[2 * t + 1]);
+	}
+}
+
+/* ---------------------------------------------------------------------------
+ * a7 generalised to k columns: merge-path SpMM with k-wide carries.
+ * ref: spmv_kernel_merge.cpp:240-302 (OmpMergeCsrmv) is the k=1 case; the
+ * k-wide generalisation keeps its structure (whole rows, partial last row,
+ * serial carry fix-up) and the oracle's B/C layouts (a3).
+ * ------------------------------------------------------------------------- */
+void oracle_spmm_merge(const int32_t *ia, const int32_t *ja, const double *a,
+                       long m, long c, const double *x, double *y, int k, int P)
+{
+	int64_t *coord = malloc(sizeof(int64_t) * 2 * (P + 1));
+	int64_t *row_carry = malloc(sizeof(int64_t) * P);
+	double *val_carry = malloc(sizeof(double) * (size_t) P * k);
+	long nnz = ia[m];
+	oracle_merge_partition(ia, m, nnz, P, coord);
+	const int32_t *row_end = ia + 1;
+	#pragma omp parallel for schedule(static)
+	for (int t = 0; t < P; t++) {
+		long r = coord[2 * t], j = coord[2 * t + 1];
+		long r_end = coord[2 * t + 2], j_end = coord[2 * t + 3];
+		double *acc = val_carry + (size_t) t * k;
+		for (; r < r_end; r++) {
+			for (int n = 0; n < k; n++) acc[n] = 0;
+			for (; j < row_end[r]; j++)
+				for (int n = 0; n < k; n++)
+					acc[n] += a[j] * x[(long) n * c + ja[j]];
+			for (int n = 0; n < k; n++) y[r * (long) k + n] = acc[n];
+		}
+		for (int n = 0; n < k; n++) acc[n] = 0;
+		for (; j < j_end; j++)
+			for (int n = 0; n < k; n++)
+				acc[n] += a[j] * x[(long) n * c + ja[j]];
+		row_carry[t] = r_end;
+	}
+	for (int t = 0; t < P - 1; t++)
+		if (row_carry[t] < m)
+			for (int n = 0; n < k; n++)
+				y[row_carry[t] * (long) k + n] += val_carry[(size_t) t * k + n];
+	free(coord); free(row_carry); free(val_carry);
+}
+
+/* ---------------------------------------------------------------------------
+ * FNV-1a 64 over raw bytes: the hash SURVEY.md 8(c) pins the generator with.
+ * ------------------------------------------------------------------------- */
+uint64_t oracle_fnv1a64(const void *buf, size_t nbytes)
+{
+	const unsigned char *p = buf;
+	uint64_t h = 0xcbf29ce484222325ULL;
+	for (size_t i = 0; i < nbytes; i++) {
+		h ^= p[i];
+		h *= 0x100000001b3ULL;
+	}
+	return h;
+}
