@@ -1,0 +1,379 @@
+#!/usr/bin/env python
+"""bench.py -- fp64 CSR SpMM (C = A*B) throughput on N B200s vs the reference's CPU kernel.
+
+Metric (BASELINE.json): GFLOP/s = 2*nnz*k / t  (reference formula, spmv_bench.cpp:406) and the
+fraction of the HBM roofline (compulsory bytes 12*nnz + 4*(m+1) + 8*k*c + 8*k*m).
+
+  python bench.py [--gpus N --steps K --warmup W]          our arm (CUDA through the C ABI)
+  python bench.py --impl reference [...]                    the reference's OpenMP compute_csr
+                                                            (oracle/_ref, else the oracle port)
+A "step" is one SpMM call over the whole matrix.  Default workload = BASELINE configs[1]
+(1M x 1M, avg 50 nnz/row, normal, k=32; generator args in WORKLOADS['cfg2']).  The matrix comes
+from the reference's own generator (oracle/_ref/libamg_ref.so, built from /root/reference);
+B is seeded uniform [0,1).  Under torchrun rows are sharded nnz-balanced over the ranks, B is
+replicated with one NCCL broadcast, C stays row-local: the matrix is fixed, so scaling is strong.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # generator args in the harness order (spmv_bench.cpp:851-862):
+    # rows cols avg std distribution placement bw skew neighbours cross_row_similarity seed
+    "cfg1": ("100000 100000 10 2 normal random 1 0 0 0 14", 1),
+    "cfg2": ("1000000 1000000 50 16.6667 normal random 0.05 0 0.05 0.05 14", 32),
+    "cfg2_bw0.3": ("1000000 1000000 50 16.6667 normal random 0.3 0 0.05 0.05 14", 32),
+    "cfg2_bw1": ("1000000 1000000 50 16.6667 normal random 1 0 0.05 0.05 14", 32),
+    "cfg3a": ("2000000 2000000 20 20 gamma random 0.3 10000 0.5 0.5 14", 32),
+    "cfg3b": ("2000000 2000000 20 40 gamma random 0.3 0 0.5 0.5 14", 32),
+    "cfg4": ("1000000 1000000 50 16.6667 normal diagonal 0.0002 0 1.9 0.95 14", 128),
+    "cfg5_large": ("8388607 8388607 5 1.6667 normal random 0.05 0 0.05 0.05 14", 128),
+    "small": ("50000 50000 20 6 normal random 0.3 0 0.05 0.05 14", 32),
+}
+METRIC = "spmm_fp64_csr_gflops"
+UNIT = "GFLOP/s"
+
+
+def algorithmic_bytes(nnz, m, c, k):
+    return 12.0 * nnz + 4.0 * (m + 1) + 8.0 * k * c + 8.0 * k * m
+
+
+def dense_b(c, k, seed=42):
+    """Seeded uniform [0,1) B in the oracle layout x[n*c + j]."""
+    return np.random.default_rng(seed).random(c * k)
+
+
+def measured_peak_gbs():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def ncu_traffic(workload, k):
+    """dram bytes per launch of the dominant kernel from the committed ncu capture, or None."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            t = json.load(f)
+        return t.get(f"{workload}_k{k}")
+    except Exception:
+        return None
+
+
+class ClockSampler:
+    """Samples SM clocks and throttle reasons with NVML while the timed region runs."""
+
+    def __init__(self, index):
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self._t = None
+        try:
+            import pynvml as N
+            N.nvmlInit()
+            self.N = N
+            self.h = N.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = N.nvmlDeviceGetMaxClockInfo(self.h, N.NVML_CLOCK_SM)
+        except Exception:
+            self.N = None
+
+    def _loop(self):
+        N = self.N
+        names = {}
+        for nm in dir(N):
+            if nm.startswith("nvmlClocksThrottleReason") or nm.startswith("nvmlClocksEventReason"):
+                v = getattr(N, nm)
+                if isinstance(v, int) and v not in (0,) and bin(v).count("1") == 1:
+                    names.setdefault(v, nm.replace("nvmlClocksThrottleReason", "").replace("nvmlClocksEventReason", ""))
+        while not self._stop.is_set():
+            try:
+                self.samples.append(N.nvmlDeviceGetClockInfo(self.h, N.NVML_CLOCK_SM))
+                try:
+                    r = N.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:
+                    r = N.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, nm in names.items():
+                    if r & bit and "Idle" not in nm and nm not in ("None", "All"):
+                        self.reasons.add(nm)
+            except Exception:
+                pass
+            time.sleep(0.01)
+
+    def start(self):
+        if self.N:
+            self._t = threading.Thread(target=self._loop, daemon=True)
+            self._t.start()
+
+    def stop(self):
+        self._stop.set()
+        if self._t:
+            self._t.join()
+        med = float(np.median(self.samples)) if self.samples else None
+        return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(self.samples)}
+
+
+# ---------------------------------------------------------------------------------------------
+# CPU legs (the only places this file executes oracle/)
+# ---------------------------------------------------------------------------------------------
+
+def cpu_spmm_timer(ia, ja, a, m, c, k, x):
+    """Returns (fn(rows)->seconds, kind, cores): one call of the reference CPU kernel on the first
+    `rows` rows.  kind = 'reference' when oracle/_ref holds the compiled reference."""
+    from oracle import loader as L
+    y = np.empty(m * k)
+    if L.have_ref():
+        lib, kind, cores = L.ref(), "reference", L.ref().ref_num_threads()
+
+        def run(rows):
+            nz = int(ia[rows])
+            t0 = time.perf_counter()
+            lib.ref_spmm_csr_nocopy(ia, ja, a, rows, c, nz, x, y, k)
+            return time.perf_counter() - t0
+    else:
+        lib, kind, cores = L.oracle(), "port", L.oracle().oracle_num_threads()
+
+        def run(rows):
+            t0 = time.perf_counter()
+            lib.oracle_spmm_csr(ia, ja, a, rows, c, x, y, k)
+            return time.perf_counter() - t0
+    return run, kind, cores
+
+
+def bounded_rows(run, ia, m, k, budget_s):
+    """Pick a row prefix so that one call costs about budget_s (full matrix if it is cheaper)."""
+    probe = max(1, min(m, 20000))
+    run(probe)
+    t = max(run(probe), 1e-6)
+    rate = 2.0 * float(ia[probe]) * k / t          # flop/s on the probe
+    full = 2.0 * float(ia[m]) * k / rate
+    if full <= budget_s:
+        return m
+    target_nnz = rate * budget_s / (2.0 * k)
+    return int(max(probe, min(m, np.searchsorted(ia, target_nnz))))
+
+
+def cpu_baseline(ia, ja, a, m, c, k, x, total_budget_s=20.0):
+    run, kind, cores = cpu_spmm_timer(ia, ja, a, m, c, k, x)
+    rows = bounded_rows(run, ia, m, k, budget_s=total_budget_s / 4.0)
+    nz = float(ia[rows])
+    times, t_start = [], time.perf_counter()
+    run(rows)                                        # warm-up
+    while len(times) < 3 or (time.perf_counter() - t_start < total_budget_s and len(times) < 20):
+        times.append(run(rows))
+    t = float(np.median(times))
+    sample = (f"full matrix ({rows} rows, {int(nz)} nnz)" if rows == m else
+              f"first {rows} of {m} rows ({int(nz)} nnz)") + f", {len(times)} timed calls after 1 warm-up, median"
+    return {"value": 2.0 * nz * k / t / 1e9, "unit": UNIT, "cores": int(cores), "kind": kind, "sample": sample}
+
+
+def reference_arm(args, ia, ja, a, m, c, k, nnz, workload_desc):
+    """--impl reference: the reference's own CPU implementation, all host threads."""
+    x = dense_b(c, k)
+    run, kind, cores = cpu_spmm_timer(ia, ja, a, m, c, k, x)
+    steps_total = args.steps + args.warmup
+    rows = bounded_rows(run, ia, m, k, budget_s=max(0.05, 150.0 / max(steps_total, 1)))
+    nz = float(ia[rows])
+    for _ in range(args.warmup):
+        run(rows)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        run(rows)
+    t = (time.perf_counter() - t0) / max(args.steps, 1)
+    val = 2.0 * nz * k / t / 1e9
+    sample = (f"full matrix per step ({int(nz)} nnz)" if rows == m else
+              f"first {rows} of {m} rows per step ({int(nz)} of {nnz} nnz)")
+    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": t * 1e3, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": workload_desc,
+            "cpu_baseline": {"value": val, "unit": UNIT, "cores": int(cores), "kind": kind, "sample": sample},
+            "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+# ---------------------------------------------------------------------------------------------
+# our arm
+# ---------------------------------------------------------------------------------------------
+
+def gpu_arm(args, ia, ja, a, m, c, k, nnz, workload_desc):
+    import torch
+    import torch.distributed as dist
+    import __graft_entry__ as g
+    pkg = g.load_package()
+
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the product has no CPU fallback)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    variant = {"auto": pkg.AUTO, "rowsplit": pkg.ROWSPLIT, "merge": pkg.MERGE, "bcsr": pkg.BCSR}[args.variant]
+    if world > 1:
+        mf = pkg.csr_to_format(ia, ja, a, m, c, nnz, k, device=local, variant=variant, rank=rank, nranks=world)
+    else:
+        mf = pkg.csr_to_format(ia, ja, a, m, c, nnz, k, device=local, variant=variant)
+    m_loc = mf.m
+
+    # B: rank 0 owns the host copy (pinned, oracle layout); replicas by ONE broadcast over NVLink
+    x_host = torch.empty(c * k, dtype=torch.float64, pin_memory=True)
+    if rank == 0:
+        x_host.numpy()[:] = dense_b(c, k)
+    y_host = torch.empty(max(m_loc * k, 1), dtype=torch.float64, pin_memory=True)
+    x_dev = torch.empty(c * k, dtype=torch.float64, device=dev)      # column-major staging
+    b_dev = torch.empty(c * k, dtype=torch.float64, device=dev)      # row-major operand
+    c_dev = torch.empty(max(m_loc * k, 1), dtype=torch.float64, device=dev)
+    stream = torch.cuda.current_stream()
+
+    def replicate_b():
+        if rank == 0:
+            x_dev.copy_(x_host, non_blocking=True)
+        if world > 1:
+            dist.broadcast(x_dev, src=0)
+        if k == 1:
+            b_dev.copy_(x_dev)
+        else:
+            mf.transpose_b_device(x_dev.data_ptr(), b_dev.data_ptr(), k, stream.cuda_stream)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(v):
+        if world == 1:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    replicate_b()
+    barrier()
+
+    # ---- device-resident timing: `value` -----------------------------------------------------
+    for _ in range(args.warmup):
+        mf.spmm_device(b_dev.data_ptr(), c_dev.data_ptr(), k, stream.cuda_stream)
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
+    sampler = ClockSampler(local)
+    launches0 = mf.launch_count()
+    barrier()
+    sampler.start()
+    ev[0].record(stream)
+    for i in range(args.steps):
+        mf.spmm_device(b_dev.data_ptr(), c_dev.data_ptr(), k, stream.cuda_stream)
+        ev[i + 1].record(stream)
+    barrier()
+    launches = mf.launch_count() - launches0
+    total_ms = ev[0].elapsed_time(ev[-1])
+    per_step = [ev[i].elapsed_time(ev[i + 1]) for i in range(args.steps)]
+    total_ms = max_over_ranks(total_ms)
+    kernel_ms = max_over_ranks(float(np.mean(per_step)))     # back-to-back launches: step = kernel(s)
+    ms_per_step = total_ms / args.steps
+    value = 2.0 * nnz * k / (ms_per_step * 1e-3) / 1e9
+
+    # ---- end to end with HOST buffers: `e2e` -----------------------------------------------------
+    e2e_steps = max(3, min(args.steps, 10))
+    def e2e_step():
+        if world == 1:
+            mf.spmm(x_host.numpy(), y_host.numpy()[: m_loc * k], k)        # the public drop-in call
+        else:
+            replicate_b()
+            mf.spmm_device(b_dev.data_ptr(), c_dev.data_ptr(), k, stream.cuda_stream)
+            y_host[: m_loc * k].copy_(c_dev[: m_loc * k], non_blocking=True)
+            torch.cuda.synchronize()
+    for _ in range(2):
+        e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        e2e_step()
+    barrier()
+    e2e_s = max_over_ranks((time.perf_counter() - t0) / e2e_steps)
+    clocks = sampler.stop()
+    e2e_val = 2.0 * nnz * k / e2e_s / 1e9
+
+    # ---- checksum so that the work cannot be skipped silently -----------------------------------
+    csum = float(c_dev[: m_loc * k].sum().item()) if m_loc else 0.0
+
+    peak, peak_src = measured_peak_gbs()
+    nnz_loc = mf.nnz
+    bytes_launch = algorithmic_bytes(nnz_loc, m_loc, c, k)
+    achieved = bytes_launch / (kernel_ms * 1e-3) / 1e9
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "f64", "data": "synthetic", "config": workload_desc,
+        "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": 8 * c * k, "d2h_bytes_per_step": 8 * m * k,
+                "ms_per_step": e2e_s * 1e3, "steps": e2e_steps},
+        "gpu_launches": int(launches),
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "traffic": ncu_traffic(args.workload, k), "peak_source": peak_src,
+                     "algorithmic_bytes_per_launch": bytes_launch, "kernel_ms": kernel_ms,
+                     "kernel": mf.format_name, "frac_of_8TBs_nominal": achieved / 8000.0,
+                     "rank0_shard": world > 1},
+        "clocks": clocks,
+        "checksum_c_rank0": csum,
+        "variant": mf.format_name,
+    }
+    if rank == 0 and world == 1 and not args.no_cpu:
+        line["cpu_baseline"] = cpu_baseline(ia, ja, a, m, c, k, x_host.numpy())
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    mf.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="cfg2", choices=sorted(WORKLOADS))
+    ap.add_argument("--k", type=int, default=None)
+    ap.add_argument("--variant", default="auto", choices=["auto", "rowsplit", "merge", "bcsr"])
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    rank = int(os.environ.get("RANK", 0))
+    if args.impl == "reference" and rank != 0:
+        return 0
+
+    from oracle import loader as L          # input generation = the reference's own generator
+    gen_args, k = WORKLOADS[args.workload]
+    if args.k:
+        k = args.k
+    if not L.have_ref():
+        raise SystemExit("bench.py: oracle/_ref/libamg_ref.so (the reference's matrix generator) is missing; "
+                         "run __graft_entry__.build() in the container that has /root/reference")
+    ia, ja, a, m, c = L.generate(gen_args)
+    nnz = len(ja)
+    desc = {"workload": f"{args.workload}: artificial-matrix-generator '{gen_args}', fp64 CSR SpMM k={k}",
+            "m": m, "c": c, "nnz": nnz, "k": k, "b_layout": "oracle column-major x[n*c+j] at the boundary, row-major on device",
+            "l2": "inputs larger than L2 (A stream + C = %.0f MB per step >> 126 MB); no flush" % ((12.0 * nnz + 8.0 * k * m) / 1e6),
+            "sharding": "nnz-balanced rows (lib/parallel_util.h:141-165), B by one NCCL broadcast, C row-local"}
+    if args.impl == "reference":
+        reference_arm(args, ia, ja, a, m, c, k, nnz, desc)
+    else:
+        gpu_arm(args, ia, ja, a, m, c, k, nnz, desc)
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -1,0 +1,134 @@
+/*
+ * spmm_b200.h -- C ABI of libspmm_b200.so: fp64 CSR sparse x dense multiply
+ * C = A*B (SpMV = k 1) on NVIDIA B200 (sm_100a), hand-written CUDA.
+ *
+ * This is the drop-in boundary for ONE path of ioannatas/SpMM-Research: the
+ * plug-in interface  `struct Matrix_Format { virtual void spmm(x, y, k) ... }`
+ * + `csr_to_format(row_ptr, col_ind, values, m, n, nnz, k)`
+ * (ref: benchmark_code/CPU/AMD/spmv_code_bench/spmv_kernel.h:9-30).  A ~100-line
+ * C++ translation unit (spmm-research_b200/csrc/spmm_kernel_b200.cpp) implements
+ * that interface on top of the functions below and links under the reference's
+ * UNCHANGED harness (spmv_bench.cpp) like any other kernel TU (Makefile_in:52-53).
+ *
+ * Conventions
+ *   - plain pointers and sizes, no C++/torch types; every call returns 0 or a
+ *     negative SPMM_B200_E* code and never calls exit() (the reference's
+ *     convention "print + exit(1)" is applied by the C++ shim, not here);
+ *   - no CPU fallback: without a usable sm_100 device every compute entry point
+ *     fails with SPMM_B200_ENODEV / SPMM_B200_ECUDA;
+ *   - int32 CSR indices (INT_T=int32_t), fp64 values (ValueType=double), 0-based,
+ *     columns sorted inside a row as the generator / coo_to_csr produce them;
+ *   - dense operand layouts follow the oracle compute_csr()
+ *     (ref: spmm_kernel_csr.cpp:88,93):  B = x = k contiguous vectors of length c
+ *     (SPMM_B200_B_COLMAJOR, x[n*c + j]);  C = y = row-major m x k (y[i*k + n]).
+ *     On the device B is kept row-major (c x k) so one gathered B row is one
+ *     coalesced read; the library transposes on upload.
+ */
+#ifndef SPMM_B200_H
+#define SPMM_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct spmm_b200 spmm_b200_t;
+
+/* kernel variants (north_star (2),(3)) */
+enum {
+	SPMM_B200_ROWSPLIT = 0,   /* sub-warp group per row, CTAs own nnz-balanced row ranges   */
+	SPMM_B200_MERGE    = 1,   /* merge-path tiles with k-wide carries (skewed rows)          */
+	SPMM_B200_BCSR     = 2,   /* blocked CSR on the FP64 tensor pipe (dense blocks only)     */
+	SPMM_B200_AUTO     = 3    /* pick from the row-length statistics of A                    */
+};
+
+/* layout of the dense operand handed to spmm_b200_run / spmm_b200_set_b */
+enum {
+	SPMM_B200_B_COLMAJOR = 0, /* oracle layout x[n*c + j]  (spmm_kernel_csr.cpp:88)          */
+	SPMM_B200_B_ROWMAJOR = 1  /* x[j*k + n]  (mkl_sparse_d_mm ROW_MAJOR, spmm_kernel_mkl_ie.cpp:143-146) */
+};
+
+/* partition modes of spmm_b200_partition (all bit-exact with the reference) */
+enum {
+	SPMM_B200_PART_ROWS   = 0, /* loop_partitioner_balance_iterations   lib/parallel_util.h:47-93,116-126 : out[2t],out[2t+1] = [start,end) */
+	SPMM_B200_PART_NNZ    = 1, /* loop_partitioner_balance_prefix_sums  lib/parallel_util.h:141-165       : out[0..P] row starts, out[P]=m  */
+	SPMM_B200_PART_MERGE  = 2  /* MergePathSearch at diagonals t*ceil((m+nnz)/P), ARM/spmv_kernel_merge.cpp:214-234,262-272 : out[2t]=row, out[2t+1]=nnz idx, t=0..P */
+};
+
+enum {
+	SPMM_B200_OK      =  0,
+	SPMM_B200_EINVAL  = -1,   /* bad argument (null pointer, negative size, k mismatch ...)   */
+	SPMM_B200_ENODEV  = -2,   /* no CUDA device / not compute capability 10.x                 */
+	SPMM_B200_ECUDA   = -3,   /* a CUDA runtime call failed (see spmm_b200_last_cuda_error)   */
+	SPMM_B200_ENOMEM  = -4,   /* device or host allocation failed                             */
+	SPMM_B200_ERANGE  = -5,   /* sizes overflow the int32 index contract (nnz, m, c < 2^31)  */
+	SPMM_B200_ENOSUP  = -6    /* variant not applicable to this matrix / k                    */
+};
+
+/* ---- format construction: replaces csr_to_format() (spmv_kernel.h:29; call site spmv_bench.cpp:996).
+ * Copies the host CSR arrays to `device`; the caller keeps ownership of the host
+ * arrays (the C++ shim frees them in its destructor as every reference kernel does,
+ * spmm_kernel_csr.cpp:34-39).  k is the number of dense columns the handle is tuned
+ * for (NUM_COLS); spmm_b200_run accepts any k >= 1. */
+int spmm_b200_create(spmm_b200_t **h,
+                     const int32_t *row_ptr, const int32_t *col_ind, const double *values,
+                     int64_t m, int64_t c, int64_t nnz, int k,
+                     int device, int variant, int b_layout);
+
+/* Same, for shard `rank` of `nranks` nnz-balanced row shards (rows
+ * [s_rank, s_rank+1) of loop_partitioner_balance_prefix_sums(P = nranks), computed
+ * on the device, bit-exact).  Only that shard's slice of A is uploaded, row_ptr is
+ * rebased; C is row-local (m_shard x k).  first_row/last_row report the shard. */
+int spmm_b200_create_shard(spmm_b200_t **h,
+                           const int32_t *row_ptr, const int32_t *col_ind, const double *values,
+                           int64_t m, int64_t c, int64_t nnz, int k,
+                           int device, int variant, int b_layout,
+                           int rank, int nranks, int64_t *first_row, int64_t *last_row);
+
+/* ---- the hot call: replaces Matrix_Format::spmm(x, y, k) (spmv_kernel.h:18; call sites
+ * spmv_bench.cpp:318,372).  HOST buffers: x (c*k doubles, layout = b_layout of the
+ * handle), y (m_local*k doubles, row-major).  Uploads x (H2D), runs the kernel(s),
+ * and when copy_back != 0 downloads y (D2H) before returning.  With
+ * copy_back == 0 the result stays on the device (spmm_b200_fetch_c reads it). */
+int spmm_b200_run(spmm_b200_t *h, const double *x_host, double *y_host, int k, int copy_back);
+
+/* Upload B once (x is constant across the reference's timed loop,
+ * spmv_bench.cpp:895-903) and run on the resident copy. */
+int spmm_b200_set_b(spmm_b200_t *h, const double *x_host, int k);
+int spmm_b200_run_resident(spmm_b200_t *h, int k);
+int spmm_b200_fetch_c(spmm_b200_t *h, double *y_host, int k);
+
+/* Device-pointer variant for callers that own device memory and streams
+ * (bench.py / torch.distributed ranks): b_dev = row-major c x k, c_dev =
+ * row-major m_local x k, both on the handle's device; `stream` is a
+ * cudaStream_t (NULL = default stream).  Asynchronous. */
+int spmm_b200_run_device(spmm_b200_t *h, const double *b_dev, double *c_dev, int k, void *stream);
+
+/* Column-major (oracle layout) -> row-major transpose of B on the device. */
+int spmm_b200_transpose_b_device(spmm_b200_t *h, const double *x_colmajor_dev, double *b_rowmajor_dev,
+                                 int k, void *stream);
+
+/* ---- partitioning, testable without an SpMM kernel (host pointers in and out,
+ * the search itself runs on the device).  `out` sizes: see the enum above. */
+int spmm_b200_partition(const int32_t *row_ptr, int64_t m, int64_t nnz, int P, int mode,
+                        int64_t *out, int device);
+
+/* ---- introspection */
+int64_t spmm_b200_rows(const spmm_b200_t *h);         /* rows held by this handle (shard)     */
+int64_t spmm_b200_nnz(const spmm_b200_t *h);
+int     spmm_b200_variant(const spmm_b200_t *h);      /* the variant AUTO resolved to         */
+double  spmm_b200_last_kernel_ms(const spmm_b200_t *h); /* CUDA-event time of the last run's kernels */
+int64_t spmm_b200_launch_count(const spmm_b200_t *h); /* kernels launched by this handle so far */
+/* replaces statistics_print_data()/statistics_print_labels() (spmv_kernel.h:20,30) */
+int     spmm_b200_stats(const spmm_b200_t *h, char *buf, long buf_n);
+int     spmm_b200_stats_labels(char *buf, long buf_n);
+void    spmm_b200_destroy(spmm_b200_t *h);
+const char *spmm_b200_strerror(int code);
+const char *spmm_b200_last_cuda_error(void);
+int     spmm_b200_device_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SPMM_B200_H */

@@ -1,0 +1,207 @@
+"""spmm-research_b200 -- host-side mirror of the reference's SpMM plug-in interface.
+
+The reference selects a kernel at link time: one translation unit supplies
+`csr_to_format(row_ptr, col_ind, values, m, n, nnz, k)` and a `Matrix_Format`
+subclass with `spmm(x, y, k)` (ref: benchmark_code/CPU/AMD/spmv_code_bench/
+spmv_kernel.h:9-30).  The C++ twin of this file, csrc/spmm_kernel_b200.cpp, is that
+translation unit for the reference's own harness; this module exposes the same
+names, argument meaning and error behaviour to Python (tests, bench.py) through
+ctypes over the C ABI in include/spmm_b200.h.
+
+There is NO CPU fallback: if lib/libspmm_b200.so is missing, or no sm_100 device is
+present, construction fails loudly.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+__all__ = ["csr_to_format", "MatrixFormat", "partition", "statistics_print_labels", "load_library",
+           "SpmmB200Error", "ROWSPLIT", "MERGE", "BCSR", "AUTO", "B_COLMAJOR", "B_ROWMAJOR",
+           "PART_ROWS", "PART_NNZ", "PART_MERGE", "LIB_PATH", "EXPORTS"]
+
+ROWSPLIT, MERGE, BCSR, AUTO = 0, 1, 2, 3
+B_COLMAJOR, B_ROWMAJOR = 0, 1
+PART_ROWS, PART_NNZ, PART_MERGE = 0, 1, 2
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "lib", "libspmm_b200.so")
+
+# every symbol include/spmm_b200.h declares
+EXPORTS = [
+    "spmm_b200_create", "spmm_b200_create_shard", "spmm_b200_run", "spmm_b200_set_b",
+    "spmm_b200_run_resident", "spmm_b200_fetch_c", "spmm_b200_run_device",
+    "spmm_b200_transpose_b_device", "spmm_b200_partition", "spmm_b200_rows", "spmm_b200_nnz",
+    "spmm_b200_variant", "spmm_b200_last_kernel_ms", "spmm_b200_launch_count", "spmm_b200_stats",
+    "spmm_b200_stats_labels", "spmm_b200_destroy", "spmm_b200_strerror", "spmm_b200_last_cuda_error",
+    "spmm_b200_device_count",
+]
+
+_lib = None
+_vp, _i64, _int, _dbl = C.c_void_p, C.c_int64, C.c_int, C.c_double
+
+
+class SpmmB200Error(RuntimeError):
+    """A C-ABI call returned a negative code.  The reference's convention is
+    print + exit(1) (lib/debug.h error()); in Python that becomes an exception."""
+
+    def __init__(self, code, where):
+        lib = load_library()
+        msg = lib.spmm_b200_strerror(code).decode()
+        detail = lib.spmm_b200_last_cuda_error().decode()
+        super().__init__(f"{where}: {msg} (code {code})" + (f" [{detail}]" if detail and code in (-2, -3, -4) else ""))
+        self.code = code
+
+
+def load_library():
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(f"{LIB_PATH} not built: run `make -C spmm-research_b200/csrc` "
+                          "(there is no CPU fallback)")
+    lib = C.CDLL(LIB_PATH)
+    lib.spmm_b200_create.argtypes = [C.POINTER(_vp), _vp, _vp, _vp, _i64, _i64, _i64, _int, _int, _int, _int]
+    lib.spmm_b200_create_shard.argtypes = lib.spmm_b200_create.argtypes + [_int, _int, C.POINTER(_i64), C.POINTER(_i64)]
+    lib.spmm_b200_run.argtypes = [_vp, _vp, _vp, _int, _int]
+    lib.spmm_b200_set_b.argtypes = [_vp, _vp, _int]
+    lib.spmm_b200_run_resident.argtypes = [_vp, _int]
+    lib.spmm_b200_fetch_c.argtypes = [_vp, _vp, _int]
+    lib.spmm_b200_run_device.argtypes = [_vp, _vp, _vp, _int, _vp]
+    lib.spmm_b200_transpose_b_device.argtypes = [_vp, _vp, _vp, _int, _vp]
+    lib.spmm_b200_partition.argtypes = [_vp, _i64, _i64, _int, _int, _vp, _int]
+    lib.spmm_b200_rows.argtypes = [_vp]; lib.spmm_b200_rows.restype = _i64
+    lib.spmm_b200_nnz.argtypes = [_vp]; lib.spmm_b200_nnz.restype = _i64
+    lib.spmm_b200_variant.argtypes = [_vp]
+    lib.spmm_b200_last_kernel_ms.argtypes = [_vp]; lib.spmm_b200_last_kernel_ms.restype = _dbl
+    lib.spmm_b200_launch_count.argtypes = [_vp]; lib.spmm_b200_launch_count.restype = _i64
+    lib.spmm_b200_stats.argtypes = [_vp, C.c_char_p, C.c_long]
+    lib.spmm_b200_stats_labels.argtypes = [C.c_char_p, C.c_long]
+    lib.spmm_b200_destroy.argtypes = [_vp]; lib.spmm_b200_destroy.restype = None
+    lib.spmm_b200_strerror.argtypes = [_int]; lib.spmm_b200_strerror.restype = C.c_char_p
+    lib.spmm_b200_last_cuda_error.restype = C.c_char_p
+    lib.spmm_b200_device_count.restype = _int
+    _lib = lib
+    return lib
+
+
+def _check(code, where):
+    if code != 0:
+        raise SpmmB200Error(code, where)
+
+
+def _host(arr, dtype, name):
+    if not isinstance(arr, np.ndarray) or arr.dtype != dtype or not arr.flags.c_contiguous:
+        raise TypeError(f"{name} must be a C-contiguous numpy array of {np.dtype(dtype).name}")
+    return arr.ctypes.data
+
+
+class MatrixFormat:
+    """Mirror of `struct Matrix_Format` (spmv_kernel.h:9-26): fields format_name, m, n,
+    nnz, mem_footprint, csr_mem_footprint; methods spmm, statistics_start,
+    statistics_print_data."""
+
+    def __init__(self, handle, m, n, nnz, k, first_row=0, m_global=None):
+        self._h = handle
+        self.m, self.n, self.nnz, self.k = int(m), int(n), int(nnz), int(k)
+        self.first_row = int(first_row)
+        self.m_global = int(m if m_global is None else m_global)
+        lib = load_library()
+        self.variant = lib.spmm_b200_variant(handle)
+        self.format_name = "B200_CSR_" + {ROWSPLIT: "ROWSPLIT", MERGE: "MERGE", BCSR: "BCSR"}.get(self.variant, "?")
+        # spmv_kernel.h:24
+        self.csr_mem_footprint = self.nnz * (8 + 4) + (self.m + 1) * 4
+        self.mem_footprint = self.csr_mem_footprint
+
+    # -- the hot call: Matrix_Format::spmm(x, y, k) with HOST buffers ------------------
+    def spmm(self, x, y, k, copy_back=True):
+        """y = A @ x.  x: float64[c*k] in the oracle layout x[n*c + j]; y: float64[m*k]
+        row-major, fully overwritten (spmm_kernel_csr.cpp:88,93)."""
+        k = int(k)
+        if x.size != self.n * k:
+            raise ValueError(f"x holds {x.size} values, expected c*k = {self.n * k}")
+        if copy_back and y.size != self.m * k:
+            raise ValueError(f"y holds {y.size} values, expected m*k = {self.m * k}")
+        xp = _host(x, np.float64, "x")
+        yp = _host(y, np.float64, "y") if copy_back else None
+        _check(load_library().spmm_b200_run(self._h, xp, yp, k, 1 if copy_back else 0), "spmm")
+
+    def set_b(self, x, k):
+        _check(load_library().spmm_b200_set_b(self._h, _host(x, np.float64, "x"), int(k)), "set_b")
+
+    def spmm_resident(self, k):
+        _check(load_library().spmm_b200_run_resident(self._h, int(k)), "spmm_resident")
+
+    def fetch_c(self, y, k):
+        _check(load_library().spmm_b200_fetch_c(self._h, _host(y, np.float64, "y"), int(k)), "fetch_c")
+
+    # -- device-pointer form for callers that own device memory / streams ---------------
+    def spmm_device(self, b_ptr, c_ptr, k, stream=0):
+        """b_ptr: device address of row-major B (c x k); c_ptr: device address of row-major
+        C (m_local x k); stream: cudaStream_t as int (0 = default).  Asynchronous."""
+        _check(load_library().spmm_b200_run_device(self._h, b_ptr, c_ptr, int(k), stream or None), "spmm_device")
+
+    def transpose_b_device(self, x_ptr, b_ptr, k, stream=0):
+        _check(load_library().spmm_b200_transpose_b_device(self._h, x_ptr, b_ptr, int(k), stream or None),
+               "transpose_b_device")
+
+    def last_kernel_ms(self):
+        return load_library().spmm_b200_last_kernel_ms(self._h)
+
+    def launch_count(self):
+        return load_library().spmm_b200_launch_count(self._h)
+
+    def statistics_start(self):
+        pass
+
+    def statistics_print_data(self, buf_n=512):
+        buf = C.create_string_buffer(buf_n)
+        load_library().spmm_b200_stats(self._h, buf, buf_n)
+        return buf.value.decode()
+
+    def close(self):
+        if self._h:
+            load_library().spmm_b200_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def csr_to_format(row_ptr, col_ind, values, m, n, nnz, k, *, device=0, variant=AUTO,
+                  b_layout=B_COLMAJOR, rank=None, nranks=None):
+    """Mirror of csr_to_format() (spmv_kernel.h:29).  With rank/nranks the handle holds
+    only that rank's nnz-balanced row shard."""
+    lib = load_library()
+    h = _vp()
+    rp = _host(row_ptr, np.int32, "row_ptr")
+    ci = _host(col_ind, np.int32, "col_ind") if nnz > 0 else None
+    va = _host(values, np.float64, "values") if nnz > 0 else None
+    if row_ptr.size < m + 1:
+        raise ValueError("row_ptr shorter than m+1")
+    if nranks is None:
+        _check(lib.spmm_b200_create(C.byref(h), rp, ci, va, m, n, nnz, k, device, variant, b_layout), "csr_to_format")
+        return MatrixFormat(h, m, n, nnz, k)
+    r0, r1 = _i64(), _i64()
+    _check(lib.spmm_b200_create_shard(C.byref(h), rp, ci, va, m, n, nnz, k, device, variant, b_layout,
+                                      int(rank), int(nranks), C.byref(r0), C.byref(r1)), "csr_to_format(shard)")
+    return MatrixFormat(h, lib.spmm_b200_rows(h), n, lib.spmm_b200_nnz(h), k, first_row=r0.value, m_global=m)
+
+
+def partition(row_ptr, m, nnz, P, mode, device=0):
+    """Device-side, bit-exact twins of the reference partitioners (include/spmm_b200.h).
+    PART_NNZ -> int64[P+1] row starts; PART_ROWS -> int64[P,2]; PART_MERGE -> int64[P+1,2]."""
+    n_out = {PART_NNZ: P + 1, PART_ROWS: 2 * P, PART_MERGE: 2 * (P + 1)}[mode]
+    out = np.zeros(n_out, dtype=np.int64)
+    rp = _host(row_ptr, np.int32, "row_ptr") if row_ptr is not None else None
+    _check(load_library().spmm_b200_partition(rp, m, nnz, P, mode, out.ctypes.data, device), "partition")
+    return out if mode == PART_NNZ else out.reshape(-1, 2)
+
+
+def statistics_print_labels(buf_n=512):
+    buf = C.create_string_buffer(buf_n)
+    load_library().spmm_b200_stats_labels(buf, buf_n)
+    return buf.value.decode()

@@ -1,0 +1,509 @@
+// spmm_b200.cu -- the C ABI of libspmm_b200.so (include/spmm_b200.h).
+//
+// Host side of the drop-in for Matrix_Format::spmm / csr_to_format
+// (ref: benchmark_code/CPU/AMD/spmv_code_bench/spmv_kernel.h:9-30).  Owns the
+// device copy of A, the CTA work lists, optional device copies of B and C, and
+// launches the hand-written sm_100a kernels in spmm_rowsplit.cuh / spmm_merge.cuh.
+// There is no CPU fallback: every compute entry point needs a CC 10.x device.
+#include "../../include/spmm_b200.h"
+#include "partition.cuh"
+#include "spmm_rowsplit.cuh"
+#include "spmm_merge.cuh"
+
+#include <cuda_runtime.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <vector>
+#include <algorithm>
+
+using namespace sb200;
+
+static thread_local char g_cuda_err[512] = "";
+
+#define CU_TRY(expr)                                                                              \
+	do {                                                                                          \
+		cudaError_t _e = (expr);                                                                  \
+		if (_e != cudaSuccess) {                                                                  \
+			snprintf(g_cuda_err, sizeof(g_cuda_err), "%s:%d: %s -> %s", __FILE__, __LINE__, #expr, \
+			         cudaGetErrorString(_e));                                                     \
+			return (_e == cudaErrorMemoryAllocation) ? SPMM_B200_ENOMEM : SPMM_B200_ECUDA;        \
+		}                                                                                         \
+	} while (0)
+
+static constexpr int THREADS = 256;
+
+struct spmm_b200 {
+	int device = 0;
+	int variant = SPMM_B200_ROWSPLIT;     // resolved variant
+	int variant_req = SPMM_B200_AUTO;
+	int b_layout = SPMM_B200_B_COLMAJOR;
+	int k = 0;                            // k the work lists were tuned for
+	int sm_count = 148;
+	int64_t m = 0, c = 0, nnz = 0;        // this handle's shard
+	int64_t first_row = 0, m_global = 0;
+	int max_row = 0;                      // longest row of the shard
+
+	int32_t* d_ia = nullptr;
+	int32_t* d_ja = nullptr;
+	double* d_a = nullptr;
+
+	// row-split work list
+	int32_t* d_cta_rows = nullptr;
+	int n_ctas = 0;
+	// merge-path work list
+	MergePlan merge;
+
+	// buffers for the host-pointer API
+	double* d_x = nullptr; size_t cap_x = 0;   // staging for the column-major upload
+	double* d_B = nullptr; size_t cap_B = 0;
+	double* d_C = nullptr; size_t cap_C = 0;
+	int resident_k = 0;
+	std::vector<void*> pinned;            // host ranges we registered
+
+	cudaStream_t stream = nullptr;
+	cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+	bool timed = false;
+	int64_t launches = 0;
+};
+
+static int env_int(const char* name, int dflt)
+{
+	const char* s = getenv(name);
+	return (s && *s) ? atoi(s) : dflt;
+}
+
+static int check_device(int device, int* sm_count)
+{
+	int n = 0;
+	cudaError_t e = cudaGetDeviceCount(&n);
+	if (e != cudaSuccess || n <= 0) {
+		snprintf(g_cuda_err, sizeof(g_cuda_err), "cudaGetDeviceCount: %s (%d devices)", cudaGetErrorString(e), n);
+		return SPMM_B200_ENODEV;
+	}
+	if (device < 0 || device >= n) return SPMM_B200_EINVAL;
+	cudaDeviceProp p;
+	CU_TRY(cudaGetDeviceProperties(&p, device));
+	if (p.major != 10) {
+		snprintf(g_cuda_err, sizeof(g_cuda_err), "device %d is sm_%d%d; this library holds sm_100a code only", device, p.major, p.minor);
+		return SPMM_B200_ENODEV;
+	}
+	if (sm_count) *sm_count = p.multiProcessorCount;
+	CU_TRY(cudaSetDevice(device));
+	return SPMM_B200_OK;
+}
+
+__global__ void rebase_kernel(int32_t* ia, int64_t n, int32_t base)
+{
+	int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+	if (i < n) ia[i] -= base;
+}
+
+__global__ void max_row_kernel(const int32_t* __restrict__ ia, int m, int* __restrict__ out)
+{
+	int best = 0;
+	for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < m; i += gridDim.x * blockDim.x)
+		best = max(best, ia[i + 1] - ia[i]);
+	for (int off = 16; off > 0; off >>= 1) best = max(best, __shfl_xor_sync(0xffffffffu, best, off));
+	if ((threadIdx.x & 31) == 0 && best > 0) atomicMax(out, best);
+}
+
+// ------------------------------------------------------------------------------------------
+// work lists
+// ------------------------------------------------------------------------------------------
+
+static int build_rowsplit_plan(spmm_b200* h)
+{
+	// One CTA per nnz-balanced row range.  Default: 8 resident CTAs x 4 waves per SM.
+	const int per_sm = std::max(1, env_int("SPMM_B200_CTAS_PER_SM", 32));
+	int64_t want = (int64_t) h->sm_count * per_sm;
+	int64_t cap = std::max<int64_t>(1, (h->m + 7) / 8);       // at least ~8 rows per CTA
+	h->n_ctas = (int) std::max<int64_t>(1, std::min(want, cap));
+	if (h->d_cta_rows) cudaFree(h->d_cta_rows);
+	CU_TRY(cudaMalloc(&h->d_cta_rows, sizeof(int32_t) * (h->n_ctas + 1)));
+	const int nb = (h->n_ctas + 1 + 255) / 256;
+	cta_rows_nnz_kernel<<<nb, 256, 0, h->stream>>>(h->d_ia, (int) h->m, h->nnz, h->n_ctas, h->d_cta_rows);
+	h->launches++;
+	CU_TRY(cudaGetLastError());
+	return SPMM_B200_OK;
+}
+
+static int pick_small_group(const spmm_b200* h)
+{
+	const double avg = h->m > 0 ? (double) h->nnz / (double) h->m : 1.0;
+	int g = 2;
+	while (g < 32 && g * 2 <= avg) g *= 2;
+	return g;
+}
+
+template <int G, int V>
+static void launch_rowsplit_gv(const spmm_b200* h, const double* B, double* C, cudaStream_t s)
+{
+	spmm_rowsplit_kernel<G, V, 4, THREADS><<<h->n_ctas, THREADS, 0, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, h->d_cta_rows);
+}
+
+template <int K>
+static void launch_smallk(const spmm_b200* h, const double* B, double* C, cudaStream_t s)
+{
+	switch (pick_small_group(h)) {
+	case 2:  spmm_smallk_kernel<K, 2, THREADS><<<h->n_ctas, THREADS, 0, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, h->d_cta_rows); break;
+	case 4:  spmm_smallk_kernel<K, 4, THREADS><<<h->n_ctas, THREADS, 0, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, h->d_cta_rows); break;
+	case 8:  spmm_smallk_kernel<K, 8, THREADS><<<h->n_ctas, THREADS, 0, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, h->d_cta_rows); break;
+	case 16: spmm_smallk_kernel<K, 16, THREADS><<<h->n_ctas, THREADS, 0, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, h->d_cta_rows); break;
+	default: spmm_smallk_kernel<K, 32, THREADS><<<h->n_ctas, THREADS, 0, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, h->d_cta_rows); break;
+	}
+}
+
+// Launches the SpMM kernel(s) of the handle's variant on stream s.  Returns kernels launched or <0.
+static int launch_spmm(spmm_b200* h, const double* B, double* C, int k, cudaStream_t s)
+{
+	if (h->m == 0) return 0;
+	int n = 1;
+	switch (k) {
+	case 1:   launch_smallk<1>(h, B, C, s); break;
+	case 2:   launch_smallk<2>(h, B, C, s); break;
+	case 4:   launch_smallk<4>(h, B, C, s); break;
+	case 8:   launch_rowsplit_gv<4, 2>(h, B, C, s); break;
+	case 16:  launch_rowsplit_gv<8, 2>(h, B, C, s); break;
+	case 32:  launch_rowsplit_gv<16, 2>(h, B, C, s); break;
+	case 64:  launch_rowsplit_gv<32, 2>(h, B, C, s); break;
+	case 128: launch_rowsplit_gv<32, 4>(h, B, C, s); break;
+	default:
+		spmm_rowsplit_generic_kernel<THREADS><<<h->n_ctas, THREADS, 0, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, h->d_cta_rows, k);
+		break;
+	}
+	cudaError_t e = cudaGetLastError();
+	if (e != cudaSuccess) {
+		snprintf(g_cuda_err, sizeof(g_cuda_err), "spmm kernel launch (k=%d): %s", k, cudaGetErrorString(e));
+		return SPMM_B200_ECUDA;
+	}
+	h->launches += n;
+	return n;
+}
+
+// ------------------------------------------------------------------------------------------
+// construction
+// ------------------------------------------------------------------------------------------
+
+static int create_from_slice(spmm_b200_t** out, const int32_t* row_ptr_slice, const int32_t* col_ind, const double* values,
+                             int64_t m_local, int64_t c, int64_t nnz_local, int32_t base, int k,
+                             int device, int variant, int b_layout, int sm_count, int64_t first_row, int64_t m_global)
+{
+	spmm_b200* h = new (std::nothrow) spmm_b200();
+	if (!h) return SPMM_B200_ENOMEM;
+	h->device = device; h->variant_req = variant; h->b_layout = b_layout; h->k = k;
+	h->sm_count = sm_count;
+	h->m = m_local; h->c = c; h->nnz = nnz_local; h->first_row = first_row; h->m_global = m_global;
+	*out = h;   // from here on the caller destroys on error
+
+	CU_TRY(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+	CU_TRY(cudaEventCreate(&h->ev0));
+	CU_TRY(cudaEventCreate(&h->ev1));
+	CU_TRY(cudaMalloc(&h->d_ia, sizeof(int32_t) * (m_local + 1)));
+	CU_TRY(cudaMalloc(&h->d_ja, sizeof(int32_t) * std::max<int64_t>(nnz_local, 1)));
+	CU_TRY(cudaMalloc(&h->d_a, sizeof(double) * std::max<int64_t>(nnz_local, 1)));
+	CU_TRY(cudaMemcpyAsync(h->d_ia, row_ptr_slice, sizeof(int32_t) * (m_local + 1), cudaMemcpyHostToDevice, h->stream));
+	if (nnz_local > 0) {
+		CU_TRY(cudaMemcpyAsync(h->d_ja, col_ind + base, sizeof(int32_t) * nnz_local, cudaMemcpyHostToDevice, h->stream));
+		CU_TRY(cudaMemcpyAsync(h->d_a, values + base, sizeof(double) * nnz_local, cudaMemcpyHostToDevice, h->stream));
+	}
+	if (base != 0) {
+		rebase_kernel<<<(unsigned) ((m_local + 1 + 255) / 256), 256, 0, h->stream>>>(h->d_ia, m_local + 1, base);
+		h->launches++;
+	}
+	// row-length statistics for AUTO
+	if (m_local > 0) {
+		int* d_max = nullptr;
+		CU_TRY(cudaMalloc(&d_max, sizeof(int)));
+		CU_TRY(cudaMemsetAsync(d_max, 0, sizeof(int), h->stream));
+		max_row_kernel<<<std::min<int64_t>(1024, (m_local + 255) / 256), 256, 0, h->stream>>>(h->d_ia, (int) m_local, d_max);
+		h->launches++;
+		CU_TRY(cudaMemcpyAsync(&h->max_row, d_max, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+		CU_TRY(cudaStreamSynchronize(h->stream));
+		cudaFree(d_max);
+	}
+	h->variant = (variant == SPMM_B200_AUTO) ? SPMM_B200_ROWSPLIT : variant;
+	if (h->variant != SPMM_B200_ROWSPLIT) return SPMM_B200_ENOSUP;
+	int rc = build_rowsplit_plan(h);
+	if (rc) return rc;
+	CU_TRY(cudaStreamSynchronize(h->stream));
+	return SPMM_B200_OK;
+}
+
+static int check_sizes(const void* rp, const void* ci, const void* va, int64_t m, int64_t c, int64_t nnz, int k)
+{
+	if (!rp || m < 0 || c < 0 || nnz < 0 || k < 1) return SPMM_B200_EINVAL;
+	if (nnz > 0 && (!ci || !va)) return SPMM_B200_EINVAL;
+	if (m >= INT32_MAX || c >= INT32_MAX || nnz >= INT32_MAX) return SPMM_B200_ERANGE;
+	return SPMM_B200_OK;
+}
+
+extern "C" int spmm_b200_create(spmm_b200_t** h, const int32_t* row_ptr, const int32_t* col_ind, const double* values,
+                                int64_t m, int64_t c, int64_t nnz, int k, int device, int variant, int b_layout)
+{
+	if (!h) return SPMM_B200_EINVAL;
+	*h = nullptr;
+	int rc = check_sizes(row_ptr, col_ind, values, m, c, nnz, k);
+	if (rc) return rc;
+	if (variant < SPMM_B200_ROWSPLIT || variant > SPMM_B200_AUTO) return SPMM_B200_EINVAL;
+	if (b_layout != SPMM_B200_B_COLMAJOR && b_layout != SPMM_B200_B_ROWMAJOR) return SPMM_B200_EINVAL;
+	int sms = 0;
+	rc = check_device(device, &sms);
+	if (rc) return rc;
+	rc = create_from_slice(h, row_ptr, col_ind, values, m, c, nnz, 0, k, device, variant, b_layout, sms, 0, m);
+	if (rc) { spmm_b200_destroy(*h); *h = nullptr; }
+	return rc;
+}
+
+extern "C" int spmm_b200_create_shard(spmm_b200_t** h, const int32_t* row_ptr, const int32_t* col_ind, const double* values,
+                                      int64_t m, int64_t c, int64_t nnz, int k, int device, int variant, int b_layout,
+                                      int rank, int nranks, int64_t* first_row, int64_t* last_row)
+{
+	if (!h) return SPMM_B200_EINVAL;
+	*h = nullptr;
+	int rc = check_sizes(row_ptr, col_ind, values, m, c, nnz, k);
+	if (rc) return rc;
+	if (nranks < 1 || rank < 0 || rank >= nranks) return SPMM_B200_EINVAL;
+	int sms = 0;
+	rc = check_device(device, &sms);
+	if (rc) return rc;
+	// shard boundaries: the reference's nnz-balanced split with P = nranks, searched on the device
+	std::vector<int64_t> bounds(nranks + 1);
+	rc = spmm_b200_partition(row_ptr, m, nnz, nranks, SPMM_B200_PART_NNZ, bounds.data(), device);
+	if (rc) return rc;
+	const int64_t r0 = bounds[rank], r1 = std::max(bounds[rank + 1], bounds[rank]);
+	if (first_row) *first_row = r0;
+	if (last_row) *last_row = r1;
+	const int32_t base = row_ptr[r0];
+	const int64_t nnz_local = (int64_t) row_ptr[r1] - base;
+	rc = create_from_slice(h, row_ptr + r0, col_ind, values, r1 - r0, c, nnz_local, base, k, device, variant, b_layout, sms, r0, m);
+	if (rc) { spmm_b200_destroy(*h); *h = nullptr; }
+	return rc;
+}
+
+extern "C" void spmm_b200_destroy(spmm_b200_t* h)
+{
+	if (!h) return;
+	cudaSetDevice(h->device);
+	if (h->stream) cudaStreamSynchronize(h->stream);
+	for (void* p : h->pinned) cudaHostUnregister(p);
+	cudaFree(h->d_ia); cudaFree(h->d_ja); cudaFree(h->d_a);
+	cudaFree(h->d_cta_rows);
+	cudaFree(h->d_x); cudaFree(h->d_B); cudaFree(h->d_C);
+	if (h->ev0) cudaEventDestroy(h->ev0);
+	if (h->ev1) cudaEventDestroy(h->ev1);
+	if (h->stream) cudaStreamDestroy(h->stream);
+	delete h;
+}
+
+// ------------------------------------------------------------------------------------------
+// the hot call
+// ------------------------------------------------------------------------------------------
+
+static int ensure(double** p, size_t* cap, size_t want)
+{
+	if (*cap >= want) return SPMM_B200_OK;
+	if (*p) cudaFree(*p);
+	*p = nullptr; *cap = 0;
+	CU_TRY(cudaMalloc(p, sizeof(double) * std::max<size_t>(want, 1)));
+	*cap = want;
+	return SPMM_B200_OK;
+}
+
+// Page-lock a caller buffer once so that the copies run at full PCIe rate and asynchronously
+// (the harness's x and y live for the whole run, spmv_bench.cpp:896-907).  Best effort.
+static void pin_once(spmm_b200* h, const void* p, size_t bytes)
+{
+	if (!p || bytes == 0 || env_int("SPMM_B200_PIN", 1) == 0) return;
+	if (std::find(h->pinned.begin(), h->pinned.end(), (void*) p) != h->pinned.end()) return;
+	cudaPointerAttributes at;
+	if (cudaPointerGetAttributes(&at, p) == cudaSuccess && at.type != cudaMemoryTypeUnregistered) return;
+	cudaGetLastError();
+	if (cudaHostRegister((void*) p, bytes, cudaHostRegisterDefault) == cudaSuccess) h->pinned.push_back((void*) p);
+	else cudaGetLastError();
+}
+
+static int upload_b(spmm_b200* h, const double* x_host, int k)
+{
+	const size_t nb = (size_t) h->c * k;
+	int rc = ensure(&h->d_B, &h->cap_B, nb);
+	if (rc) return rc;
+	pin_once(h, x_host, nb * sizeof(double));
+	if (h->b_layout == SPMM_B200_B_ROWMAJOR || k == 1) {
+		CU_TRY(cudaMemcpyAsync(h->d_B, x_host, nb * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+	} else {
+		rc = ensure(&h->d_x, &h->cap_x, nb);
+		if (rc) return rc;
+		CU_TRY(cudaMemcpyAsync(h->d_x, x_host, nb * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+		rc = spmm_b200_transpose_b_device(h, h->d_x, h->d_B, k, h->stream);
+		if (rc) return rc;
+	}
+	h->resident_k = k;
+	return SPMM_B200_OK;
+}
+
+extern "C" int spmm_b200_transpose_b_device(spmm_b200_t* h, const double* x_dev, double* b_dev, int k, void* stream)
+{
+	if (!h || !x_dev || !b_dev || k < 1) return SPMM_B200_EINVAL;
+	if (h->c == 0) return SPMM_B200_OK;
+	CU_TRY(cudaSetDevice(h->device));
+	dim3 grid((unsigned) ((h->c + 31) / 32), (unsigned) ((k + 31) / 32)), block(32, 8);
+	transpose_b_kernel<<<grid, block, 0, (cudaStream_t) stream>>>(x_dev, b_dev, h->c, k);
+	h->launches++;
+	CU_TRY(cudaGetLastError());
+	return SPMM_B200_OK;
+}
+
+extern "C" int spmm_b200_run_device(spmm_b200_t* h, const double* b_dev, double* c_dev, int k, void* stream)
+{
+	if (!h || k < 1) return SPMM_B200_EINVAL;
+	if ((h->c > 0 && h->nnz > 0 && !b_dev) || (h->m > 0 && !c_dev)) return SPMM_B200_EINVAL;
+	CU_TRY(cudaSetDevice(h->device));
+	cudaStream_t s = (cudaStream_t) stream;
+	CU_TRY(cudaEventRecord(h->ev0, s));
+	int n = launch_spmm(h, b_dev, c_dev, k, s);
+	if (n < 0) return n;
+	CU_TRY(cudaEventRecord(h->ev1, s));
+	h->timed = true;
+	return SPMM_B200_OK;
+}
+
+extern "C" int spmm_b200_set_b(spmm_b200_t* h, const double* x_host, int k)
+{
+	if (!h || !x_host || k < 1) return SPMM_B200_EINVAL;
+	CU_TRY(cudaSetDevice(h->device));
+	int rc = upload_b(h, x_host, k);
+	if (rc) return rc;
+	CU_TRY(cudaStreamSynchronize(h->stream));
+	return SPMM_B200_OK;
+}
+
+extern "C" int spmm_b200_run_resident(spmm_b200_t* h, int k)
+{
+	if (!h || k < 1 || h->resident_k != k) return SPMM_B200_EINVAL;
+	int rc = ensure(&h->d_C, &h->cap_C, (size_t) h->m * k);
+	if (rc) return rc;
+	rc = spmm_b200_run_device(h, h->d_B, h->d_C, k, h->stream);
+	if (rc) return rc;
+	CU_TRY(cudaStreamSynchronize(h->stream));
+	return SPMM_B200_OK;
+}
+
+extern "C" int spmm_b200_fetch_c(spmm_b200_t* h, double* y_host, int k)
+{
+	if (!h || !y_host || k < 1 || h->cap_C < (size_t) h->m * k) return SPMM_B200_EINVAL;
+	CU_TRY(cudaSetDevice(h->device));
+	CU_TRY(cudaMemcpyAsync(y_host, h->d_C, sizeof(double) * h->m * k, cudaMemcpyDeviceToHost, h->stream));
+	CU_TRY(cudaStreamSynchronize(h->stream));
+	return SPMM_B200_OK;
+}
+
+extern "C" int spmm_b200_run(spmm_b200_t* h, const double* x_host, double* y_host, int k, int copy_back)
+{
+	if (!h || !x_host || k < 1 || (copy_back && !y_host)) return SPMM_B200_EINVAL;
+	CU_TRY(cudaSetDevice(h->device));
+	int rc = upload_b(h, x_host, k);
+	if (rc) return rc;
+	rc = ensure(&h->d_C, &h->cap_C, (size_t) h->m * k);
+	if (rc) return rc;
+	rc = spmm_b200_run_device(h, h->d_B, h->d_C, k, h->stream);
+	if (rc) return rc;
+	if (copy_back && h->m > 0) {
+		pin_once(h, y_host, sizeof(double) * h->m * k);
+		CU_TRY(cudaMemcpyAsync(y_host, h->d_C, sizeof(double) * h->m * k, cudaMemcpyDeviceToHost, h->stream));
+	}
+	CU_TRY(cudaStreamSynchronize(h->stream));
+	return SPMM_B200_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// partitioning (device search, host pointers in and out)
+// ------------------------------------------------------------------------------------------
+
+extern "C" int spmm_b200_partition(const int32_t* row_ptr, int64_t m, int64_t nnz, int P, int mode, int64_t* out, int device)
+{
+	if (!out || P < 1 || m < 0 || nnz < 0) return SPMM_B200_EINVAL;
+	if (mode != SPMM_B200_PART_ROWS && !row_ptr) return SPMM_B200_EINVAL;
+	if (mode < SPMM_B200_PART_ROWS || mode > SPMM_B200_PART_MERGE) return SPMM_B200_EINVAL;
+	int rc = check_device(device, nullptr);
+	if (rc) return rc;
+	const size_t n_out = (mode == SPMM_B200_PART_NNZ) ? (size_t) P + 1 : (mode == SPMM_B200_PART_ROWS ? 2 * (size_t) P : 2 * ((size_t) P + 1));
+	int32_t* d_ia = nullptr;
+	int64_t* d_out = nullptr;
+	CU_TRY(cudaMalloc(&d_out, sizeof(int64_t) * n_out));
+	if (mode != SPMM_B200_PART_ROWS) {
+		cudaError_t e = cudaMalloc(&d_ia, sizeof(int32_t) * (m + 1));
+		if (e != cudaSuccess) { cudaFree(d_out); CU_TRY(e); }
+		e = cudaMemcpy(d_ia, row_ptr, sizeof(int32_t) * (m + 1), cudaMemcpyHostToDevice);
+		if (e != cudaSuccess) { cudaFree(d_out); cudaFree(d_ia); CU_TRY(e); }
+	}
+	const unsigned nb = (unsigned) ((P + 1 + 255) / 256);
+	if (mode == SPMM_B200_PART_NNZ) partition_nnz_kernel<<<nb, 256>>>(d_ia, m, nnz, P, d_out);
+	else if (mode == SPMM_B200_PART_ROWS) partition_rows_kernel<<<nb, 256>>>(0, m, P, d_out);
+	else partition_merge_kernel<<<nb, 256>>>(d_ia, m, nnz, P, d_out);
+	cudaError_t e = cudaGetLastError();
+	if (e == cudaSuccess) e = cudaMemcpy(out, d_out, sizeof(int64_t) * n_out, cudaMemcpyDeviceToHost);
+	cudaFree(d_out); cudaFree(d_ia);
+	CU_TRY(e);
+	return SPMM_B200_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// introspection
+// ------------------------------------------------------------------------------------------
+
+extern "C" int64_t spmm_b200_rows(const spmm_b200_t* h) { return h ? h->m : -1; }
+extern "C" int64_t spmm_b200_nnz(const spmm_b200_t* h) { return h ? h->nnz : -1; }
+extern "C" int spmm_b200_variant(const spmm_b200_t* h) { return h ? h->variant : SPMM_B200_EINVAL; }
+extern "C" int64_t spmm_b200_launch_count(const spmm_b200_t* h) { return h ? h->launches : -1; }
+
+extern "C" double spmm_b200_last_kernel_ms(const spmm_b200_t* h)
+{
+	if (!h || !h->timed) return -1.0;
+	float ms = 0.f;
+	if (cudaEventSynchronize(h->ev1) != cudaSuccess) return -1.0;
+	if (cudaEventElapsedTime(&ms, h->ev0, h->ev1) != cudaSuccess) return -1.0;
+	return (double) ms;
+}
+
+extern "C" int spmm_b200_stats_labels(char* buf, long buf_n)
+{
+	if (!buf || buf_n <= 0) return 0;
+	return snprintf(buf, buf_n, ",b200_variant,b200_ctas,b200_max_row,b200_kernel_ms,b200_kernel_gflops,b200_hbm_roofline_frac_8TBs");
+}
+
+extern "C" int spmm_b200_stats(const spmm_b200_t* h, char* buf, long buf_n)
+{
+	if (!h || !buf || buf_n <= 0) return 0;
+	const double ms = spmm_b200_last_kernel_ms(h);
+	const int k = h->resident_k > 0 ? h->resident_k : h->k;
+	const double gflops = ms > 0 ? 2.0 * h->nnz * k / (ms * 1e6) : 0.0;
+	const double bytes = 12.0 * h->nnz + 4.0 * (h->m + 1) + 8.0 * k * (double) h->c + 8.0 * k * (double) h->m;
+	const double frac = ms > 0 ? (bytes / 8.0e12) / (ms * 1e-3) : 0.0;
+	static const char* names[] = {"rowsplit", "merge", "bcsr", "auto"};
+	return snprintf(buf, buf_n, ",%s,%d,%d,%g,%g,%g", names[h->variant & 3],
+	                h->variant == SPMM_B200_MERGE ? h->merge.ntiles : h->n_ctas, h->max_row, ms, gflops, frac);
+}
+
+extern "C" const char* spmm_b200_strerror(int code)
+{
+	switch (code) {
+	case SPMM_B200_OK:     return "ok";
+	case SPMM_B200_EINVAL: return "invalid argument";
+	case SPMM_B200_ENODEV: return "no usable sm_100 CUDA device (this library has no CPU fallback)";
+	case SPMM_B200_ECUDA:  return "CUDA runtime error";
+	case SPMM_B200_ENOMEM: return "out of memory";
+	case SPMM_B200_ERANGE: return "size exceeds the int32 index contract";
+	case SPMM_B200_ENOSUP: return "variant not supported for this input";
+	default:               return "unknown error";
+	}
+}
+
+extern "C" const char* spmm_b200_last_cuda_error(void) { return g_cuda_err; }
+
+extern "C" int spmm_b200_device_count(void)
+{
+	int n = 0;
+	if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+	return n;
+}

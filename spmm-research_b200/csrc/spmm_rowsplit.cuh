@@ -1,0 +1,207 @@
+// spmm_rowsplit.cuh -- CSR SpMM, "row-split" variant (north_star kernel (2), warp-per-row family).
+//
+// Computes what the reference's compute_csr does
+// (benchmark_code/CPU/AMD/spmv_code_bench/spmm_kernel_csr.cpp:69-97):
+//     C[i*k + n] = sum_{j in [ia[i], ia[i+1])} a[j] * B[ja[j]][n]
+// but with the loop nest turned inside out: A is streamed ONCE (not k times) and every
+// gathered B row (k contiguous doubles, B kept row-major on the device) is consumed for
+// all k columns at once.  The per-row sum runs left to right like the oracle's.
+//
+// Work mapping
+//   * CTA b owns the contiguous rows [cta_rows[b], cta_rows[b+1]) of the nnz-balanced
+//     split (partition.cuh: cta_rows_nnz_kernel, bit-exact with lib/parallel_util.h:141-165).
+//   * Inside a CTA a group of G lanes owns one row at a time; a lane owns V of the k = G*V
+//     dense columns, so one group-wide load of a B row is k*8 contiguous bytes
+//     (k=32: 16 lanes x 16 B = 256 B = two full 128-B lines).
+//   * (col, val) of a nonzero are read once per group as same-address (broadcast) loads
+//     through L1; UNROLL nonzeros are in flight per group so that each warp keeps
+//     UNROLL * 32/G independent B gathers outstanding (the kernel is bound by L2->SM
+//     gather bandwidth, not by HBM).
+#pragma once
+#include <stdint.h>
+#include <cuda_runtime.h>
+
+namespace sb200 {
+
+template <int V> struct Frag { double v[V]; };
+
+// Load this lane's V columns of B row `col`.  Columns are dealt to lanes in pairs:
+// lane l holds columns {2l, 2l+1} (+ 2G for the second pair when V == 4), so every
+// load instruction of the group covers one contiguous span.
+template <int G, int V>
+__device__ __forceinline__ Frag<V> load_b(const double* __restrict__ B, int col, int lig)
+{
+	constexpr int K = G * V;
+	Frag<V> f;
+	const double* p = B + (size_t) col * K;
+	if constexpr (V == 1) {
+		f.v[0] = __ldg(p + lig);
+	} else if constexpr (V == 2) {
+		double2 t = __ldg(reinterpret_cast<const double2*>(p) + lig);
+		f.v[0] = t.x; f.v[1] = t.y;
+	} else {
+		static_assert(V == 4, "V must be 1, 2 or 4");
+		double2 t = __ldg(reinterpret_cast<const double2*>(p) + lig);
+		double2 u = __ldg(reinterpret_cast<const double2*>(p) + G + lig);
+		f.v[0] = t.x; f.v[1] = t.y; f.v[2] = u.x; f.v[3] = u.y;
+	}
+	return f;
+}
+
+template <int G, int V>
+__device__ __forceinline__ void store_c(double* __restrict__ C, size_t row, int lig, const double (&acc)[V])
+{
+	constexpr int K = G * V;
+	double* p = C + row * K;
+	if constexpr (V == 1) {
+		p[lig] = acc[0];
+	} else if constexpr (V == 2) {
+		reinterpret_cast<double2*>(p)[lig] = make_double2(acc[0], acc[1]);
+	} else {
+		reinterpret_cast<double2*>(p)[lig] = make_double2(acc[0], acc[1]);
+		reinterpret_cast<double2*>(p)[G + lig] = make_double2(acc[2], acc[3]);
+	}
+}
+
+template <int G, int V, int UNROLL, int THREADS>
+__global__ void __launch_bounds__(THREADS)
+spmm_rowsplit_kernel(const int32_t* __restrict__ ia, const int32_t* __restrict__ ja, const double* __restrict__ a,
+                     const double* __restrict__ B, double* __restrict__ C,
+                     const int32_t* __restrict__ cta_rows)
+{
+	constexpr int NG = THREADS / G;          // row groups per CTA
+	const int lig = threadIdx.x % G;         // lane in group
+	const int gid = threadIdx.x / G;
+	const int r0 = cta_rows[blockIdx.x];
+	const int r1 = cta_rows[blockIdx.x + 1];
+
+	for (int row = r0 + gid; row < r1; row += NG) {
+		int j = __ldg(ia + row);
+		const int je = __ldg(ia + row + 1);
+		double acc[V];
+		#pragma unroll
+		for (int v = 0; v < V; v++) acc[v] = 0.0;
+
+		for (; j + UNROLL <= je; j += UNROLL) {
+			int cc[UNROLL];
+			double vv[UNROLL];
+			Frag<V> bb[UNROLL];
+			#pragma unroll
+			for (int u = 0; u < UNROLL; u++) cc[u] = __ldg(ja + j + u);
+			#pragma unroll
+			for (int u = 0; u < UNROLL; u++) bb[u] = load_b<G, V>(B, cc[u], lig);
+			#pragma unroll
+			for (int u = 0; u < UNROLL; u++) vv[u] = __ldg(a + j + u);
+			#pragma unroll
+			for (int u = 0; u < UNROLL; u++) {
+				#pragma unroll
+				for (int v = 0; v < V; v++) acc[v] = fma(vv[u], bb[u].v[v], acc[v]);
+			}
+		}
+		for (; j < je; j++) {
+			const int cc = __ldg(ja + j);
+			const double vv = __ldg(a + j);
+			Frag<V> bb = load_b<G, V>(B, cc, lig);
+			#pragma unroll
+			for (int v = 0; v < V; v++) acc[v] = fma(vv, bb.v[v], acc[v]);
+		}
+		store_c<G, V>(C, (size_t) row, lig, acc);
+	}
+}
+
+// Any k: one warp per row, lanes own columns, column chunks of 32 (A re-read per chunk
+// out of L1/L2).  Used for k values without a specialised instantiation.
+template <int THREADS>
+__global__ void __launch_bounds__(THREADS)
+spmm_rowsplit_generic_kernel(const int32_t* __restrict__ ia, const int32_t* __restrict__ ja, const double* __restrict__ a,
+                             const double* __restrict__ B, double* __restrict__ C,
+                             const int32_t* __restrict__ cta_rows, int k)
+{
+	constexpr int NW = THREADS / 32;
+	const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+	const int r0 = cta_rows[blockIdx.x], r1 = cta_rows[blockIdx.x + 1];
+	for (int row = r0 + wid; row < r1; row += NW) {
+		const int js = __ldg(ia + row), je = __ldg(ia + row + 1);
+		for (int n0 = 0; n0 < k; n0 += 32) {
+			const int n = n0 + lane;
+			double acc = 0.0;
+			if (n < k) {
+				for (int j = js; j < je; j++)
+					acc = fma(__ldg(a + j), __ldg(B + (size_t) __ldg(ja + j) * k + n), acc);
+				C[(size_t) row * k + n] = acc;
+			}
+		}
+	}
+}
+
+// Small k (1, 2, 4): the SpMV-like regime.  G lanes share a row and stride over its
+// nonzeros (coalesced reads of ja/a), each lane keeps K partial sums, then a shuffle
+// tree combines them.  Summation order differs from the oracle's (tolerance, not bits).
+template <int K, int G, int THREADS>
+__global__ void __launch_bounds__(THREADS)
+spmm_smallk_kernel(const int32_t* __restrict__ ia, const int32_t* __restrict__ ja, const double* __restrict__ a,
+                   const double* __restrict__ B, double* __restrict__ C,
+                   const int32_t* __restrict__ cta_rows)
+{
+	constexpr int NG = THREADS / G;
+	const int lig = threadIdx.x % G, gid = threadIdx.x / G;
+	const int r0 = cta_rows[blockIdx.x], r1 = cta_rows[blockIdx.x + 1];
+	// all groups of a warp must run the same number of iterations for the shuffles
+	const int nrows = r1 - r0;
+	const int iters = (nrows + NG - 1) / NG;
+	for (int it = 0; it < iters; it++) {
+		const int row = r0 + it * NG + gid;
+		const bool live = row < r1;
+		double acc[K];
+		#pragma unroll
+		for (int n = 0; n < K; n++) acc[n] = 0.0;
+		if (live) {
+			const int js = __ldg(ia + row), je = __ldg(ia + row + 1);
+			for (int j = js + lig; j < je; j += G) {
+				const double v = __ldg(a + j);
+				const double* p = B + (size_t) __ldg(ja + j) * K;
+				if constexpr (K == 1) {
+					acc[0] = fma(v, __ldg(p), acc[0]);
+				} else if constexpr (K == 2) {
+					double2 t = __ldg(reinterpret_cast<const double2*>(p));
+					acc[0] = fma(v, t.x, acc[0]); acc[1] = fma(v, t.y, acc[1]);
+				} else {
+					double2 t = __ldg(reinterpret_cast<const double2*>(p));
+					double2 u = __ldg(reinterpret_cast<const double2*>(p) + 1);
+					acc[0] = fma(v, t.x, acc[0]); acc[1] = fma(v, t.y, acc[1]);
+					acc[2] = fma(v, u.x, acc[2]); acc[3] = fma(v, u.y, acc[3]);
+				}
+			}
+		}
+		#pragma unroll
+		for (int off = G / 2; off > 0; off >>= 1) {
+			#pragma unroll
+			for (int n = 0; n < K; n++) acc[n] += __shfl_down_sync(0xffffffffu, acc[n], off, G);
+		}
+		if (live && lig == 0) {
+			#pragma unroll
+			for (int n = 0; n < K; n++) C[(size_t) row * K + n] = acc[n];
+		}
+	}
+}
+
+// B upload helper: oracle layout x[n*c + j] (k vectors of length c) -> row-major B[j*k + n].
+__global__ void transpose_b_kernel(const double* __restrict__ x, double* __restrict__ B, int64_t c, int k)
+{
+	__shared__ double tile[32][33];
+	const int64_t j0 = (int64_t) blockIdx.x * 32;
+	const int n0 = blockIdx.y * 32;
+	for (int dy = threadIdx.y; dy < 32; dy += blockDim.y) {
+		const int n = n0 + dy;
+		const int64_t j = j0 + threadIdx.x;
+		if (n < k && j < c) tile[dy][threadIdx.x] = x[(int64_t) n * c + j];
+	}
+	__syncthreads();
+	for (int dy = threadIdx.y; dy < 32; dy += blockDim.y) {
+		const int64_t j = j0 + dy;
+		const int n = n0 + threadIdx.x;
+		if (n < k && j < c) B[j * k + n] = tile[threadIdx.x][dy];
+	}
+}
+
+} // namespace sb200
