@@ -27,6 +27,7 @@
 #ifndef SPMM_B200_H
 #define SPMM_B200_H
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -92,6 +93,13 @@ int spmm_b200_create_shard(spmm_b200_t **h,
  * and when copy_back != 0 downloads y (D2H) before returning.  With
  * copy_back == 0 the result stays on the device (spmm_b200_fetch_c reads it). */
 int spmm_b200_run(spmm_b200_t *h, const double *x_host, double *y_host, int k, int copy_back);
+
+/* Optional: page-lock a caller-owned host range (x or y) so that spmm_b200_run copies at full
+ * PCIe rate.  The caller promises the range stays mapped until spmm_b200_unregister_host /
+ * spmm_b200_destroy -- true for the harness's x and y (spmv_bench.cpp:896-907).  Ranges that
+ * are already page-locked (cudaHostAlloc, torch pin_memory) are accepted and left alone. */
+int spmm_b200_register_host(spmm_b200_t *h, const void *p, size_t bytes);
+int spmm_b200_unregister_host(spmm_b200_t *h, const void *p);
 
 /* Upload B once (x is constant across the reference's timed loop,
  * spmv_bench.cpp:895-903) and run on the resident copy. */

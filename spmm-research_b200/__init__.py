@@ -30,6 +30,7 @@ LIB_PATH = os.path.join(HERE, "lib", "libspmm_b200.so")
 # every symbol include/spmm_b200.h declares
 EXPORTS = [
     "spmm_b200_create", "spmm_b200_create_shard", "spmm_b200_run", "spmm_b200_set_b",
+    "spmm_b200_register_host", "spmm_b200_unregister_host",
     "spmm_b200_run_resident", "spmm_b200_fetch_c", "spmm_b200_run_device",
     "spmm_b200_transpose_b_device", "spmm_b200_partition", "spmm_b200_rows", "spmm_b200_nnz",
     "spmm_b200_variant", "spmm_b200_last_kernel_ms", "spmm_b200_launch_count", "spmm_b200_stats",
@@ -65,6 +66,8 @@ def load_library():
     lib.spmm_b200_create_shard.argtypes = lib.spmm_b200_create.argtypes + [_int, _int, C.POINTER(_i64), C.POINTER(_i64)]
     lib.spmm_b200_run.argtypes = [_vp, _vp, _vp, _int, _int]
     lib.spmm_b200_set_b.argtypes = [_vp, _vp, _int]
+    lib.spmm_b200_register_host.argtypes = [_vp, _vp, C.c_size_t]
+    lib.spmm_b200_unregister_host.argtypes = [_vp, _vp]
     lib.spmm_b200_run_resident.argtypes = [_vp, _int]
     lib.spmm_b200_fetch_c.argtypes = [_vp, _vp, _int]
     lib.spmm_b200_run_device.argtypes = [_vp, _vp, _vp, _int, _vp]

@@ -154,10 +154,102 @@ static void launch_smallk(const spmm_b200* h, const double* B, double* C, cudaSt
 	}
 }
 
+// ---- merge-path plan: tile coordinates depend on the tile size, which depends on k ----------
+template <int G, int V, int IPG>
+struct MergeLaunch {
+	using Cfg = MergeCfg<G, V, IPG, THREADS>;
+	static int items() { return Cfg::ITEMS; }
+	static cudaError_t launch(const spmm_b200* h, const double* B, double* C, cudaStream_t s)
+	{
+		auto kern = spmm_merge_kernel<G, V, IPG, 4, THREADS>;
+		static bool attr_set = false;
+		if (!attr_set && Cfg::SMEM > 48 * 1024) {
+			cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) Cfg::SMEM);
+			if (e != cudaSuccess) return e;
+			attr_set = true;
+		}
+		kern<<<h->merge.ntiles, THREADS, Cfg::SMEM, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, h->merge.d_tile,
+		                                                h->merge.d_carry, h->merge.d_carry_row);
+		return cudaGetLastError();
+	}
+};
+
+// k -> (G, V, IPG) of the merge kernel; 0 items = no specialised instantiation
+#define MERGE_DISPATCH(k, WHAT)                                    \
+	switch (k) {                                                   \
+	case 1:   WHAT(1, 1, 16); break;                               \
+	case 2:   WHAT(1, 2, 16); break;                               \
+	case 4:   WHAT(2, 2, 16); break;                               \
+	case 8:   WHAT(4, 2, 32); break;                               \
+	case 16:  WHAT(8, 2, 32); break;                               \
+	case 32:  WHAT(16, 2, 64); break;                              \
+	case 64:  WHAT(32, 2, 128); break;                             \
+	case 128: WHAT(32, 4, 128); break;                             \
+	default: break;                                                \
+	}
+
+static int merge_items_for_k(int k)
+{
+	int items = 0;
+#define WHAT(G, V, IPG) items = MergeLaunch<G, V, IPG>::items()
+	MERGE_DISPATCH(k, WHAT)
+#undef WHAT
+	return items;
+}
+
+static bool merge_supports_k(int k) { return merge_items_for_k(k) > 0; }
+
+static int build_merge_plan(spmm_b200* h, int k, cudaStream_t s)
+{
+	const int items = merge_items_for_k(k);
+	if (items <= 0) return SPMM_B200_ENOSUP;
+	MergePlan& p = h->merge;
+	if (p.items == items && p.carry_k >= k && p.d_tile) return SPMM_B200_OK;
+	const int64_t L = h->m + h->nnz;
+	const int ntiles = (int) ((L + items - 1) / items);
+	cudaFree(p.d_tile); cudaFree(p.d_carry); cudaFree(p.d_carry_row);
+	p.d_tile = nullptr; p.d_carry = nullptr; p.d_carry_row = nullptr;
+	CU_TRY(cudaMalloc(&p.d_tile, sizeof(int2) * ((size_t) ntiles + 1)));
+	CU_TRY(cudaMalloc(&p.d_carry, sizeof(double) * std::max<size_t>((size_t) ntiles * k, 1)));
+	CU_TRY(cudaMalloc(&p.d_carry_row, sizeof(int32_t) * std::max(ntiles, 1)));
+	p.ntiles = ntiles; p.items = items; p.carry_k = k;
+	tile_merge_kernel<<<(ntiles + 1 + 255) / 256, 256, 0, s>>>(h->d_ia, (int) h->m, h->nnz, items, ntiles, p.d_tile);
+	h->launches++;
+	CU_TRY(cudaGetLastError());
+	return SPMM_B200_OK;
+}
+
+static int launch_merge(spmm_b200* h, const double* B, double* C, int k, cudaStream_t s)
+{
+	int rc = build_merge_plan(h, k, s);     // no-op when the plan matches k (stream-ordered otherwise)
+	if (rc) return rc;
+	if (h->merge.ntiles == 0) return 0;
+	cudaError_t e = cudaErrorInvalidValue;
+#define WHAT(G, V, IPG) e = MergeLaunch<G, V, IPG>::launch(h, B, C, s)
+	MERGE_DISPATCH(k, WHAT)
+#undef WHAT
+	if (e != cudaSuccess) {
+		snprintf(g_cuda_err, sizeof(g_cuda_err), "merge kernel launch (k=%d): %s", k, cudaGetErrorString(e));
+		return SPMM_B200_ECUDA;
+	}
+	const int64_t n = (int64_t) h->merge.ntiles * k;
+	spmm_merge_fixup_kernel<THREADS><<<(unsigned) ((n + THREADS - 1) / THREADS), THREADS, 0, s>>>(
+		h->merge.d_carry, h->merge.d_carry_row, h->merge.ntiles, (int) h->m, k, C);
+	e = cudaGetLastError();
+	if (e != cudaSuccess) {
+		snprintf(g_cuda_err, sizeof(g_cuda_err), "merge fixup launch (k=%d): %s", k, cudaGetErrorString(e));
+		return SPMM_B200_ECUDA;
+	}
+	h->launches += 2;
+	return 2;
+}
+
 // Launches the SpMM kernel(s) of the handle's variant on stream s.  Returns kernels launched or <0.
 static int launch_spmm(spmm_b200* h, const double* B, double* C, int k, cudaStream_t s)
 {
 	if (h->m == 0) return 0;
+	// merge-path has no instantiation for odd k: those run on the row-split generic kernel
+	if (h->variant == SPMM_B200_MERGE && merge_supports_k(k)) return launch_merge(h, B, C, k, s);
 	int n = 1;
 	switch (k) {
 	case 1:   launch_smallk<1>(h, B, C, s); break;
@@ -222,10 +314,22 @@ static int create_from_slice(spmm_b200_t** out, const int32_t* row_ptr_slice, co
 		CU_TRY(cudaStreamSynchronize(h->stream));
 		cudaFree(d_max);
 	}
-	h->variant = (variant == SPMM_B200_AUTO) ? SPMM_B200_ROWSPLIT : variant;
-	if (h->variant != SPMM_B200_ROWSPLIT) return SPMM_B200_ENOSUP;
-	int rc = build_rowsplit_plan(h);
+	if (variant == SPMM_B200_AUTO) {
+		// row-split serialises a row on one lane group: switch to merge-path when one row is far
+		// longer than the mean (SURVEY 8(d) cfg 3: 200 040 nnz against a mean of 20)
+		const double avg = m_local > 0 ? (double) nnz_local / (double) m_local : 0.0;
+		const int thr = env_int("SPMM_B200_MERGE_MAXROW", 4096);
+		h->variant = (h->max_row >= thr && h->max_row > 16.0 * avg) ? SPMM_B200_MERGE : SPMM_B200_ROWSPLIT;
+	} else {
+		h->variant = variant;
+	}
+	if (h->variant == SPMM_B200_BCSR) return SPMM_B200_ENOSUP;
+	int rc = build_rowsplit_plan(h);        // always: the fallback for k without a merge instantiation
 	if (rc) return rc;
+	if (h->variant == SPMM_B200_MERGE && merge_supports_k(k)) {
+		rc = build_merge_plan(h, k, h->stream);
+		if (rc) return rc;
+	}
 	CU_TRY(cudaStreamSynchronize(h->stream));
 	return SPMM_B200_OK;
 }
@@ -289,6 +393,7 @@ extern "C" void spmm_b200_destroy(spmm_b200_t* h)
 	for (void* p : h->pinned) cudaHostUnregister(p);
 	cudaFree(h->d_ia); cudaFree(h->d_ja); cudaFree(h->d_a);
 	cudaFree(h->d_cta_rows);
+	cudaFree(h->merge.d_tile); cudaFree(h->merge.d_carry); cudaFree(h->merge.d_carry_row);
 	cudaFree(h->d_x); cudaFree(h->d_B); cudaFree(h->d_C);
 	if (h->ev0) cudaEventDestroy(h->ev0);
 	if (h->ev1) cudaEventDestroy(h->ev1);
@@ -310,17 +415,32 @@ static int ensure(double** p, size_t* cap, size_t want)
 	return SPMM_B200_OK;
 }
 
-// Page-lock a caller buffer once so that the copies run at full PCIe rate and asynchronously
-// (the harness's x and y live for the whole run, spmv_bench.cpp:896-907).  Best effort.
-static void pin_once(spmm_b200* h, const void* p, size_t bytes)
+// Page-lock a caller buffer so that the copies run at full PCIe rate.  Only on explicit request
+// (spmm_b200_register_host): the caller promises the range stays mapped until it is unregistered
+// or the handle is destroyed (true for the harness's x and y, spmv_bench.cpp:896-907; NOT true
+// for short-lived buffers, where a stale registration would send DMA to recycled pages).
+extern "C" int spmm_b200_register_host(spmm_b200_t* h, const void* p, size_t bytes)
 {
-	if (!p || bytes == 0 || env_int("SPMM_B200_PIN", 1) == 0) return;
-	if (std::find(h->pinned.begin(), h->pinned.end(), (void*) p) != h->pinned.end()) return;
+	if (!h || !p || bytes == 0) return SPMM_B200_EINVAL;
+	if (std::find(h->pinned.begin(), h->pinned.end(), (void*) p) != h->pinned.end()) return SPMM_B200_OK;
+	CU_TRY(cudaSetDevice(h->device));
 	cudaPointerAttributes at;
-	if (cudaPointerGetAttributes(&at, p) == cudaSuccess && at.type != cudaMemoryTypeUnregistered) return;
+	if (cudaPointerGetAttributes(&at, p) == cudaSuccess && at.type != cudaMemoryTypeUnregistered) return SPMM_B200_OK;
 	cudaGetLastError();
-	if (cudaHostRegister((void*) p, bytes, cudaHostRegisterDefault) == cudaSuccess) h->pinned.push_back((void*) p);
-	else cudaGetLastError();
+	CU_TRY(cudaHostRegister((void*) p, bytes, cudaHostRegisterDefault));
+	h->pinned.push_back((void*) p);
+	return SPMM_B200_OK;
+}
+
+extern "C" int spmm_b200_unregister_host(spmm_b200_t* h, const void* p)
+{
+	if (!h || !p) return SPMM_B200_EINVAL;
+	auto it = std::find(h->pinned.begin(), h->pinned.end(), (void*) p);
+	if (it == h->pinned.end()) return SPMM_B200_EINVAL;
+	h->pinned.erase(it);
+	CU_TRY(cudaSetDevice(h->device));
+	CU_TRY(cudaHostUnregister((void*) p));
+	return SPMM_B200_OK;
 }
 
 static int upload_b(spmm_b200* h, const double* x_host, int k)
@@ -328,7 +448,6 @@ static int upload_b(spmm_b200* h, const double* x_host, int k)
 	const size_t nb = (size_t) h->c * k;
 	int rc = ensure(&h->d_B, &h->cap_B, nb);
 	if (rc) return rc;
-	pin_once(h, x_host, nb * sizeof(double));
 	if (h->b_layout == SPMM_B200_B_ROWMAJOR || k == 1) {
 		CU_TRY(cudaMemcpyAsync(h->d_B, x_host, nb * sizeof(double), cudaMemcpyHostToDevice, h->stream));
 	} else {
@@ -409,7 +528,6 @@ extern "C" int spmm_b200_run(spmm_b200_t* h, const double* x_host, double* y_hos
 	rc = spmm_b200_run_device(h, h->d_B, h->d_C, k, h->stream);
 	if (rc) return rc;
 	if (copy_back && h->m > 0) {
-		pin_once(h, y_host, sizeof(double) * h->m * k);
 		CU_TRY(cudaMemcpyAsync(y_host, h->d_C, sizeof(double) * h->m * k, cudaMemcpyDeviceToHost, h->stream));
 	}
 	CU_TRY(cudaStreamSynchronize(h->stream));

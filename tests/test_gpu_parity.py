@@ -15,7 +15,9 @@ KS = [1, 2, 4, 8, 16, 32, 64, 128, 3, 20, 100]
 
 
 def variants(pkg):
-    return [pkg.ROWSPLIT, pkg.MERGE, pkg.AUTO]
+    names = os.environ.get("SPMM_B200_TEST_VARIANTS", "rowsplit,merge,auto").split(",")
+    table = {"rowsplit": pkg.ROWSPLIT, "merge": pkg.MERGE, "bcsr": pkg.BCSR, "auto": pkg.AUTO}
+    return [table[n] for n in names if n]
 
 
 def run_spmm(pkg, ia, ja, a, m, c, x, k, variant, **kw):
