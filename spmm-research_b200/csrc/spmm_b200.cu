@@ -139,7 +139,14 @@ static int pick_small_group(const spmm_b200* h)
 template <int G, int V>
 static void launch_rowsplit_gv(const spmm_b200* h, const double* B, double* C, cudaStream_t s)
 {
-	spmm_rowsplit_kernel<G, V, 4, THREADS><<<h->n_ctas, THREADS, 0, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, h->d_cta_rows);
+	// B-row gathers in flight per lane group; tuning knob, default from the ncu study in profiles/
+	static const int unroll = env_int("SPMM_B200_UNROLL", 4);
+	if (unroll >= 8 && G >= 8)
+		spmm_rowsplit_kernel<G, V, 8, THREADS><<<h->n_ctas, THREADS, 0, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, h->d_cta_rows);
+	else if (unroll <= 2)
+		spmm_rowsplit_kernel<G, V, 2, THREADS><<<h->n_ctas, THREADS, 0, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, h->d_cta_rows);
+	else
+		spmm_rowsplit_kernel<G, V, 4, THREADS><<<h->n_ctas, THREADS, 0, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, h->d_cta_rows);
 }
 
 template <int K>

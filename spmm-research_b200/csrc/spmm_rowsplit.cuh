@@ -63,6 +63,22 @@ __device__ __forceinline__ void store_c(double* __restrict__ C, size_t row, int 
 	}
 }
 
+// Broadcast of a double inside a lane group of width G.
+template <int G>
+__device__ __forceinline__ double shfl_f64(double v, int src)
+{
+	int lo = __double2loint(v), hi = __double2hiint(v);
+	lo = __shfl_sync(0xffffffffu, lo, src, G);
+	hi = __shfl_sync(0xffffffffu, hi, src, G);
+	return __hiloint2double(hi, lo);
+}
+
+// (col, val) staging: the G lanes of a group read G consecutive nonzeros of their row with ONE
+// coalesced load each (the 32/G groups of a warp own consecutive rows, so the warp's loads are
+// contiguous in ja / a) and hand them round with shuffles.  The previous version read every
+// (col, val) as a same-address load per group; ncu (profiles/r1_rowsplit_cfg2.md) showed those
+// broadcast loads were half of the L1 data-pipe wavefronts, the busiest unit of the kernel.
+// The per-row sum still runs strictly left to right.
 template <int G, int V, int UNROLL, int THREADS>
 __global__ void __launch_bounds__(THREADS)
 spmm_rowsplit_kernel(const int32_t* __restrict__ ia, const int32_t* __restrict__ ja, const double* __restrict__ a,
@@ -70,42 +86,54 @@ spmm_rowsplit_kernel(const int32_t* __restrict__ ia, const int32_t* __restrict__
                      const int32_t* __restrict__ cta_rows)
 {
 	constexpr int NG = THREADS / G;          // row groups per CTA
+	static_assert(G % UNROLL == 0 || UNROLL % G == 0, "UNROLL and G must nest");
+	constexpr int U = UNROLL < G ? UNROLL : G;
 	const int lig = threadIdx.x % G;         // lane in group
 	const int gid = threadIdx.x / G;
 	const int r0 = cta_rows[blockIdx.x];
 	const int r1 = cta_rows[blockIdx.x + 1];
 
-	for (int row = r0 + gid; row < r1; row += NG) {
-		int j = __ldg(ia + row);
-		const int je = __ldg(ia + row + 1);
+	// all lanes of a warp run the same trip counts (the shuffles need the full warp)
+	for (int base = r0; base < r1; base += NG) {
+		const int row = base + gid;
+		const bool live = row < r1;
+		int j = 0, je = 0;
+		if (live) { j = __ldg(ia + row); je = __ldg(ia + row + 1); }
 		double acc[V];
 		#pragma unroll
 		for (int v = 0; v < V; v++) acc[v] = 0.0;
 
-		for (; j + UNROLL <= je; j += UNROLL) {
-			int cc[UNROLL];
-			double vv[UNROLL];
-			Frag<V> bb[UNROLL];
-			#pragma unroll
-			for (int u = 0; u < UNROLL; u++) cc[u] = __ldg(ja + j + u);
-			#pragma unroll
-			for (int u = 0; u < UNROLL; u++) bb[u] = load_b<G, V>(B, cc[u], lig);
-			#pragma unroll
-			for (int u = 0; u < UNROLL; u++) vv[u] = __ldg(a + j + u);
-			#pragma unroll
-			for (int u = 0; u < UNROLL; u++) {
+		while (true) {
+			const int rem = je - j;                                   // nonzeros left in my row
+			const int rem_warp = __reduce_max_sync(0xffffffffu, rem); // longest row of the warp
+			if (rem_warp <= 0) break;
+			int cj = 0;
+			double ca = 0.0;
+			if (lig < rem) { cj = __ldg(ja + j + lig); ca = __ldg(a + j + lig); }
+			const int cnt = min(rem_warp, G);
+			for (int u = 0; u < cnt; u += U) {
+				int cc[U];
+				double vv[U];
+				Frag<V> bb[U];
 				#pragma unroll
-				for (int v = 0; v < V; v++) acc[v] = fma(vv[u], bb[u].v[v], acc[v]);
+				for (int i = 0; i < U; i++) {
+					cc[i] = __shfl_sync(0xffffffffu, cj, u + i, G);
+					vv[i] = shfl_f64<G>(ca, u + i);
+				}
+				#pragma unroll
+				for (int i = 0; i < U; i++)
+					if (u + i < rem) bb[i] = load_b<G, V>(B, cc[i], lig);
+				#pragma unroll
+				for (int i = 0; i < U; i++) {
+					if (u + i < rem) {
+						#pragma unroll
+						for (int v = 0; v < V; v++) acc[v] = fma(vv[i], bb[i].v[v], acc[v]);
+					}
+				}
 			}
+			j += G;
 		}
-		for (; j < je; j++) {
-			const int cc = __ldg(ja + j);
-			const double vv = __ldg(a + j);
-			Frag<V> bb = load_b<G, V>(B, cc, lig);
-			#pragma unroll
-			for (int v = 0; v < V; v++) acc[v] = fma(vv, bb.v[v], acc[v]);
-		}
-		store_c<G, V>(C, (size_t) row, lig, acc);
+		if (live) store_c<G, V>(C, (size_t) row, lig, acc);
 	}
 }
 
