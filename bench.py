@@ -222,7 +222,8 @@ def gpu_arm(args, ia, ja, a, m, c, k, nnz, workload_desc):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
-    variant = {"auto": pkg.AUTO, "rowsplit": pkg.ROWSPLIT, "merge": pkg.MERGE, "bcsr": pkg.BCSR}[args.variant]
+    variant = {"auto": pkg.AUTO, "rowsplit": pkg.ROWSPLIT, "merge": pkg.MERGE, "bcsr": pkg.BCSR,
+               "bcsr_fma": pkg.BCSR_FMA}[args.variant]
     if world > 1:
         mf = pkg.csr_to_format(ia, ja, a, m, c, nnz, k, device=local, variant=variant, rank=rank, nranks=world)
     else:
@@ -329,6 +330,7 @@ def gpu_arm(args, ia, ja, a, m, c, k, nnz, workload_desc):
         "clocks": clocks,
         "checksum_c_rank0": csum,
         "variant": mf.format_name,
+        "bcsr_fill": mf.bcsr_fill(),
     }
     if rank == 0 and world == 1 and not args.no_cpu:
         line["cpu_baseline"] = cpu_baseline(ia, ja, a, m, c, k, x_host.numpy())
@@ -347,7 +349,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="cfg2", choices=sorted(WORKLOADS))
     ap.add_argument("--k", type=int, default=None)
-    ap.add_argument("--variant", default="auto", choices=["auto", "rowsplit", "merge", "bcsr"])
+    ap.add_argument("--variant", default="auto", choices=["auto", "rowsplit", "merge", "bcsr", "bcsr_fma"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup

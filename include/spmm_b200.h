@@ -41,7 +41,8 @@ enum {
 	SPMM_B200_ROWSPLIT = 0,   /* sub-warp group per row, CTAs own nnz-balanced row ranges   */
 	SPMM_B200_MERGE    = 1,   /* merge-path tiles with k-wide carries (skewed rows)          */
 	SPMM_B200_BCSR     = 2,   /* blocked CSR on the FP64 tensor pipe (dense blocks only)     */
-	SPMM_B200_AUTO     = 3    /* pick from the row-length statistics of A                    */
+	SPMM_B200_AUTO     = 3,   /* pick from the row-length statistics of A                    */
+	SPMM_B200_BCSR_FMA = 4    /* same 8x1 blocked CSR on the FP64 FMA pipe, absent rows skipped */
 };
 
 /* layout of the dense operand handed to spmm_b200_run / spmm_b200_set_b */
@@ -126,6 +127,7 @@ int spmm_b200_partition(const int32_t *row_ptr, int64_t m, int64_t nnz, int P, i
 int64_t spmm_b200_rows(const spmm_b200_t *h);         /* rows held by this handle (shard)     */
 int64_t spmm_b200_nnz(const spmm_b200_t *h);
 int     spmm_b200_variant(const spmm_b200_t *h);      /* the variant AUTO resolved to         */
+int64_t spmm_b200_bcsr_blocks(const spmm_b200_t *h);  /* 8x1 blocks stored (0 unless a BCSR variant); fill = nnz / (8*blocks) */
 double  spmm_b200_last_kernel_ms(const spmm_b200_t *h); /* CUDA-event time of the last run's kernels */
 int64_t spmm_b200_launch_count(const spmm_b200_t *h); /* kernels launched by this handle so far */
 /* replaces statistics_print_data()/statistics_print_labels() (spmv_kernel.h:20,30) */

@@ -17,10 +17,10 @@ import os
 import numpy as np
 
 __all__ = ["csr_to_format", "MatrixFormat", "partition", "statistics_print_labels", "load_library",
-           "SpmmB200Error", "ROWSPLIT", "MERGE", "BCSR", "AUTO", "B_COLMAJOR", "B_ROWMAJOR",
+           "SpmmB200Error", "ROWSPLIT", "MERGE", "BCSR", "AUTO", "BCSR_FMA", "B_COLMAJOR", "B_ROWMAJOR",
            "PART_ROWS", "PART_NNZ", "PART_MERGE", "LIB_PATH", "EXPORTS"]
 
-ROWSPLIT, MERGE, BCSR, AUTO = 0, 1, 2, 3
+ROWSPLIT, MERGE, BCSR, AUTO, BCSR_FMA = 0, 1, 2, 3, 4
 B_COLMAJOR, B_ROWMAJOR = 0, 1
 PART_ROWS, PART_NNZ, PART_MERGE = 0, 1, 2
 
@@ -33,7 +33,7 @@ EXPORTS = [
     "spmm_b200_register_host", "spmm_b200_unregister_host",
     "spmm_b200_run_resident", "spmm_b200_fetch_c", "spmm_b200_run_device",
     "spmm_b200_transpose_b_device", "spmm_b200_partition", "spmm_b200_rows", "spmm_b200_nnz",
-    "spmm_b200_variant", "spmm_b200_last_kernel_ms", "spmm_b200_launch_count", "spmm_b200_stats",
+    "spmm_b200_variant", "spmm_b200_bcsr_blocks", "spmm_b200_last_kernel_ms", "spmm_b200_launch_count", "spmm_b200_stats",
     "spmm_b200_stats_labels", "spmm_b200_destroy", "spmm_b200_strerror", "spmm_b200_last_cuda_error",
     "spmm_b200_device_count",
 ]
@@ -76,6 +76,7 @@ def load_library():
     lib.spmm_b200_rows.argtypes = [_vp]; lib.spmm_b200_rows.restype = _i64
     lib.spmm_b200_nnz.argtypes = [_vp]; lib.spmm_b200_nnz.restype = _i64
     lib.spmm_b200_variant.argtypes = [_vp]
+    lib.spmm_b200_bcsr_blocks.argtypes = [_vp]; lib.spmm_b200_bcsr_blocks.restype = _i64
     lib.spmm_b200_last_kernel_ms.argtypes = [_vp]; lib.spmm_b200_last_kernel_ms.restype = _dbl
     lib.spmm_b200_launch_count.argtypes = [_vp]; lib.spmm_b200_launch_count.restype = _i64
     lib.spmm_b200_stats.argtypes = [_vp, C.c_char_p, C.c_long]
@@ -111,7 +112,7 @@ class MatrixFormat:
         self.m_global = int(m if m_global is None else m_global)
         lib = load_library()
         self.variant = lib.spmm_b200_variant(handle)
-        self.format_name = "B200_CSR_" + {ROWSPLIT: "ROWSPLIT", MERGE: "MERGE", BCSR: "BCSR"}.get(self.variant, "?")
+        self.format_name = "B200_CSR_" + {ROWSPLIT: "ROWSPLIT", MERGE: "MERGE", BCSR: "BCSR_DMMA", BCSR_FMA: "BCSR_FMA"}.get(self.variant, "?")
         # spmv_kernel.h:24
         self.csr_mem_footprint = self.nnz * (8 + 4) + (self.m + 1) * 4
         self.mem_footprint = self.csr_mem_footprint
@@ -147,6 +148,11 @@ class MatrixFormat:
     def transpose_b_device(self, x_ptr, b_ptr, k, stream=0):
         _check(load_library().spmm_b200_transpose_b_device(self._h, x_ptr, b_ptr, int(k), stream or None),
                "transpose_b_device")
+
+    def bcsr_fill(self):
+        """nnz / (8 * stored 8x1 blocks); None for the CSR variants."""
+        nb = load_library().spmm_b200_bcsr_blocks(self._h)
+        return self.nnz / (8.0 * nb) if nb > 0 else None
 
     def last_kernel_ms(self):
         return load_library().spmm_b200_last_kernel_ms(self._h)

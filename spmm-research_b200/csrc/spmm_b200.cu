@@ -9,6 +9,8 @@
 #include "partition.cuh"
 #include "spmm_rowsplit.cuh"
 #include "spmm_merge.cuh"
+#include "scan.cuh"
+#include "spmm_bcsr.cuh"
 
 #include <cuda_runtime.h>
 #include <stdio.h>
@@ -53,6 +55,8 @@ struct spmm_b200 {
 	int n_ctas = 0;
 	// merge-path work list
 	MergePlan merge;
+	// blocked CSR (8x1)
+	BcsrPlan bcsr;
 
 	// buffers for the host-pointer API
 	double* d_x = nullptr; size_t cap_x = 0;   // staging for the column-major upload
@@ -251,12 +255,84 @@ static int launch_merge(spmm_b200* h, const double* B, double* C, int k, cudaStr
 	return 2;
 }
 
+// ---- blocked CSR (8x1): conversion on the device + launch -------------------------------------
+static bool bcsr_supports_k(int variant, int k)
+{
+	if (variant == SPMM_B200_BCSR) return k == 16 || k == 32 || k == 64 || k == 128;
+	return k == 32 || k == 64 || k == 128;
+}
+
+static int build_bcsr_plan(spmm_b200* h)
+{
+	BcsrPlan& p = h->bcsr;
+	const int mb = (int) ((h->m + 7) / 8);
+	p.mb = mb;
+	int32_t* d_tmp = nullptr;
+	CU_TRY(cudaMalloc(&p.d_brow, sizeof(int32_t) * ((size_t) mb + 1)));
+	CU_TRY(cudaMemsetAsync(p.d_brow, 0, sizeof(int32_t) * ((size_t) mb + 1), h->stream));
+	CU_TRY(cudaMalloc(&d_tmp, sizeof(int32_t) * scan_tmp_elems(mb + 1)));
+	const unsigned nb = (unsigned) (((int64_t) mb * 8 + 255) / 256);
+	if (mb > 0) {
+		bcsr_convert_kernel<false><<<nb, 256, 0, h->stream>>>(h->d_ia, h->d_ja, h->d_a, (int) h->m, mb, p.d_brow, nullptr, nullptr, nullptr);
+		h->launches++;
+	}
+	h->launches += exclusive_scan_i32(p.d_brow, (int64_t) mb + 1, d_tmp, h->stream);
+	int32_t nnzb = 0;
+	CU_TRY(cudaMemcpyAsync(&nnzb, p.d_brow + mb, sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
+	CU_TRY(cudaStreamSynchronize(h->stream));
+	cudaFree(d_tmp);
+	p.nnzb = nnzb;
+	CU_TRY(cudaMalloc(&p.d_bcol, sizeof(int32_t) * std::max<size_t>((size_t) nnzb, 1)));
+	CU_TRY(cudaMalloc(&p.d_bmask, std::max<size_t>((size_t) nnzb, 1)));
+	CU_TRY(cudaMalloc(&p.d_bval, sizeof(double) * 8 * std::max<size_t>((size_t) nnzb, 1)));
+	if (mb > 0 && nnzb > 0) {
+		bcsr_convert_kernel<true><<<nb, 256, 0, h->stream>>>(h->d_ia, h->d_ja, h->d_a, (int) h->m, mb, p.d_brow, p.d_bcol, p.d_bval, p.d_bmask);
+		h->launches++;
+	}
+	CU_TRY(cudaGetLastError());
+	CU_TRY(cudaStreamSynchronize(h->stream));
+	return SPMM_B200_OK;
+}
+
+template <int K>
+static void launch_bcsr_k(const spmm_b200* h, const double* B, double* C, cudaStream_t s)
+{
+	constexpr int WARPS = 4;
+	const BcsrPlan& p = h->bcsr;
+	const unsigned grid = (unsigned) ((p.mb + WARPS - 1) / WARPS);
+	if (h->variant == SPMM_B200_BCSR)
+		spmm_bcsr_dmma_kernel<K, WARPS><<<grid, WARPS * 32, 0, s>>>(p.d_brow, p.d_bcol, p.d_bval, B, C, (int) h->m, p.mb);
+	else if constexpr (K % 32 == 0)
+		spmm_bcsr_simt_kernel<K, WARPS><<<grid, WARPS * 32, 0, s>>>(p.d_brow, p.d_bcol, p.d_bval, p.d_bmask, B, C, (int) h->m, p.mb);
+}
+
+static int launch_bcsr(spmm_b200* h, const double* B, double* C, int k, cudaStream_t s)
+{
+	switch (k) {
+	case 16:  launch_bcsr_k<16>(h, B, C, s); break;
+	case 32:  launch_bcsr_k<32>(h, B, C, s); break;
+	case 64:  launch_bcsr_k<64>(h, B, C, s); break;
+	case 128: launch_bcsr_k<128>(h, B, C, s); break;
+	default: return SPMM_B200_ENOSUP;
+	}
+	cudaError_t e = cudaGetLastError();
+	if (e != cudaSuccess) {
+		snprintf(g_cuda_err, sizeof(g_cuda_err), "bcsr kernel launch (k=%d): %s", k, cudaGetErrorString(e));
+		return SPMM_B200_ECUDA;
+	}
+	h->launches += 1;
+	return 1;
+}
+
 // Launches the SpMM kernel(s) of the handle's variant on stream s.  Returns kernels launched or <0.
 static int launch_spmm(spmm_b200* h, const double* B, double* C, int k, cudaStream_t s)
 {
 	if (h->m == 0) return 0;
 	// merge-path has no instantiation for odd k: those run on the row-split generic kernel
 	if (h->variant == SPMM_B200_MERGE && merge_supports_k(k)) return launch_merge(h, B, C, k, s);
+	// blocked variants need k % 16 (tensor pipe) / k % 32 (FMA pipe); other k run on the CSR kernels
+	if ((h->variant == SPMM_B200_BCSR || h->variant == SPMM_B200_BCSR_FMA) && bcsr_supports_k(h->variant, k))
+		return launch_bcsr(h, B, C, k, s);
 	int n = 1;
 	switch (k) {
 	case 1:   launch_smallk<1>(h, B, C, s); break;
@@ -325,14 +401,19 @@ static int create_from_slice(spmm_b200_t** out, const int32_t* row_ptr_slice, co
 		// row-split serialises a row on one lane group: switch to merge-path when one row is far
 		// longer than the mean (SURVEY 8(d) cfg 3: 200 040 nnz against a mean of 20)
 		const double avg = m_local > 0 ? (double) nnz_local / (double) m_local : 0.0;
-		const int thr = env_int("SPMM_B200_MERGE_MAXROW", 4096);
-		h->variant = (h->max_row >= thr && h->max_row > 16.0 * avg) ? SPMM_B200_MERGE : SPMM_B200_ROWSPLIT;
+		// measured (gpurun_out/r2_*): cfg3b (max 866, mean 20) merge 1.24 ms vs row-split 2.03 ms;
+		// cfg2 (max 131, mean 50) row-split 0.91 ms vs merge 0.96 ms
+		const int thr = env_int("SPMM_B200_MERGE_MAXROW", 256);
+		h->variant = (h->max_row >= thr && h->max_row > 8.0 * avg) ? SPMM_B200_MERGE : SPMM_B200_ROWSPLIT;
 	} else {
 		h->variant = variant;
 	}
-	if (h->variant == SPMM_B200_BCSR) return SPMM_B200_ENOSUP;
-	int rc = build_rowsplit_plan(h);        // always: the fallback for k without a merge instantiation
+	int rc = build_rowsplit_plan(h);        // always: the fallback for k without a specialised instantiation
 	if (rc) return rc;
+	if (h->variant == SPMM_B200_BCSR || h->variant == SPMM_B200_BCSR_FMA) {
+		rc = build_bcsr_plan(h);
+		if (rc) return rc;
+	}
 	if (h->variant == SPMM_B200_MERGE && merge_supports_k(k)) {
 		rc = build_merge_plan(h, k, h->stream);
 		if (rc) return rc;
@@ -356,7 +437,7 @@ extern "C" int spmm_b200_create(spmm_b200_t** h, const int32_t* row_ptr, const i
 	*h = nullptr;
 	int rc = check_sizes(row_ptr, col_ind, values, m, c, nnz, k);
 	if (rc) return rc;
-	if (variant < SPMM_B200_ROWSPLIT || variant > SPMM_B200_AUTO) return SPMM_B200_EINVAL;
+	if (variant < SPMM_B200_ROWSPLIT || variant > SPMM_B200_BCSR_FMA) return SPMM_B200_EINVAL;
 	if (b_layout != SPMM_B200_B_COLMAJOR && b_layout != SPMM_B200_B_ROWMAJOR) return SPMM_B200_EINVAL;
 	int sms = 0;
 	rc = check_device(device, &sms);
@@ -401,6 +482,7 @@ extern "C" void spmm_b200_destroy(spmm_b200_t* h)
 	cudaFree(h->d_ia); cudaFree(h->d_ja); cudaFree(h->d_a);
 	cudaFree(h->d_cta_rows);
 	cudaFree(h->merge.d_tile); cudaFree(h->merge.d_carry); cudaFree(h->merge.d_carry_row);
+	cudaFree(h->bcsr.d_brow); cudaFree(h->bcsr.d_bcol); cudaFree(h->bcsr.d_bval); cudaFree(h->bcsr.d_bmask);
 	cudaFree(h->d_x); cudaFree(h->d_B); cudaFree(h->d_C);
 	if (h->ev0) cudaEventDestroy(h->ev0);
 	if (h->ev1) cudaEventDestroy(h->ev1);
@@ -580,6 +662,7 @@ extern "C" int spmm_b200_partition(const int32_t* row_ptr, int64_t m, int64_t nn
 extern "C" int64_t spmm_b200_rows(const spmm_b200_t* h) { return h ? h->m : -1; }
 extern "C" int64_t spmm_b200_nnz(const spmm_b200_t* h) { return h ? h->nnz : -1; }
 extern "C" int spmm_b200_variant(const spmm_b200_t* h) { return h ? h->variant : SPMM_B200_EINVAL; }
+extern "C" int64_t spmm_b200_bcsr_blocks(const spmm_b200_t* h) { return h ? h->bcsr.nnzb : -1; }
 extern "C" int64_t spmm_b200_launch_count(const spmm_b200_t* h) { return h ? h->launches : -1; }
 
 extern "C" double spmm_b200_last_kernel_ms(const spmm_b200_t* h)
@@ -605,8 +688,8 @@ extern "C" int spmm_b200_stats(const spmm_b200_t* h, char* buf, long buf_n)
 	const double gflops = ms > 0 ? 2.0 * h->nnz * k / (ms * 1e6) : 0.0;
 	const double bytes = 12.0 * h->nnz + 4.0 * (h->m + 1) + 8.0 * k * (double) h->c + 8.0 * k * (double) h->m;
 	const double frac = ms > 0 ? (bytes / 8.0e12) / (ms * 1e-3) : 0.0;
-	static const char* names[] = {"rowsplit", "merge", "bcsr", "auto"};
-	return snprintf(buf, buf_n, ",%s,%d,%d,%g,%g,%g", names[h->variant & 3],
+	static const char* names[] = {"rowsplit", "merge", "bcsr_dmma", "auto", "bcsr_fma"};
+	return snprintf(buf, buf_n, ",%s,%d,%d,%g,%g,%g", names[h->variant >= 0 && h->variant <= 4 ? h->variant : 3],
 	                h->variant == SPMM_B200_MERGE ? h->merge.ntiles : h->n_ctas, h->max_row, ms, gflops, frac);
 }
 

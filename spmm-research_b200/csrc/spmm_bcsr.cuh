@@ -1,0 +1,216 @@
+// spmm_bcsr.cuh -- blocked-CSR SpMM (north_star kernel (3)) with 8x1 blocks.
+//
+// The reference has no BCSR of its own: the only definition is the cuSPARSE BSR wrapper
+// SpmvBsrData{blockDim, nnzb, rowPtr, colInd, values} filled by cusparseDcsr2bsr with
+// CUSPARSE_DIRECTION_COLUMN (benchmark_code/GPU/spmv_code_cusparse-11.x/inc/spmv_operator.hpp:56-62,
+// src/CuSPARSE.cu:41,104-172): block rows, explicit zeros for fill, column-major inside a block.
+// Parity for this format is pinned through the SpMM result (compute_csr).
+//
+// Layout here (same three arrays, rectangular block 8 rows x 1 column):
+//   mb = ceil(m/8) block rows;  brow_ptr[mb+1];  bcol[nnzb] = sorted distinct columns of the
+//   8 rows;  bval[nnzb][8] = the column's 8 values (zeros where a row has no entry; this IS
+//   column-major inside the block);  bmask[nnzb] = which of the 8 rows really hold an entry.
+// Why 8x1: the FP64 tensor instruction on sm_100a is mma.sync.m8n8k4 (tcgen05 has no FP64
+// kind), D(8x8) += A(8x4) * B(4x8).  M = 8 matrix rows, K = 4 block columns -- and nothing
+// requires the 4 columns to be adjacent, each K slot gathers its own B row.  8x1 blocks keep
+// the fill ratio at its maximum for an 8-row slab (cfg4: 0.40 against 0.32 for aligned 8x4).
+//
+// Two kernels over the same arrays:
+//   spmm_bcsr_dmma_kernel   tensor pipe: one DMMA per (4 block columns, 8 dense columns);
+//                           executes 8 FMAs per stored slot, so it pays only when blocks are
+//                           dense ("a genuine contraction");
+//   spmm_bcsr_simt_kernel   FP64 FMA pipe: one B-row gather per block column feeds up to 8 row
+//                           accumulators held in registers; absent rows are skipped through
+//                           the (warp-uniform) mask, so it executes only the real 2*nnz*k flops.
+// Both cut the L1/L2 gather traffic of the CSR kernels by the block fill (nnz / nnzb).
+#pragma once
+#include <stdint.h>
+#include <limits.h>
+#include <cuda_runtime.h>
+#include "spmm_rowsplit.cuh"
+
+namespace sb200 {
+
+struct BcsrPlan {
+	int mb = 0;
+	int64_t nnzb = 0;
+	int32_t* d_brow = nullptr;
+	int32_t* d_bcol = nullptr;
+	double* d_bval = nullptr;
+	uint8_t* d_bmask = nullptr;
+};
+
+// ---- CSR -> BCSR(8x1): 8 lanes per block row run an 8-way merge of the sorted column lists ----
+// FILL = false: count distinct columns per block row into brow[br]; FILL = true: write the blocks.
+template <bool FILL>
+__global__ void __launch_bounds__(256)
+bcsr_convert_kernel(const int32_t* __restrict__ ia, const int32_t* __restrict__ ja, const double* __restrict__ a,
+                    int m, int mb, int32_t* __restrict__ brow,
+                    int32_t* __restrict__ bcol, double* __restrict__ bval, uint8_t* __restrict__ bmask)
+{
+	const int t = blockIdx.x * blockDim.x + threadIdx.x;
+	const int br = t >> 3, r = t & 7;
+	if (br >= mb) return;                                   // whole 8-lane groups leave together
+	const unsigned gmask = 0xFFu << ((threadIdx.x & 31) & ~7);
+	const int gshift = (threadIdx.x & 31) & ~7;
+	const int row = br * 8 + r;
+	int p = 0, pe = 0;
+	if (row < m) { p = ia[row]; pe = ia[row + 1]; }
+	int out = FILL ? brow[br] : 0;
+	int count = 0;
+	while (true) {
+		const int cur = p < pe ? ja[p] : INT_MAX;
+		int mn = cur;
+		mn = min(mn, __shfl_xor_sync(gmask, mn, 1));
+		mn = min(mn, __shfl_xor_sync(gmask, mn, 2));
+		mn = min(mn, __shfl_xor_sync(gmask, mn, 4));
+		if (mn == INT_MAX) break;
+		const bool hit = cur == mn;
+		if (FILL) {
+			const unsigned bal = __ballot_sync(gmask, hit);
+			bval[(size_t) out * 8 + r] = hit ? a[p] : 0.0;
+			if (r == 0) { bcol[out] = mn; bmask[out] = (uint8_t) ((bal >> gshift) & 0xFFu); }
+			out++;
+		}
+		if (hit) p++;
+		count++;
+	}
+	if (!FILL && r == 0) brow[br] = count;
+}
+
+// ---- tensor-pipe kernel -------------------------------------------------------------------------
+__device__ __forceinline__ void dmma_m8n8k4(double& d0, double& d1, double a, double b)
+{
+	asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
+	             : "+d"(d0), "+d"(d1) : "d"(a), "d"(b));
+}
+
+// One warp per block row, all K dense columns (K % 16 == 0).  Fragment roles of lane (g = lane/4,
+// t = lane%4):  A[g][t] = bval[e+t][g];  B[t][n] with n = g;  D[g][2t], D[g][2t+1].
+// Dense columns are dealt to the two DMMAs of a 16-column chunk in an interleaved way (DMMA #0
+// takes the even columns, #1 the odd ones) so that a lane's B operand for both is ONE 16-byte
+// load and its four D values are four consecutive columns of C.
+template <int K, int WARPS>
+__global__ void __launch_bounds__(WARPS * 32)
+spmm_bcsr_dmma_kernel(const int32_t* __restrict__ brow, const int32_t* __restrict__ bcol, const double* __restrict__ bval,
+                      const double* __restrict__ B, double* __restrict__ C, int m, int mb)
+{
+	static_assert(K % 16 == 0, "the tensor-pipe kernel needs k to be a multiple of 16");
+	constexpr int Q = K / 16;
+	const int lane = threadIdx.x & 31;
+	const int g = lane >> 2, t = lane & 3;
+	const int br = blockIdx.x * WARPS + (threadIdx.x >> 5);
+	if (br >= mb) return;
+	const int bs = __ldg(brow + br), be = __ldg(brow + br + 1);
+	double acc[Q][4];
+	#pragma unroll
+	for (int q = 0; q < Q; q++) { acc[q][0] = acc[q][1] = acc[q][2] = acc[q][3] = 0.0; }
+
+	for (int e = bs; e < be; e += 4) {
+		const int idx = e + t;
+		const bool valid = idx < be;
+		const int col = __ldg(bcol + (valid ? idx : be - 1));
+		const double av = valid ? __ldg(bval + (size_t) idx * 8 + g) : 0.0;
+		const double2* bp = reinterpret_cast<const double2*>(B + (size_t) col * K) + g;
+		double2 bb[Q];
+		#pragma unroll
+		for (int q = 0; q < Q; q++) bb[q] = __ldg(bp + q * 8);
+		#pragma unroll
+		for (int q = 0; q < Q; q++) {
+			dmma_m8n8k4(acc[q][0], acc[q][2], av, bb[q].x);     // columns 16q + 4t + {0, 2}
+			dmma_m8n8k4(acc[q][1], acc[q][3], av, bb[q].y);     // columns 16q + 4t + {1, 3}
+		}
+	}
+	const int row = br * 8 + g;
+	if (row < m) {
+		double2* cp = reinterpret_cast<double2*>(C + (size_t) row * K) + 2 * t;
+		#pragma unroll
+		for (int q = 0; q < Q; q++) {
+			cp[q * 8] = make_double2(acc[q][0], acc[q][1]);
+			cp[q * 8 + 1] = make_double2(acc[q][2], acc[q][3]);
+		}
+	}
+}
+
+// ---- FP64-FMA kernel with register reuse of the gathered B row ----------------------------------
+// One warp per block row; lane owns V = K/32 dense columns (K % 32 == 0) of all 8 rows.
+// The warp reads 32 block columns' (col, mask) and 4 block columns' 32 values with coalesced
+// loads and hands them round with shuffles.
+template <int K, int WARPS>
+__global__ void __launch_bounds__(WARPS * 32)
+spmm_bcsr_simt_kernel(const int32_t* __restrict__ brow, const int32_t* __restrict__ bcol, const double* __restrict__ bval,
+                      const uint8_t* __restrict__ bmask, const double* __restrict__ B, double* __restrict__ C, int m, int mb)
+{
+	static_assert(K % 32 == 0, "the blocked FMA kernel needs k to be a multiple of 32");
+	constexpr int V = K / 32;
+	constexpr int VV = V >= 2 ? 2 : 1;                       // doubles per load
+	const int lane = threadIdx.x & 31;
+	const int br = blockIdx.x * WARPS + (threadIdx.x >> 5);
+	if (br >= mb) return;
+	const int bs = __ldg(brow + br), be = __ldg(brow + br + 1);
+	double acc[8][V];
+	#pragma unroll
+	for (int r = 0; r < 8; r++)
+		#pragma unroll
+		for (int v = 0; v < V; v++) acc[r][v] = 0.0;
+
+	for (int e0 = bs; e0 < be; e0 += 32) {
+		const int n32 = min(32, be - e0);
+		int my_col = 0, my_mask = 0;
+		if (lane < n32) { my_col = __ldg(bcol + e0 + lane); my_mask = __ldg(bmask + e0 + lane); }
+		for (int e4 = 0; e4 < n32; e4 += 4) {
+			// 4 block columns x 8 rows = 32 values, one per lane
+			const int vidx = (e0 + e4) * 8 + lane;
+			const double my_val = (e4 * 8 + lane < n32 * 8) ? __ldg(bval + (size_t) vidx) : 0.0;
+			int cc[4], mm[4];
+			double bb[4][V];
+			#pragma unroll
+			for (int i = 0; i < 4; i++) {
+				cc[i] = __shfl_sync(0xffffffffu, my_col, e4 + i);
+				mm[i] = __shfl_sync(0xffffffffu, my_mask, e4 + i);   // lanes past n32 hold mask 0
+			}
+			#pragma unroll
+			for (int i = 0; i < 4; i++) {
+				if (mm[i]) {
+					const double* bp = B + (size_t) cc[i] * K;
+					if constexpr (VV == 2) {
+						#pragma unroll
+						for (int v2 = 0; v2 < V / 2; v2++) {
+							double2 tmp = __ldg(reinterpret_cast<const double2*>(bp) + v2 * 32 + lane);
+							bb[i][2 * v2] = tmp.x; bb[i][2 * v2 + 1] = tmp.y;
+						}
+					} else {
+						bb[i][0] = __ldg(bp + lane);
+					}
+				}
+			}
+			#pragma unroll
+			for (int i = 0; i < 4; i++) {
+				#pragma unroll
+				for (int r = 0; r < 8; r++) {
+					if (mm[i] & (1 << r)) {                             // warp-uniform
+						const double val = shfl_f64<32>(my_val, i * 8 + r);
+						#pragma unroll
+						for (int v = 0; v < V; v++) acc[r][v] = fma(val, bb[i][v], acc[r][v]);
+					}
+				}
+			}
+		}
+	}
+	#pragma unroll
+	for (int r = 0; r < 8; r++) {
+		const int row = br * 8 + r;
+		if (row < m) {
+			double* cp = C + (size_t) row * K;
+			if constexpr (VV == 2) {
+				#pragma unroll
+				for (int v2 = 0; v2 < V / 2; v2++)
+					reinterpret_cast<double2*>(cp)[v2 * 32 + lane] = make_double2(acc[r][2 * v2], acc[r][2 * v2 + 1]);
+			} else {
+				cp[lane] = acc[r][0];
+			}
+		}
+	}
+}
+
+} // namespace sb200

@@ -114,6 +114,7 @@ csr_to_format(INT_T * row_ptr, INT_T * col_ind, ValueType * values, long m, long
 		if (!strcmp(v, "rowsplit")) variant = SPMM_B200_ROWSPLIT;
 		else if (!strcmp(v, "merge")) variant = SPMM_B200_MERGE;
 		else if (!strcmp(v, "bcsr")) variant = SPMM_B200_BCSR;
+		else if (!strcmp(v, "bcsr_fma")) variant = SPMM_B200_BCSR_FMA;
 	}
 	const char * d = getenv("SPMM_B200_DEVICE");
 	const char * cb = getenv("SPMM_B200_COPYBACK");
@@ -123,8 +124,9 @@ csr_to_format(INT_T * row_ptr, INT_T * col_ind, ValueType * values, long m, long
 	f->a = values;
 	int rc = spmm_b200_create(&f->handle, row_ptr, col_ind, values, m, n, nnz, k, d ? atoi(d) : 0, variant, SPMM_B200_B_COLMAJOR);
 	if (rc) die("csr_to_format", rc);
-	static const char * names[] = {"B200_CSR_ROWSPLIT", "B200_CSR_MERGE", "B200_BCSR", "B200_CSR"};
-	snprintf(f->name, sizeof(f->name), "%s", names[spmm_b200_variant(f->handle) & 3]);
+	static const char * names[] = {"B200_CSR_ROWSPLIT", "B200_CSR_MERGE", "B200_BCSR_DMMA", "B200_CSR", "B200_BCSR_FMA"};
+	int vr = spmm_b200_variant(f->handle);
+	snprintf(f->name, sizeof(f->name), "%s", names[(vr >= 0 && vr <= 4) ? vr : 3]);
 	f->format_name = f->name;
 	f->mem_footprint = f->csr_mem_footprint;
 	return f;

@@ -15,8 +15,8 @@ KS = [1, 2, 4, 8, 16, 32, 64, 128, 3, 20, 100]
 
 
 def variants(pkg):
-    names = os.environ.get("SPMM_B200_TEST_VARIANTS", "rowsplit,merge,auto").split(",")
-    table = {"rowsplit": pkg.ROWSPLIT, "merge": pkg.MERGE, "bcsr": pkg.BCSR, "auto": pkg.AUTO}
+    names = os.environ.get("SPMM_B200_TEST_VARIANTS", "rowsplit,merge,auto,bcsr,bcsr_fma").split(",")
+    table = {"rowsplit": pkg.ROWSPLIT, "merge": pkg.MERGE, "bcsr": pkg.BCSR, "auto": pkg.AUTO, "bcsr_fma": pkg.BCSR_FMA}
     return [table[n] for n in names if n]
 
 
@@ -128,6 +128,37 @@ def test_generated_configs_against_oracle(pkg, L, pins):
         for v in variants(pkg):
             y, info = run_spmm(pkg, ia, ja, a, m, c, x, k, v)
             assert max_rel_err(y, y_ref) <= FP64_TOL, (args, k, info)
+
+
+def test_bcsr_block_count_and_banded_parity(pkg, L):
+    """CSR -> BCSR(8x1) on the device: the number of stored blocks equals the number of distinct
+    (row // 8, col) pairs, and both blocked kernels reproduce the oracle on a banded matrix with
+    similar neighbouring rows (the structure the blocked path is for) at k = 32 and 128."""
+    rng = np.random.default_rng(3)
+    m, c = 5003, 4000                         # m not a multiple of 8: ragged last block row
+    cols = []
+    prev = np.sort(rng.choice(200, 40, replace=False))
+    for i in range(m):
+        keep = prev[rng.random(prev.size) < 0.9]
+        lo = max(0, min(c - 200, i * c // m - 100))
+        new = lo + rng.choice(200, 6, replace=False)
+        cur = np.unique(np.concatenate([keep, new]))
+        cur = cur[(cur >= lo) & (cur < lo + 200)]
+        cols.append(cur)
+        prev = cur
+    ia = np.zeros(m + 1, np.int32); ia[1:] = np.cumsum([len(x) for x in cols])
+    ja = np.concatenate(cols).astype(np.int32)
+    a = rng.random(len(ja)) + 0.1
+    rows = np.repeat(np.arange(m, dtype=np.int64), np.diff(ia))
+    nblocks = len(np.unique((rows // 8) * c + ja))
+    for k in (32, 128):
+        x = dense_b(c, k, 11)
+        y_ref = L.spmm_oracle(ia, ja, a, m, c, x, k)
+        for v in (pkg.BCSR, pkg.BCSR_FMA):
+            mf = pkg.csr_to_format(ia, ja, a, m, c, len(ja), k, variant=v)
+            assert abs(mf.bcsr_fill() - len(ja) / (8.0 * nblocks)) < 1e-12
+            y = np.full(m * k, np.nan); mf.spmm(x, y, k); mf.close()
+            assert max_rel_err(y, y_ref) <= FP64_TOL, (k, v)
 
 
 def test_shards_cover_rows_and_match_reference_split(pkg, L):
