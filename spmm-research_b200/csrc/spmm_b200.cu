@@ -284,7 +284,9 @@ static int build_bcsr_plan(spmm_b200* h)
 	p.nnzb = nnzb;
 	CU_TRY(cudaMalloc(&p.d_bcol, sizeof(int32_t) * std::max<size_t>((size_t) nnzb, 1)));
 	CU_TRY(cudaMalloc(&p.d_bmask, std::max<size_t>((size_t) nnzb, 1)));
-	CU_TRY(cudaMalloc(&p.d_bval, sizeof(double) * 8 * std::max<size_t>((size_t) nnzb, 1)));
+	// +4 blocks of slack: the TMA kernel fetches the A values of a step as one 256-byte bulk copy
+	CU_TRY(cudaMalloc(&p.d_bval, sizeof(double) * 8 * ((size_t) nnzb + 4)));
+	CU_TRY(cudaMemsetAsync(p.d_bval + (size_t) nnzb * 8, 0, sizeof(double) * 32, h->stream));
 	if (mb > 0 && nnzb > 0) {
 		bcsr_convert_kernel<true><<<nb, 256, 0, h->stream>>>(h->d_ia, h->d_ja, h->d_a, (int) h->m, mb, p.d_brow, p.d_bcol, p.d_bval, p.d_bmask);
 		h->launches++;
@@ -294,13 +296,36 @@ static int build_bcsr_plan(spmm_b200* h)
 	return SPMM_B200_OK;
 }
 
+template <int K, int WARPS, int STAGES>
+static void launch_bcsr_tma(const BcsrPlan& p, const double* B, double* C, int m, int brw, unsigned grid, cudaStream_t s)
+{
+	using Cfg = BcsrTmaCfg<K, WARPS, STAGES>;
+	auto kern = spmm_bcsr_dmma_tma_kernel<K, WARPS, STAGES>;
+	static bool attr_set = false;
+	if (!attr_set) {
+		cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) Cfg::SMEM);
+		attr_set = true;
+	}
+	kern<<<grid, WARPS * 32, Cfg::SMEM, s>>>(p.d_brow, p.d_bcol, p.d_bval, B, C, m, p.mb, brw);
+}
+
 template <int K>
 static void launch_bcsr_k(const spmm_b200* h, const double* B, double* C, cudaStream_t s)
 {
 	constexpr int WARPS = 4;
 	const BcsrPlan& p = h->bcsr;
 	const unsigned grid = (unsigned) ((p.mb + WARPS - 1) / WARPS);
-	if (h->variant == SPMM_B200_BCSR)
+	static const int use_tma = env_int("SPMM_B200_BCSR_TMA", 1);
+	if (h->variant == SPMM_B200_BCSR && use_tma && ((uintptr_t) B % 16) == 0) {
+		static const int stages = env_int("SPMM_B200_BCSR_STAGES", 4);
+		static const int brw_env = env_int("SPMM_B200_BCSR_BRW", 0);
+		// block rows per warp: enough to keep the ring flowing, few enough for >= 8 CTAs per SM
+		const int brw = brw_env > 0 ? brw_env : (int) std::max<int64_t>(1, std::min<int64_t>(8, p.mb / ((int64_t) h->sm_count * WARPS * 8)));
+		const unsigned g2 = (unsigned) ((p.mb + (int64_t) WARPS * brw - 1) / ((int64_t) WARPS * brw));
+		if (stages <= 2) launch_bcsr_tma<K, WARPS, 2>(p, B, C, (int) h->m, brw, g2, s);
+		else if (stages == 3) launch_bcsr_tma<K, WARPS, 3>(p, B, C, (int) h->m, brw, g2, s);
+		else launch_bcsr_tma<K, WARPS, 4>(p, B, C, (int) h->m, brw, g2, s);
+	} else if (h->variant == SPMM_B200_BCSR)
 		spmm_bcsr_dmma_kernel<K, WARPS><<<grid, WARPS * 32, 0, s>>>(p.d_brow, p.d_bcol, p.d_bval, B, C, (int) h->m, p.mb);
 	else if constexpr (K % 32 == 0)
 		spmm_bcsr_simt_kernel<K, WARPS><<<grid, WARPS * 32, 0, s>>>(p.d_brow, p.d_bcol, p.d_bval, p.d_bmask, B, C, (int) h->m, p.mb);

@@ -132,6 +132,150 @@ spmm_bcsr_dmma_kernel(const int32_t* __restrict__ brow, const int32_t* __restric
 	}
 }
 
+// ---- tensor-pipe kernel, operands gathered by the TMA engine ------------------------------------
+// ncu on the kernel above (profiles/r1_bcsr_cfg4.md): the m8n8k4 fragment layout makes the gathered
+// row index the fastest-varying lane index, so every quarter-warp of a fragment load touches four
+// different B rows -> 16 L1 wavefronts per 512 B, L1 data pipe 73 % busy, 104 registers, 16 warps
+// per SM, tensor pipe 34 %.  Here the four B rows (and the 32 A values) of a step are fetched with
+// 1-D bulk copies (cp.async.bulk -> UBLKCP) into a per-warp ring of STAGES shared-memory stages,
+// completion on an mbarrier, and fragments are read from shared memory without bank conflicts
+// (row stride = 8K + 32 bytes).  A warp owns `brw` consecutive block rows and keeps the ring
+// flowing across their boundaries; no CTA-wide barrier is used.
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t) __cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count)
+{
+	asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes)
+{
+	asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity)
+{
+	uint32_t ok;
+	asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}"
+	             : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+	return ok != 0;
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar)
+{
+	asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+	             ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+
+template <int K, int WARPS, int STAGES>
+struct BcsrTmaCfg {
+	static constexpr int ROW_BYTES = K * 8;
+	static constexpr int ROW_STRIDE = ROW_BYTES + 32;
+	static constexpr int STAGE_BYTES = 4 * ROW_STRIDE + 256;
+	static constexpr size_t SMEM = (size_t) WARPS * STAGES * STAGE_BYTES + (size_t) WARPS * STAGES * 8;
+};
+
+template <int K, int WARPS, int STAGES>
+__global__ void __launch_bounds__(WARPS * 32)
+spmm_bcsr_dmma_tma_kernel(const int32_t* __restrict__ brow, const int32_t* __restrict__ bcol, const double* __restrict__ bval,
+                          const double* __restrict__ B, double* __restrict__ C, int m, int mb, int brw)
+{
+	using Cfg = BcsrTmaCfg<K, WARPS, STAGES>;
+	constexpr int Q = K / 16;
+	extern __shared__ __align__(128) unsigned char bcsr_smem[];
+	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	const int g = lane >> 2, t = lane & 3;
+	// Warp gw owns block rows gw, gw + W, gw + 2W, ... (W = warps in the grid): CTAs that run at the
+	// same time then work on ADJACENT block rows, whose gathered B rows overlap on banded matrices
+	// and stay in L2 (contiguous ownership made the live B window 8x larger and DRAM reads 3.5x).
+	const int W = gridDim.x * WARPS;
+	const int br0 = blockIdx.x * WARPS + warp;
+	const int br1 = min(br0 + (brw - 1) * W + 1, mb);      // exclusive bound of the strided walk
+	if (br0 >= mb) return;
+	unsigned char* ring = bcsr_smem + (size_t) warp * STAGES * Cfg::STAGE_BYTES;
+	const uint32_t ring_u = smem_u32(ring);
+	const uint32_t bar_u = smem_u32(bcsr_smem + (size_t) WARPS * STAGES * Cfg::STAGE_BYTES) + warp * STAGES * 8;
+	if (lane == 0) {
+		#pragma unroll
+		for (int s = 0; s < STAGES; s++) mbar_init(bar_u + s * 8, 1);
+		asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+		asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+	}
+	__syncwarp();
+
+	// producer cursor over the flattened (block row, step) stream; empty block rows produce nothing
+	int p_br = br0, p_e = 0, p_be = 0;
+	while (p_br < br1) {
+		p_e = __ldg(brow + p_br); p_be = __ldg(brow + p_br + 1);
+		if (p_e < p_be) break;
+		p_br += W;
+	}
+	int p_col = 0;                                        // lanes 0..3: column of slot `lane` of the next step
+	if (p_br < br1 && lane < 4) p_col = __ldg(bcol + min(p_e + lane, p_be - 1));
+	int pit = 0;
+	auto produce = [&]() {
+		const int stage = pit % STAGES;
+		const uint32_t dst = ring_u + stage * Cfg::STAGE_BYTES, bar = bar_u + stage * 8;
+		// one lane issues all five copies (per-lane issue makes ptxas loop over the active lanes to
+		// move each lane's operands into uniform registers: ~100 instructions per step, see profiles/)
+		const int c0 = __shfl_sync(0xffffffffu, p_col, 0), c1 = __shfl_sync(0xffffffffu, p_col, 1);
+		const int c2 = __shfl_sync(0xffffffffu, p_col, 2), c3 = __shfl_sync(0xffffffffu, p_col, 3);
+		if (lane == 0) {
+			mbar_expect_tx(bar, 4 * Cfg::ROW_BYTES + 256);
+			bulk_g2s(dst, B + (size_t) c0 * K, Cfg::ROW_BYTES, bar);
+			bulk_g2s(dst + Cfg::ROW_STRIDE, B + (size_t) c1 * K, Cfg::ROW_BYTES, bar);
+			bulk_g2s(dst + 2 * Cfg::ROW_STRIDE, B + (size_t) c2 * K, Cfg::ROW_BYTES, bar);
+			bulk_g2s(dst + 3 * Cfg::ROW_STRIDE, B + (size_t) c3 * K, Cfg::ROW_BYTES, bar);
+			bulk_g2s(dst + 4 * Cfg::ROW_STRIDE, bval + (size_t) p_e * 8, 256, bar);
+		}
+		pit++;
+		p_e += 4;
+		if (p_e >= p_be) {
+			p_br += W;
+			while (p_br < br1) {
+				p_e = __ldg(brow + p_br); p_be = __ldg(brow + p_br + 1);
+				if (p_e < p_be) break;
+				p_br += W;
+			}
+		}
+		if (p_br < br1 && lane < 4) p_col = __ldg(bcol + min(p_e + lane, p_be - 1));
+	};
+	#pragma unroll 1
+	for (int s = 0; s < STAGES - 1; s++)
+		if (p_br < br1) produce();
+
+	int it = 0;
+	for (int br = br0; br < br1; br += W) {
+		const int bs = __ldg(brow + br), be = __ldg(brow + br + 1);
+		double acc[Q][4];
+		#pragma unroll
+		for (int q = 0; q < Q; q++) { acc[q][0] = acc[q][1] = acc[q][2] = acc[q][3] = 0.0; }
+		for (int e = bs; e < be; e += 4) {
+			if (p_br < br1) produce();                       // refills the stage consumed one step ago
+			const int stage = it % STAGES;
+			const uint32_t parity = (it / STAGES) & 1;
+			while (!mbar_try_wait(bar_u + stage * 8, parity)) {}
+			const unsigned char* st = ring + (size_t) stage * Cfg::STAGE_BYTES;
+			const double av = (e + t < be) ? reinterpret_cast<const double*>(st + 4 * Cfg::ROW_STRIDE)[t * 8 + g] : 0.0;
+			const double2* bp = reinterpret_cast<const double2*>(st + t * Cfg::ROW_STRIDE) + g;
+			#pragma unroll
+			for (int q = 0; q < Q; q++) {
+				const double2 bb = bp[q * 8];
+				dmma_m8n8k4(acc[q][0], acc[q][2], av, bb.x);
+				dmma_m8n8k4(acc[q][1], acc[q][3], av, bb.y);
+			}
+			__syncwarp();                                    // every lane has read the stage
+			it++;
+		}
+		const int row = br * 8 + g;
+		if (row < m) {
+			double2* cp = reinterpret_cast<double2*>(C + (size_t) row * K) + 2 * t;
+			#pragma unroll
+			for (int q = 0; q < Q; q++) {
+				cp[q * 8] = make_double2(acc[q][0], acc[q][1]);
+				cp[q * 8 + 1] = make_double2(acc[q][2], acc[q][3]);
+			}
+		}
+	}
+}
+
 // ---- FP64-FMA kernel with register reuse of the gathered B row ----------------------------------
 // One warp per block row; lane owns V = K/32 dense columns (K % 32 == 0) of all 8 rows.
 // The warp reads 32 block columns' (col, mask) and 4 block columns' 32 values with coalesced
