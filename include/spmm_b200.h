@@ -123,6 +123,19 @@ int spmm_b200_transpose_b_device(spmm_b200_t *h, const double *x_colmajor_dev, d
 int spmm_b200_partition(const int32_t *row_ptr, int64_t m, int64_t nnz, int P, int mode,
                         int64_t *out, int device);
 
+/* Same integers computed on the host (shard planning before a device exists; no SpMM arithmetic). */
+int spmm_b200_partition_host(const int32_t *row_ptr, int64_t m, int64_t nnz, int P, int mode, int64_t *out);
+
+/* ---- COO -> CSR: replaces coo_to_csr(R, C, V, m, n, nnz, row_ptr, col_idx, values, sort_columns,
+ * transpose) (lib/storage_formats/csr/csr_gen.c:162-217; call site spmv_bench.cpp:823) including
+ * csr_sort_columns (csr_gen.c:82-156).  Host pointers; histogram, scan, scatter and the per-row
+ * column sort run on the device.  row_ptr has m+1 entries (n+1 with transpose).  V/values may both
+ * be NULL.  Entries of a row are ordered by (column, position in the input) -- identical to the
+ * reference whenever no (row, col) pair repeats; with sort_columns == 0 by input position. */
+int spmm_b200_coo_to_csr(const int32_t *R, const int32_t *C, const double *V, int64_t m, int64_t n, int64_t nnz,
+                         int32_t *row_ptr, int32_t *col_idx, double *values, int sort_columns, int transpose,
+                         int device);
+
 /* ---- introspection */
 int64_t spmm_b200_rows(const spmm_b200_t *h);         /* rows held by this handle (shard)     */
 int64_t spmm_b200_nnz(const spmm_b200_t *h);

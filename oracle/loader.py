@@ -44,6 +44,9 @@ def oracle():
         lib.oracle_balance_prefix_sums.argtypes = [_i32p, C.c_long, C.c_long, C.c_long, _i64p]
         lib.oracle_balance_iterations.argtypes = [C.c_long, C.c_long, C.c_long, _i64p]
         lib.oracle_merge_partition.argtypes = [_i32p, C.c_long, C.c_long, C.c_long, _i64p]
+        lib.oracle_coo_to_csr.argtypes = [_i32p, _i32p, C.c_void_p, C.c_long, C.c_long, C.c_long,
+                                          _i32p, _i32p, C.c_void_p, C.c_int, C.c_int]
+        lib.oracle_coo_to_csr.restype = None
         lib.oracle_fnv1a64.argtypes = [C.c_void_p, C.c_size_t]
         lib.oracle_fnv1a64.restype = C.c_uint64
         lib.oracle_num_threads.restype = C.c_int
@@ -74,6 +77,43 @@ def merge_ref():
         lib.ref_spmv_merge.restype = None
         lib._typed = True
     return lib
+
+
+def coo_ref():
+    """The reference's coo_to_csr (csr_gen.c:162-217), instantiated by lib/aux/csr_converter_double.c."""
+    lib = _load(os.path.join(HERE, "_ref", "libcoo_ref.so"))
+    if not hasattr(lib, "_typed"):
+        f = lib.coo_to_csr_csr_converter_double
+        f.argtypes = [_i32p, _i32p, C.c_void_p, C.c_long, C.c_long, C.c_long, _i32p, _i32p, C.c_void_p, C.c_int, C.c_int]
+        f.restype = None
+        lib._typed = True
+    return lib
+
+
+def have_coo_ref():
+    return os.path.exists(os.path.join(HERE, "_ref", "libcoo_ref.so"))
+
+
+def _coo_call(fn, R, Cc, V, m, n, sort_columns, transpose):
+    nnz = len(R)
+    nrows = n if transpose else m
+    row_ptr = np.zeros(nrows + 1, np.int32)
+    col_idx = np.zeros(max(nnz, 1), np.int32)
+    values = np.zeros(max(nnz, 1), np.float64) if V is not None else None
+    Rb = np.ascontiguousarray(R, np.int32) if nnz else np.zeros(1, np.int32)
+    Cb = np.ascontiguousarray(Cc, np.int32) if nnz else np.zeros(1, np.int32)
+    Vb = np.ascontiguousarray(V, np.float64) if V is not None else None
+    fn(Rb.copy(), Cb.copy(), Vb.ctypes.data if Vb is not None else None, m, n, nnz,
+       row_ptr, col_idx, values.ctypes.data if values is not None else None, sort_columns, transpose)
+    return row_ptr, col_idx[:nnz], (values[:nnz] if values is not None else None)
+
+
+def coo_to_csr_oracle(R, Cc, V, m, n, sort_columns=1, transpose=0):
+    return _coo_call(oracle().oracle_coo_to_csr, R, Cc, V, m, n, sort_columns, transpose)
+
+
+def coo_to_csr_ref(R, Cc, V, m, n, sort_columns=1, transpose=0):
+    return _coo_call(coo_ref().coo_to_csr_csr_converter_double, R, Cc, V, m, n, sort_columns, transpose)
 
 
 class _CsrHead(C.Structure):

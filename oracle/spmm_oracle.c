@@ -227,3 +227,59 @@ uint64_t oracle_fnv1a64(const void *buf, size_t nbytes)
 	}
 	return h;
 }
+
+/* ---------------------------------------------------------------------------
+ * a8: COO -> CSR with per-row column sort.
+ * ref: lib/storage_formats/csr/csr_gen.c:162-217 (coo_to_csr) and :82-156
+ *      (csr_sort_columns); lib/sort/bucketsort/bucketsort_gen.c:163-205.
+ *
+ * Reference: histogram of the row ids, prefix sums -> row_ptr, every element
+ * takes a free slot of its row (atomic decrement of the row's offset: the
+ * slot order inside a row depends on the thread schedule), then each row is
+ * sorted by column (quicksort on a permutation, or a stable bucket sort for
+ * rows longer than n/5).  With transpose != 0 the roles of R and C (and of m
+ * and n) are swapped.  The output is therefore defined up to the order of
+ * duplicate (row, col) pairs; this restatement orders a row by (column,
+ * position in the input), and with sort_columns == 0 by input position.
+ * ------------------------------------------------------------------------- */
+typedef struct { int32_t col; int64_t pos; } oracle_ent_t;
+
+static int oracle_ent_cmp(const void *pa, const void *pb)
+{
+	const oracle_ent_t *a = pa, *b = pb;
+	if (a->col != b->col)
+		return (a->col < b->col) ? -1 : 1;
+	return (a->pos < b->pos) ? -1 : (a->pos > b->pos);
+}
+
+void oracle_coo_to_csr(const int32_t *R, const int32_t *C, const double *V, long m, long n, long nnz,
+                       int32_t *row_ptr, int32_t *col_idx, double *values, int sort_columns, int transpose)
+{
+	const int32_t *rows = transpose ? C : R;
+	const int32_t *cols = transpose ? R : C;
+	long nrows = transpose ? n : m;
+	long *cursor = malloc(sizeof(long) * (nrows + 1));
+	oracle_ent_t *ent = malloc(sizeof(oracle_ent_t) * (nnz > 0 ? nnz : 1));
+	memset(row_ptr, 0, sizeof(int32_t) * (nrows + 1));
+	for (long i = 0; i < nnz; i++)
+		row_ptr[rows[i] + 1]++;
+	for (long r = 0; r < nrows; r++)
+		row_ptr[r + 1] += row_ptr[r];
+	for (long r = 0; r <= nrows; r++)
+		cursor[r] = row_ptr[r];
+	for (long i = 0; i < nnz; i++) {                 /* stable scatter */
+		long p = cursor[rows[i]]++;
+		ent[p].col = sort_columns ? cols[i] : 0;
+		ent[p].pos = i;
+	}
+	if (sort_columns)
+		for (long r = 0; r < nrows; r++)
+			qsort(ent + row_ptr[r], row_ptr[r + 1] - row_ptr[r], sizeof(oracle_ent_t), oracle_ent_cmp);
+	for (long j = 0; j < nnz; j++) {
+		col_idx[j] = cols[ent[j].pos];
+		if (V != NULL)
+			values[j] = V[ent[j].pos];
+	}
+	free(cursor);
+	free(ent);
+}

@@ -16,7 +16,7 @@ import os
 
 import numpy as np
 
-__all__ = ["csr_to_format", "MatrixFormat", "partition", "statistics_print_labels", "load_library",
+__all__ = ["csr_to_format", "coo_to_csr", "MatrixFormat", "partition", "shard_slices", "statistics_print_labels", "load_library",
            "SpmmB200Error", "ROWSPLIT", "MERGE", "BCSR", "AUTO", "BCSR_FMA", "B_COLMAJOR", "B_ROWMAJOR",
            "PART_ROWS", "PART_NNZ", "PART_MERGE", "LIB_PATH", "EXPORTS"]
 
@@ -32,7 +32,7 @@ EXPORTS = [
     "spmm_b200_create", "spmm_b200_create_shard", "spmm_b200_run", "spmm_b200_set_b",
     "spmm_b200_register_host", "spmm_b200_unregister_host",
     "spmm_b200_run_resident", "spmm_b200_fetch_c", "spmm_b200_run_device",
-    "spmm_b200_transpose_b_device", "spmm_b200_partition", "spmm_b200_rows", "spmm_b200_nnz",
+    "spmm_b200_transpose_b_device", "spmm_b200_partition", "spmm_b200_partition_host", "spmm_b200_coo_to_csr", "spmm_b200_rows", "spmm_b200_nnz",
     "spmm_b200_variant", "spmm_b200_bcsr_blocks", "spmm_b200_last_kernel_ms", "spmm_b200_launch_count", "spmm_b200_stats",
     "spmm_b200_stats_labels", "spmm_b200_destroy", "spmm_b200_strerror", "spmm_b200_last_cuda_error",
     "spmm_b200_device_count",
@@ -73,6 +73,8 @@ def load_library():
     lib.spmm_b200_run_device.argtypes = [_vp, _vp, _vp, _int, _vp]
     lib.spmm_b200_transpose_b_device.argtypes = [_vp, _vp, _vp, _int, _vp]
     lib.spmm_b200_partition.argtypes = [_vp, _i64, _i64, _int, _int, _vp, _int]
+    lib.spmm_b200_partition_host.argtypes = [_vp, _i64, _i64, _int, _int, _vp]
+    lib.spmm_b200_coo_to_csr.argtypes = [_vp, _vp, _vp, _i64, _i64, _i64, _vp, _vp, _vp, _int, _int, _int]
     lib.spmm_b200_rows.argtypes = [_vp]; lib.spmm_b200_rows.restype = _i64
     lib.spmm_b200_nnz.argtypes = [_vp]; lib.spmm_b200_nnz.restype = _i64
     lib.spmm_b200_variant.argtypes = [_vp]
@@ -200,14 +202,46 @@ def csr_to_format(row_ptr, col_ind, values, m, n, nnz, k, *, device=0, variant=A
     return MatrixFormat(h, lib.spmm_b200_rows(h), n, lib.spmm_b200_nnz(h), k, first_row=r0.value, m_global=m)
 
 
-def partition(row_ptr, m, nnz, P, mode, device=0):
-    """Device-side, bit-exact twins of the reference partitioners (include/spmm_b200.h).
+def partition(row_ptr, m, nnz, P, mode, device=0, host=False):
+    """Bit-exact twins of the reference partitioners (include/spmm_b200.h), searched on the device
+    (host=True: the same integer functions on the CPU, for shard planning).
     PART_NNZ -> int64[P+1] row starts; PART_ROWS -> int64[P,2]; PART_MERGE -> int64[P+1,2]."""
     n_out = {PART_NNZ: P + 1, PART_ROWS: 2 * P, PART_MERGE: 2 * (P + 1)}[mode]
     out = np.zeros(n_out, dtype=np.int64)
     rp = _host(row_ptr, np.int32, "row_ptr") if row_ptr is not None else None
-    _check(load_library().spmm_b200_partition(rp, m, nnz, P, mode, out.ctypes.data, device), "partition")
+    if host:
+        _check(load_library().spmm_b200_partition_host(rp, m, nnz, P, mode, out.ctypes.data), "partition_host")
+    else:
+        _check(load_library().spmm_b200_partition(rp, m, nnz, P, mode, out.ctypes.data, device), "partition")
     return out if mode == PART_NNZ else out.reshape(-1, 2)
+
+
+def shard_slices(row_ptr, m, nnz, nranks):
+    """Row range and nnz range of every rank under the reference's nnz-balanced split
+    (lib/parallel_util.h:141-165): [(r0, r1, j0, j1)] * nranks."""
+    b = partition(row_ptr, m, nnz, nranks, PART_NNZ, host=True)
+    out = []
+    for r in range(nranks):
+        r0, r1 = int(b[r]), int(max(b[r + 1], b[r]))
+        out.append((r0, r1, int(row_ptr[r0]), int(row_ptr[r1])))
+    return out
+
+
+def coo_to_csr(R, C, V, m, n, nnz, sort_columns=1, transpose=0, device=0):
+    """Mirror of coo_to_csr() (lib/storage_formats/csr/csr_gen.c:162-217), conversion on the device.
+    Returns (row_ptr int32[m+1 | n+1], col_idx int32[nnz], values f64[nnz] | None)."""
+    nrows = n if transpose else m
+    row_ptr = np.zeros(nrows + 1, dtype=np.int32)
+    col_idx = np.zeros(max(nnz, 1), dtype=np.int32)[:nnz]
+    values = np.zeros(max(nnz, 1), dtype=np.float64)[:nnz] if V is not None else None
+    rp = _host(R, np.int32, "R") if nnz > 0 else None
+    cp = _host(C, np.int32, "C") if nnz > 0 else None
+    vp = _host(V, np.float64, "V") if (V is not None and nnz > 0) else None
+    _check(load_library().spmm_b200_coo_to_csr(
+        rp, cp, vp, m, n, nnz, row_ptr.ctypes.data, col_idx.ctypes.data if nnz > 0 else None,
+        values.ctypes.data if (values is not None and nnz > 0) else None, int(sort_columns), int(transpose), device),
+        "coo_to_csr")
+    return row_ptr, col_idx, values
 
 
 def statistics_print_labels(buf_n=512):

@@ -11,6 +11,7 @@
 #include "spmm_merge.cuh"
 #include "scan.cuh"
 #include "spmm_bcsr.cuh"
+#include "coo_to_csr.cuh"
 
 #include <cuda_runtime.h>
 #include <stdio.h>
@@ -677,6 +678,103 @@ extern "C" int spmm_b200_partition(const int32_t* row_ptr, int64_t m, int64_t nn
 	if (e == cudaSuccess) e = cudaMemcpy(out, d_out, sizeof(int64_t) * n_out, cudaMemcpyDeviceToHost);
 	cudaFree(d_out); cudaFree(d_ia);
 	CU_TRY(e);
+	return SPMM_B200_OK;
+}
+
+// Host twin of spmm_b200_partition: the same integer functions (partition.cuh, __host__ __device__)
+// evaluated on the CPU.  Shard planning only -- O(P log m) integer work, no SpMM arithmetic --
+// so that a launcher can size per-rank buffers before any device exists (and so that the
+// multi-rank plumbing can be tested with gloo on a CPU box).
+extern "C" int spmm_b200_partition_host(const int32_t* row_ptr, int64_t m, int64_t nnz, int P, int mode, int64_t* out)
+{
+	if (!out || P < 1 || m < 0 || nnz < 0) return SPMM_B200_EINVAL;
+	if (mode < SPMM_B200_PART_ROWS || mode > SPMM_B200_PART_MERGE) return SPMM_B200_EINVAL;
+	if (mode != SPMM_B200_PART_ROWS && !row_ptr) return SPMM_B200_EINVAL;
+	if (mode == SPMM_B200_PART_NNZ) {
+		for (int64_t t = 0; t <= P; t++) out[t] = nnz_split_start(row_ptr, m, nnz, P, t);
+	} else if (mode == SPMM_B200_PART_ROWS) {
+		for (int64_t t = 0; t < P; t++) equal_split(0, m, P, t, &out[2 * t], &out[2 * t + 1]);
+	} else {
+		const int64_t L = m + nnz, items = (L + P - 1) / P;
+		for (int64_t t = 0; t <= P; t++) {
+			int64_t d = items * t; if (d > L) d = L;
+			merge_path_search(d, row_ptr + 1, m, nnz, &out[2 * t], &out[2 * t + 1]);
+		}
+	}
+	return SPMM_B200_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// COO -> CSR (host pointers in and out, all work on the device)
+// ------------------------------------------------------------------------------------------
+
+namespace {
+struct DevBuf {
+	void* p = nullptr;
+	~DevBuf() { if (p) cudaFree(p); }
+	template <typename T> T* as() { return static_cast<T*>(p); }
+};
+}
+
+extern "C" int spmm_b200_coo_to_csr(const int32_t* R, const int32_t* C, const double* V, int64_t m, int64_t n, int64_t nnz,
+                                    int32_t* row_ptr, int32_t* col_idx, double* values, int sort_columns, int transpose, int device)
+{
+	if (m < 0 || n < 0 || nnz < 0 || !row_ptr) return SPMM_B200_EINVAL;
+	if (nnz > 0 && (!R || !C || !col_idx)) return SPMM_B200_EINVAL;
+	if ((V == nullptr) != (values == nullptr) && nnz > 0) return SPMM_B200_EINVAL;
+	if (m >= INT32_MAX || n >= INT32_MAX || nnz >= INT32_MAX) return SPMM_B200_ERANGE;
+	int rc = check_device(device, nullptr);
+	if (rc) return rc;
+	const int64_t nrows = transpose ? n : m;                 // csr_gen.c:170-173
+	const int32_t* h_rows = transpose ? C : R;
+	const int32_t* h_cols = transpose ? R : C;
+	for (int64_t i = 0; i < nnz; i++)                         // the device histogram must stay in bounds
+		if (h_rows[i] < 0 || h_rows[i] >= nrows) return SPMM_B200_EINVAL;
+
+	DevBuf d_rows, d_cols, d_vals, d_ptr, d_cursor, d_keys, d_tmp, d_long, d_nlong, d_colout, d_valout;
+	const size_t nz = (size_t) std::max<int64_t>(nnz, 1);
+	CU_TRY(cudaMalloc(&d_rows.p, nz * 4));
+	CU_TRY(cudaMalloc(&d_cols.p, nz * 4));
+	if (V) CU_TRY(cudaMalloc(&d_vals.p, nz * 8));
+	CU_TRY(cudaMalloc(&d_ptr.p, ((size_t) nrows + 1) * 4));
+	CU_TRY(cudaMalloc(&d_cursor.p, ((size_t) nrows + 1) * 4));
+	CU_TRY(cudaMalloc(&d_keys.p, nz * 8));
+	CU_TRY(cudaMalloc(&d_tmp.p, scan_tmp_elems(nrows + 1) * 4));
+	CU_TRY(cudaMalloc(&d_long.p, (size_t) std::max<int64_t>(nrows, 1) * 4));
+	CU_TRY(cudaMalloc(&d_nlong.p, 4));
+	CU_TRY(cudaMalloc(&d_colout.p, nz * 4));
+	if (V) CU_TRY(cudaMalloc(&d_valout.p, nz * 8));
+	cudaStream_t s = nullptr;
+	if (nnz > 0) {
+		CU_TRY(cudaMemcpyAsync(d_rows.p, h_rows, nnz * 4, cudaMemcpyHostToDevice, s));
+		CU_TRY(cudaMemcpyAsync(d_cols.p, h_cols, nnz * 4, cudaMemcpyHostToDevice, s));
+		if (V) CU_TRY(cudaMemcpyAsync(d_vals.p, V, nnz * 8, cudaMemcpyHostToDevice, s));
+	}
+	CU_TRY(cudaMemsetAsync(d_ptr.p, 0, ((size_t) nrows + 1) * 4, s));
+	CU_TRY(cudaMemsetAsync(d_nlong.p, 0, 4, s));
+	const unsigned nb = (unsigned) std::min<int64_t>(148 * 16, (nnz + 255) / 256);
+	if (nnz > 0) coo_histogram_kernel<<<nb, 256, 0, s>>>(d_rows.as<int32_t>(), nnz, d_ptr.as<int32_t>());
+	exclusive_scan_i32(d_ptr.as<int32_t>(), nrows + 1, d_tmp.as<int32_t>(), s);
+	CU_TRY(cudaMemcpyAsync(d_cursor.p, d_ptr.p, ((size_t) nrows + 1) * 4, cudaMemcpyDeviceToDevice, s));
+	int32_t n_long = 0;
+	if (nnz > 0) {
+		coo_scatter_kernel<<<nb, 256, 0, s>>>(d_rows.as<int32_t>(), d_cols.as<int32_t>(), nnz, d_cursor.as<int32_t>(),
+		                                     d_keys.as<unsigned long long>(), sort_columns ? 1 : 0);
+		coo_sort_rows_warp_kernel<<<(unsigned) ((nrows + 7) / 8), 256, 0, s>>>(d_ptr.as<int32_t>(), (int) nrows, d_keys.as<unsigned long long>());
+		coo_list_long_rows_kernel<<<(unsigned) ((nrows + 255) / 256), 256, 0, s>>>(d_ptr.as<int32_t>(), (int) nrows, d_long.as<int32_t>(), d_nlong.as<int32_t>());
+		CU_TRY(cudaMemcpyAsync(&n_long, d_nlong.p, 4, cudaMemcpyDeviceToHost, s));
+		CU_TRY(cudaStreamSynchronize(s));
+		if (n_long > 0)
+			coo_sort_rows_cta_kernel<<<(unsigned) n_long, 256, 0, s>>>(d_ptr.as<int32_t>(), d_long.as<int32_t>(), d_keys.as<unsigned long long>());
+		coo_gather_kernel<<<nb, 256, 0, s>>>(d_keys.as<unsigned long long>(), nnz, d_cols.as<int32_t>(), d_vals.as<double>(),
+		                                    d_colout.as<int32_t>(), d_valout.as<double>());
+		CU_TRY(cudaGetLastError());
+		CU_TRY(cudaMemcpyAsync(col_idx, d_colout.p, nnz * 4, cudaMemcpyDeviceToHost, s));
+		if (V) CU_TRY(cudaMemcpyAsync(values, d_valout.p, nnz * 8, cudaMemcpyDeviceToHost, s));
+	}
+	CU_TRY(cudaMemcpyAsync(row_ptr, d_ptr.p, ((size_t) nrows + 1) * 4, cudaMemcpyDeviceToHost, s));
+	CU_TRY(cudaStreamSynchronize(s));
+	CU_TRY(cudaGetLastError());
 	return SPMM_B200_OK;
 }
 

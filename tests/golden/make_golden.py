@@ -82,6 +82,19 @@ def main():
     np.savez_compressed(os.path.join(HERE, "spmm_reference_outputs.npz"), **out)
     print("wrote", len(SPMM_CASES), "reference SpMM outputs")
 
+    # COO -> CSR: output of the reference's coo_to_csr (csr_gen.c:162-217) on a shuffled COO of a
+    # small generated matrix, plain and transposed.
+    ia, ja, a, m, c = L.generate("3000 2500 12 6 gamma random 0.5 50 0.3 0.3 14")
+    R = np.repeat(np.arange(m, dtype=np.int32), np.diff(ia))
+    perm = np.random.default_rng(7).permutation(len(ja))
+    R, C, V = R[perm].copy(), ja[perm].copy(), a[perm].copy()
+    rp, ci, va = L.coo_to_csr_ref(R, C, V, m, c, 1, 0)
+    assert np.array_equal(rp, ia) and np.array_equal(ci, ja) and np.array_equal(va, a)
+    rpt, cit, vat = L.coo_to_csr_ref(R, C, V, m, c, 1, 1)
+    np.savez_compressed(os.path.join(HERE, "coo_to_csr_reference.npz"), R=R, C=C, V=V, m=m, n=c,
+                        row_ptr=rp, col_idx=ci, values=va, row_ptr_t=rpt, col_idx_t=cit, values_t=vat)
+    print("wrote coo_to_csr reference vector, nnz =", len(R))
+
 
 if __name__ == "__main__":
     main()
