@@ -1,0 +1,68 @@
+#!/usr/bin/env python
+"""BASELINE configs[4]: parameter sweep over a subset of synthetic_matrices_medium_dataset.txt
+(bench/medium_subset.txt) at k in {1, 8, 32, 128} on ONE B200, kernel time by CUDA events inside
+the library (spmm_b200_last_kernel_ms), B and A resident.  Prints a markdown table and writes
+gpurun_out/sweep_medium.json.  Matrices come from the reference generator (oracle/_ref)."""
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import __graft_entry__ as g          # noqa: E402
+from oracle import loader as L       # noqa: E402  (input generation only)
+
+PEAK = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"] if os.path.exists(
+    os.path.join(ROOT, "MEASURED_PEAKS.json")) else 6650.0
+
+
+def main():
+    pkg = g.load_package()
+    ks = [int(x) for x in os.environ.get("SWEEP_KS", "1,8,32,128").split(",")]
+    variants = os.environ.get("SWEEP_VARIANTS", "auto").split(",")
+    vmap = {"auto": pkg.AUTO, "rowsplit": pkg.ROWSPLIT, "merge": pkg.MERGE, "bcsr": pkg.BCSR}
+    lines = [l.strip() for l in open(os.path.join(ROOT, "bench", "medium_subset.txt")) if l.strip() and l[0] != "#"]
+    limit = int(os.environ.get("SWEEP_LIMIT", "0"))
+    if limit:
+        lines = lines[:limit]
+    rows = []
+    print("| rows | avg | bw | skew | nnz | k | variant | ms | GFLOP/s | alg. GB/s | frac of %.0f GB/s |" % PEAK)
+    print("|---|---|---|---|---|---|---|---|---|---|---|")
+    for args in lines:
+        f = args.split()
+        t0 = time.time()
+        ia, ja, a, m, c = L.generate(args)
+        nnz = len(ja)
+        gen_s = time.time() - t0
+        for k in ks:
+            if (m + c) * k * 8 > 24e9:
+                continue
+            x = np.random.default_rng(1).random(c * k)
+            for vname in variants:
+                mf = pkg.csr_to_format(ia, ja, a, m, c, nnz, k, variant=vmap[vname])
+                mf.set_b(x, k)
+                for _ in range(3):
+                    mf.spmm_resident(k)
+                ts = []
+                for _ in range(10):
+                    mf.spmm_resident(k)
+                    ts.append(mf.last_kernel_ms())
+                ms = float(np.median(ts))
+                name = mf.format_name
+                mf.close()
+                byts = 12.0 * nnz + 4.0 * (m + 1) + 8.0 * k * c + 8.0 * k * m
+                gf = 2.0 * nnz * k / (ms * 1e-3) / 1e9
+                gbs = byts / (ms * 1e-3) / 1e9
+                rows.append(dict(args=args, m=m, nnz=nnz, k=k, variant=name, ms=ms, gflops=gf, alg_gbs=gbs,
+                                 frac=gbs / PEAK, gen_s=gen_s))
+                print(f"| {m} | {f[2]} | {f[6]} | {f[7]} | {nnz} | {k} | {name.replace('B200_CSR_', '')} | {ms:.4f} | {gf:.0f} | {gbs:.0f} | {gbs / PEAK:.3f} |",
+                      flush=True)
+    os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+    json.dump(rows, open(os.path.join(ROOT, "gpurun_out", "sweep_medium.json"), "w"), indent=1)
+
+
+if __name__ == "__main__":
+    main()
