@@ -263,7 +263,8 @@ static bool bcsr_supports_k(int variant, int k)
 	return k == 32 || k == 64 || k == 128;
 }
 
-static int build_bcsr_plan(spmm_b200* h)
+// Pass 1 of the conversion: distinct columns per 8-row slab -> brow_ptr, nnzb (also AUTO's fill probe).
+static int bcsr_count(spmm_b200* h)
 {
 	BcsrPlan& p = h->bcsr;
 	const int mb = (int) ((h->m + 7) / 8);
@@ -283,6 +284,23 @@ static int build_bcsr_plan(spmm_b200* h)
 	CU_TRY(cudaStreamSynchronize(h->stream));
 	cudaFree(d_tmp);
 	p.nnzb = nnzb;
+	return SPMM_B200_OK;
+}
+
+static void bcsr_release(spmm_b200* h)
+{
+	BcsrPlan& p = h->bcsr;
+	cudaFree(p.d_brow); cudaFree(p.d_bcol); cudaFree(p.d_bval); cudaFree(p.d_bmask);
+	p = BcsrPlan();
+}
+
+// Pass 2: write bcol / bval / bmask.
+static int bcsr_fill(spmm_b200* h)
+{
+	BcsrPlan& p = h->bcsr;
+	const int mb = p.mb;
+	const int64_t nnzb = p.nnzb;
+	const unsigned nb = (unsigned) (((int64_t) mb * 8 + 255) / 256);
 	CU_TRY(cudaMalloc(&p.d_bcol, sizeof(int32_t) * std::max<size_t>((size_t) nnzb, 1)));
 	CU_TRY(cudaMalloc(&p.d_bmask, std::max<size_t>((size_t) nnzb, 1)));
 	// +4 blocks of slack: the TMA kernel fetches the A values of a step as one 256-byte bulk copy
@@ -295,6 +313,13 @@ static int build_bcsr_plan(spmm_b200* h)
 	CU_TRY(cudaGetLastError());
 	CU_TRY(cudaStreamSynchronize(h->stream));
 	return SPMM_B200_OK;
+}
+
+static int build_bcsr_plan(spmm_b200* h)
+{
+	int rc = bcsr_count(h);
+	if (rc) return rc;
+	return bcsr_fill(h);
 }
 
 template <int K, int WARPS, int STAGES>
@@ -317,8 +342,10 @@ static void launch_bcsr_k(const spmm_b200* h, const double* B, double* C, cudaSt
 	const BcsrPlan& p = h->bcsr;
 	const unsigned grid = (unsigned) ((p.mb + WARPS - 1) / WARPS);
 	static const int use_tma = env_int("SPMM_B200_BCSR_TMA", 1);
-	if (h->variant == SPMM_B200_BCSR && use_tma && ((uintptr_t) B % 16) == 0) {
-		static const int stages = env_int("SPMM_B200_BCSR_STAGES", 4);
+	// bulk copies of 8K bytes per B row pay from K = 64 on (cfg4: K=32 0.57 ms fragment loads vs 0.63 ms TMA;
+	// K=128 2.55 ms vs 1.23 ms); 2 stages = most warps per SM, which is what the tensor pipe needs
+	if (h->variant == SPMM_B200_BCSR && (use_tma == 2 || (use_tma == 1 && K >= 64)) && ((uintptr_t) B % 16) == 0) {
+		static const int stages = env_int("SPMM_B200_BCSR_STAGES", 2);
 		static const int brw_env = env_int("SPMM_B200_BCSR_BRW", 0);
 		// block rows per warp: enough to keep the ring flowing, few enough for >= 8 CTAs per SM
 		const int brw = brw_env > 0 ? brw_env : (int) std::max<int64_t>(1, std::min<int64_t>(8, p.mb / ((int64_t) h->sm_count * WARPS * 8)));
@@ -436,7 +463,23 @@ static int create_from_slice(spmm_b200_t** out, const int32_t* row_ptr_slice, co
 	}
 	int rc = build_rowsplit_plan(h);        // always: the fallback for k without a specialised instantiation
 	if (rc) return rc;
-	if (h->variant == SPMM_B200_BCSR || h->variant == SPMM_B200_BCSR_FMA) {
+	if (variant == SPMM_B200_AUTO && h->variant == SPMM_B200_ROWSPLIT && k >= 32 && bcsr_supports_k(SPMM_B200_BCSR, k)
+	    && m_local >= 8 && nnz_local > 0) {
+		// "tensor cores only where dense blocks make it a genuine contraction": probe the 8x1 block
+		// fill with pass 1 of the conversion.  Break-even measured on B200: fill 0.15
+		// at k=128, 0.25 at k=32; below 0.30 the CSR kernels stay.
+		rc = bcsr_count(h);
+		if (rc) return rc;
+		const double fill = h->bcsr.nnzb > 0 ? (double) nnz_local / (8.0 * (double) h->bcsr.nnzb) : 0.0;
+		const double thr = env_int("SPMM_B200_BCSR_FILL_PCT", 30) / 100.0;
+		if (fill >= thr) {
+			rc = bcsr_fill(h);
+			if (rc) return rc;
+			h->variant = SPMM_B200_BCSR;
+		} else {
+			bcsr_release(h);
+		}
+	} else if (h->variant == SPMM_B200_BCSR || h->variant == SPMM_B200_BCSR_FMA) {
 		rc = build_bcsr_plan(h);
 		if (rc) return rc;
 	}
