@@ -289,14 +289,23 @@ def gpu_arm(args, ia, ja, a, m, c, k, nnz, workload_desc):
 
     # ---- end to end with HOST buffers: `e2e` -----------------------------------------------------
     e2e_steps = max(3, min(args.steps, 10))
+
+    class _DevArray:           # library-owned device range -> torch tensor (for the broadcast callback)
+        def __init__(self, ptr, n):
+            self.__cuda_array_interface__ = {"shape": (n,), "typestr": "<f8", "data": (ptr, False), "version": 2}
+
+    def bcast(ptr, count, cuda_stream):
+        t = torch.as_tensor(_DevArray(ptr, count), device=dev)
+        with torch.cuda.stream(torch.cuda.ExternalStream(cuda_stream, device=dev)):
+            dist.broadcast(t, src=0)
+
     def e2e_step():
+        # the public drop-in call with HOST buffers: upload (root) -> broadcast -> kernel -> download of the
+        # row-local C, pipelined over 16-column slices inside the library
         if world == 1:
-            mf.spmm(x_host.numpy(), y_host.numpy()[: m_loc * k], k)        # the public drop-in call
+            mf.spmm(x_host.numpy(), y_host.numpy()[: m_loc * k], k)
         else:
-            replicate_b()
-            mf.spmm_device(b_dev.data_ptr(), c_dev.data_ptr(), k, stream.cuda_stream)
-            y_host[: m_loc * k].copy_(c_dev[: m_loc * k], non_blocking=True)
-            torch.cuda.synchronize()
+            mf.spmm_replicated(x_host.numpy() if rank == 0 else None, y_host.numpy()[: m_loc * k], k, bcast)
     for _ in range(2):
         e2e_step()
     barrier()
@@ -310,6 +319,9 @@ def gpu_arm(args, ia, ja, a, m, c, k, nnz, workload_desc):
 
     # ---- checksum so that the work cannot be skipped silently -----------------------------------
     csum = float(c_dev[: m_loc * k].sum().item()) if m_loc else 0.0
+    csum_e2e = float(y_host[: m_loc * k].sum().item()) if m_loc else 0.0      # what the host-buffer call returned
+    if abs(csum_e2e - csum) > 1e-9 * max(abs(csum), 1.0):
+        raise SystemExit(f"bench.py: e2e result differs from the device-resident result ({csum_e2e} vs {csum})")
 
     peak, peak_src = measured_peak_gbs()
     nnz_loc = mf.nnz
@@ -328,7 +340,7 @@ def gpu_arm(args, ia, ja, a, m, c, k, nnz, workload_desc):
                      "kernel": mf.format_name, "frac_of_8TBs_nominal": achieved / 8000.0,
                      "rank0_shard": world > 1},
         "clocks": clocks,
-        "checksum_c_rank0": csum,
+        "checksum_c_rank0": csum, "checksum_c_e2e_rank0": csum_e2e,
         "variant": mf.format_name,
         "bcsr_fill": mf.bcsr_fill(),
     }

@@ -65,7 +65,8 @@ enum {
 	SPMM_B200_ECUDA   = -3,   /* a CUDA runtime call failed (see spmm_b200_last_cuda_error)   */
 	SPMM_B200_ENOMEM  = -4,   /* device or host allocation failed                             */
 	SPMM_B200_ERANGE  = -5,   /* sizes overflow the int32 index contract (nnz, m, c < 2^31)  */
-	SPMM_B200_ENOSUP  = -6    /* variant not applicable to this matrix / k                    */
+	SPMM_B200_ENOSUP  = -6,   /* variant not applicable to this matrix / k                    */
+	SPMM_B200_ECOMM   = -7    /* the caller-supplied broadcast callback returned non-zero     */
 };
 
 /* ---- format construction: replaces csr_to_format() (spmv_kernel.h:29; call site spmv_bench.cpp:996).
@@ -92,8 +93,23 @@ int spmm_b200_create_shard(spmm_b200_t **h,
  * spmv_bench.cpp:318,372).  HOST buffers: x (c*k doubles, layout = b_layout of the
  * handle), y (m_local*k doubles, row-major).  Uploads x (H2D), runs the kernel(s),
  * and when copy_back != 0 downloads y (D2H) before returning.  With
- * copy_back == 0 the result stays on the device (spmm_b200_fetch_c reads it). */
+ * copy_back == 0 the result stays on the device (spmm_b200_fetch_c reads it).
+ * The call is PCIe-bound; for k >= 32 (k % 16 == 0) and operands of >= 8 MB the columns are cut into
+ * 16-column slices so that the upload of slice s+1, the kernel on slice s and the download of
+ * C[:, slice s-1] overlap (SPMM_B200_PIPELINE_COLS=0 turns it off).  Results are identical. */
 int spmm_b200_run(spmm_b200_t *h, const double *x_host, double *y_host, int k, int copy_back);
+
+/* Multi-GPU form of the hot call (one process per GPU, handle from spmm_b200_create_shard).  The
+ * only collective on this path is the replication of B; the library does not link a
+ * communication library, the caller supplies it: `bcast(ctx, dev_ptr, count, stream)` must enqueue a
+ * broadcast of `count` doubles at `dev_ptr` from the root rank on `stream` (a cudaStream_t), e.g.
+ * ncclBroadcast(dev_ptr, dev_ptr, count, ncclDouble, root, comm, stream), and return 0.  x_host is
+ * the host B on the root rank and NULL elsewhere; y_host receives this rank's row-local C.  For
+ * k >= 32 the columns go through in 16-column slices so that upload, broadcast, kernel and the
+ * download of C overlap; with bcast == NULL it is spmm_b200_run with the same pipeline. */
+typedef int (*spmm_b200_bcast_fn)(void *ctx, double *dev_ptr, size_t count, void *stream);
+int spmm_b200_run_replicated(spmm_b200_t *h, const double *x_host, double *y_host, int k, int copy_back,
+                             spmm_b200_bcast_fn bcast, void *bcast_ctx);
 
 /* Optional: page-lock a caller-owned host range (x or y) so that spmm_b200_run copies at full
  * PCIe rate.  The caller promises the range stays mapped until spmm_b200_unregister_host /

@@ -69,6 +69,11 @@ struct spmm_b200 {
 	cudaStream_t stream = nullptr;
 	cudaEvent_t ev0 = nullptr, ev1 = nullptr;
 	bool timed = false;
+	// k-sliced host pipeline of spmm_b200_run (upload slice s+1 | kernel slice s | download slice s-1)
+	cudaStream_t s_up = nullptr, s_down = nullptr;
+	std::vector<cudaEvent_t> ev_slice;    // per slice: uploaded, kernel start, kernel end
+	int c_slices = 1;                     // >1: d_C holds c_slices blocks of m x (k / c_slices)
+	int timed_slices = 0;                 // >0: last_kernel_ms sums the slices' kernel events
 	int64_t launches = 0;
 };
 
@@ -555,6 +560,9 @@ extern "C" void spmm_b200_destroy(spmm_b200_t* h)
 	cudaFree(h->d_x); cudaFree(h->d_B); cudaFree(h->d_C);
 	if (h->ev0) cudaEventDestroy(h->ev0);
 	if (h->ev1) cudaEventDestroy(h->ev1);
+	for (cudaEvent_t e : h->ev_slice) cudaEventDestroy(e);
+	if (h->s_up) cudaStreamDestroy(h->s_up);
+	if (h->s_down) cudaStreamDestroy(h->s_down);
 	if (h->stream) cudaStreamDestroy(h->stream);
 	delete h;
 }
@@ -631,17 +639,24 @@ extern "C" int spmm_b200_transpose_b_device(spmm_b200_t* h, const double* x_dev,
 	return SPMM_B200_OK;
 }
 
+static int run_between(spmm_b200* h, const double* b_dev, double* c_dev, int k, cudaStream_t s, cudaEvent_t e0, cudaEvent_t e1)
+{
+	CU_TRY(cudaEventRecord(e0, s));
+	int n = launch_spmm(h, b_dev, c_dev, k, s);
+	if (n < 0) return n;
+	CU_TRY(cudaEventRecord(e1, s));
+	return SPMM_B200_OK;
+}
+
 extern "C" int spmm_b200_run_device(spmm_b200_t* h, const double* b_dev, double* c_dev, int k, void* stream)
 {
 	if (!h || k < 1) return SPMM_B200_EINVAL;
 	if ((h->c > 0 && h->nnz > 0 && !b_dev) || (h->m > 0 && !c_dev)) return SPMM_B200_EINVAL;
 	CU_TRY(cudaSetDevice(h->device));
-	cudaStream_t s = (cudaStream_t) stream;
-	CU_TRY(cudaEventRecord(h->ev0, s));
-	int n = launch_spmm(h, b_dev, c_dev, k, s);
-	if (n < 0) return n;
-	CU_TRY(cudaEventRecord(h->ev1, s));
+	int rc = run_between(h, b_dev, c_dev, k, (cudaStream_t) stream, h->ev0, h->ev1);
+	if (rc) return rc;
 	h->timed = true;
+	h->timed_slices = 0;
 	return SPMM_B200_OK;
 }
 
@@ -660,18 +675,115 @@ extern "C" int spmm_b200_run_resident(spmm_b200_t* h, int k)
 	if (!h || k < 1 || h->resident_k != k) return SPMM_B200_EINVAL;
 	int rc = ensure(&h->d_C, &h->cap_C, (size_t) h->m * k);
 	if (rc) return rc;
+	h->c_slices = 1;
 	rc = spmm_b200_run_device(h, h->d_B, h->d_C, k, h->stream);
 	if (rc) return rc;
 	CU_TRY(cudaStreamSynchronize(h->stream));
 	return SPMM_B200_OK;
 }
 
+// d_C -> y_host (row-major m x k).  After a k-sliced run d_C holds c_slices blocks of m x k/c_slices.
+static int download_c(spmm_b200* h, double* y_host, int k, cudaStream_t s)
+{
+	if (h->m == 0) return SPMM_B200_OK;
+	if (h->c_slices <= 1) {
+		CU_TRY(cudaMemcpyAsync(y_host, h->d_C, sizeof(double) * h->m * k, cudaMemcpyDeviceToHost, s));
+		return SPMM_B200_OK;
+	}
+	const int ks = k / h->c_slices;
+	for (int i = 0; i < h->c_slices; i++)
+		CU_TRY(cudaMemcpy2DAsync(y_host + (size_t) i * ks, sizeof(double) * k, h->d_C + (size_t) i * h->m * ks, sizeof(double) * ks,
+		                         sizeof(double) * ks, (size_t) h->m, cudaMemcpyDeviceToHost, s));
+	return SPMM_B200_OK;
+}
+
 extern "C" int spmm_b200_fetch_c(spmm_b200_t* h, double* y_host, int k)
 {
 	if (!h || !y_host || k < 1 || h->cap_C < (size_t) h->m * k) return SPMM_B200_EINVAL;
+	if (h->c_slices > 1 && k % h->c_slices) return SPMM_B200_EINVAL;
 	CU_TRY(cudaSetDevice(h->device));
-	CU_TRY(cudaMemcpyAsync(y_host, h->d_C, sizeof(double) * h->m * k, cudaMemcpyDeviceToHost, h->stream));
+	int rc = download_c(h, y_host, k, h->stream);
+	if (rc) return rc;
 	CU_TRY(cudaStreamSynchronize(h->stream));
+	return SPMM_B200_OK;
+}
+
+// ---- k-sliced host pipeline --------------------------------------------------------------------
+// spmm_b200_run is PCIe-bound (cfg2, k=32: 4.6 ms up + 0.9 ms kernel + 4.5 ms down).  The link is full
+// duplex (measured 50 GB/s each way at once, profiles/r1_pcie_probe.md) and the oracle layout of B is k
+// contiguous vectors, so the columns are cut into slices of 16: slice s+1 uploads while the kernel
+// runs on slice s and C[:, slice s-1] downloads.  A 16-column slice of the row-major C is a 128-byte
+// wide 2-D copy, which the copy engine still moves at 52.6 GB/s (64 bytes: 31 GB/s -- hence 16).
+static int slice_width(const spmm_b200* h, int k)
+{
+	int w = env_int("SPMM_B200_PIPELINE_COLS", -1);                  // 0 = off, -1 = choose
+	if (w < 0) {
+		// at most 4 slices: every slice re-reads A, and wider slices run the better kernels
+		// (cfg4, k=128: 27.8 ms with 32-column slices, 29.3 ms with 16, 38.8 ms unsliced)
+		w = 16;
+		while (k / w > 4 && k % (2 * w) == 0) w *= 2;
+	}
+	if (w <= 0 || k < 2 * w || k % w) return 0;
+	// small operands are latency-bound, not bandwidth-bound: one upload, one kernel, one download
+	const size_t min_bytes = (size_t) env_int("SPMM_B200_PIPELINE_MIN_KB", 8 << 10) << 10;
+	if ((size_t) h->c * k * sizeof(double) < min_bytes) return 0;
+	return w;
+}
+
+static int run_pipelined(spmm_b200* h, const double* x_host, double* y_host, int k, int ks,
+                         spmm_b200_bcast_fn bcast = nullptr, void* bcast_ctx = nullptr)
+{
+	const int S = k / ks;
+	const size_t nb = (size_t) h->c * k;
+	int rc = ensure(&h->d_B, &h->cap_B, nb);
+	if (rc) return rc;
+	if (h->b_layout == SPMM_B200_B_COLMAJOR) {
+		rc = ensure(&h->d_x, &h->cap_x, nb);
+		if (rc) return rc;
+	}
+	rc = ensure(&h->d_C, &h->cap_C, (size_t) h->m * k);
+	if (rc) return rc;
+	if (!h->s_up) CU_TRY(cudaStreamCreateWithFlags(&h->s_up, cudaStreamNonBlocking));
+	if (!h->s_down) CU_TRY(cudaStreamCreateWithFlags(&h->s_down, cudaStreamNonBlocking));
+	while (h->ev_slice.size() < (size_t) 3 * S) {
+		cudaEvent_t e;
+		CU_TRY(cudaEventCreate(&e));
+		h->ev_slice.push_back(e);
+	}
+	h->resident_k = 0;                       // d_B is about to hold slices, not the c x k operand
+	const size_t bslice = (size_t) h->c * ks, cslice = (size_t) h->m * ks;
+	for (int s = 0; s < S; s++) {
+		double* Bs = h->d_B + s * bslice;
+		if (h->b_layout == SPMM_B200_B_COLMAJOR) {
+			// columns [s*ks, (s+1)*ks) are contiguous in x: one H2D, then transpose to row-major c x ks
+			if (x_host)
+				CU_TRY(cudaMemcpyAsync(h->d_x + s * bslice, x_host + s * bslice, bslice * sizeof(double), cudaMemcpyHostToDevice, h->s_up));
+			if (bcast && bslice > 0 && bcast(bcast_ctx, h->d_x + s * bslice, bslice, h->s_up)) return SPMM_B200_ECOMM;
+			rc = spmm_b200_transpose_b_device(h, h->d_x + s * bslice, Bs, ks, h->s_up);
+			if (rc) return rc;
+		} else {
+			if (x_host)
+				CU_TRY(cudaMemcpy2DAsync(Bs, sizeof(double) * ks, x_host + (size_t) s * ks, sizeof(double) * k, sizeof(double) * ks,
+				                         (size_t) h->c, cudaMemcpyHostToDevice, h->s_up));
+			if (bcast && bslice > 0 && bcast(bcast_ctx, Bs, bslice, h->s_up)) return SPMM_B200_ECOMM;
+		}
+		CU_TRY(cudaEventRecord(h->ev_slice[3 * s], h->s_up));
+	}
+	for (int s = 0; s < S; s++) {
+		CU_TRY(cudaStreamWaitEvent(h->stream, h->ev_slice[3 * s], 0));
+		rc = run_between(h, h->d_B + s * bslice, h->d_C + s * cslice, ks, h->stream, h->ev_slice[3 * s + 1], h->ev_slice[3 * s + 2]);
+		if (rc) return rc;
+		if (y_host && h->m > 0) {
+			CU_TRY(cudaStreamWaitEvent(h->s_down, h->ev_slice[3 * s + 2], 0));
+			CU_TRY(cudaMemcpy2DAsync(y_host + (size_t) s * ks, sizeof(double) * k, h->d_C + s * cslice, sizeof(double) * ks,
+			                         sizeof(double) * ks, (size_t) h->m, cudaMemcpyDeviceToHost, h->s_down));
+		}
+	}
+	h->c_slices = S;
+	h->timed = true;
+	h->timed_slices = S;
+	CU_TRY(cudaStreamSynchronize(h->stream));
+	CU_TRY(cudaStreamSynchronize(h->s_down));
 	return SPMM_B200_OK;
 }
 
@@ -679,17 +791,34 @@ extern "C" int spmm_b200_run(spmm_b200_t* h, const double* x_host, double* y_hos
 {
 	if (!h || !x_host || k < 1 || (copy_back && !y_host)) return SPMM_B200_EINVAL;
 	CU_TRY(cudaSetDevice(h->device));
+	const int ks = slice_width(h, k);
+	if (ks > 0) return run_pipelined(h, x_host, copy_back ? y_host : nullptr, k, ks);
 	int rc = upload_b(h, x_host, k);
 	if (rc) return rc;
 	rc = ensure(&h->d_C, &h->cap_C, (size_t) h->m * k);
 	if (rc) return rc;
+	h->c_slices = 1;
 	rc = spmm_b200_run_device(h, h->d_B, h->d_C, k, h->stream);
 	if (rc) return rc;
-	if (copy_back && h->m > 0) {
-		CU_TRY(cudaMemcpyAsync(y_host, h->d_C, sizeof(double) * h->m * k, cudaMemcpyDeviceToHost, h->stream));
+	if (copy_back) {
+		rc = download_c(h, y_host, k, h->stream);
+		if (rc) return rc;
 	}
 	CU_TRY(cudaStreamSynchronize(h->stream));
 	return SPMM_B200_OK;
+}
+
+// Multi-GPU form of the hot call: the root rank holds x on the host, every rank gets the
+// replica through the caller's broadcast (ncclBroadcast / torch.distributed.broadcast on the stream
+// handed to it), slice by slice, so that upload, broadcast, kernel and download of C overlap.
+extern "C" int spmm_b200_run_replicated(spmm_b200_t* h, const double* x_host, double* y_host, int k, int copy_back,
+                                        spmm_b200_bcast_fn bcast, void* bcast_ctx)
+{
+	if (!h || k < 1 || (copy_back && !y_host) || (!x_host && !bcast)) return SPMM_B200_EINVAL;
+	CU_TRY(cudaSetDevice(h->device));
+	int ks = slice_width(h, k);
+	if (ks <= 0) ks = k;
+	return run_pipelined(h, x_host, copy_back ? y_host : nullptr, k, ks, bcast, bcast_ctx);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -835,6 +964,15 @@ extern "C" double spmm_b200_last_kernel_ms(const spmm_b200_t* h)
 {
 	if (!h || !h->timed) return -1.0;
 	float ms = 0.f;
+	if (h->timed_slices > 0) {               // k-sliced run: sum of the slices' kernel times
+		double sum = 0.0;
+		for (int s = 0; s < h->timed_slices; s++) {
+			if (cudaEventSynchronize(h->ev_slice[3 * s + 2]) != cudaSuccess) return -1.0;
+			if (cudaEventElapsedTime(&ms, h->ev_slice[3 * s + 1], h->ev_slice[3 * s + 2]) != cudaSuccess) return -1.0;
+			sum += ms;
+		}
+		return sum;
+	}
 	if (cudaEventSynchronize(h->ev1) != cudaSuccess) return -1.0;
 	if (cudaEventElapsedTime(&ms, h->ev0, h->ev1) != cudaSuccess) return -1.0;
 	return (double) ms;
@@ -869,6 +1007,7 @@ extern "C" const char* spmm_b200_strerror(int code)
 	case SPMM_B200_ENOMEM: return "out of memory";
 	case SPMM_B200_ERANGE: return "size exceeds the int32 index contract";
 	case SPMM_B200_ENOSUP: return "variant not supported for this input";
+	case SPMM_B200_ECOMM:  return "the caller's broadcast callback failed";
 	default:               return "unknown error";
 	}
 }

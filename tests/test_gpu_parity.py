@@ -223,3 +223,31 @@ def test_reference_harness_dropin(pkg):
     row = r.stderr.strip().splitlines()[-1].split(",")
     assert row[0] == "synthetic" and row[6] == "999475" and row[23].startswith("B200_CSR")
     assert float(row[25]) > 0          # gflops column
+
+
+@pytest.mark.parametrize("layout", ["col", "row"])
+def test_k_sliced_host_pipeline(pkg, L, layout, monkeypatch):
+    """spmm() with HOST buffers cuts k into 16-column slices (upload | kernel | download overlap,
+    DESIGN 5.3).  Forced on for a small matrix: same result as the oracle for every variant, for
+    copy_back=False + fetch_c, and the one-shot path still works on the same handle afterwards."""
+    monkeypatch.setenv("SPMM_B200_PIPELINE_MIN_KB", "0")
+    ia, ja, a = random_csr(3001, 2500, 9.0, seed=21, empty_frac=0.1, long_row=1200)
+    a = np.abs(a) + 0.01
+    m, c = 3001, 2500
+    for k in (32, 48, 128):
+        x = dense_b(c, k, 5)
+        y_ref = L.spmm_oracle(ia, ja, a, m, c, x, k)
+        xin = x if layout == "col" else np.ascontiguousarray(x.reshape(k, c).T).ravel()
+        lay = pkg.B_COLMAJOR if layout == "col" else pkg.B_ROWMAJOR
+        for v in variants(pkg):
+            mf = pkg.csr_to_format(ia, ja, a, m, c, len(ja), k, variant=v, b_layout=lay)
+            y = np.full(m * k, np.nan); mf.spmm(xin, y, k)
+            assert max_rel_err(y, y_ref) <= FP64_TOL, (k, v, layout)
+            assert mf.last_kernel_ms() > 0
+            y2 = np.full(m * k, np.nan); mf.spmm(xin, None, k, copy_back=False); mf.fetch_c(y2, k)
+            assert np.array_equal(y, y2)
+            monkeypatch.setenv("SPMM_B200_PIPELINE_COLS", "0")          # one-shot path on the same handle
+            y3 = np.full(m * k, np.nan); mf.spmm(xin, y3, k)
+            monkeypatch.delenv("SPMM_B200_PIPELINE_COLS")
+            assert max_rel_err(y3, y_ref) <= FP64_TOL
+            mf.close()
