@@ -147,16 +147,16 @@ static int pick_small_group(const spmm_b200* h)
 }
 
 template <int G, int V>
-static void launch_rowsplit_gv(const spmm_b200* h, const double* B, double* C, cudaStream_t s)
+static void launch_rowsplit_gv(const spmm_b200* h, const double* B, double* C, cudaStream_t s, int ldb = G * V, int ldc = G * V)
 {
 	// B-row gathers in flight per lane group; tuning knob, default from the ncu study in profiles/
 	static const int unroll = env_int("SPMM_B200_UNROLL", 4);
 	if (unroll >= 8 && G >= 8)
-		spmm_rowsplit_kernel<G, V, 8, THREADS><<<h->n_ctas, THREADS, 0, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, h->d_cta_rows);
+		spmm_rowsplit_kernel<G, V, 8, THREADS><<<h->n_ctas, THREADS, 0, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, h->d_cta_rows, ldb, ldc);
 	else if (unroll <= 2)
-		spmm_rowsplit_kernel<G, V, 2, THREADS><<<h->n_ctas, THREADS, 0, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, h->d_cta_rows);
+		spmm_rowsplit_kernel<G, V, 2, THREADS><<<h->n_ctas, THREADS, 0, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, h->d_cta_rows, ldb, ldc);
 	else
-		spmm_rowsplit_kernel<G, V, 4, THREADS><<<h->n_ctas, THREADS, 0, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, h->d_cta_rows);
+		spmm_rowsplit_kernel<G, V, 4, THREADS><<<h->n_ctas, THREADS, 0, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, h->d_cta_rows, ldb, ldc);
 }
 
 template <int K>
@@ -392,6 +392,26 @@ static int launch_spmm(spmm_b200* h, const double* B, double* C, int k, cudaStre
 	if ((h->variant == SPMM_B200_BCSR || h->variant == SPMM_B200_BCSR_FMA) && bcsr_supports_k(h->variant, k))
 		return launch_bcsr(h, B, C, k, s);
 	int n = 1;
+	// L2-aware k slicing (experiment knob): run the k columns as k/w launches on w-column slices of the
+	// same row-major B and C, so that the B rows a launch gathers (touched window x 8w bytes) stay in L2
+	const int w = env_int("SPMM_B200_KSLICE", 0);
+	if (w > 0 && w < k && k % w == 0 && (w == 8 || w == 16 || w == 32 || w == 64)) {
+		for (int off = 0; off < k; off += w) {
+			switch (w) {
+			case 8:  launch_rowsplit_gv<4, 2>(h, B + off, C + off, s, k, k); break;
+			case 16: launch_rowsplit_gv<8, 2>(h, B + off, C + off, s, k, k); break;
+			case 32: launch_rowsplit_gv<16, 2>(h, B + off, C + off, s, k, k); break;
+			default: launch_rowsplit_gv<32, 2>(h, B + off, C + off, s, k, k); break;
+			}
+		}
+		cudaError_t e = cudaGetLastError();
+		if (e != cudaSuccess) {
+			snprintf(g_cuda_err, sizeof(g_cuda_err), "sliced spmm launch (k=%d, w=%d): %s", k, w, cudaGetErrorString(e));
+			return SPMM_B200_ECUDA;
+		}
+		h->launches += k / w;
+		return k / w;
+	}
 	switch (k) {
 	case 1:   launch_smallk<1>(h, B, C, s); break;
 	case 2:   launch_smallk<2>(h, B, C, s); break;

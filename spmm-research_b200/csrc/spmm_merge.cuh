@@ -100,13 +100,13 @@ spmm_merge_kernel(const int32_t* __restrict__ ia, const int32_t* __restrict__ ja
 			const bool live = j + u < je;
 			const int jj = live ? j + u : je - 1;
 			vv[u] = live ? s_a[jj] : 0.0;
-			bb[u] = load_b<G, V>(B, s_ja[jj], lig);
+			bb[u] = load_b<G, V>(B, s_ja[jj], lig, G * V);
 		}
 		#pragma unroll
 		for (int u = 0; u < UNROLL; u++) {
 			if (j + u < je) {
 				while (j + u >= next_end) {      // rows that ended before this nonzero
-					store_c<G, V>(C, (size_t) (r0 + row), lig, acc);
+					store_c<G, V>(C, (size_t) (r0 + row), lig, acc, G * V);
 					#pragma unroll
 					for (int v = 0; v < V; v++) acc[v] = 0.0;
 					row++;
@@ -118,12 +118,12 @@ spmm_merge_kernel(const int32_t* __restrict__ ia, const int32_t* __restrict__ ja
 		}
 	}
 	for (; row < row_e; row++) {                 // row ends after the group's last nonzero
-		store_c<G, V>(C, (size_t) (r0 + row), lig, acc);
+		store_c<G, V>(C, (size_t) (r0 + row), lig, acc, G * V);
 		#pragma unroll
 		for (int v = 0; v < V; v++) acc[v] = 0.0;
 	}
 	// what is left belongs to tile-local row row_e, which ends in a later group or tile
-	store_c<G, V>(s_carry, (size_t) gid, lig, acc);
+	store_c<G, V>(s_carry, (size_t) gid, lig, acc, G * V);
 	if (lig == 0) s_crow[gid] = row_e;
 	__syncthreads();
 

@@ -29,11 +29,10 @@ template <int V> struct Frag { double v[V]; };
 // lane l holds columns {2l, 2l+1} (+ 2G for the second pair when V == 4), so every
 // load instruction of the group covers one contiguous span.
 template <int G, int V>
-__device__ __forceinline__ Frag<V> load_b(const double* __restrict__ B, int col, int lig)
+__device__ __forceinline__ Frag<V> load_b(const double* __restrict__ B, int col, int lig, int ldb)
 {
-	constexpr int K = G * V;
 	Frag<V> f;
-	const double* p = B + (size_t) col * K;
+	const double* p = B + (size_t) col * ldb;
 	if constexpr (V == 1) {
 		f.v[0] = __ldg(p + lig);
 	} else if constexpr (V == 2) {
@@ -49,10 +48,9 @@ __device__ __forceinline__ Frag<V> load_b(const double* __restrict__ B, int col,
 }
 
 template <int G, int V>
-__device__ __forceinline__ void store_c(double* __restrict__ C, size_t row, int lig, const double (&acc)[V])
+__device__ __forceinline__ void store_c(double* __restrict__ C, size_t row, int lig, const double (&acc)[V], int ldc)
 {
-	constexpr int K = G * V;
-	double* p = C + row * K;
+	double* p = C + row * ldc;
 	if constexpr (V == 1) {
 		p[lig] = acc[0];
 	} else if constexpr (V == 2) {
@@ -83,8 +81,10 @@ template <int G, int V, int UNROLL, int THREADS>
 __global__ void __launch_bounds__(THREADS)
 spmm_rowsplit_kernel(const int32_t* __restrict__ ia, const int32_t* __restrict__ ja, const double* __restrict__ a,
                      const double* __restrict__ B, double* __restrict__ C,
-                     const int32_t* __restrict__ cta_rows)
+                     const int32_t* __restrict__ cta_rows, int ldb, int ldc)
 {
+	// ldb / ldc = row strides of B and C in doubles (G*V for a whole operand; larger when the launch
+	// works on a column slice of a wider B / C, see launch_spmm's L2-aware k slicing)
 	constexpr int NG = THREADS / G;          // row groups per CTA
 	static_assert(G % UNROLL == 0 || UNROLL % G == 0, "UNROLL and G must nest");
 	constexpr int U = UNROLL < G ? UNROLL : G;
@@ -122,7 +122,7 @@ spmm_rowsplit_kernel(const int32_t* __restrict__ ia, const int32_t* __restrict__
 				}
 				#pragma unroll
 				for (int i = 0; i < U; i++)
-					if (u + i < rem) bb[i] = load_b<G, V>(B, cc[i], lig);
+					if (u + i < rem) bb[i] = load_b<G, V>(B, cc[i], lig, ldb);
 				#pragma unroll
 				for (int i = 0; i < U; i++) {
 					if (u + i < rem) {
@@ -133,7 +133,7 @@ spmm_rowsplit_kernel(const int32_t* __restrict__ ia, const int32_t* __restrict__
 			}
 			j += G;
 		}
-		if (live) store_c<G, V>(C, (size_t) row, lig, acc);
+		if (live) store_c<G, V>(C, (size_t) row, lig, acc, ldc);
 	}
 }
 
