@@ -66,7 +66,9 @@ enum {
 	SPMM_B200_ENOMEM  = -4,   /* device or host allocation failed                             */
 	SPMM_B200_ERANGE  = -5,   /* sizes overflow the int32 index contract (nnz, m, c < 2^31)  */
 	SPMM_B200_ENOSUP  = -6,   /* variant not applicable to this matrix / k                    */
-	SPMM_B200_ECOMM   = -7    /* the caller-supplied broadcast callback returned non-zero     */
+	SPMM_B200_ECOMM   = -7,   /* the caller-supplied broadcast callback returned non-zero     */
+	SPMM_B200_EIO     = -8,   /* a matrix file could not be opened / read                     */
+	SPMM_B200_EFORMAT = -9    /* a matrix file is malformed (the reference would exit(1))     */
 };
 
 /* ---- format construction: replaces csr_to_format() (spmv_kernel.h:29; call site spmv_bench.cpp:996).
@@ -151,6 +153,40 @@ int spmm_b200_partition_host(const int32_t *row_ptr, int64_t m, int64_t nnz, int
 int spmm_b200_coo_to_csr(const int32_t *R, const int32_t *C, const double *V, int64_t m, int64_t n, int64_t nnz,
                          int32_t *row_ptr, int32_t *col_idx, double *values, int sort_columns, int transpose,
                          int device);
+
+/* ---- on-disk formats (host parsing; the arrays then go through spmm_b200_coo_to_csr / spmm_b200_create).
+ * Output arrays are allocated by the library (64-byte aligned); release them with spmm_b200_free.
+ *
+ * spmm_b200_read_mtx replaces mtx_read(file, expand_symmetry, pattern_dummy_vals = 1)
+ * (lib/storage_formats/matrix_market/matrix_market.c:249-322) together with the value conversion the
+ * harness applies to its result (spmv_bench.cpp:723-763): Matrix Market "coordinate" files with field
+ * real | integer | complex | pattern and symmetry general | symmetric | Hermitian | skew-symmetric ->
+ * 0-based COO with fp64 values (integer -> (double), complex -> |z|, pattern -> 1.0); with
+ * expand_symmetry the mirrored off-diagonal entries follow the file's entries in file order, negated for
+ * skew-symmetric.  Indices and values are bit-identical with the reference's arrays (same strtol/strtod).
+ * field16 (may be NULL) receives the field name.  "array" files: SPMM_B200_ENOSUP. */
+int spmm_b200_read_mtx(const char *path, int expand_symmetry, int64_t *m, int64_t *n, int64_t *nnz,
+                       int32_t **R, int32_t **C, double **V, char *field16);
+
+/* spmm_b200_read_smtx replaces smtx_read (lib/storage_formats/dlcm_matrices/dlcm_matrix.c:257-324,
+ * dlcm_matrix_gen.c:54-118; call site spmv_bench.cpp:682-695): DLMC ".smtx" text = "m, k, nnz" / m+1 row
+ * offsets / nnz column indices -> CSR.  The file holds no values; the reference draws them from rand()
+ * seeded with time(NULL) (not reproducible), here values[j] = uniform [-1, 1) from splitmix64(seed, j). */
+int spmm_b200_read_smtx(const char *path, uint64_t seed, int64_t *m, int64_t *n, int64_t *nnz,
+                        int32_t **row_ptr, int32_t **col_ind, double **values);
+void spmm_b200_free(void *p);
+
+/* ---- accuracy check: replaces CheckAccuracy() (spmv_bench.cpp:121-206; call site :480).  Computes the
+ * gold result of y = A*x on the device in double-double arithmetic (fp64 products as in the reference,
+ * summed with ~106 significant bits -- the reference uses __float128 with Kahan compensation) and the reference's
+ * error statistics of y_host against it.  x_host: c*k (layout of the handle), y_host: m_local*k row-major.
+ * stats[0] = max relative difference over entries with gold > 1e-10 (the reference's "Test failed" figure),
+ * [1] mae, [2] max_ae, [3] mse, [4] mape, [5] smape, [6] lnQ_error, [7] mlare, [8] gmare
+ * (lib/array_metrics.c), [9] = 1.0 if stats[0] <= 1e-10 else 0.0.  y_gold_host (may be NULL) receives the
+ * gold result rounded to fp64. */
+enum { SPMM_B200_NSTATS = 10 };
+int spmm_b200_check_accuracy(spmm_b200_t *h, const double *x_host, const double *y_host, int k,
+                             double *stats, double *y_gold_host);
 
 /* ---- introspection */
 int64_t spmm_b200_rows(const spmm_b200_t *h);         /* rows held by this handle (shard)     */

@@ -116,6 +116,65 @@ def coo_to_csr_ref(R, Cc, V, m, n, sort_columns=1, transpose=0):
     return _coo_call(coo_ref().coo_to_csr_csr_converter_double, R, Cc, V, m, n, sort_columns, transpose)
 
 
+class _MtxHead(C.Structure):
+    # struct Matrix_Market (lib/storage_formats/matrix_market/matrix_market.h:29-46); struct DLCM_Matrix is laid out alike
+    _fields_ = [("filename", C.c_char_p), ("format", C.c_char_p), ("field", C.c_char_p),
+                ("symmetric", C.c_int), ("skew_symmetric", C.c_int),
+                ("m", C.c_long), ("k", C.c_long), ("nnz", C.c_long), ("nnz_sym", C.c_long),
+                ("R", C.POINTER(C.c_int)), ("C", C.POINTER(C.c_int)), ("V", C.c_void_p)]
+
+
+def have_io_ref():
+    return os.path.exists(os.path.join(HERE, "_ref", "libio_ref.so"))
+
+
+def io_ref():
+    lib = _load(os.path.join(HERE, "_ref", "libio_ref.so"))
+    if not hasattr(lib, "_typed"):
+        lib.mtx_read.argtypes = [C.c_char_p, C.c_long, C.c_long]
+        lib.mtx_read.restype = C.POINTER(_MtxHead)
+        lib.smtx_read.argtypes = [C.c_char_p, C.c_long, C.c_long]
+        lib.smtx_read.restype = C.POINTER(_MtxHead)
+        lib._typed = True
+    return lib
+
+
+def mtx_read_ref(path):
+    """The reference's mtx_read(file, expand_symmetry=1, pattern_dummy_vals=1) followed by the value conversion of
+    spmv_bench.cpp:730-763.  Returns (m, k, R, C, V as float64, field)."""
+    h = io_ref().mtx_read(path.encode(), 1, 1).contents
+    nnz, field = int(h.nnz), h.field.decode()
+    R = np.ctypeslib.as_array(h.R, shape=(max(nnz, 1),))[:nnz].astype(np.int32, copy=True)
+    Cc = np.ctypeslib.as_array(h.C, shape=(max(nnz, 1),))[:nnz].astype(np.int32, copy=True)
+    if field == "integer":
+        V = np.ctypeslib.as_array(C.cast(h.V, C.POINTER(C.c_int)), shape=(max(nnz, 1),))[:nnz].astype(np.float64)
+    elif field == "complex":
+        z = np.ctypeslib.as_array(C.cast(h.V, C.POINTER(C.c_double)), shape=(2 * max(nnz, 1),))[:2 * nnz]
+        V = np.hypot(z[0::2], z[1::2])          # cabs()
+    else:
+        V = np.ctypeslib.as_array(C.cast(h.V, C.POINTER(C.c_double)), shape=(max(nnz, 1),))[:nnz].astype(np.float64, copy=True)
+    return int(h.m), int(h.k), R, Cc, V, field
+
+
+def smtx_read_ref(path):
+    """The reference's smtx_read: (m, k, row_ptr, col_ind).  Its values are time-seeded rand(): not comparable."""
+    h = io_ref().smtx_read(path.encode(), 0, 0).contents
+    m, nnz = int(h.m), int(h.nnz)
+    ia = np.ctypeslib.as_array(h.R, shape=(m + 1,)).astype(np.int32, copy=True)
+    ja = np.ctypeslib.as_array(h.C, shape=(max(nnz, 1),))[:nnz].astype(np.int32, copy=True)
+    return m, int(h.k), ia, ja
+
+
+def check_accuracy_oracle(ia, ja, a, m, c, x, y, k):
+    lib = oracle()
+    lib.oracle_check_accuracy.argtypes = [_i32p, _i32p, _f64p, C.c_long, C.c_long, _f64p, _f64p, C.c_int, _f64p, _f64p]
+    lib.oracle_check_accuracy.restype = None
+    stats = np.zeros(10)
+    gold = np.zeros(max(m * k, 1))
+    lib.oracle_check_accuracy(ia, ja, a, m, c, x, y, k, stats, gold)
+    return stats, gold[:m * k]
+
+
 class _CsrHead(C.Structure):
     # leading fields of struct csr_matrix (artificial_matrix_generation.h:10-17)
     _fields_ = [("row_ptr", C.POINTER(C.c_int)), ("col_ind", C.POINTER(C.c_int)),

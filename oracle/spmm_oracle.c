@@ -283,3 +283,78 @@ void oracle_coo_to_csr(const int32_t *R, const int32_t *C, const double *V, long
 	free(cursor);
 	free(ent);
 }
+
+/* ---------------------------------------------------------------------------
+ * a10 / N1: CheckAccuracy -- fp128 Kahan gold + the error metrics the harness prints
+ * ref: benchmark_code/CPU/AMD/spmv_code_bench/spmv_bench.cpp:121-206 (gold :141-160,
+ *      maxDiff :163-188, metrics :189-202) and lib/array_metrics.c (mae, max_ae, mse,
+ *      mare->mape, smare->smape, lnQ_error, mlare, gmare: *_process / *_output).
+ *
+ *   gold[i*k+n]: sum in __float128 with Kahan compensation over val = a[j]*x[n*c+ja[j]]
+ *                (csr_a_ref and x_ref are double*, so the product itself is rounded to fp64);
+ *   stats[0] = max over entries with gold > eps of |gold - y| / |gold|   (eps = 1e-10, fp64 build)
+ *   stats[1..8] = mae, max_ae, mse, mape, smape, lnQ_error, mlare, gmare over
+ *                 a = (double) gold, f = y;  stats[9] = (stats[0] <= eps).
+ * y_gold (may be NULL) receives (double) gold.
+ * ------------------------------------------------------------------------- */
+#include <math.h>
+#include <float.h>
+void oracle_check_accuracy(const int32_t *ia, const int32_t *ja, const double *a, long m, long c,
+                           const double *x, const double *y, int k, double *stats, double *y_gold)
+{
+	const long N = m * (long) k;
+	const __float128 eps = 1e-10;
+	double *gold = (double *) malloc(sizeof(double) * (N > 0 ? N : 1));
+	__float128 max_diff = 0;
+	#pragma omp parallel
+	{
+		__float128 local_max = 0;
+		#pragma omp for
+		for (long i = 0; i < m; i++) {
+			for (long n = 0; n < k; n++) {
+				__float128 sum = 0, comp = 0, val, tmp;
+				for (long j = ia[i]; j < ia[i + 1]; j++) {
+					val = a[j] * x[n * c + ja[j]] - comp;   /* fp64 product (both operands are double*, :152), fp128 from there */
+					tmp = sum + val;
+					comp = (tmp - sum) - val;
+					sum = tmp;
+				}
+				gold[i * k + n] = (double) sum;
+				if (sum > eps) {
+					__float128 d = sum - (__float128) y[i * k + n];
+					if (d < 0) d = -d;
+					d = d / (sum < 0 ? -sum : sum);
+					if (d > local_max) local_max = d;
+				}
+			}
+		}
+		#pragma omp critical
+		if (local_max > max_diff) max_diff = local_max;
+	}
+	double s_ae = 0, max_ae = 0, s_se = 0, s_are = 0, s_sare = 0, s_lnq = 0;
+	for (long i = 0; i < N; i++) {
+		const double g = gold[i], f = y[i];
+		const double ae = fabs(g - f);
+		s_ae += ae;
+		if (ae > max_ae) max_ae = ae;
+		s_se += (g - f) * (g - f);
+		s_are += ae / fmax(fabs(g), DBL_EPSILON);
+		s_sare += ae / fmax(fabs(g) + fabs(f), DBL_EPSILON);
+		s_lnq += log10(fmax(fabs(f), DBL_EPSILON)) - log10(fmax(fabs(g), DBL_EPSILON));
+	}
+	stats[0] = (double) max_diff;
+	stats[1] = s_ae / N;
+	stats[2] = max_ae;
+	stats[3] = s_se / N;
+	stats[4] = 100.0 * (s_are / N);
+	stats[5] = 100.0 * (s_sare / N);
+	stats[6] = s_lnq / N;
+	{
+		long double e = stats[6];
+		stats[7] = (double) log10l(fabsl(powl(10, e) - 1));
+	}
+	stats[8] = pow(10, stats[7]);
+	stats[9] = (max_diff <= eps) ? 1.0 : 0.0;
+	if (y_gold) memcpy(y_gold, gold, sizeof(double) * N);
+	free(gold);
+}

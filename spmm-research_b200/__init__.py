@@ -16,7 +16,7 @@ import os
 
 import numpy as np
 
-__all__ = ["csr_to_format", "coo_to_csr", "MatrixFormat", "partition", "shard_slices", "statistics_print_labels", "load_library",
+__all__ = ["csr_to_format", "coo_to_csr", "read_mtx", "read_smtx", "MatrixFormat", "partition", "shard_slices", "statistics_print_labels", "load_library",
            "SpmmB200Error", "ROWSPLIT", "MERGE", "BCSR", "AUTO", "BCSR_FMA", "B_COLMAJOR", "B_ROWMAJOR",
            "PART_ROWS", "PART_NNZ", "PART_MERGE", "LIB_PATH", "EXPORTS"]
 
@@ -35,7 +35,7 @@ EXPORTS = [
     "spmm_b200_transpose_b_device", "spmm_b200_partition", "spmm_b200_partition_host", "spmm_b200_coo_to_csr", "spmm_b200_rows", "spmm_b200_nnz",
     "spmm_b200_variant", "spmm_b200_bcsr_blocks", "spmm_b200_last_kernel_ms", "spmm_b200_launch_count", "spmm_b200_stats",
     "spmm_b200_stats_labels", "spmm_b200_destroy", "spmm_b200_strerror", "spmm_b200_last_cuda_error",
-    "spmm_b200_device_count",
+    "spmm_b200_device_count", "spmm_b200_read_mtx", "spmm_b200_read_smtx", "spmm_b200_free", "spmm_b200_check_accuracy",
 ]
 
 _lib = None
@@ -92,6 +92,11 @@ def load_library():
     lib.spmm_b200_strerror.argtypes = [_int]; lib.spmm_b200_strerror.restype = C.c_char_p
     lib.spmm_b200_last_cuda_error.restype = C.c_char_p
     lib.spmm_b200_device_count.restype = _int
+    _pp = C.POINTER(_vp)
+    lib.spmm_b200_read_mtx.argtypes = [C.c_char_p, _int, C.POINTER(_i64), C.POINTER(_i64), C.POINTER(_i64), _pp, _pp, _pp, C.c_char_p]
+    lib.spmm_b200_read_smtx.argtypes = [C.c_char_p, C.c_uint64, C.POINTER(_i64), C.POINTER(_i64), C.POINTER(_i64), _pp, _pp, _pp]
+    lib.spmm_b200_free.argtypes = [_vp]; lib.spmm_b200_free.restype = None
+    lib.spmm_b200_check_accuracy.argtypes = [_vp, _vp, _vp, _int, _vp, _vp]
     _lib = lib
     return lib
 
@@ -158,6 +163,20 @@ class MatrixFormat:
         if err:
             raise err[0]
         _check(rc, "spmm_replicated")
+
+    ACCURACY_LABELS = ("max_rel_diff", "mae", "max_ae", "mse", "mape", "smape", "lnQ_error", "mlare", "gmare", "passed")
+
+    def check_accuracy(self, x, y, k, return_gold=False):
+        """Mirror of CheckAccuracy() (spmv_bench.cpp:121-206): gold y = A*x on the device in
+        double-double and the reference's error metrics of y against it -> dict (+ gold)."""
+        k = int(k)
+        stats = np.zeros(10)
+        gold = np.zeros(max(self.m * k, 1)) if return_gold else None
+        _check(load_library().spmm_b200_check_accuracy(self._h, _host(x, np.float64, "x"), _host(y, np.float64, "y"), k,
+                                                       stats.ctypes.data, gold.ctypes.data if return_gold else None),
+               "check_accuracy")
+        out = dict(zip(self.ACCURACY_LABELS, stats.tolist()))
+        return (out, gold[: self.m * k]) if return_gold else out
 
     def set_b(self, x, k):
         _check(load_library().spmm_b200_set_b(self._h, _host(x, np.float64, "x"), int(k)), "set_b")
@@ -269,6 +288,37 @@ def coo_to_csr(R, C, V, m, n, nnz, sort_columns=1, transpose=0, device=0):
         values.ctypes.data if (values is not None and nnz > 0) else None, int(sort_columns), int(transpose), device),
         "coo_to_csr")
     return row_ptr, col_idx, values
+
+
+def _take(ptr, n, dtype):
+    """Copy a library-owned array into numpy and release it with spmm_b200_free."""
+    n = int(n)
+    ctype = {np.int32: C.c_int32, np.float64: C.c_double}[dtype]
+    out = np.ctypeslib.as_array(C.cast(ptr, C.POINTER(ctype)), shape=(max(n, 1),))[:n].astype(dtype, copy=True)
+    load_library().spmm_b200_free(ptr)
+    return out
+
+
+def read_mtx(path, expand_symmetry=1):
+    """Mirror of mtx_read(file, expand_symmetry, 1) + the harness's value conversion
+    (matrix_market.c:249-322, spmv_bench.cpp:723-763).  Returns (m, n, R, C, V, field): 0-based COO, fp64 values."""
+    m, n, nnz = _i64(), _i64(), _i64()
+    R, Cc, V = _vp(), _vp(), _vp()
+    field = C.create_string_buffer(16)
+    _check(load_library().spmm_b200_read_mtx(os.fsencode(path), int(expand_symmetry), C.byref(m), C.byref(n), C.byref(nnz),
+                                             C.byref(R), C.byref(Cc), C.byref(V), field), f"read_mtx({path})")
+    return (m.value, n.value, _take(R, nnz.value, np.int32), _take(Cc, nnz.value, np.int32), _take(V, nnz.value, np.float64),
+            field.value.decode())
+
+
+def read_smtx(path, seed=0):
+    """Mirror of smtx_read (dlcm_matrix.c:257-324): DLMC .smtx -> (m, n, row_ptr, col_ind, values); the file has no
+    values, they are uniform [-1, 1) from `seed` (the reference seeds rand() with time(NULL))."""
+    m, n, nnz = _i64(), _i64(), _i64()
+    ia, ja, a = _vp(), _vp(), _vp()
+    _check(load_library().spmm_b200_read_smtx(os.fsencode(path), int(seed), C.byref(m), C.byref(n), C.byref(nnz),
+                                              C.byref(ia), C.byref(ja), C.byref(a)), f"read_smtx({path})")
+    return m.value, n.value, _take(ia, m.value + 1, np.int32), _take(ja, nnz.value, np.int32), _take(a, nnz.value, np.float64)
 
 
 def statistics_print_labels(buf_n=512):

@@ -12,11 +12,13 @@
 #include "scan.cuh"
 #include "spmm_bcsr.cuh"
 #include "coo_to_csr.cuh"
+#include "check_accuracy.cuh"
 
 #include <cuda_runtime.h>
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <math.h>
 #include <vector>
 #include <algorithm>
 
@@ -971,6 +973,55 @@ extern "C" int spmm_b200_coo_to_csr(const int32_t* R, const int32_t* C, const do
 }
 
 // ------------------------------------------------------------------------------------------
+// accuracy check (CheckAccuracy twin): gold SpMM in double-double + the reference's error metrics
+// ------------------------------------------------------------------------------------------
+
+extern "C" int spmm_b200_check_accuracy(spmm_b200_t* h, const double* x_host, const double* y_host, int k,
+                                        double* stats, double* y_gold_host)
+{
+	if (!h || !x_host || !y_host || !stats || k < 1) return SPMM_B200_EINVAL;
+	CU_TRY(cudaSetDevice(h->device));
+	int rc = upload_b(h, x_host, k);             // row-major c x k on the device
+	if (rc) return rc;
+	const int64_t n = h->m * (int64_t) k;
+	DevBuf d_gold, d_test, d_part;
+	const int nblocks = (int) std::max<int64_t>(1, std::min<int64_t>((int64_t) h->sm_count * 4, (n + 255) / 256));
+	CU_TRY(cudaMalloc(&d_gold.p, sizeof(double) * std::max<int64_t>(n, 1)));
+	CU_TRY(cudaMalloc(&d_test.p, sizeof(double) * std::max<int64_t>(n, 1)));
+	CU_TRY(cudaMalloc(&d_part.p, sizeof(double) * ACC_NPART * nblocks));
+	std::vector<double> part((size_t) ACC_NPART * nblocks, 0.0);
+	if (n > 0) {
+		CU_TRY(cudaMemcpyAsync(d_test.p, y_host, sizeof(double) * n, cudaMemcpyHostToDevice, h->stream));
+		gold_spmm_kernel<<<(unsigned) ((n + 255) / 256), 256, 0, h->stream>>>(h->d_ia, h->d_ja, h->d_a, h->d_B, d_gold.as<double>(), h->m, k);
+		accuracy_stats_kernel<256><<<nblocks, 256, 0, h->stream>>>(d_gold.as<double>(), d_test.as<double>(), n, 1e-10, d_part.as<double>());
+		h->launches += 2;
+		CU_TRY(cudaGetLastError());
+		CU_TRY(cudaMemcpyAsync(part.data(), d_part.p, sizeof(double) * part.size(), cudaMemcpyDeviceToHost, h->stream));
+		if (y_gold_host) CU_TRY(cudaMemcpyAsync(y_gold_host, d_gold.p, sizeof(double) * n, cudaMemcpyDeviceToHost, h->stream));
+	}
+	CU_TRY(cudaStreamSynchronize(h->stream));
+	double acc[ACC_NPART] = {0, 0, 0, 0, 0, 0, 0};
+	for (int b = 0; b < nblocks; b++)
+		for (int i = 0; i < ACC_NPART; i++) {
+			const double v = part[(size_t) b * ACC_NPART + i];
+			acc[i] = (i == 0 || i == 2) ? std::max(acc[i], v) : acc[i] + v;
+		}
+	const double N = (double) n;
+	stats[0] = acc[0];
+	stats[1] = acc[1] / N;                        // mae        (array_metrics.c ARRAY_METRICS_mae_output)
+	stats[2] = acc[2];                            // max_ae
+	stats[3] = acc[3] / N;                        // mse
+	stats[4] = 100.0 * (acc[4] / N);              // mape = 100 * mare
+	stats[5] = 100.0 * (acc[5] / N);              // smape = 100 * smare
+	stats[6] = acc[6] / N;                        // lnQ_error
+	const long double e = stats[6];               // ARRAY_METRICS_mlare_output: extended precision for the power
+	stats[7] = (double) log10l(fabsl(powl(10, e) - 1));
+	stats[8] = pow(10, stats[7]);                 // gmare
+	stats[9] = (acc[0] <= 1e-10) ? 1.0 : 0.0;
+	return SPMM_B200_OK;
+}
+
+// ------------------------------------------------------------------------------------------
 // introspection
 // ------------------------------------------------------------------------------------------
 
@@ -1028,6 +1079,8 @@ extern "C" const char* spmm_b200_strerror(int code)
 	case SPMM_B200_ERANGE: return "size exceeds the int32 index contract";
 	case SPMM_B200_ENOSUP: return "variant not supported for this input";
 	case SPMM_B200_ECOMM:  return "the caller's broadcast callback failed";
+	case SPMM_B200_EIO:    return "cannot open or read the matrix file";
+	case SPMM_B200_EFORMAT: return "malformed matrix file";
 	default:               return "unknown error";
 	}
 }
