@@ -984,16 +984,17 @@ extern "C" int spmm_b200_check_accuracy(spmm_b200_t* h, const double* x_host, co
 	int rc = upload_b(h, x_host, k);             // row-major c x k on the device
 	if (rc) return rc;
 	const int64_t n = h->m * (int64_t) k;
-	DevBuf d_gold, d_test, d_part;
+	DevBuf d_gold, d_lo, d_test, d_part;
 	const int nblocks = (int) std::max<int64_t>(1, std::min<int64_t>((int64_t) h->sm_count * 4, (n + 255) / 256));
 	CU_TRY(cudaMalloc(&d_gold.p, sizeof(double) * std::max<int64_t>(n, 1)));
+	CU_TRY(cudaMalloc(&d_lo.p, sizeof(double) * std::max<int64_t>(n, 1)));
 	CU_TRY(cudaMalloc(&d_test.p, sizeof(double) * std::max<int64_t>(n, 1)));
 	CU_TRY(cudaMalloc(&d_part.p, sizeof(double) * ACC_NPART * nblocks));
 	std::vector<double> part((size_t) ACC_NPART * nblocks, 0.0);
 	if (n > 0) {
 		CU_TRY(cudaMemcpyAsync(d_test.p, y_host, sizeof(double) * n, cudaMemcpyHostToDevice, h->stream));
-		gold_spmm_kernel<<<(unsigned) ((n + 255) / 256), 256, 0, h->stream>>>(h->d_ia, h->d_ja, h->d_a, h->d_B, d_gold.as<double>(), h->m, k);
-		accuracy_stats_kernel<256><<<nblocks, 256, 0, h->stream>>>(d_gold.as<double>(), d_test.as<double>(), n, 1e-10, d_part.as<double>());
+		gold_spmm_kernel<<<(unsigned) ((n + 255) / 256), 256, 0, h->stream>>>(h->d_ia, h->d_ja, h->d_a, h->d_B, d_gold.as<double>(), d_lo.as<double>(), h->m, k);
+		accuracy_stats_kernel<256><<<nblocks, 256, 0, h->stream>>>(d_gold.as<double>(), d_lo.as<double>(), d_test.as<double>(), n, 1e-10, d_part.as<double>());
 		h->launches += 2;
 		CU_TRY(cudaGetLastError());
 		CU_TRY(cudaMemcpyAsync(part.data(), d_part.p, sizeof(double) * part.size(), cudaMemcpyDeviceToHost, h->stream));
