@@ -56,6 +56,11 @@ struct spmm_b200 {
 	// row-split work list
 	int32_t* d_cta_rows = nullptr;
 	int n_ctas = 0;
+	// row-padded copy of A for the vectorised row-split kernel (rows padded to multiples of 4 entries)
+	int32_t* d_iap = nullptr;
+	int32_t* d_jap = nullptr;
+	double* d_ap = nullptr;
+	int64_t nnz_pad = 0;
 	// merge-path work list
 	MergePlan merge;
 	// blocked CSR (8x1)
@@ -140,6 +145,37 @@ static int build_rowsplit_plan(spmm_b200* h)
 	return SPMM_B200_OK;
 }
 
+// Row-padded copy of A for spmm_rowsplit_vec_kernel: iap = exclusive scan of the padded row lengths.
+static int build_padded_plan(spmm_b200* h)
+{
+	if (h->d_iap || h->m == 0) return SPMM_B200_OK;
+	if (h->nnz + 3 * h->m >= INT32_MAX) return SPMM_B200_ENOSUP;
+	const int m = (int) h->m;
+	int32_t* d_tmp = nullptr;
+	CU_TRY(cudaMalloc(&h->d_iap, sizeof(int32_t) * ((size_t) m + 1)));
+	CU_TRY(cudaMalloc(&d_tmp, sizeof(int32_t) * scan_tmp_elems(m + 1)));
+	pad_len_kernel<<<(m + 1 + 255) / 256, 256, 0, h->stream>>>(h->d_ia, m, h->d_iap);
+	h->launches += 1 + exclusive_scan_i32(h->d_iap, (int64_t) m + 1, d_tmp, h->stream);
+	int32_t total = 0;
+	CU_TRY(cudaMemcpyAsync(&total, h->d_iap + m, sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
+	CU_TRY(cudaStreamSynchronize(h->stream));
+	cudaFree(d_tmp);
+	h->nnz_pad = total;
+	CU_TRY(cudaMalloc(&h->d_jap, sizeof(int32_t) * std::max<size_t>((size_t) total, 4)));
+	CU_TRY(cudaMalloc(&h->d_ap, sizeof(double) * std::max<size_t>((size_t) total, 4)));
+	pad_fill_kernel<<<(unsigned) (((int64_t) m * 32 + 255) / 256), 256, 0, h->stream>>>(h->d_ia, h->d_iap, h->d_ja, h->d_a, m, h->d_jap, h->d_ap);
+	h->launches++;
+	CU_TRY(cudaGetLastError());
+	CU_TRY(cudaStreamSynchronize(h->stream));
+	return SPMM_B200_OK;
+}
+
+template <int G, int V>
+static void launch_rowsplit_vec(const spmm_b200* h, const double* B, double* C, cudaStream_t s, int ldb = G * V, int ldc = G * V)
+{
+	spmm_rowsplit_vec_kernel<G, V, THREADS><<<h->n_ctas, THREADS, 0, s>>>(h->d_ia, h->d_iap, h->d_jap, h->d_ap, B, C, h->d_cta_rows, ldb, ldc);
+}
+
 static int pick_small_group(const spmm_b200* h)
 {
 	const double avg = h->m > 0 ? (double) h->nnz / (double) h->m : 1.0;
@@ -201,8 +237,8 @@ struct MergeLaunch {
 	case 4:   WHAT(2, 2, 16); break;                               \
 	case 8:   WHAT(4, 2, 32); break;                               \
 	case 16:  WHAT(8, 2, 32); break;                               \
-	case 32:  WHAT(16, 2, 64); break;                              \
-	case 64:  WHAT(32, 2, 128); break;                             \
+	case 32:  WHAT(8, 4, 64); break;                               \
+	case 64:  WHAT(16, 4, 128); break;                             \
 	case 128: WHAT(32, 4, 128); break;                             \
 	default: break;                                                \
 	}
@@ -414,14 +450,52 @@ static int launch_spmm(spmm_b200* h, const double* B, double* C, int k, cudaStre
 		h->launches += k / w;
 		return k / w;
 	}
+	const int vec = env_int("SPMM_B200_VEC", 0);
+	if (vec && h->d_iap && (k == 16 || k == 32 || k == 64 || k == 128) && ((uintptr_t) B % 16) == 0) {
+		switch (k) {
+		case 16:  if (vec == 2) launch_rowsplit_vec<8, 2>(h, B, C, s); else launch_rowsplit_vec<4, 4>(h, B, C, s); break;
+		case 32:  if (vec == 2) launch_rowsplit_vec<16, 2>(h, B, C, s); else launch_rowsplit_vec<8, 4>(h, B, C, s); break;
+		case 64:  if (vec == 2) launch_rowsplit_vec<32, 2>(h, B, C, s); else launch_rowsplit_vec<16, 4>(h, B, C, s); break;
+		default:  launch_rowsplit_vec<32, 4>(h, B, C, s); break;
+		}
+		cudaError_t e = cudaGetLastError();
+		if (e != cudaSuccess) {
+			snprintf(g_cuda_err, sizeof(g_cuda_err), "vec spmm launch (k=%d): %s", k, cudaGetErrorString(e));
+			return SPMM_B200_ECUDA;
+		}
+		h->launches += 1;
+		return 1;
+	}
+	// experiment knob: lane-group shape "GxVxU" (G lanes per row, V columns per lane, U gathers in flight)
+	const int gvu = env_int("SPMM_B200_GVU", 0);       // e.g. 842 = G 8, V 4, U 2;  1682 = G 16, V 8, U 2
+	if (gvu > 0) {
+		const int G = gvu / 100, V = (gvu / 10) % 10, U = gvu % 10;
+		bool ok = true;
+#define TRY_GVU(g, v, u) else if (G == g && V == v && U == u && k == g * v) \
+		spmm_rowsplit_kernel<g, v, u, THREADS><<<h->n_ctas, THREADS, 0, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, h->d_cta_rows, k, k)
+		if (false) {}
+		TRY_GVU(8, 4, 2); TRY_GVU(8, 4, 4); TRY_GVU(8, 4, 8);
+		TRY_GVU(8, 8, 2); TRY_GVU(8, 8, 4); TRY_GVU(16, 4, 2); TRY_GVU(16, 4, 4);
+		TRY_GVU(16, 8, 2); TRY_GVU(16, 8, 4); TRY_GVU(32, 4, 2); TRY_GVU(32, 4, 4);
+		TRY_GVU(8, 2, 4); TRY_GVU(8, 2, 8); TRY_GVU(4, 4, 4);
+		else ok = false;
+#undef TRY_GVU
+		if (ok) {
+			h->launches += 1;
+			return cudaGetLastError() == cudaSuccess ? 1 : SPMM_B200_ECUDA;
+		}
+	}
 	switch (k) {
 	case 1:   launch_smallk<1>(h, B, C, s); break;
 	case 2:   launch_smallk<2>(h, B, C, s); break;
 	case 4:   launch_smallk<4>(h, B, C, s); break;
+	// lane-group shapes from the sweep in profiles/r1_gvu_probe.md: V = 4 columns per lane (two 16-byte loads)
+	// makes a group of 8 lanes cover one 128-byte line per load and halves the shuffle traffic per nonzero
+	// (cfg2: k=32 0.935 -> 0.786 ms, k=64 1.563 -> 1.336 ms); V = 8 costs too many registers
 	case 8:   launch_rowsplit_gv<4, 2>(h, B, C, s); break;
 	case 16:  launch_rowsplit_gv<8, 2>(h, B, C, s); break;
-	case 32:  launch_rowsplit_gv<16, 2>(h, B, C, s); break;
-	case 64:  launch_rowsplit_gv<32, 2>(h, B, C, s); break;
+	case 32:  launch_rowsplit_gv<8, 4>(h, B, C, s); break;
+	case 64:  launch_rowsplit_gv<16, 4>(h, B, C, s); break;
 	case 128: launch_rowsplit_gv<32, 4>(h, B, C, s); break;
 	default:
 		spmm_rowsplit_generic_kernel<THREADS><<<h->n_ctas, THREADS, 0, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, h->d_cta_rows, k);
@@ -490,6 +564,10 @@ static int create_from_slice(spmm_b200_t** out, const int32_t* row_ptr_slice, co
 	}
 	int rc = build_rowsplit_plan(h);        // always: the fallback for k without a specialised instantiation
 	if (rc) return rc;
+	if (env_int("SPMM_B200_VEC", 0) && k >= 16) {
+		rc = build_padded_plan(h);
+		if (rc && rc != SPMM_B200_ENOSUP) return rc;
+	}
 	if (variant == SPMM_B200_AUTO && h->variant == SPMM_B200_ROWSPLIT && k >= 32 && bcsr_supports_k(SPMM_B200_BCSR, k)
 	    && m_local >= 8 && nnz_local > 0) {
 		// "tensor cores only where dense blocks make it a genuine contraction": probe the 8x1 block
@@ -577,6 +655,7 @@ extern "C" void spmm_b200_destroy(spmm_b200_t* h)
 	for (void* p : h->pinned) cudaHostUnregister(p);
 	cudaFree(h->d_ia); cudaFree(h->d_ja); cudaFree(h->d_a);
 	cudaFree(h->d_cta_rows);
+	cudaFree(h->d_iap); cudaFree(h->d_jap); cudaFree(h->d_ap);
 	cudaFree(h->merge.d_tile); cudaFree(h->merge.d_carry); cudaFree(h->merge.d_carry_row);
 	cudaFree(h->bcsr.d_brow); cudaFree(h->bcsr.d_bcol); cudaFree(h->bcsr.d_bval); cudaFree(h->bcsr.d_bmask);
 	cudaFree(h->d_x); cudaFree(h->d_B); cudaFree(h->d_C);

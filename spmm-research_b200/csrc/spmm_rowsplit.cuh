@@ -35,14 +35,15 @@ __device__ __forceinline__ Frag<V> load_b(const double* __restrict__ B, int col,
 	const double* p = B + (size_t) col * ldb;
 	if constexpr (V == 1) {
 		f.v[0] = __ldg(p + lig);
-	} else if constexpr (V == 2) {
-		double2 t = __ldg(reinterpret_cast<const double2*>(p) + lig);
-		f.v[0] = t.x; f.v[1] = t.y;
 	} else {
-		static_assert(V == 4, "V must be 1, 2 or 4");
-		double2 t = __ldg(reinterpret_cast<const double2*>(p) + lig);
-		double2 u = __ldg(reinterpret_cast<const double2*>(p) + G + lig);
-		f.v[0] = t.x; f.v[1] = t.y; f.v[2] = u.x; f.v[3] = u.y;
+		// V/2 16-byte loads per lane; load i of the group covers the contiguous span [i*G*16, (i+1)*G*16) bytes
+		// of the row, so with G = 8 every load instruction of a group is exactly one 128-byte line
+		static_assert(V % 2 == 0, "V must be 1 or even");
+		#pragma unroll
+		for (int i = 0; i < V / 2; i++) {
+			const double2 t = __ldg(reinterpret_cast<const double2*>(p) + i * G + lig);
+			f.v[2 * i] = t.x; f.v[2 * i + 1] = t.y;
+		}
 	}
 	return f;
 }
@@ -53,11 +54,10 @@ __device__ __forceinline__ void store_c(double* __restrict__ C, size_t row, int 
 	double* p = C + row * ldc;
 	if constexpr (V == 1) {
 		p[lig] = acc[0];
-	} else if constexpr (V == 2) {
-		reinterpret_cast<double2*>(p)[lig] = make_double2(acc[0], acc[1]);
 	} else {
-		reinterpret_cast<double2*>(p)[lig] = make_double2(acc[0], acc[1]);
-		reinterpret_cast<double2*>(p)[G + lig] = make_double2(acc[2], acc[3]);
+		#pragma unroll
+		for (int i = 0; i < V / 2; i++)
+			reinterpret_cast<double2*>(p)[i * G + lig] = make_double2(acc[2 * i], acc[2 * i + 1]);
 	}
 }
 
@@ -229,6 +229,97 @@ __global__ void transpose_b_kernel(const double* __restrict__ x, double* __restr
 		const int64_t j = j0 + dy;
 		const int n = n0 + threadIdx.x;
 		if (n < k && j < c) B[j * k + n] = tile[threadIdx.x][dy];
+	}
+}
+
+} // namespace sb200
+
+namespace sb200 {
+
+// ------------------------------------------------------------------------------------------------
+// Row-split on a row-PADDED copy of A ("vec" variant).
+//
+// ncu on spmm_rowsplit_kernel (profiles/r1_rowsplit_cfg2_v2.md) shows 13.9 warp instructions and ~3.5 L1
+// data-pipe wavefronts per nonzero (2 for the 256-byte B row, the rest for handing (col, val) round a lane
+// group with shuffles), issue slots 67 % and the L1 data pipe 78 % busy -- while a pure gather of the same B
+// rows reaches 21.6 TB/s against the kernel's 14.6 (scripts/gather_probe.cu).  The cure is fewer
+// instructions and wavefronts per nonzero, not more loads in flight:
+//   * every row of A is padded to a multiple of 4 entries (col = the row's last column, val = 0), so a
+//     lane reads 4 column indices with ONE 16-byte load and 4 values with TWO, as same-address loads of
+//     its lane group (one wavefront per group and load, no shuffles, no per-step warp votes);
+//   * lane groups are independent: no shuffle means no warp-synchronous trip counts;
+//   * 4 B-row gathers (V doubles each) are in flight per lane and step.
+// The row sum still runs left to right; padded entries are skipped by a predicate, never multiplied.
+// ------------------------------------------------------------------------------------------------
+template <int G, int V, int THREADS>
+__global__ void __launch_bounds__(THREADS)
+spmm_rowsplit_vec_kernel(const int32_t* __restrict__ ia, const int32_t* __restrict__ iap,
+                         const int32_t* __restrict__ jap, const double* __restrict__ ap,
+                         const double* __restrict__ B, double* __restrict__ C,
+                         const int32_t* __restrict__ cta_rows, int ldb, int ldc)
+{
+	constexpr int NG = THREADS / G;
+	const int lig = threadIdx.x % G;
+	const int gid = threadIdx.x / G;
+	const int r0 = cta_rows[blockIdx.x];
+	const int r1 = cta_rows[blockIdx.x + 1];
+	for (int row = r0 + gid; row < r1; row += NG) {
+		const int len = __ldg(ia + row + 1) - __ldg(ia + row);
+		const int p = __ldg(iap + row);
+		const int4* cp = reinterpret_cast<const int4*>(jap + p);
+		const double2* vp = reinterpret_cast<const double2*>(ap + p);
+		double acc[V];
+		#pragma unroll
+		for (int v = 0; v < V; v++) acc[v] = 0.0;
+		for (int u = 0; u < len; u += 4) {
+			const int4 c4 = __ldg(cp + (u >> 2));
+			const double2 v01 = __ldg(vp + (u >> 1));
+			const double2 v23 = __ldg(vp + (u >> 1) + 1);
+			const Frag<V> b0 = load_b<G, V>(B, c4.x, lig, ldb);
+			const Frag<V> b1 = load_b<G, V>(B, c4.y, lig, ldb);
+			const Frag<V> b2 = load_b<G, V>(B, c4.z, lig, ldb);
+			const Frag<V> b3 = load_b<G, V>(B, c4.w, lig, ldb);
+			const int rem = len - u;
+			#pragma unroll
+			for (int v = 0; v < V; v++) acc[v] = fma(v01.x, b0.v[v], acc[v]);
+			if (rem > 1) {
+				#pragma unroll
+				for (int v = 0; v < V; v++) acc[v] = fma(v01.y, b1.v[v], acc[v]);
+			}
+			if (rem > 2) {
+				#pragma unroll
+				for (int v = 0; v < V; v++) acc[v] = fma(v23.x, b2.v[v], acc[v]);
+			}
+			if (rem > 3) {
+				#pragma unroll
+				for (int v = 0; v < V; v++) acc[v] = fma(v23.y, b3.v[v], acc[v]);
+			}
+		}
+		store_c<G, V>(C, (size_t) row, lig, acc, ldc);
+	}
+}
+
+// padded row lengths: out[i] = (len_i + 3) & ~3 for i < m, out[m] = 0 (then exclusive scan -> iap)
+__global__ void pad_len_kernel(const int32_t* __restrict__ ia, int m, int32_t* __restrict__ out)
+{
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i < m) out[i] = (ia[i + 1] - ia[i] + 3) & ~3;
+	else if (i == m) out[i] = 0;
+}
+
+// one thread per padded slot of a row group of 4: copies (col, val), pads with (last col of the row, 0)
+__global__ void pad_fill_kernel(const int32_t* __restrict__ ia, const int32_t* __restrict__ iap,
+                                const int32_t* __restrict__ ja, const double* __restrict__ a, int m,
+                                int32_t* __restrict__ jap, double* __restrict__ ap)
+{
+	const int lane = threadIdx.x & 31;
+	const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;      // a warp per row
+	if (row >= m) return;
+	const int s = ia[row], len = ia[row + 1] - s, p = iap[row], plen = iap[row + 1] - p;
+	const int last = len > 0 ? ja[s + len - 1] : 0;
+	for (int u = lane; u < plen; u += 32) {
+		jap[p + u] = u < len ? ja[s + u] : last;
+		ap[p + u] = u < len ? a[s + u] : 0.0;
 	}
 }
 
