@@ -126,10 +126,26 @@ class ClockSampler:
 # CPU legs (the only places this file executes oracle/)
 # ---------------------------------------------------------------------------------------------
 
+def use_all_host_threads():
+    """torchrun exports OMP_NUM_THREADS=1 to every rank; the CPU arm must use the cores the process may run on."""
+    import ctypes
+    n = len(os.sched_getaffinity(0))
+    try:
+        ctypes.CDLL("libgomp.so.1").omp_set_num_threads(n)
+    except OSError:
+        pass
+    return n
+
+
 def cpu_spmm_timer(ia, ja, a, m, c, k, x):
     """Returns (fn(rows)->seconds, kind, cores): one call of the reference CPU kernel on the first
     `rows` rows.  kind = 'reference' when oracle/_ref holds the compiled reference."""
     from oracle import loader as L
+    if L.have_ref():
+        L.ref()
+    else:
+        L.oracle()
+    use_all_host_threads()          # after the library (and its libgomp) is loaded
     y = np.empty(m * k)
     if L.have_ref():
         lib, kind, cores = L.ref(), "reference", L.ref().ref_num_threads()
@@ -376,6 +392,8 @@ def main():
     if not L.have_ref():
         raise SystemExit("bench.py: oracle/_ref/libamg_ref.so (the reference's matrix generator) is missing; "
                          "run __graft_entry__.build() in the container that has /root/reference")
+    L.amg()
+    use_all_host_threads()              # the generator's output does not depend on the thread count
     ia, ja, a, m, c = L.generate(gen_args)
     nnz = len(ja)
     desc = {"workload": f"{args.workload}: artificial-matrix-generator '{gen_args}', fp64 CSR SpMM k={k}",
