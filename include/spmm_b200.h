@@ -188,6 +188,25 @@ enum { SPMM_B200_NSTATS = 10 };
 int spmm_b200_check_accuracy(spmm_b200_t *h, const double *x_host, const double *y_host, int k,
                              double *stats, double *y_gold_host);
 
+/* ---- fp32 ("_f" builds of the reference, make.sh:98-108: ValueType = float).  Same plug-in interface
+ * (spmv_kernel.h:9-30) and layouts as the fp64 entry points above, int32 indices, fp32 values / x / y;
+ * row-split CSR kernels, the same bit-exact partitioners for CTA work lists and shards.  The row sum runs
+ * left to right in fp32 with fused multiply-add. */
+typedef struct spmm_b200_f32 spmm_b200_f32_t;
+int spmm_b200_create_f32(spmm_b200_f32_t **h, const int32_t *row_ptr, const int32_t *col_ind, const float *values,
+                         int64_t m, int64_t c, int64_t nnz, int k, int device, int b_layout);
+int spmm_b200_create_shard_f32(spmm_b200_f32_t **h, const int32_t *row_ptr, const int32_t *col_ind, const float *values,
+                               int64_t m, int64_t c, int64_t nnz, int k, int device, int b_layout,
+                               int rank, int nranks, int64_t *first_row, int64_t *last_row);
+int spmm_b200_run_f32(spmm_b200_f32_t *h, const float *x_host, float *y_host, int k, int copy_back);
+int spmm_b200_run_device_f32(spmm_b200_f32_t *h, const float *b_dev, float *c_dev, int k, void *stream);
+int spmm_b200_fetch_c_f32(spmm_b200_f32_t *h, float *y_host, int k);
+int64_t spmm_b200_rows_f32(const spmm_b200_f32_t *h);
+int64_t spmm_b200_nnz_f32(const spmm_b200_f32_t *h);
+int64_t spmm_b200_launch_count_f32(const spmm_b200_f32_t *h);
+double  spmm_b200_last_kernel_ms_f32(const spmm_b200_f32_t *h);
+void    spmm_b200_destroy_f32(spmm_b200_f32_t *h);
+
 /* ---- introspection */
 int64_t spmm_b200_rows(const spmm_b200_t *h);         /* rows held by this handle (shard)     */
 int64_t spmm_b200_nnz(const spmm_b200_t *h);

@@ -69,6 +69,32 @@ def ref():
     return lib
 
 
+_f32p = np.ctypeslib.ndpointer(np.float32, flags="C_CONTIGUOUS")
+
+
+def have_ref_f32():
+    return os.path.exists(os.path.join(HERE, "_ref", "libspmm_ref_f.so"))
+
+
+def spmm_ref_f32(ia, ja, a, m, c, x, k):
+    """The reference's compute_csr in an "_f" build (ValueType = float)."""
+    lib = _load(os.path.join(HERE, "_ref", "libspmm_ref_f.so"))
+    lib.ref_spmm_csr.argtypes = [_i32p, _i32p, _f32p, C.c_long, C.c_long, C.c_long, _f32p, _f32p, C.c_int]
+    lib.ref_spmm_csr.restype = None
+    y = np.empty(m * k, dtype=np.float32)
+    lib.ref_spmm_csr(ia, ja, a, m, c, len(ja), x, y, k)
+    return y
+
+
+def spmm_oracle_f32(ia, ja, a, m, c, x, k):
+    lib = oracle()
+    lib.oracle_spmm_csr_f32.argtypes = [_i32p, _i32p, _f32p, C.c_long, C.c_long, _f32p, _f32p, C.c_int]
+    lib.oracle_spmm_csr_f32.restype = None
+    y = np.empty(m * k, dtype=np.float32)
+    lib.oracle_spmm_csr_f32(ia, ja, a, m, c, x, y, k)
+    return y
+
+
 def merge_ref():
     lib = _load(os.path.join(HERE, "_ref", "libmerge_ref.so"))
     if not hasattr(lib, "_typed"):

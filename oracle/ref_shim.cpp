@@ -22,8 +22,8 @@ extern "C" {
 /* y = A*x through the reference plug-in interface.  The format object takes
  * ownership of the CSR arrays (its dtor frees them), so hand it private copies
  * exactly as the harness does (spmv_bench.cpp:871-893). */
-void ref_spmm_csr(const int32_t *ia, const int32_t *ja, const double *a,
-                  long m, long c, long nnz, double *x, double *y, int k)
+void ref_spmm_csr(const int32_t *ia, const int32_t *ja, const ValueType *a,
+                  long m, long c, long nnz, ValueType *x, ValueType *y, int k)
 {
 	INT_T *ia2 = (INT_T *) aligned_alloc(64, (((m + 1 + VECTOR_ELEM_NUM) * sizeof(INT_T) + 63) / 64) * 64);
 	INT_T *ja2 = (INT_T *) aligned_alloc(64, (((nnz + VECTOR_ELEM_NUM) * sizeof(INT_T) + 63) / 64) * 64);
@@ -37,8 +37,8 @@ void ref_spmm_csr(const int32_t *ia, const int32_t *ja, const double *a,
 }
 
 /* Zero-copy variant for timing loops: the caller keeps ownership. */
-void ref_spmm_csr_nocopy(int32_t *ia, int32_t *ja, double *a,
-                         long m, long c, long nnz, double *x, double *y, int k)
+void ref_spmm_csr_nocopy(int32_t *ia, int32_t *ja, ValueType *a,
+                         long m, long c, long nnz, ValueType *x, ValueType *y, int k)
 {
 	CSRArrays csr(m, c, nnz);
 	csr.ia = ia; csr.ja = ja; csr.a = a;

@@ -358,3 +358,24 @@ void oracle_check_accuracy(const int32_t *ia, const int32_t *ja, const double *a
 	if (y_gold) memcpy(y_gold, gold, sizeof(double) * N);
 	free(gold);
 }
+
+/* ---------------------------------------------------------------------------
+ * N3: the same naive CSR SpMM in fp32 -- what spmm_kernel_csr.cpp:69-97 computes in an "_f" build
+ * (ValueType = float, make.sh:98-108): float sum, float product, left to right.
+ * ------------------------------------------------------------------------- */
+void oracle_spmm_csr_f32(const int32_t *ia, const int32_t *ja, const float *a,
+                         long m, long c, const float *x, float *y, int k)
+{
+	#pragma omp parallel
+	{
+		for (long n = 0; n < k; n++) {
+			#pragma omp for
+			for (long i = 0; i < m; i++) {
+				float sum = 0;
+				for (long j = ia[i]; j < ia[i + 1]; j++)
+					sum += a[j] * x[n * c + ja[j]];
+				y[i * (long) k + n] = sum;
+			}
+		}
+	}
+}

@@ -16,7 +16,7 @@ import os
 
 import numpy as np
 
-__all__ = ["csr_to_format", "coo_to_csr", "read_mtx", "read_smtx", "MatrixFormat", "partition", "shard_slices", "statistics_print_labels", "load_library",
+__all__ = ["csr_to_format", "csr_to_format_f32", "MatrixFormatF32", "coo_to_csr", "read_mtx", "read_smtx", "MatrixFormat", "partition", "shard_slices", "statistics_print_labels", "load_library",
            "SpmmB200Error", "ROWSPLIT", "MERGE", "BCSR", "AUTO", "BCSR_FMA", "B_COLMAJOR", "B_ROWMAJOR",
            "PART_ROWS", "PART_NNZ", "PART_MERGE", "LIB_PATH", "EXPORTS"]
 
@@ -35,6 +35,9 @@ EXPORTS = [
     "spmm_b200_transpose_b_device", "spmm_b200_partition", "spmm_b200_partition_host", "spmm_b200_coo_to_csr", "spmm_b200_rows", "spmm_b200_nnz",
     "spmm_b200_variant", "spmm_b200_bcsr_blocks", "spmm_b200_last_kernel_ms", "spmm_b200_launch_count", "spmm_b200_stats",
     "spmm_b200_stats_labels", "spmm_b200_destroy", "spmm_b200_strerror", "spmm_b200_last_cuda_error",
+    "spmm_b200_create_f32", "spmm_b200_create_shard_f32", "spmm_b200_run_f32", "spmm_b200_run_device_f32",
+    "spmm_b200_fetch_c_f32", "spmm_b200_rows_f32", "spmm_b200_nnz_f32", "spmm_b200_launch_count_f32",
+    "spmm_b200_last_kernel_ms_f32", "spmm_b200_destroy_f32",
     "spmm_b200_device_count", "spmm_b200_read_mtx", "spmm_b200_read_smtx", "spmm_b200_free", "spmm_b200_check_accuracy",
 ]
 
@@ -97,6 +100,16 @@ def load_library():
     lib.spmm_b200_read_smtx.argtypes = [C.c_char_p, C.c_uint64, C.POINTER(_i64), C.POINTER(_i64), C.POINTER(_i64), _pp, _pp, _pp]
     lib.spmm_b200_free.argtypes = [_vp]; lib.spmm_b200_free.restype = None
     lib.spmm_b200_check_accuracy.argtypes = [_vp, _vp, _vp, _int, _vp, _vp]
+    lib.spmm_b200_create_f32.argtypes = [C.POINTER(_vp), _vp, _vp, _vp, _i64, _i64, _i64, _int, _int, _int]
+    lib.spmm_b200_create_shard_f32.argtypes = lib.spmm_b200_create_f32.argtypes + [_int, _int, C.POINTER(_i64), C.POINTER(_i64)]
+    lib.spmm_b200_run_f32.argtypes = [_vp, _vp, _vp, _int, _int]
+    lib.spmm_b200_run_device_f32.argtypes = [_vp, _vp, _vp, _int, _vp]
+    lib.spmm_b200_fetch_c_f32.argtypes = [_vp, _vp, _int]
+    lib.spmm_b200_rows_f32.argtypes = [_vp]; lib.spmm_b200_rows_f32.restype = _i64
+    lib.spmm_b200_nnz_f32.argtypes = [_vp]; lib.spmm_b200_nnz_f32.restype = _i64
+    lib.spmm_b200_launch_count_f32.argtypes = [_vp]; lib.spmm_b200_launch_count_f32.restype = _i64
+    lib.spmm_b200_last_kernel_ms_f32.argtypes = [_vp]; lib.spmm_b200_last_kernel_ms_f32.restype = _dbl
+    lib.spmm_b200_destroy_f32.argtypes = [_vp]; lib.spmm_b200_destroy_f32.restype = None
     _lib = lib
     return lib
 
@@ -226,6 +239,68 @@ class MatrixFormat:
             self.close()
         except Exception:
             pass
+
+
+class MatrixFormatF32:
+    """fp32 twin of MatrixFormat: the reference's "_f" builds (ValueType = float, make.sh:98-108)."""
+
+    def __init__(self, handle, m, n, nnz, k, first_row=0):
+        self._h = handle
+        self.m, self.n, self.nnz, self.k, self.first_row = int(m), int(n), int(nnz), int(k), int(first_row)
+        self.format_name = "B200_CSR_ROWSPLIT_F32"
+        self.csr_mem_footprint = self.nnz * (4 + 4) + (self.m + 1) * 4
+        self.mem_footprint = self.csr_mem_footprint
+
+    def spmm(self, x, y, k, copy_back=True):
+        k = int(k)
+        if x.size != self.n * k:
+            raise ValueError(f"x holds {x.size} values, expected c*k = {self.n * k}")
+        if copy_back and y.size != self.m * k:
+            raise ValueError(f"y holds {y.size} values, expected m*k = {self.m * k}")
+        _check(load_library().spmm_b200_run_f32(self._h, _host(x, np.float32, "x"), _host(y, np.float32, "y") if copy_back else None,
+                                                k, 1 if copy_back else 0), "spmm(f32)")
+
+    def spmm_device(self, b_ptr, c_ptr, k, stream=0):
+        _check(load_library().spmm_b200_run_device_f32(self._h, b_ptr, c_ptr, int(k), stream or None), "spmm_device(f32)")
+
+    def fetch_c(self, y, k):
+        _check(load_library().spmm_b200_fetch_c_f32(self._h, _host(y, np.float32, "y"), int(k)), "fetch_c(f32)")
+
+    def last_kernel_ms(self):
+        return load_library().spmm_b200_last_kernel_ms_f32(self._h)
+
+    def launch_count(self):
+        return load_library().spmm_b200_launch_count_f32(self._h)
+
+    def statistics_start(self):
+        pass
+
+    def close(self):
+        if self._h:
+            load_library().spmm_b200_destroy_f32(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def csr_to_format_f32(row_ptr, col_ind, values, m, n, nnz, k, *, device=0, b_layout=B_COLMAJOR, rank=None, nranks=None):
+    """csr_to_format() of an "_f" build: values float32."""
+    lib = load_library()
+    h = _vp()
+    rp = _host(row_ptr, np.int32, "row_ptr")
+    ci = _host(col_ind, np.int32, "col_ind") if nnz > 0 else None
+    va = _host(values, np.float32, "values") if nnz > 0 else None
+    if nranks is None:
+        _check(lib.spmm_b200_create_f32(C.byref(h), rp, ci, va, m, n, nnz, k, device, b_layout), "csr_to_format_f32")
+        return MatrixFormatF32(h, m, n, nnz, k)
+    r0, r1 = _i64(), _i64()
+    _check(lib.spmm_b200_create_shard_f32(C.byref(h), rp, ci, va, m, n, nnz, k, device, b_layout, int(rank), int(nranks),
+                                          C.byref(r0), C.byref(r1)), "csr_to_format_f32(shard)")
+    return MatrixFormatF32(h, lib.spmm_b200_rows_f32(h), n, lib.spmm_b200_nnz_f32(h), k, first_row=r0.value)
 
 
 def csr_to_format(row_ptr, col_ind, values, m, n, nnz, k, *, device=0, variant=AUTO,

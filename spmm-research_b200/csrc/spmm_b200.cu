@@ -1173,3 +1173,8 @@ extern "C" int spmm_b200_device_count(void)
 	if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
 	return n;
 }
+
+// ------------------------------------------------------------------------------------------
+// fp32 entry points (the reference's "_f" builds)
+// ------------------------------------------------------------------------------------------
+#include "spmm_b200_f32.inl"

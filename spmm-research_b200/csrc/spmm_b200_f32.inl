@@ -1,0 +1,232 @@
+// spmm_b200_f32.cu -- fp32 entry points of the C ABI (include/spmm_b200.h, "_f32" functions).
+//
+// The reference builds every kernel twice, "_d" (ValueType = double) and "_f" (ValueType = float,
+// make.sh:98-108); this file is the "_f" side of the drop-in: same plug-in interface
+// (spmv_kernel.h:9-30), int32 CSR indices, fp32 values / B / C.  Row-split CSR kernels only
+// (spmm_f32.cuh); CTA work lists and shard boundaries come from the same bit-exact partitioners as the
+// fp64 path (partition.cuh).  No CPU fallback.
+// Included at the end of spmm_b200.cu (one translation unit: the kernels of partition.cuh must not be
+// defined twice, and CU_TRY / g_cuda_err are shared).
+#include "spmm_f32.cuh"
+
+struct spmm_b200_f32 {
+	int device = 0, b_layout = SPMM_B200_B_COLMAJOR, k = 0, sm_count = 148;
+	int64_t m = 0, c = 0, nnz = 0, first_row = 0;
+	int32_t* d_ia = nullptr;
+	int32_t* d_ja = nullptr;
+	float* d_a = nullptr;
+	int32_t* d_cta_rows = nullptr;
+	int n_ctas = 0;
+	float* d_x = nullptr; size_t cap_x = 0;
+	float* d_B = nullptr; size_t cap_B = 0;
+	float* d_C = nullptr; size_t cap_C = 0;
+	cudaStream_t stream = nullptr;
+	cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+	bool timed = false;
+	int64_t launches = 0;
+};
+
+__global__ void rebase_f32_kernel(int32_t* ia, int64_t n, int32_t base)
+{
+	int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+	if (i < n) ia[i] -= base;
+}
+
+static int device_ok(int device, int* sms)
+{
+	int n = 0;
+	if (cudaGetDeviceCount(&n) != cudaSuccess || n <= 0) { cudaGetLastError(); return SPMM_B200_ENODEV; }
+	if (device < 0 || device >= n) return SPMM_B200_EINVAL;
+	cudaDeviceProp p;
+	CU_TRY(cudaGetDeviceProperties(&p, device));
+	if (p.major != 10) return SPMM_B200_ENODEV;
+	*sms = p.multiProcessorCount;
+	CU_TRY(cudaSetDevice(device));
+	return SPMM_B200_OK;
+}
+
+static int create_slice(spmm_b200_f32** out, const int32_t* ia_slice, const int32_t* ja, const float* a, int64_t m, int64_t c,
+                        int64_t nnz, int32_t base, int k, int device, int b_layout, int sms, int64_t first_row)
+{
+	spmm_b200_f32* h = new (std::nothrow) spmm_b200_f32();
+	if (!h) return SPMM_B200_ENOMEM;
+	*out = h;
+	h->device = device; h->b_layout = b_layout; h->k = k; h->sm_count = sms;
+	h->m = m; h->c = c; h->nnz = nnz; h->first_row = first_row;
+	CU_TRY(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+	CU_TRY(cudaEventCreate(&h->ev0));
+	CU_TRY(cudaEventCreate(&h->ev1));
+	CU_TRY(cudaMalloc(&h->d_ia, sizeof(int32_t) * (m + 1)));
+	CU_TRY(cudaMalloc(&h->d_ja, sizeof(int32_t) * std::max<int64_t>(nnz, 1)));
+	CU_TRY(cudaMalloc(&h->d_a, sizeof(float) * std::max<int64_t>(nnz, 1)));
+	CU_TRY(cudaMemcpyAsync(h->d_ia, ia_slice, sizeof(int32_t) * (m + 1), cudaMemcpyHostToDevice, h->stream));
+	if (nnz > 0) {
+		CU_TRY(cudaMemcpyAsync(h->d_ja, ja + base, sizeof(int32_t) * nnz, cudaMemcpyHostToDevice, h->stream));
+		CU_TRY(cudaMemcpyAsync(h->d_a, a + base, sizeof(float) * nnz, cudaMemcpyHostToDevice, h->stream));
+	}
+	if (base != 0) {
+		rebase_f32_kernel<<<(unsigned) ((m + 1 + 255) / 256), 256, 0, h->stream>>>(h->d_ia, m + 1, base);
+		h->launches++;
+	}
+	// CTA work list: the reference's nnz-balanced row split with P = 32 CTAs per SM
+	const int64_t want = (int64_t) sms * 32, cap = std::max<int64_t>(1, (m + 7) / 8);
+	h->n_ctas = (int) std::max<int64_t>(1, std::min(want, cap));
+	CU_TRY(cudaMalloc(&h->d_cta_rows, sizeof(int32_t) * (h->n_ctas + 1)));
+	cta_rows_nnz_kernel<<<(h->n_ctas + 1 + 255) / 256, 256, 0, h->stream>>>(h->d_ia, (int) m, nnz, h->n_ctas, h->d_cta_rows);
+	h->launches++;
+	CU_TRY(cudaGetLastError());
+	CU_TRY(cudaStreamSynchronize(h->stream));
+	return SPMM_B200_OK;
+}
+
+static int check_args(const void* rp, const void* ci, const void* va, int64_t m, int64_t c, int64_t nnz, int k, int b_layout)
+{
+	if (!rp || m < 0 || c < 0 || nnz < 0 || k < 1) return SPMM_B200_EINVAL;
+	if (nnz > 0 && (!ci || !va)) return SPMM_B200_EINVAL;
+	if (b_layout != SPMM_B200_B_COLMAJOR && b_layout != SPMM_B200_B_ROWMAJOR) return SPMM_B200_EINVAL;
+	if (m >= INT32_MAX || c >= INT32_MAX || nnz >= INT32_MAX) return SPMM_B200_ERANGE;
+	return SPMM_B200_OK;
+}
+
+extern "C" int spmm_b200_create_f32(spmm_b200_f32_t** h, const int32_t* row_ptr, const int32_t* col_ind, const float* values,
+                                    int64_t m, int64_t c, int64_t nnz, int k, int device, int b_layout)
+{
+	if (!h) return SPMM_B200_EINVAL;
+	*h = nullptr;
+	int rc = check_args(row_ptr, col_ind, values, m, c, nnz, k, b_layout);
+	if (rc) return rc;
+	int sms = 0;
+	rc = device_ok(device, &sms);
+	if (rc) return rc;
+	rc = create_slice(h, row_ptr, col_ind, values, m, c, nnz, 0, k, device, b_layout, sms, 0);
+	if (rc) { spmm_b200_destroy_f32(*h); *h = nullptr; }
+	return rc;
+}
+
+extern "C" int spmm_b200_create_shard_f32(spmm_b200_f32_t** h, const int32_t* row_ptr, const int32_t* col_ind, const float* values,
+                                          int64_t m, int64_t c, int64_t nnz, int k, int device, int b_layout,
+                                          int rank, int nranks, int64_t* first_row, int64_t* last_row)
+{
+	if (!h) return SPMM_B200_EINVAL;
+	*h = nullptr;
+	int rc = check_args(row_ptr, col_ind, values, m, c, nnz, k, b_layout);
+	if (rc) return rc;
+	if (nranks < 1 || rank < 0 || rank >= nranks) return SPMM_B200_EINVAL;
+	int sms = 0;
+	rc = device_ok(device, &sms);
+	if (rc) return rc;
+	std::vector<int64_t> bounds(nranks + 1);
+	rc = spmm_b200_partition_host(row_ptr, m, nnz, nranks, SPMM_B200_PART_NNZ, bounds.data());   // same integers as the device search
+	if (rc) return rc;
+	const int64_t r0 = bounds[rank], r1 = std::max(bounds[rank + 1], bounds[rank]);
+	if (first_row) *first_row = r0;
+	if (last_row) *last_row = r1;
+	const int32_t base = row_ptr[r0];
+	rc = create_slice(h, row_ptr + r0, col_ind, values, r1 - r0, c, (int64_t) row_ptr[r1] - base, base, k, device, b_layout, sms, r0);
+	if (rc) { spmm_b200_destroy_f32(*h); *h = nullptr; }
+	return rc;
+}
+
+extern "C" void spmm_b200_destroy_f32(spmm_b200_f32_t* h)
+{
+	if (!h) return;
+	cudaSetDevice(h->device);
+	if (h->stream) cudaStreamSynchronize(h->stream);
+	cudaFree(h->d_ia); cudaFree(h->d_ja); cudaFree(h->d_a); cudaFree(h->d_cta_rows);
+	cudaFree(h->d_x); cudaFree(h->d_B); cudaFree(h->d_C);
+	if (h->ev0) cudaEventDestroy(h->ev0);
+	if (h->ev1) cudaEventDestroy(h->ev1);
+	if (h->stream) cudaStreamDestroy(h->stream);
+	delete h;
+}
+
+template <int G, int V, int U>
+static void launch_gv(const spmm_b200_f32* h, const float* B, float* C, cudaStream_t s)
+{
+	spmm_rowsplit_f32_kernel<G, V, U, THREADS><<<h->n_ctas, THREADS, 0, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, h->d_cta_rows, G * V, G * V);
+}
+
+extern "C" int spmm_b200_run_device_f32(spmm_b200_f32_t* h, const float* b_dev, float* c_dev, int k, void* stream)
+{
+	if (!h || k < 1) return SPMM_B200_EINVAL;
+	if ((h->c > 0 && h->nnz > 0 && !b_dev) || (h->m > 0 && !c_dev)) return SPMM_B200_EINVAL;
+	CU_TRY(cudaSetDevice(h->device));
+	cudaStream_t s = (cudaStream_t) stream;
+	CU_TRY(cudaEventRecord(h->ev0, s));
+	if (h->m > 0) {
+		const bool aligned = ((uintptr_t) b_dev % 16) == 0 && ((uintptr_t) c_dev % 16) == 0;
+		// a group of 8 lanes covers one 128-byte line per 16-byte load (see profiles/r1_gvu_probe.md)
+		if (aligned && k == 16) launch_gv<4, 4, 4>(h, b_dev, c_dev, s);
+		else if (aligned && k == 32) launch_gv<8, 4, 4>(h, b_dev, c_dev, s);
+		else if (aligned && k == 64) launch_gv<8, 8, 4>(h, b_dev, c_dev, s);
+		else if (aligned && k == 128) launch_gv<16, 8, 4>(h, b_dev, c_dev, s);
+		else if (aligned && k == 256) launch_gv<32, 8, 4>(h, b_dev, c_dev, s);
+		else spmm_rowsplit_generic_f32_kernel<THREADS><<<h->n_ctas, THREADS, 0, s>>>(h->d_ia, h->d_ja, h->d_a, b_dev, c_dev, h->d_cta_rows, k);
+		h->launches++;
+		CU_TRY(cudaGetLastError());
+	}
+	CU_TRY(cudaEventRecord(h->ev1, s));
+	h->timed = true;
+	return SPMM_B200_OK;
+}
+
+static int ensure32(float** p, size_t* cap, size_t want)
+{
+	if (*cap >= want) return SPMM_B200_OK;
+	if (*p) cudaFree(*p);
+	*p = nullptr; *cap = 0;
+	CU_TRY(cudaMalloc(p, sizeof(float) * std::max<size_t>(want, 1)));
+	*cap = want;
+	return SPMM_B200_OK;
+}
+
+extern "C" int spmm_b200_run_f32(spmm_b200_f32_t* h, const float* x_host, float* y_host, int k, int copy_back)
+{
+	if (!h || !x_host || k < 1 || (copy_back && !y_host)) return SPMM_B200_EINVAL;
+	CU_TRY(cudaSetDevice(h->device));
+	const size_t nb = (size_t) h->c * k;
+	int rc = ensure32(&h->d_B, &h->cap_B, nb);
+	if (rc) return rc;
+	rc = ensure32(&h->d_C, &h->cap_C, (size_t) h->m * k);
+	if (rc) return rc;
+	if (h->b_layout == SPMM_B200_B_ROWMAJOR || k == 1) {
+		CU_TRY(cudaMemcpyAsync(h->d_B, x_host, nb * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+	} else {
+		rc = ensure32(&h->d_x, &h->cap_x, nb);
+		if (rc) return rc;
+		CU_TRY(cudaMemcpyAsync(h->d_x, x_host, nb * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+		if (h->c > 0) {
+			dim3 grid((unsigned) ((h->c + 31) / 32), (unsigned) ((k + 31) / 32)), block(32, 8);
+			transpose_b_f32_kernel<<<grid, block, 0, h->stream>>>(h->d_x, h->d_B, h->c, k);
+			h->launches++;
+		}
+	}
+	rc = spmm_b200_run_device_f32(h, h->d_B, h->d_C, k, h->stream);
+	if (rc) return rc;
+	if (copy_back && h->m > 0)
+		CU_TRY(cudaMemcpyAsync(y_host, h->d_C, sizeof(float) * h->m * k, cudaMemcpyDeviceToHost, h->stream));
+	CU_TRY(cudaStreamSynchronize(h->stream));
+	return SPMM_B200_OK;
+}
+
+extern "C" int spmm_b200_fetch_c_f32(spmm_b200_f32_t* h, float* y_host, int k)
+{
+	if (!h || !y_host || k < 1 || h->cap_C < (size_t) h->m * k) return SPMM_B200_EINVAL;
+	CU_TRY(cudaSetDevice(h->device));
+	if (h->m > 0) CU_TRY(cudaMemcpyAsync(y_host, h->d_C, sizeof(float) * h->m * k, cudaMemcpyDeviceToHost, h->stream));
+	CU_TRY(cudaStreamSynchronize(h->stream));
+	return SPMM_B200_OK;
+}
+
+extern "C" int64_t spmm_b200_rows_f32(const spmm_b200_f32_t* h) { return h ? h->m : -1; }
+extern "C" int64_t spmm_b200_nnz_f32(const spmm_b200_f32_t* h) { return h ? h->nnz : -1; }
+extern "C" int64_t spmm_b200_launch_count_f32(const spmm_b200_f32_t* h) { return h ? h->launches : -1; }
+
+extern "C" double spmm_b200_last_kernel_ms_f32(const spmm_b200_f32_t* h)
+{
+	if (!h || !h->timed) return -1.0;
+	float ms = 0.f;
+	if (cudaEventSynchronize(h->ev1) != cudaSuccess) return -1.0;
+	if (cudaEventElapsedTime(&ms, h->ev0, h->ev1) != cudaSuccess) return -1.0;
+	return (double) ms;
+}

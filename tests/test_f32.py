@@ -1,0 +1,92 @@
+"""N3: fp32 ("_f" builds, ValueType = float).  CPU: the oracle's fp32 restatement against the reference's own
+compute_csr compiled with ValueType = float (oracle/_ref/libspmm_ref_f.so) and against committed outputs of it.
+GPU: the fp32 kernels through the C ABI against the oracle.  Tolerance (stated): fp32 left-to-right sums on
+positive operands, relative error <= 2e-6 per entry (bit-identical in practice: same order, same FMA contraction);
+with mixed signs the comparison is absolute against sum |a||x| * 2e-6."""
+import os
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, random_csr
+
+F32_TOL = 2e-6
+
+
+def case(m, c, avg, seed, k, long_row=0):
+    ia, ja, a = random_csr(m, c, avg, seed=seed, empty_frac=0.1, long_row=long_row)
+    a = (np.abs(a) + 0.01).astype(np.float32)
+    x = np.random.default_rng(seed + 100).random(c * k, dtype=np.float32)
+    return ia, ja, a, x
+
+
+def rel_err(y, y_ref):
+    return float(np.max(np.abs(y.astype(np.float64) - y_ref) / np.maximum(np.abs(y_ref), 1e-30))) if y.size else 0.0
+
+
+def test_oracle_f32_matches_reference_f_build(L):
+    if not L.have_ref_f32():
+        pytest.skip("oracle/_ref/libspmm_ref_f.so not built")
+    for seed, k in ((1, 1), (2, 8), (3, 32), (4, 7)):
+        ia, ja, a, x = case(3000, 2500, 9.0, seed, k, long_row=900)
+        y_o = L.spmm_oracle_f32(ia, ja, a, 3000, 2500, x, k)
+        y_r = L.spmm_ref_f32(ia, ja, a, 3000, 2500, x, k)
+        assert np.array_equal(y_o, y_r)                     # same source order, same flags: bit-identical
+
+
+def test_oracle_f32_matches_committed_reference_output(L):
+    z = np.load(os.path.join(GOLDEN, "spmm_reference_outputs_f32.npz"))
+    y_o = L.spmm_oracle_f32(z["ia"], z["ja"], z["a"], int(z["m"]), int(z["c"]), z["x"], int(z["k"]))
+    assert rel_err(y_o, z["y"].astype(np.float64)) <= F32_TOL
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("k", [1, 2, 4, 8, 16, 32, 64, 128, 256, 3, 20, 100])
+def test_gpu_f32_all_k(pkg, L, k):
+    m, c = 4000, 3500
+    ia, ja, a, x = case(m, c, 9.0, k, k, long_row=1500)
+    y_ref = L.spmm_oracle_f32(ia, ja, a, m, c, x, k).astype(np.float64)
+    mf = pkg.csr_to_format_f32(ia, ja, a, m, c, len(ja), k)
+    y = np.full(m * k, np.nan, np.float32); mf.spmm(x, y, k)
+    assert mf.last_kernel_ms() > 0 and mf.launch_count() >= 2
+    mf.close()
+    assert not np.isnan(y).any()
+    assert rel_err(y, y_ref) <= F32_TOL, k
+    # row-major B gives the same result
+    x_rm = np.ascontiguousarray(x.reshape(k, c).T).ravel()
+    mf = pkg.csr_to_format_f32(ia, ja, a, m, c, len(ja), k, b_layout=pkg.B_ROWMAJOR)
+    y2 = np.full(m * k, np.nan, np.float32); mf.spmm(x_rm, y2, k); mf.close()
+    assert np.array_equal(y, y2)
+
+
+@pytest.mark.gpu
+def test_gpu_f32_edge_cases_and_shards(pkg, L):
+    for m, c, ia, ja in ((0, 5, np.zeros(1, np.int32), np.zeros(0, np.int32)),
+                         (7, 5, np.zeros(8, np.int32), np.zeros(0, np.int32))):
+        mf = pkg.csr_to_format_f32(ia, ja, np.zeros(0, np.float32), m, c, 0, 32)
+        y = np.full(m * 32, np.nan, np.float32); mf.spmm(np.ones(c * 32, np.float32), y, 32); mf.close()
+        assert not np.isnan(y).any() and not y.any()
+    m, c, k = 6000, 2000, 32
+    ia, ja, a, x = case(m, c, 11.0, 4, k, long_row=1800)
+    y_ref = L.spmm_oracle_f32(ia, ja, a, m, c, x, k).astype(np.float64)
+    bounds = np.zeros(5, np.int64); L.oracle().oracle_balance_prefix_sums(ia, m, len(ja), 4, bounds)
+    parts = []
+    for r in range(4):
+        mf = pkg.csr_to_format_f32(ia, ja, a, m, c, len(ja), k, rank=r, nranks=4)
+        assert (mf.first_row, mf.first_row + mf.m) == (bounds[r], bounds[r + 1])
+        y = np.empty(mf.m * k, np.float32); mf.spmm(x, y, k); mf.close(); parts.append(y)
+    assert rel_err(np.concatenate(parts), y_ref) <= F32_TOL
+
+
+@pytest.mark.gpu
+def test_gpu_f32_generated_matrix(pkg, L):
+    if not L.have_ref():
+        pytest.skip("reference generator not built")
+    ia, ja, a64, m, c = L.generate("200000 200000 20 10 gamma random 0.3 1000 0.5 0.5 14")
+    a = a64.astype(np.float32)
+    for k in (32, 128):
+        x = np.random.default_rng(k).random(c * k, dtype=np.float32)
+        y_ref = L.spmm_oracle_f32(ia, ja, a, m, c, x, k).astype(np.float64)
+        mf = pkg.csr_to_format_f32(ia, ja, a, m, c, len(ja), k)
+        y = np.empty(m * k, np.float32); mf.spmm(x, y, k); mf.close()
+        assert rel_err(y, y_ref) <= F32_TOL
