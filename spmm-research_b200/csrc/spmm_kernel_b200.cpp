@@ -25,6 +25,15 @@
 #include "spmv_kernel.h"
 #include "spmm_b200.h"
 
+#if DOUBLE == 0
+	// "_f" build (make.sh:98-108): ValueType = float -> the fp32 entry points
+	typedef spmm_b200_f32_t b200_handle_t;
+	#define B200_DESTROY spmm_b200_destroy_f32
+#else
+	typedef spmm_b200_t b200_handle_t;
+	#define B200_DESTROY spmm_b200_destroy
+#endif
+
 static void die(const char * where, int code)
 {
 	// reference convention: message on stdout (stderr is the CSV channel), then exit(1)
@@ -37,7 +46,7 @@ struct B200Arrays : Matrix_Format
 	INT_T * ia;
 	INT_T * ja;
 	ValueType * a;
-	spmm_b200_t * handle;
+	b200_handle_t * handle;
 	int copy_back;
 	int x_resident;
 	int registered;
@@ -50,12 +59,28 @@ struct B200Arrays : Matrix_Format
 
 	~B200Arrays()
 	{
-		spmm_b200_destroy(handle);
+		B200_DESTROY(handle);
 		free(a);
 		free(ia);
 		free(ja);
 	}
 
+#if DOUBLE == 0
+	void spmm(ValueType * x, ValueType * y, INT_T k)
+	{
+		int rc = spmm_b200_run_f32(handle, x, y, k, 1);
+		if (rc) die("spmm", rc);
+	}
+
+	void sync_y() {}
+
+	void statistics_start() {}
+
+	int statistics_print_data(char * buf, long buf_n)
+	{
+		return snprintf(buf, buf_n, ",rowsplit_f32,0,0,%g,0,0", spmm_b200_last_kernel_ms_f32(handle));
+	}
+#else
 	void spmm(ValueType * x, ValueType * y, INT_T k)
 	{
 		int rc;
@@ -100,12 +125,13 @@ struct B200Arrays : Matrix_Format
 		sync_y();
 		return spmm_b200_stats(handle, buf, buf_n);
 	}
+#endif
 };
 
 struct Matrix_Format *
 csr_to_format(INT_T * row_ptr, INT_T * col_ind, ValueType * values, long m, long n, long nnz, int k)
 {
-	static_assert(sizeof(INT_T) == 4 && sizeof(ValueType) == 8, "the B200 path is int32 / fp64 (build the _d target)");
+	static_assert(sizeof(INT_T) == 4 && sizeof(ValueType) == (DOUBLE ? 8 : 4), "the B200 path is int32 indices with fp64 (_d) or fp32 (_f) values");
 	struct B200Arrays * f = new B200Arrays(m, n, nnz);
 	const char * v = getenv("SPMM_B200_VARIANT");
 	int variant = SPMM_B200_AUTO;
@@ -122,11 +148,18 @@ csr_to_format(INT_T * row_ptr, INT_T * col_ind, ValueType * values, long m, long
 	f->ia = row_ptr;
 	f->ja = col_ind;
 	f->a = values;
+#if DOUBLE == 0
+	(void) variant;
+	int rc = spmm_b200_create_f32(&f->handle, row_ptr, col_ind, values, m, n, nnz, k, d ? atoi(d) : 0, SPMM_B200_B_COLMAJOR);
+	if (rc) die("csr_to_format", rc);
+	snprintf(f->name, sizeof(f->name), "B200_CSR_ROWSPLIT_F32");
+#else
 	int rc = spmm_b200_create(&f->handle, row_ptr, col_ind, values, m, n, nnz, k, d ? atoi(d) : 0, variant, SPMM_B200_B_COLMAJOR);
 	if (rc) die("csr_to_format", rc);
 	static const char * names[] = {"B200_CSR_ROWSPLIT", "B200_CSR_MERGE", "B200_BCSR_DMMA", "B200_CSR", "B200_BCSR_FMA"};
 	int vr = spmm_b200_variant(f->handle);
 	snprintf(f->name, sizeof(f->name), "%s", names[(vr >= 0 && vr <= 4) ? vr : 3]);
+#endif
 	f->format_name = f->name;
 	f->mem_footprint = f->csr_mem_footprint;
 	return f;

@@ -90,3 +90,21 @@ def test_gpu_f32_generated_matrix(pkg, L):
         mf = pkg.csr_to_format_f32(ia, ja, a, m, c, len(ja), k)
         y = np.empty(m * k, np.float32); mf.spmm(x, y, k); mf.close()
         assert rel_err(y, y_ref) <= F32_TOL
+
+
+@pytest.mark.gpu
+def test_reference_harness_dropin_f_build(pkg):
+    """The reference's unchanged harness compiled as an "_f" build (ValueType = float) with our plug-in TU."""
+    import subprocess
+    from conftest import ROOT
+    exe = os.path.join(ROOT, "oracle", "_ref", "spmm_b200_f.exe")
+    if not os.path.exists(exe):
+        pytest.skip("oracle/_ref/spmm_b200_f.exe not built")
+    env = dict(os.environ, USE_PROCESSES="0", USE_ARTIFICIAL_MATRICES="1", USE_DLCM_MATRICES="0", NUM_COLS="32",
+               COOLDOWN="0", RAPL_REGISTERS="0", OMP_NUM_THREADS="4")
+    r = subprocess.run([exe] + "100000 100000 10 2 normal random 1 0 0 0 14".split(), env=env,
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:]
+    row = r.stderr.strip().splitlines()[-1].split(",")
+    assert row[0] == "synthetic" and row[6] == "999475" and row[23] == "B200_CSR_ROWSPLIT_F32"
+    assert float(row[25]) > 0
