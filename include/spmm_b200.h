@@ -129,7 +129,10 @@ int spmm_b200_fetch_c(spmm_b200_t *h, double *y_host, int k);
 /* Device-pointer variant for callers that own device memory and streams
  * (bench.py / torch.distributed ranks): b_dev = row-major c x k, c_dev =
  * row-major m_local x k, both on the handle's device; `stream` is a
- * cudaStream_t (NULL = default stream).  Asynchronous. */
+ * cudaStream_t (NULL = default stream).  Asynchronous -- except that, when the B rows the matrix touches
+ * (column span x 8k bytes) are far beyond the 126 MB L2 and k >= 64, the first 8 calls with that k each run and
+ * time one candidate column-slice width of the row-split kernel (same bits for every candidate) and block
+ * until their kernels finish; the fastest is kept (spmm_b200_kslice).  SPMM_B200_KSLICE=-1 turns this off. */
 int spmm_b200_run_device(spmm_b200_t *h, const double *b_dev, double *c_dev, int k, void *stream);
 
 /* Column-major (oracle layout) -> row-major transpose of B on the device. */
@@ -212,6 +215,7 @@ int64_t spmm_b200_rows(const spmm_b200_t *h);         /* rows held by this handl
 int64_t spmm_b200_nnz(const spmm_b200_t *h);
 int     spmm_b200_variant(const spmm_b200_t *h);      /* the variant AUTO resolved to         */
 int64_t spmm_b200_bcsr_blocks(const spmm_b200_t *h);  /* 8x1 blocks stored (0 unless a BCSR variant); fill = nnz / (8*blocks) */
+int     spmm_b200_kslice(const spmm_b200_t *h);       /* column-slice width the row-split path settled on for its last k (0: none / still measuring; k: one launch) */
 double  spmm_b200_last_kernel_ms(const spmm_b200_t *h); /* CUDA-event time of the last run's kernels */
 int64_t spmm_b200_launch_count(const spmm_b200_t *h); /* kernels launched by this handle so far */
 /* replaces statistics_print_data()/statistics_print_labels() (spmv_kernel.h:20,30) */

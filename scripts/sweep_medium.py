@@ -44,7 +44,7 @@ def main():
             for vname in variants:
                 mf = pkg.csr_to_format(ia, ja, a, m, c, nnz, k, variant=vmap[vname])
                 mf.set_b(x, k)
-                for _ in range(3):
+                for _ in range(9):          # 8 = the k-slice measurement calls of a large-window matrix
                     mf.spmm_resident(k)
                 ts = []
                 for _ in range(10):
@@ -52,13 +52,14 @@ def main():
                     ts.append(mf.last_kernel_ms())
                 ms = float(np.median(ts))
                 name = mf.format_name
+                ksl = mf.kslice()
                 mf.close()
                 byts = 12.0 * nnz + 4.0 * (m + 1) + 8.0 * k * c + 8.0 * k * m
                 gf = 2.0 * nnz * k / (ms * 1e-3) / 1e9
                 gbs = byts / (ms * 1e-3) / 1e9
-                rows.append(dict(args=args, m=m, nnz=nnz, k=k, variant=name, ms=ms, gflops=gf, alg_gbs=gbs,
+                rows.append(dict(args=args, m=m, nnz=nnz, k=k, variant=name, kslice=ksl, ms=ms, gflops=gf, alg_gbs=gbs,
                                  frac=gbs / PEAK, gen_s=gen_s))
-                print(f"| {m} | {f[2]} | {f[6]} | {f[7]} | {nnz} | {k} | {name.replace('B200_CSR_', '')} | {ms:.4f} | {gf:.0f} | {gbs:.0f} | {gbs / PEAK:.3f} |",
+                print(f"| {m} | {f[2]} | {f[6]} | {f[7]} | {nnz} | {k} | {name.replace('B200_CSR_', '')}{'/w' + str(ksl) if ksl and ksl != k else ''} | {ms:.4f} | {gf:.0f} | {gbs:.0f} | {gbs / PEAK:.3f} |",
                       flush=True)
     os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
     json.dump(rows, open(os.path.join(ROOT, "gpurun_out", "sweep_medium.json"), "w"), indent=1)

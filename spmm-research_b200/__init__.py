@@ -33,7 +33,7 @@ EXPORTS = [
     "spmm_b200_register_host", "spmm_b200_unregister_host",
     "spmm_b200_run_resident", "spmm_b200_fetch_c", "spmm_b200_run_device",
     "spmm_b200_transpose_b_device", "spmm_b200_partition", "spmm_b200_partition_host", "spmm_b200_coo_to_csr", "spmm_b200_rows", "spmm_b200_nnz",
-    "spmm_b200_variant", "spmm_b200_bcsr_blocks", "spmm_b200_last_kernel_ms", "spmm_b200_launch_count", "spmm_b200_stats",
+    "spmm_b200_variant", "spmm_b200_bcsr_blocks", "spmm_b200_kslice", "spmm_b200_last_kernel_ms", "spmm_b200_launch_count", "spmm_b200_stats",
     "spmm_b200_stats_labels", "spmm_b200_destroy", "spmm_b200_strerror", "spmm_b200_last_cuda_error",
     "spmm_b200_create_f32", "spmm_b200_create_shard_f32", "spmm_b200_run_f32", "spmm_b200_run_device_f32",
     "spmm_b200_fetch_c_f32", "spmm_b200_rows_f32", "spmm_b200_nnz_f32", "spmm_b200_launch_count_f32",
@@ -87,6 +87,7 @@ def load_library():
     lib.spmm_b200_nnz.argtypes = [_vp]; lib.spmm_b200_nnz.restype = _i64
     lib.spmm_b200_variant.argtypes = [_vp]
     lib.spmm_b200_bcsr_blocks.argtypes = [_vp]; lib.spmm_b200_bcsr_blocks.restype = _i64
+    lib.spmm_b200_kslice.argtypes = [_vp]
     lib.spmm_b200_last_kernel_ms.argtypes = [_vp]; lib.spmm_b200_last_kernel_ms.restype = _dbl
     lib.spmm_b200_launch_count.argtypes = [_vp]; lib.spmm_b200_launch_count.restype = _i64
     lib.spmm_b200_stats.argtypes = [_vp, C.c_char_p, C.c_long]
@@ -220,6 +221,10 @@ class MatrixFormat:
 
     def launch_count(self):
         return load_library().spmm_b200_launch_count(self._h)
+
+    def kslice(self):
+        """Column-slice width the row-split path settled on (0: none / still measuring)."""
+        return load_library().spmm_b200_kslice(self._h)
 
     def statistics_start(self):
         pass

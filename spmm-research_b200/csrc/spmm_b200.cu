@@ -18,6 +18,7 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <limits.h>
 #include <math.h>
 #include <vector>
 #include <algorithm>
@@ -48,6 +49,13 @@ struct spmm_b200 {
 	int64_t m = 0, c = 0, nnz = 0;        // this handle's shard
 	int64_t first_row = 0, m_global = 0;
 	int max_row = 0;                      // longest row of the shard
+	int64_t col_span = 0;                 // max column - min column + 1 over the shard's nonzeros
+	// L2-aware k slicing of the row-split kernel, chosen by timing the candidates on the first calls
+	int ks_k = 0;                         // k the choice below is for
+	int ks_best = 0;                      // chosen slice width (== k: one launch); 0 while still measuring
+	int ks_try = 0;                       // index of the candidate the next call runs
+	int ks_cand[4] = {0, 0, 0, 0};
+	float ks_ms[4] = {0.f, 0.f, 0.f, 0.f};
 
 	int32_t* d_ia = nullptr;
 	int32_t* d_ja = nullptr;
@@ -123,6 +131,20 @@ __global__ void max_row_kernel(const int32_t* __restrict__ ia, int m, int* __res
 		best = max(best, ia[i + 1] - ia[i]);
 	for (int off = 16; off > 0; off >>= 1) best = max(best, __shfl_xor_sync(0xffffffffu, best, off));
 	if ((threadIdx.x & 31) == 0 && best > 0) atomicMax(out, best);
+}
+
+__global__ void col_span_kernel(const int32_t* __restrict__ ja, int64_t nnz, int* __restrict__ out_min, int* __restrict__ out_max)
+{
+	int lo = INT32_MAX, hi = -1;
+	for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < nnz; i += (int64_t) gridDim.x * blockDim.x) {
+		const int c = ja[i];
+		lo = min(lo, c); hi = max(hi, c);
+	}
+	for (int off = 16; off > 0; off >>= 1) {
+		lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, off));
+		hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, off));
+	}
+	if ((threadIdx.x & 31) == 0 && hi >= 0) { atomicMin(out_min, lo); atomicMax(out_max, hi); }
 }
 
 // ------------------------------------------------------------------------------------------
@@ -430,16 +452,20 @@ static int launch_spmm(spmm_b200* h, const double* B, double* C, int k, cudaStre
 	if ((h->variant == SPMM_B200_BCSR || h->variant == SPMM_B200_BCSR_FMA) && bcsr_supports_k(h->variant, k))
 		return launch_bcsr(h, B, C, k, s);
 	int n = 1;
-	// L2-aware k slicing (experiment knob): run the k columns as k/w launches on w-column slices of the
-	// same row-major B and C, so that the B rows a launch gathers (touched window x 8w bytes) stay in L2
-	const int w = env_int("SPMM_B200_KSLICE", 0);
+	// L2-aware k slicing: run the k columns as k/w launches on w-column slices of the same row-major B and C,
+	// so that the B rows a launch gathers (touched window x 8w bytes) stay in L2.  It pays when the window is
+	// far larger than L2 AND rows are long (every slice re-reads A and pays the per-row overhead again):
+	// profiles/r1_kslice_probe.md, r1_sweep_medium.md.  SPMM_B200_KSLICE=w forces a width, =0 (default) lets the
+	// handle time the candidates on its first calls (spmm_b200_run_device), =-1 turns slicing off.
+	int w = env_int("SPMM_B200_KSLICE", 0);
+	if (w == 0 && h->ks_k == k) w = h->ks_best > 0 ? h->ks_best : h->ks_cand[h->ks_try / 2];
 	if (w > 0 && w < k && k % w == 0 && (w == 8 || w == 16 || w == 32 || w == 64)) {
 		for (int off = 0; off < k; off += w) {
 			switch (w) {
 			case 8:  launch_rowsplit_gv<4, 2>(h, B + off, C + off, s, k, k); break;
 			case 16: launch_rowsplit_gv<8, 2>(h, B + off, C + off, s, k, k); break;
-			case 32: launch_rowsplit_gv<16, 2>(h, B + off, C + off, s, k, k); break;
-			default: launch_rowsplit_gv<32, 2>(h, B + off, C + off, s, k, k); break;
+			case 32: launch_rowsplit_gv<8, 4>(h, B + off, C + off, s, k, k); break;
+			default: launch_rowsplit_gv<16, 4>(h, B + off, C + off, s, k, k); break;
 			}
 		}
 		cudaError_t e = cudaGetLastError();
@@ -550,6 +576,19 @@ static int create_from_slice(spmm_b200_t** out, const int32_t* row_ptr_slice, co
 		CU_TRY(cudaMemcpyAsync(&h->max_row, d_max, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
 		CU_TRY(cudaStreamSynchronize(h->stream));
 		cudaFree(d_max);
+	}
+	if (nnz_local > 0) {
+		// touched window of B (for the L2-aware k slicing)
+		int* d_mm = nullptr;
+		int mm[2] = {INT32_MAX, -1};
+		CU_TRY(cudaMalloc(&d_mm, 2 * sizeof(int)));
+		CU_TRY(cudaMemcpyAsync(d_mm, mm, sizeof(mm), cudaMemcpyHostToDevice, h->stream));
+		col_span_kernel<<<(unsigned) std::min<int64_t>(148 * 8, (nnz_local + 255) / 256), 256, 0, h->stream>>>(h->d_ja, nnz_local, d_mm, d_mm + 1);
+		h->launches++;
+		CU_TRY(cudaMemcpyAsync(mm, d_mm, sizeof(mm), cudaMemcpyDeviceToHost, h->stream));
+		CU_TRY(cudaStreamSynchronize(h->stream));
+		cudaFree(d_mm);
+		h->col_span = mm[1] >= mm[0] ? (int64_t) mm[1] - mm[0] + 1 : 0;
 	}
 	if (variant == SPMM_B200_AUTO) {
 		// row-split serialises a row on one lane group: switch to merge-path when one row is far
@@ -754,10 +793,40 @@ extern "C" int spmm_b200_run_device(spmm_b200_t* h, const double* b_dev, double*
 	if (!h || k < 1) return SPMM_B200_EINVAL;
 	if ((h->c > 0 && h->nnz > 0 && !b_dev) || (h->m > 0 && !c_dev)) return SPMM_B200_EINVAL;
 	CU_TRY(cudaSetDevice(h->device));
+	// L2-aware k slicing: when the touched window of B (col_span x 8k bytes) is far beyond L2, the first calls with
+	// this k run one candidate slice width each and are timed (they block until their kernels finish; every
+	// candidate computes the same bits), then the fastest is kept.
+	const bool tunable = h->variant == SPMM_B200_ROWSPLIT && k >= 64 && k % 16 == 0 && env_int("SPMM_B200_KSLICE", 0) == 0
+	                     && (double) h->col_span * 8.0 * k > 192e6 && h->nnz > 0;
+	if (tunable && h->ks_k != k) {
+		h->ks_k = k; h->ks_best = 0; h->ks_try = 0;
+		int n = 0;
+		h->ks_cand[n++] = k;
+		for (int w = 64; w >= 16 && n < 4; w /= 2)
+			if (w < k && k % w == 0) h->ks_cand[n++] = w;
+		for (; n < 4; n++) h->ks_cand[n] = 0;
+	} else if (!tunable && h->ks_k == k) {
+		h->ks_k = 0;
+	}
 	int rc = run_between(h, b_dev, c_dev, k, (cudaStream_t) stream, h->ev0, h->ev1);
 	if (rc) return rc;
 	h->timed = true;
 	h->timed_slices = 0;
+	if (tunable && h->ks_best == 0) {
+		float ms = 0.f;
+		CU_TRY(cudaEventSynchronize(h->ev1));
+		CU_TRY(cudaEventElapsedTime(&ms, h->ev0, h->ev1));
+		// every candidate runs twice; the second run (warm caches, plan already resident) is the one that counts
+		if (h->ks_try & 1) h->ks_ms[h->ks_try / 2] = ms;
+		h->ks_try++;
+		const int ncand = h->ks_try / 2;
+		if ((h->ks_try & 1) == 0 && (ncand >= 4 || h->ks_cand[ncand] == 0)) {
+			int best = 0;
+			for (int i = 1; i < ncand; i++)
+				if (h->ks_ms[i] < h->ks_ms[best]) best = i;
+			h->ks_best = h->ks_cand[best];
+		}
+	}
 	return SPMM_B200_OK;
 }
 
@@ -1109,6 +1178,7 @@ extern "C" int64_t spmm_b200_rows(const spmm_b200_t* h) { return h ? h->m : -1; 
 extern "C" int64_t spmm_b200_nnz(const spmm_b200_t* h) { return h ? h->nnz : -1; }
 extern "C" int spmm_b200_variant(const spmm_b200_t* h) { return h ? h->variant : SPMM_B200_EINVAL; }
 extern "C" int64_t spmm_b200_bcsr_blocks(const spmm_b200_t* h) { return h ? h->bcsr.nnzb : -1; }
+extern "C" int spmm_b200_kslice(const spmm_b200_t* h) { return h ? h->ks_best : SPMM_B200_EINVAL; }
 extern "C" int64_t spmm_b200_launch_count(const spmm_b200_t* h) { return h ? h->launches : -1; }
 
 extern "C" double spmm_b200_last_kernel_ms(const spmm_b200_t* h)
