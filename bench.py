@@ -246,10 +246,11 @@ def gpu_arm(args, ia, ja, a, m, c, k, nnz, workload_desc):
         mf = pkg.csr_to_format(ia, ja, a, m, c, nnz, k, device=local, variant=variant)
     m_loc = mf.m
 
-    # B: rank 0 owns the host copy (pinned, oracle layout); replicas by ONE broadcast over NVLink
+    # B: every rank holds the seeded host copy (pinned, oracle layout).  Device-resident leg: rank 0 uploads, one NCCL
+    # broadcast replicates.  e2e leg: every rank uploads its 1/N part over its own PCIe link, the parts are exchanged
+    # over NVLink (one broadcast per owner = all-gather)
     x_host = torch.empty(c * k, dtype=torch.float64, pin_memory=True)
-    if rank == 0:
-        x_host.numpy()[:] = dense_b(c, k)
+    x_host.numpy()[:] = dense_b(c, k)        # SPMD: every rank generates the (seeded) inputs, like A above
     y_host = torch.empty(max(m_loc * k, 1), dtype=torch.float64, pin_memory=True)
     x_dev = torch.empty(c * k, dtype=torch.float64, device=dev)      # column-major staging
     b_dev = torch.empty(c * k, dtype=torch.float64, device=dev)      # row-major operand
@@ -310,10 +311,20 @@ def gpu_arm(args, ia, ja, a, m, c, k, nnz, workload_desc):
         def __init__(self, ptr, n):
             self.__cuda_array_interface__ = {"shape": (n,), "typestr": "<f8", "data": (ptr, False), "version": 2}
 
-    def bcast(ptr, count, cuda_stream):
+    def bcast(ptr, count, parts, cuda_stream):
         t = torch.as_tensor(_DevArray(ptr, count), device=dev)
         with torch.cuda.stream(torch.cuda.ExternalStream(cuda_stream, device=dev)):
-            dist.broadcast(t, src=0)
+            if parts == 1:
+                dist.broadcast(t, src=0)
+            elif count % parts == 0:          # every rank's part has the same length: one all-gather = P broadcasts
+                per = count // parts
+                dist.all_gather_into_tensor(t, t[rank * per:(rank + 1) * per])
+            else:
+                per = (count + parts - 1) // parts
+                works = [dist.broadcast(t[r * per:min(count, (r + 1) * per)], src=r, async_op=True)
+                         for r in range(parts) if r * per < count]
+                for w in works:
+                    w.wait()
 
     def e2e_step():
         # the public drop-in call with HOST buffers: upload (root) -> broadcast -> kernel -> download of the
@@ -321,7 +332,7 @@ def gpu_arm(args, ia, ja, a, m, c, k, nnz, workload_desc):
         if world == 1:
             mf.spmm(x_host.numpy(), y_host.numpy()[: m_loc * k], k)
         else:
-            mf.spmm_replicated(x_host.numpy() if rank == 0 else None, y_host.numpy()[: m_loc * k], k, bcast)
+            mf.spmm_replicated(x_host.numpy(), y_host.numpy()[: m_loc * k], k, bcast, x_on_every_rank=True)
     for _ in range(2):
         e2e_step()
     barrier()

@@ -101,17 +101,23 @@ int spmm_b200_create_shard(spmm_b200_t **h,
  * C[:, slice s-1] overlap (SPMM_B200_PIPELINE_COLS=0 turns it off).  Results are identical. */
 int spmm_b200_run(spmm_b200_t *h, const double *x_host, double *y_host, int k, int copy_back);
 
-/* Multi-GPU form of the hot call (one process per GPU, handle from spmm_b200_create_shard).  The
- * only collective on this path is the replication of B; the library does not link a
- * communication library, the caller supplies it: `bcast(ctx, dev_ptr, count, stream)` must enqueue a
- * broadcast of `count` doubles at `dev_ptr` from the root rank on `stream` (a cudaStream_t), e.g.
- * ncclBroadcast(dev_ptr, dev_ptr, count, ncclDouble, root, comm, stream), and return 0.  x_host is
- * the host B on the root rank and NULL elsewhere; y_host receives this rank's row-local C.  For
- * k >= 32 the columns go through in 16-column slices so that upload, broadcast, kernel and the
- * download of C overlap; with bcast == NULL it is spmm_b200_run with the same pipeline. */
-typedef int (*spmm_b200_bcast_fn)(void *ctx, double *dev_ptr, size_t count, void *stream);
+/* Multi-GPU form of the hot call (one process per GPU, handle from spmm_b200_create_shard).  The only
+ * collective on this path is the replication of B; the library does not link a communication
+ * library, the caller supplies it:  `bcast(ctx, dev_ptr, count, parts, stream)` must enqueue on `stream`
+ * (a cudaStream_t) the replication of `count` doubles at `dev_ptr` and return 0:
+ *   parts == 1: broadcast from rank 0, e.g. ncclBroadcast(p, p, count, ncclDouble, 0, comm, stream);
+ *   parts == P: the range is cut into P parts of ceil(count/P) doubles (the last ones shorter or empty), part r
+ *               is valid on rank r; broadcast every part from its owner (ncclBroadcast with root r inside one
+ *               ncclGroupStart/End, or ncclAllGather when count % P == 0).
+ * x_on_every_rank == 0: x_host is the host B on rank 0 and NULL elsewhere; rank 0 uploads all of it.
+ * x_on_every_rank != 0: every rank passes the same host B (SPMD launchers generate their inputs on every rank);
+ *   each rank uploads only ITS part over its own PCIe link and the parts are exchanged over NVLink
+ *   (oracle layout only; otherwise it falls back to the rank-0 upload).
+ * y_host receives this rank's row-local C.  For k >= 32 the columns go through in slices so that upload,
+ * replication, kernel and the download of C overlap; with bcast == NULL it is spmm_b200_run. */
+typedef int (*spmm_b200_bcast_fn)(void *ctx, double *dev_ptr, size_t count, int parts, void *stream);
 int spmm_b200_run_replicated(spmm_b200_t *h, const double *x_host, double *y_host, int k, int copy_back,
-                             spmm_b200_bcast_fn bcast, void *bcast_ctx);
+                             spmm_b200_bcast_fn bcast, void *bcast_ctx, int x_on_every_rank);
 
 /* Optional: page-lock a caller-owned host range (x or y) so that spmm_b200_run copies at full
  * PCIe rate.  The caller promises the range stays mapped until spmm_b200_unregister_host /

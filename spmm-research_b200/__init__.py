@@ -45,8 +45,8 @@ _lib = None
 _vp, _i64, _int, _dbl = C.c_void_p, C.c_int64, C.c_int, C.c_double
 
 
-# int (*spmm_b200_bcast_fn)(void *ctx, double *dev_ptr, size_t count, void *stream)
-BCAST_FN = C.CFUNCTYPE(_int, _vp, _vp, C.c_size_t, _vp)
+# int (*spmm_b200_bcast_fn)(void *ctx, double *dev_ptr, size_t count, int parts, void *stream)
+BCAST_FN = C.CFUNCTYPE(_int, _vp, _vp, C.c_size_t, _int, _vp)
 
 
 class SpmmB200Error(RuntimeError):
@@ -72,7 +72,7 @@ def load_library():
     lib.spmm_b200_create.argtypes = [C.POINTER(_vp), _vp, _vp, _vp, _i64, _i64, _i64, _int, _int, _int, _int]
     lib.spmm_b200_create_shard.argtypes = lib.spmm_b200_create.argtypes + [_int, _int, C.POINTER(_i64), C.POINTER(_i64)]
     lib.spmm_b200_run.argtypes = [_vp, _vp, _vp, _int, _int]
-    lib.spmm_b200_run_replicated.argtypes = [_vp, _vp, _vp, _int, _int, BCAST_FN, _vp]
+    lib.spmm_b200_run_replicated.argtypes = [_vp, _vp, _vp, _int, _int, BCAST_FN, _vp, _int]
     lib.spmm_b200_set_b.argtypes = [_vp, _vp, _int]
     lib.spmm_b200_register_host.argtypes = [_vp, _vp, C.c_size_t]
     lib.spmm_b200_unregister_host.argtypes = [_vp, _vp]
@@ -156,24 +156,26 @@ class MatrixFormat:
         yp = _host(y, np.float64, "y") if copy_back else None
         _check(load_library().spmm_b200_run(self._h, xp, yp, k, 1 if copy_back else 0), "spmm")
 
-    def spmm_replicated(self, x, y, k, bcast, copy_back=True):
-        """Multi-GPU spmm(): x is the host B on the root rank (None elsewhere); `bcast(dev_ptr,
-        count, stream)` must enqueue the broadcast of `count` doubles at `dev_ptr` on the CUDA
-        stream `stream` (e.g. torch.distributed.broadcast under an ExternalStream)."""
+    def spmm_replicated(self, x, y, k, bcast, copy_back=True, x_on_every_rank=False):
+        """Multi-GPU spmm().  x is the host B on the root rank (None elsewhere), or -- with
+        x_on_every_rank -- the same host B on every rank, of which each rank uploads only its part.
+        `bcast(dev_ptr, count, parts, stream)` must enqueue the replication of `count` doubles at
+        `dev_ptr` on the CUDA stream `stream` (parts == 1: broadcast from rank 0; parts == P: part r
+        of ceil(count/P) doubles comes from rank r), see include/spmm_b200.h."""
         k = int(k)
         xp = _host(x, np.float64, "x") if x is not None else None
         yp = _host(y, np.float64, "y") if copy_back else None
         err = []
 
-        def _cb(_ctx, ptr, count, stream):
+        def _cb(_ctx, ptr, count, parts, stream):
             try:
-                bcast(ptr, count, stream)
+                bcast(ptr, count, parts, stream)
                 return 0
             except Exception as e:      # an exception must not unwind through the C frames
                 err.append(e)
                 return 1
         cb = BCAST_FN(_cb) if bcast is not None else C.cast(None, BCAST_FN)
-        rc = load_library().spmm_b200_run_replicated(self._h, xp, yp, k, 1 if copy_back else 0, cb, None)
+        rc = load_library().spmm_b200_run_replicated(self._h, xp, yp, k, 1 if copy_back else 0, cb, None, 1 if x_on_every_rank else 0)
         if err:
             raise err[0]
         _check(rc, "spmm_replicated")

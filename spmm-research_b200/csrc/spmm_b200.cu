@@ -48,6 +48,7 @@ struct spmm_b200 {
 	int sm_count = 148;
 	int64_t m = 0, c = 0, nnz = 0;        // this handle's shard
 	int64_t first_row = 0, m_global = 0;
+	int rank = 0, nranks = 1;             // shard identity (spmm_b200_create_shard)
 	int max_row = 0;                      // longest row of the shard
 	int64_t col_span = 0;                 // max column - min column + 1 over the shard's nonzeros
 	// L2-aware k slicing of the row-split kernel, chosen by timing the candidates on the first calls
@@ -683,6 +684,7 @@ extern "C" int spmm_b200_create_shard(spmm_b200_t** h, const int32_t* row_ptr, c
 	const int64_t nnz_local = (int64_t) row_ptr[r1] - base;
 	rc = create_from_slice(h, row_ptr + r0, col_ind, values, r1 - r0, c, nnz_local, base, k, device, variant, b_layout, sms, r0, m);
 	if (rc) { spmm_b200_destroy(*h); *h = nullptr; }
+	else { (*h)->rank = rank; (*h)->nranks = nranks; }
 	return rc;
 }
 
@@ -901,7 +903,7 @@ static int slice_width(const spmm_b200* h, int k)
 }
 
 static int run_pipelined(spmm_b200* h, const double* x_host, double* y_host, int k, int ks,
-                         spmm_b200_bcast_fn bcast = nullptr, void* bcast_ctx = nullptr)
+                         spmm_b200_bcast_fn bcast = nullptr, void* bcast_ctx = nullptr, int parts = 1)
 {
 	const int S = k / ks;
 	const size_t nb = (size_t) h->c * k;
@@ -926,16 +928,24 @@ static int run_pipelined(spmm_b200* h, const double* x_host, double* y_host, int
 		double* Bs = h->d_B + s * bslice;
 		if (h->b_layout == SPMM_B200_B_COLMAJOR) {
 			// columns [s*ks, (s+1)*ks) are contiguous in x: one H2D, then transpose to row-major c x ks
-			if (x_host)
+			if (x_host && parts > 1) {
+				// every rank holds x: upload only part `rank` of the slice over this GPU's own PCIe link;
+				// the replication callback then fills in the other ranks' parts over NVLink
+				const size_t per = (bslice + parts - 1) / parts;
+				const size_t lo = std::min(bslice, per * (size_t) h->rank), hi = std::min(bslice, lo + per);
+				if (hi > lo)
+					CU_TRY(cudaMemcpyAsync(h->d_x + s * bslice + lo, x_host + s * bslice + lo, (hi - lo) * sizeof(double), cudaMemcpyHostToDevice, h->s_up));
+			} else if (x_host) {
 				CU_TRY(cudaMemcpyAsync(h->d_x + s * bslice, x_host + s * bslice, bslice * sizeof(double), cudaMemcpyHostToDevice, h->s_up));
-			if (bcast && bslice > 0 && bcast(bcast_ctx, h->d_x + s * bslice, bslice, h->s_up)) return SPMM_B200_ECOMM;
+			}
+			if (bcast && bslice > 0 && bcast(bcast_ctx, h->d_x + s * bslice, bslice, parts, h->s_up)) return SPMM_B200_ECOMM;
 			rc = spmm_b200_transpose_b_device(h, h->d_x + s * bslice, Bs, ks, h->s_up);
 			if (rc) return rc;
 		} else {
 			if (x_host)
 				CU_TRY(cudaMemcpy2DAsync(Bs, sizeof(double) * ks, x_host + (size_t) s * ks, sizeof(double) * k, sizeof(double) * ks,
 				                         (size_t) h->c, cudaMemcpyHostToDevice, h->s_up));
-			if (bcast && bslice > 0 && bcast(bcast_ctx, Bs, bslice, h->s_up)) return SPMM_B200_ECOMM;
+			if (bcast && bslice > 0 && bcast(bcast_ctx, Bs, bslice, 1, h->s_up)) return SPMM_B200_ECOMM;
 		}
 		CU_TRY(cudaEventRecord(h->ev_slice[3 * s], h->s_up));
 	}
@@ -982,13 +992,17 @@ extern "C" int spmm_b200_run(spmm_b200_t* h, const double* x_host, double* y_hos
 // replica through the caller's broadcast (ncclBroadcast / torch.distributed.broadcast on the stream
 // handed to it), slice by slice, so that upload, broadcast, kernel and download of C overlap.
 extern "C" int spmm_b200_run_replicated(spmm_b200_t* h, const double* x_host, double* y_host, int k, int copy_back,
-                                        spmm_b200_bcast_fn bcast, void* bcast_ctx)
+                                        spmm_b200_bcast_fn bcast, void* bcast_ctx, int x_on_every_rank)
 {
 	if (!h || k < 1 || (copy_back && !y_host) || (!x_host && !bcast)) return SPMM_B200_EINVAL;
+	if (x_on_every_rank && !x_host) return SPMM_B200_EINVAL;
 	CU_TRY(cudaSetDevice(h->device));
 	int ks = slice_width(h, k);
 	if (ks <= 0) ks = k;
-	return run_pipelined(h, x_host, copy_back ? y_host : nullptr, k, ks, bcast, bcast_ctx);
+	// split uploads need the oracle layout (a slice of x is one contiguous range) and a communicator
+	const int parts = (x_on_every_rank && bcast && h->nranks > 1 && h->b_layout == SPMM_B200_B_COLMAJOR) ? h->nranks : 1;
+	if (x_on_every_rank && parts == 1 && h->rank != 0) x_host = nullptr;      // fall back: only the root uploads
+	return run_pipelined(h, x_host, copy_back ? y_host : nullptr, k, ks, bcast, bcast_ctx, parts);
 }
 
 // ------------------------------------------------------------------------------------------
