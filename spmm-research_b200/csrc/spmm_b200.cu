@@ -154,12 +154,12 @@ __global__ void col_span_kernel(const int32_t* __restrict__ ja, int64_t nnz, int
 
 static int build_rowsplit_plan(spmm_b200* h)
 {
-	// One CTA per nnz-balanced row range.  The V = 4 kernels (k >= 32) hold 64 registers -> 4 resident CTAs per SM:
+	// One CTA per nnz-balanced row range.  The k = 32 kernel <8,4,4> holds 64 registers -> 4 resident CTAs per SM:
 	// 2 waves (8 per SM) is the optimum for a whole matrix, exactly 1 wave (4 per SM) for small shards, where the
 	// tail of a second wave is a visible fraction of the run (profiles/r1_shard_probe.md: 1/8 of cfg2 0.128 -> 0.118 ms;
 	// cfg2 0.787 -> 0.780 ms).  The small-k kernels (32 registers, 8 resident CTAs) keep 4 waves.
 	int dflt = 32;
-	if (h->k >= 32) dflt = (h->nnz / ((int64_t) h->sm_count * 8) < 8192) ? 4 : 8;
+	if (h->k == 32) dflt = (h->nnz / ((int64_t) h->sm_count * 8) < 8192) ? 4 : 8;      // k = 64, 128 measured flat-to-better with more CTAs (r1_gvu_probe.md)
 	const int per_sm = std::max(1, env_int("SPMM_B200_CTAS_PER_SM", dflt));
 	int64_t want = (int64_t) h->sm_count * per_sm;
 	int64_t cap = std::max<int64_t>(1, (h->m + 7) / 8);       // at least ~8 rows per CTA
