@@ -217,10 +217,14 @@ static void launch_rowsplit_gv(const spmm_b200* h, const double* B, double* C, c
 {
 	// B-row gathers in flight per lane group; tuning knob, default from the ncu study in profiles/
 	static const int unroll = env_int("SPMM_B200_UNROLL", 4);
+	constexpr int K = G * V;
 	if (unroll >= 8 && G >= 8)
 		spmm_rowsplit_kernel<G, V, 8, THREADS><<<h->n_ctas, THREADS, 0, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, h->d_cta_rows, ldb, ldc);
 	else if (unroll <= 2)
 		spmm_rowsplit_kernel<G, V, 2, THREADS><<<h->n_ctas, THREADS, 0, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, h->d_cta_rows, ldb, ldc);
+	else if (ldb == K && (uint64_t) h->c * K < (1ull << 32) && env_int("SPMM_B200_CONST_LD", 1))
+		// whole operand: compile-time row stride, 32-bit element offsets
+		spmm_rowsplit_kernel<G, V, 4, THREADS, K><<<h->n_ctas, THREADS, 0, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, h->d_cta_rows, ldb, ldc);
 	else
 		spmm_rowsplit_kernel<G, V, 4, THREADS><<<h->n_ctas, THREADS, 0, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, h->d_cta_rows, ldb, ldc);
 }

@@ -28,11 +28,14 @@ template <int V> struct Frag { double v[V]; };
 // Load this lane's V columns of B row `col`.  Columns are dealt to lanes in pairs:
 // lane l holds columns {2l, 2l+1} (+ 2G for the second pair when V == 4), so every
 // load instruction of the group covers one contiguous span.
-template <int G, int V>
+template <int G, int V, int LD = 0>
 __device__ __forceinline__ Frag<V> load_b(const double* __restrict__ B, int col, int lig, int ldb)
 {
 	Frag<V> f;
-	const double* p = B + (size_t) col * ldb;
+	// LD > 0: the row stride is a compile-time constant and c*LD < 2^32 (checked by the launcher), so the element
+	// offset is ONE 32-bit multiply by a constant instead of a 64-bit multiply by a kernel parameter that the
+	// compiler re-reads from constant memory under every predicate (SASS study in profiles/r1_rowsplit_cfg2_v3.md)
+	const double* p = LD > 0 ? B + (unsigned) col * (unsigned) LD : B + (size_t) col * ldb;
 	if constexpr (V == 1) {
 		f.v[0] = __ldg(p + lig);
 	} else {
@@ -77,7 +80,7 @@ __device__ __forceinline__ double shfl_f64(double v, int src)
 // (col, val) as a same-address load per group; ncu (profiles/r1_rowsplit_cfg2.md) showed those
 // broadcast loads were half of the L1 data-pipe wavefronts, the busiest unit of the kernel.
 // The per-row sum still runs strictly left to right.
-template <int G, int V, int UNROLL, int THREADS>
+template <int G, int V, int UNROLL, int THREADS, int LD = 0>
 __global__ void __launch_bounds__(THREADS)
 spmm_rowsplit_kernel(const int32_t* __restrict__ ia, const int32_t* __restrict__ ja, const double* __restrict__ a,
                      const double* __restrict__ B, double* __restrict__ C,
@@ -111,7 +114,10 @@ spmm_rowsplit_kernel(const int32_t* __restrict__ ia, const int32_t* __restrict__
 			double ca = 0.0;
 			if (lig < rem) { cj = __ldg(ja + j + lig); ca = __ldg(a + j + lig); }
 			const int cnt = min(rem_warp, G);
-			for (int u = 0; u < cnt; u += U) {
+			// at most G/U steps: unrolled so that the shuffle source lanes are immediates
+			#pragma unroll
+			for (int u = 0; u < G; u += U) {
+				if (u >= cnt) break;                                  // warp-uniform
 				int cc[U];
 				double vv[U];
 				Frag<V> bb[U];
@@ -122,7 +128,7 @@ spmm_rowsplit_kernel(const int32_t* __restrict__ ia, const int32_t* __restrict__
 				}
 				#pragma unroll
 				for (int i = 0; i < U; i++)
-					if (u + i < rem) bb[i] = load_b<G, V>(B, cc[i], lig, ldb);
+					if (u + i < rem) bb[i] = load_b<G, V, LD>(B, cc[i], lig, ldb);
 				#pragma unroll
 				for (int i = 0; i < U; i++) {
 					if (u + i < rem) {

@@ -251,3 +251,28 @@ def test_k_sliced_host_pipeline(pkg, L, layout, monkeypatch):
             monkeypatch.delenv("SPMM_B200_PIPELINE_COLS")
             assert max_rel_err(y3, y_ref) <= FP64_TOL
             mf.close()
+
+
+def test_kslice_measurement_keeps_results_identical(pkg, L):
+    """L2-aware k slicing: a matrix whose touched B window (column span x 8k bytes) exceeds
+    192 MB makes the handle time the candidate slice widths on its first 8 device calls.  Every one of those
+    calls -- whatever width it runs -- must produce the oracle's result, and a width must have been chosen."""
+    m, c, k = 3000, 210000, 128                     # span ~210k columns x 1 KB = 215 MB
+    rng = np.random.default_rng(12)
+    deg = rng.integers(1, 9, m)
+    ia = np.zeros(m + 1, np.int32); ia[1:] = np.cumsum(deg)
+    ja = np.concatenate([np.sort(rng.choice(c, d, replace=False)) for d in deg]).astype(np.int32)
+    ja[0], ja[-1] = 0, c - 1                        # pin the span
+    ja[: deg[0]].sort(); ja[-deg[-1]:].sort()
+    a = rng.random(len(ja)) + 0.05
+    x = dense_b(c, k, 4)
+    y_ref = L.spmm_oracle(ia, ja, a, m, c, x, k)
+    mf = pkg.csr_to_format(ia, ja, a, m, c, len(ja), k, variant=pkg.ROWSPLIT)
+    mf.set_b(x, k)
+    assert mf.kslice() == 0
+    for call in range(10):
+        mf.spmm_resident(k)
+        y = np.full(m * k, np.nan); mf.fetch_c(y, k)
+        assert max_rel_err(y, y_ref) <= FP64_TOL, call
+    assert mf.kslice() in (16, 32, 64, 128)
+    mf.close()
