@@ -276,3 +276,44 @@ def test_kslice_measurement_keeps_results_identical(pkg, L):
         assert max_rel_err(y, y_ref) <= FP64_TOL, call
     assert mf.kslice() in (16, 32, 64, 128)
     mf.close()
+
+
+@pytest.mark.parametrize("args,k,expect", [
+    ("2000000 2000000 20 20 gamma random 0.3 10000 0.5 0.5 14", 32, "MERGE"),              # cfg3a: one 200 040-nnz row
+    ("1000000 1000000 50 16.6667 normal diagonal 0.0002 0 1.9 0.95 14", 128, "BCSR_DMMA"),   # cfg4: banded, blocked path
+    ("8388607 8388607 5 1.6667 normal random 0.05 0 0.05 0.05 14", 8, "ROWSPLIT"),           # cfg5-large matrix at k=8 (host arrays stay < 1 GB each)
+])
+def test_full_size_properties_other_configs(pkg, L, pins, args, k, expect):
+    """BASELINE configs[2..4] at full size through size-independent properties: generator pins (the input is the
+    reference's matrix), AUTO's choice of kernel, row sums with B = 1, linearity, and sampled rows vs the oracle."""
+    if not L.have_ref():
+        pytest.skip("reference generator not built")
+    ia, ja, a, m, c = L.generate(args)
+    nnz = len(ja)
+    if args in pins:
+        assert L.fnv(ia) == pins[args]["fnv_row_ptr"] and L.fnv(ja) == pins[args]["fnv_col_ind"]
+    mf = pkg.csr_to_format(ia, ja, a, m, c, nnz, k)
+    assert mf.format_name.endswith(expect), mf.format_name
+    y1 = np.empty(m * k); mf.spmm(np.ones(c * k), y1, k)
+    starts = ia[:-1].astype(np.int64)
+    rowsum = np.add.reduceat(np.concatenate([a, [0.0]]), np.minimum(starts, nnz))
+    rowsum[ia[1:] == ia[:-1]] = 0.0
+    # merge-path and the blocked kernels reorder the sum of a row: tolerance against sum |a|
+    scale = np.maximum(np.abs(rowsum), 1e-300)
+    for col in (0, k - 1):
+        assert np.max(np.abs(y1.reshape(m, k)[:, col] - rowsum) / scale) <= 1e-11
+    x1, x2 = dense_b(c, k, 1), dense_b(c, k, 2)
+    ya = np.empty(m * k); mf.spmm(x1, ya, k)
+    yb = np.empty(m * k); mf.spmm(x2, yb, k)
+    yc = np.empty(m * k); mf.spmm(x1 + 2.0 * x2, yc, k)
+    assert max_rel_err(yc, ya + 2.0 * yb) <= 1e-10
+    mf.close()
+    rows = np.random.default_rng(0).choice(m, 1500, replace=False); rows.sort()
+    if expect == "MERGE":
+        rows[0] = int(np.argmax(np.diff(ia)))        # include the monster row
+        rows.sort()
+    sub_ia = np.zeros(len(rows) + 1, np.int32)
+    sub_ia[1:] = np.cumsum(ia[rows + 1] - ia[rows])
+    idx = np.concatenate([np.arange(ia[r], ia[r + 1]) for r in rows])
+    y_ref = L.spmm_oracle(sub_ia, ja[idx].copy(), a[idx].copy(), len(rows), c, x1, k)
+    assert max_rel_err(ya.reshape(m, k)[rows].ravel(), y_ref) <= 1e-11
