@@ -513,7 +513,7 @@ static int launch_spmm(spmm_b200* h, const double* B, double* C, int k, cudaStre
 		TRY_GVU(8, 4, 2); TRY_GVU(8, 4, 4); TRY_GVU(8, 4, 8);
 		TRY_GVU(8, 8, 2); TRY_GVU(8, 8, 4); TRY_GVU(16, 4, 2); TRY_GVU(16, 4, 4);
 		TRY_GVU(16, 8, 2); TRY_GVU(16, 8, 4); TRY_GVU(32, 4, 2); TRY_GVU(32, 4, 4);
-		TRY_GVU(8, 2, 4); TRY_GVU(8, 2, 8); TRY_GVU(4, 4, 4);
+		TRY_GVU(8, 2, 4); TRY_GVU(8, 2, 8); TRY_GVU(4, 4, 4); TRY_GVU(2, 2, 2); TRY_GVU(4, 1, 4); TRY_GVU(2, 1, 2); TRY_GVU(4, 2, 4); TRY_GVU(2, 4, 2);
 		else ok = false;
 #undef TRY_GVU
 		if (ok) {
@@ -524,7 +524,7 @@ static int launch_spmm(spmm_b200* h, const double* B, double* C, int k, cudaStre
 	switch (k) {
 	case 1:   launch_smallk<1>(h, B, C, s); break;
 	case 2:   launch_smallk<2>(h, B, C, s); break;
-	case 4:   launch_smallk<4>(h, B, C, s); break;
+	case 4:   launch_rowsplit_gv<2, 2>(h, B, C, s); break;      // 16 rows per warp: cfg2 0.496 -> 0.380 ms, cfg5-large 0.440 -> 0.284 ms vs the small-k kernel
 	// lane-group shapes from the sweep in profiles/r1_gvu_probe.md: V = 4 columns per lane (two 16-byte loads)
 	// makes a group of 8 lanes cover one 128-byte line per load and halves the shuffle traffic per nonzero
 	// (cfg2: k=32 0.935 -> 0.786 ms, k=64 1.563 -> 1.336 ms); V = 8 costs too many registers
