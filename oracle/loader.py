@@ -256,3 +256,85 @@ def spmm_ref(ia, ja, a, m, c, x, k):
     y = np.empty(m * k, dtype=np.float64)
     ref().ref_spmm_csr(ia, ja, a, m, c, len(ja), x, y, k)
     return y
+
+
+# ---- N4: sparse-attention pipeline (pipeline_code_bench) ---------------------------------------------------
+
+def _pipeline_oracle():
+    lib = oracle()
+    if not hasattr(lib, "_typed_pipeline"):
+        lib.oracle_csrmm_rowmajor.argtypes = [_i32p, _i32p, _f64p, C.c_long, C.c_long, _f64p, _f64p]
+        lib.oracle_csrmm_rowmajor.restype = None
+        lib.oracle_sddmm.argtypes = [_i32p, _i32p, _f64p, C.c_long, C.c_long, _f64p, _f64p, _f64p, C.c_int]
+        lib.oracle_sddmm.restype = None
+        lib.oracle_softmax.argtypes = [_f64p, C.c_long]
+        lib.oracle_softmax.restype = None
+        lib.oracle_softmax_rows.argtypes = [_i32p, C.c_long, _f64p]
+        lib.oracle_softmax_rows.restype = None
+        lib._typed_pipeline = True
+    return lib
+
+
+def csrmm_oracle(ia, ja, a, m, n, x):
+    """y (m x n row-major) = CSR(ia, ja, a) * x (k x n row-major)."""
+    y = np.empty(m * n, dtype=np.float64)
+    _pipeline_oracle().oracle_csrmm_rowmajor(ia, ja, a, m, n, np.ascontiguousarray(x, dtype=np.float64).ravel(), y)
+    return y
+
+
+def sddmm_oracle(ia, ja, mask, m, n, Q, K, mode=0):
+    y = np.empty(max(len(ja), 1), dtype=np.float64)
+    _pipeline_oracle().oracle_sddmm(ia, ja, mask, m, n, np.ascontiguousarray(Q).ravel(), np.ascontiguousarray(K).ravel(), y, mode)
+    return y[:len(ja)]
+
+
+def softmax_oracle(y, ia=None):
+    """ia None: the reference's softmax over the whole array; else row by row."""
+    v = np.array(y, dtype=np.float64, copy=True)
+    if ia is None:
+        _pipeline_oracle().oracle_softmax(v, len(v))
+    else:
+        _pipeline_oracle().oracle_softmax_rows(ia, len(ia) - 1, v)
+    return v
+
+
+def pipeline_oracle(mask, weights, x, n, mode=0, softmax=0):
+    """mask = (ia, ja, a, m); weights = {'K'|'Q'|'V': (ia, ja, a)}.  Returns dict K, Q, V, y, y_final."""
+    mia, mja, ma, m = mask
+    out = {t: csrmm_oracle(*weights[t], m, n, x) for t in "KQV"}
+    y = sddmm_oracle(mia, mja, ma, m, n, out["Q"], out["K"], mode)
+    if softmax:
+        y = softmax_oracle(y, None if softmax == 1 else mia)
+    out["y"] = y
+    out["y_final"] = csrmm_oracle(mia, mja, np.ascontiguousarray(y), m, n, out["V"])
+    return out
+
+
+def have_pipeline_ref():
+    return os.path.exists(os.path.join(HERE, "_ref", "libpipeline_ref.so"))
+
+
+def pipeline_ref_lib():
+    lib = _load(os.path.join(HERE, "_ref", "libpipeline_ref.so"))
+    if not hasattr(lib, "_typed"):
+        csr = [_i32p, _i32p, _f64p]
+        lib.ref_pipeline.argtypes = csr + [C.c_long, C.c_long, C.c_int] + csr * 3 + [C.c_long] + [_f64p] * 6 + [C.c_int]
+        lib.ref_pipeline.restype = None
+        lib.ref_sddmm.argtypes = csr + [C.c_long, C.c_long, C.c_int, _f64p, _f64p, _f64p]
+        lib.ref_sddmm.restype = None
+        lib.ref_softmax.argtypes = [_f64p, C.c_int]
+        lib.ref_softmax.restype = None
+        lib._typed = True
+    return lib
+
+
+def pipeline_ref(mask, weights, x, n, kdim, softmax=0):
+    """The reference's own csr_to_format / spmm('K','Q','V') / sddmm / spmm('final') sequence."""
+    mia, mja, ma, m = mask
+    nnz = len(mja)
+    K, Q, V, yf = (np.zeros(m * n) for _ in range(4))
+    y = np.zeros(max(nnz, 1))
+    xx = np.ascontiguousarray(x, dtype=np.float64).ravel()
+    pipeline_ref_lib().ref_pipeline(mia, mja, ma, m, nnz, n, *weights["K"], *weights["Q"], *weights["V"], kdim,
+                                    xx, K, Q, V, y, yf, softmax)
+    return {"K": K, "Q": Q, "V": V, "y": y[:nnz], "y_final": yf}

@@ -379,3 +379,80 @@ void oracle_spmm_csr_f32(const int32_t *ia, const int32_t *ja, const float *a,
 		}
 	}
 }
+
+/* ---------------------------------------------------------------------------
+ * N4: sparse-attention pipeline (benchmark_code/CPU/AMD/pipeline_code_bench).
+ *
+ * oracle_csrmm_rowmajor -- Matrix_Format::spmm of sddmm_taco_naive.cpp:232-275.  The reference calls
+ *   mkl_dcsrmm('N', m, n, k, alpha = 1, "GLNC", a, ja, ia, ia+1, x, ldb = n, beta = 0, y, ldc = n).
+ *   Intel MKL (oneMKL Sparse BLAS level 3, deprecated mkl_?csrmm) is a third-party dependency absent from
+ *   /root/reference; its published contract: C := alpha*A*B + beta*C, and with matdescra[3] = 'C' zero-based
+ *   indices and ROW-major B (k x n) and C (m x n).  The summation order inside MKL is unspecified; this
+ *   restatement sums each row left to right like the reference's own gold (spmm_helper, sddmm_bench.cpp:
+ *   130-162), so agreement with an MKL build is to rounding (1e-12 relative), not bit for bit.
+ * ------------------------------------------------------------------------- */
+void oracle_csrmm_rowmajor(const int32_t *ia, const int32_t *ja, const double *a,
+                           long m, long n, const double *x, double *y)
+{
+	#pragma omp parallel for
+	for (long i = 0; i < m; i++) {
+		for (long d = 0; d < n; d++) {
+			double sum = 0;
+			for (long j = ia[i]; j < ia[i + 1]; j++)
+				sum = __builtin_fma(a[j], x[(long) ja[j] * n + d], sum);   /* what gcc -O3 -mfma makes of `sum += a*x` in the scalar gather loop */
+			y[i * n + d] = sum;
+		}
+	}
+}
+
+/* oracle_sddmm -- Matrix_Format::sddmm, sddmm_taco_naive.cpp:294-303 (compute_csr: y[] = 0, then compute2) and
+ *   compute2, :96-133:
+ *       for row i, for nonzero p of row i (column kA = ja[p]):
+ *           for d < n:  y[p] += Q[i*n + d] * K[i*n + d]          <- BOTH factors at the output row (pO2, :121)
+ *           y[p] *= mask[p]
+ *   mode 0 restates exactly that.  mode 1 is the sampled product the variable names describe (pD2 = kA*n + d
+ *   is computed at :117 and left unused): K is read at row ja[p].
+ *   Rounding: gcc -O3 -mfma vectorises the reference's d loop as rounded products (vmulpd) followed by in-order
+ *   adds, i.e. NO fused multiply-add anywhere in the sum (checked against oracle/_ref/libpipeline_ref.so for
+ *   widths that are and are not multiples of the vector length); contraction is therefore switched off here. */
+__attribute__((optimize("-ffp-contract=off")))
+void oracle_sddmm(const int32_t *ia, const int32_t *ja, const double *mask, long m, long n,
+                  const double *Q, const double *K, double *y, int mode)
+{
+	#pragma omp parallel for
+	for (long i = 0; i < m; i++) {
+		for (long p = ia[i]; p < ia[i + 1]; p++) {
+			const double *krow = K + (mode ? (long) ja[p] : i) * n;
+			double s = 0.0;
+			for (long d = 0; d < n; d++)
+				s += Q[i * n + d] * krow[d];
+			y[p] = s * mask[p];
+		}
+	}
+}
+
+/* oracle_softmax -- softmax(input, size), sddmm_taco_naive.cpp:207-225 (its call sites are commented out,
+ *   :231 and sddmm_bench.cpp:279): one softmax over the whole value array, sequential sums. */
+#include <math.h>
+void oracle_softmax(double *v, long size)
+{
+	if (size <= 0)
+		return;
+	double mx = v[0], sum = 0.0;
+	for (long i = 1; i < size; i++)
+		if (v[i] > mx)
+			mx = v[i];
+	for (long i = 0; i < size; i++) {
+		v[i] = exp(v[i] - mx);
+		sum += v[i];
+	}
+	for (long i = 0; i < size; i++)
+		v[i] /= sum;
+}
+
+/* row-wise variant (not in the reference): the same three passes per mask row */
+void oracle_softmax_rows(const int32_t *ia, long m, double *v)
+{
+	for (long i = 0; i < m; i++)
+		oracle_softmax(v + ia[i], ia[i + 1] - ia[i]);
+}

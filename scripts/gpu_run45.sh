@@ -1,0 +1,7 @@
+#!/bin/bash
+mkdir -p gpurun_out
+timeout 900 python -m pytest tests/test_pipeline.py tests/test_abi.py -m gpu -q > gpurun_out/r45_pytest.log 2>&1; echo "pytest rc=$?" >> gpurun_out/r45_pytest.log
+tail -15 gpurun_out/r45_pytest.log
+timeout 600 python scripts/pipeline_probe.py 8192 64 0.05 16 > gpurun_out/r45_probe_8k.log 2>&1; tail -16 gpurun_out/r45_probe_8k.log
+timeout 600 python scripts/pipeline_probe.py 16384 64 0.05 16 > gpurun_out/r45_probe_16k.log 2>&1; tail -16 gpurun_out/r45_probe_16k.log
+timeout 600 python scripts/pipeline_probe.py 8192 128 0.05 16 > gpurun_out/r45_probe_8k_n128.log 2>&1; tail -16 gpurun_out/r45_probe_8k_n128.log

@@ -18,7 +18,8 @@ import numpy as np
 
 __all__ = ["csr_to_format", "csr_to_format_f32", "MatrixFormatF32", "coo_to_csr", "read_mtx", "read_smtx", "MatrixFormat", "partition", "shard_slices", "statistics_print_labels", "load_library",
            "SpmmB200Error", "ROWSPLIT", "MERGE", "BCSR", "AUTO", "BCSR_FMA", "B_COLMAJOR", "B_ROWMAJOR",
-           "PART_ROWS", "PART_NNZ", "PART_MERGE", "LIB_PATH", "EXPORTS"]
+           "PART_ROWS", "PART_NNZ", "PART_MERGE", "LIB_PATH", "EXPORTS",
+           "PipelineFormat", "csr_to_pipeline_format", "SDDMM_REFERENCE", "SDDMM_ATTENTION", "SDDMM_ATTENTION_ORDERED"]
 
 ROWSPLIT, MERGE, BCSR, AUTO, BCSR_FMA = 0, 1, 2, 3, 4
 B_COLMAJOR, B_ROWMAJOR = 0, 1
@@ -39,6 +40,11 @@ EXPORTS = [
     "spmm_b200_fetch_c_f32", "spmm_b200_rows_f32", "spmm_b200_nnz_f32", "spmm_b200_launch_count_f32",
     "spmm_b200_last_kernel_ms_f32", "spmm_b200_destroy_f32",
     "spmm_b200_device_count", "spmm_b200_read_mtx", "spmm_b200_read_smtx", "spmm_b200_free", "spmm_b200_check_accuracy",
+    # include/spmm_b200_pipeline.h
+    "spmm_b200_pipeline_create", "spmm_b200_pipeline_spmm", "spmm_b200_pipeline_sddmm", "spmm_b200_pipeline_softmax",
+    "spmm_b200_pipeline_final", "spmm_b200_pipeline_set_weight", "spmm_b200_pipeline_attention",
+    "spmm_b200_pipeline_device_ptr", "spmm_b200_pipeline_last_kernel_ms", "spmm_b200_pipeline_launch_count",
+    "spmm_b200_pipeline_destroy",
 ]
 
 _lib = None
@@ -111,6 +117,17 @@ def load_library():
     lib.spmm_b200_launch_count_f32.argtypes = [_vp]; lib.spmm_b200_launch_count_f32.restype = _i64
     lib.spmm_b200_last_kernel_ms_f32.argtypes = [_vp]; lib.spmm_b200_last_kernel_ms_f32.restype = _dbl
     lib.spmm_b200_destroy_f32.argtypes = [_vp]; lib.spmm_b200_destroy_f32.restype = None
+    lib.spmm_b200_pipeline_create.argtypes = [C.POINTER(_vp), _vp, _vp, _vp, _i64, _i64, _int, _int]
+    lib.spmm_b200_pipeline_spmm.argtypes = [_vp, C.c_char, _i64, _i64, _int, _vp, _vp, _vp, _vp, _vp]
+    lib.spmm_b200_pipeline_sddmm.argtypes = [_vp, _vp, _int]
+    lib.spmm_b200_pipeline_softmax.argtypes = [_vp, _vp, _int]
+    lib.spmm_b200_pipeline_final.argtypes = [_vp, _vp]
+    lib.spmm_b200_pipeline_set_weight.argtypes = [_vp, C.c_char, _i64, _i64, _i64, _vp, _vp, _vp]
+    lib.spmm_b200_pipeline_attention.argtypes = [_vp, _vp, _vp, _int, _int]
+    lib.spmm_b200_pipeline_device_ptr.argtypes = [_vp, C.c_char]; lib.spmm_b200_pipeline_device_ptr.restype = _vp
+    lib.spmm_b200_pipeline_last_kernel_ms.argtypes = [_vp]; lib.spmm_b200_pipeline_last_kernel_ms.restype = _dbl
+    lib.spmm_b200_pipeline_launch_count.argtypes = [_vp]; lib.spmm_b200_pipeline_launch_count.restype = _i64
+    lib.spmm_b200_pipeline_destroy.argtypes = [_vp]; lib.spmm_b200_pipeline_destroy.restype = None
     _lib = lib
     return lib
 
@@ -292,6 +309,94 @@ class MatrixFormatF32:
             self.close()
         except Exception:
             pass
+
+
+SDDMM_REFERENCE, SDDMM_ATTENTION, SDDMM_ATTENTION_ORDERED = 0, 1, 2
+
+
+class PipelineFormat:
+    """Mirror of the pipeline bench's `struct Matrix_Format` (pipeline_code_bench/sddmm_kernel.h:9-31):
+    fields m, n, nnz; methods spmm(type, m, k, n, ia, ja, a, x, y), sddmm(y).  Built from the attention
+    mask by csr_to_pipeline_format (csr_to_format(row_ptr, col_ind, values, m, nnz, n), sddmm_kernel.h:32).
+    Host numpy arrays in and out; K, Q, V, y stay on the device between calls."""
+
+    format_name = "B200_CSR_PIPELINE"
+
+    def __init__(self, handle, m, nnz, n, keep):
+        self._h = handle
+        self.m, self.nnz, self.n = int(m), int(nnz), int(n)
+        self._keep = list(keep)          # the C side remembers host pointers: keep the arrays alive
+
+    def spmm(self, type, m, k, n, ia, ja, a, x, y):
+        """y = CSR(ia, ja, a; m x k) * x (k x n row-major).  type 'K'|'Q'|'V' also keeps the result on the
+        device for sddmm(); any other type (the harness passes 'final') is a plain product."""
+        t = type.encode()[:1] if isinstance(type, str) else bytes(type)[:1]
+        yp = None if y is None else _host(y, np.float64, "y")
+        if y is not None and y.size < m * n:
+            raise ValueError("y holds fewer than m*n values")
+        if x.size < k * n:
+            raise ValueError("x holds fewer than k*n values")
+        if t in (b"K", b"Q", b"V"):
+            self._keep += [ia, ja, a]
+        _check(load_library().spmm_b200_pipeline_spmm(self._h, t, m, k, n, _host(ia, np.int32, "ia"),
+               _host(ja, np.int32, "ja") if len(ja) else None, _host(a, np.float64, "a") if len(a) else None,
+               _host(x, np.float64, "x") if x.size else None, yp), "spmm_b200_pipeline_spmm")
+
+    def sddmm(self, y=None, mode=SDDMM_REFERENCE):
+        if y is not None and y.size < self.nnz:
+            raise ValueError("y holds fewer than nnz values")
+        _check(load_library().spmm_b200_pipeline_sddmm(self._h, None if y is None else _host(y, np.float64, "y"), mode),
+               "spmm_b200_pipeline_sddmm")
+
+    def softmax(self, y=None, rowwise=False):
+        _check(load_library().spmm_b200_pipeline_softmax(self._h, None if y is None else _host(y, np.float64, "y"), int(bool(rowwise))),
+               "spmm_b200_pipeline_softmax")
+
+    def final(self, y_final):
+        if y_final.size < self.m * self.n:
+            raise ValueError("y_final holds fewer than m*n values")
+        _check(load_library().spmm_b200_pipeline_final(self._h, _host(y_final, np.float64, "y_final")), "spmm_b200_pipeline_final")
+
+    def set_weight(self, type, m, k, ia, ja, a):
+        self._keep += [ia, ja, a]
+        _check(load_library().spmm_b200_pipeline_set_weight(self._h, type.encode()[:1], m, k, len(ja), _host(ia, np.int32, "ia"),
+               _host(ja, np.int32, "ja") if len(ja) else None, _host(a, np.float64, "a") if len(a) else None),
+               "spmm_b200_pipeline_set_weight")
+
+    def attention(self, x, y_final, mode=SDDMM_REFERENCE, softmax=0):
+        """The whole layer, one upload of x and one download of y_final."""
+        _check(load_library().spmm_b200_pipeline_attention(self._h, _host(x, np.float64, "x") if x.size else None,
+               _host(y_final, np.float64, "y_final"), mode, softmax), "spmm_b200_pipeline_attention")
+
+    def device_ptr(self, which):
+        return load_library().spmm_b200_pipeline_device_ptr(self._h, which.encode()[:1])
+
+    def last_kernel_ms(self):
+        return load_library().spmm_b200_pipeline_last_kernel_ms(self._h)
+
+    def launch_count(self):
+        return load_library().spmm_b200_pipeline_launch_count(self._h)
+
+    def close(self):
+        if self._h:
+            load_library().spmm_b200_pipeline_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def csr_to_pipeline_format(row_ptr, col_ind, values, m, nnz, n, *, device=0):
+    """csr_to_format(row_ptr, col_ind, values, m, nnz, n) of the pipeline bench (sddmm_kernel.h:32): the format
+    is built from the m x m attention mask; n is the dense width."""
+    h = _vp()
+    _check(load_library().spmm_b200_pipeline_create(C.byref(h), _host(row_ptr, np.int32, "row_ptr"),
+           _host(col_ind, np.int32, "col_ind") if nnz else None, _host(values, np.float64, "values") if nnz else None,
+           m, nnz, n, device), "spmm_b200_pipeline_create")
+    return PipelineFormat(h, m, nnz, n, (row_ptr, col_ind, values))
 
 
 def csr_to_format_f32(row_ptr, col_ind, values, m, n, nnz, k, *, device=0, b_layout=B_COLMAJOR, rank=None, nranks=None):

@@ -1271,3 +1271,8 @@ extern "C" int spmm_b200_device_count(void)
 // fp32 entry points (the reference's "_f" builds)
 // ------------------------------------------------------------------------------------------
 #include "spmm_b200_f32.inl"
+
+// ------------------------------------------------------------------------------------------
+// sparse-attention pipeline entry points (include/spmm_b200_pipeline.h)
+// ------------------------------------------------------------------------------------------
+#include "spmm_b200_pipeline.inl"

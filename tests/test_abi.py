@@ -12,9 +12,14 @@ from conftest import ROOT, random_csr
 
 
 def _header_symbols():
-    src = open(os.path.join(ROOT, "include", "spmm_b200.h")).read()
-    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
-    return sorted(set(re.findall(r"\b(spmm_b200_[a-z_0-9]+)\s*\(", src)))
+    syms = set()
+    for name in sorted(os.listdir(os.path.join(ROOT, "include"))):      # spmm_b200.h, spmm_b200_pipeline.h
+        if not name.endswith(".h"):
+            continue
+        src = open(os.path.join(ROOT, "include", name)).read()
+        src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+        syms |= set(re.findall(r"\b(spmm_b200_[a-z_0-9]+)\s*\(", src))
+    return sorted(syms)
 
 
 def test_library_exports_every_declared_symbol(pkg):
@@ -22,7 +27,7 @@ def test_library_exports_every_declared_symbol(pkg):
     syms = _header_symbols()
     assert len(syms) >= 18
     for s in syms:
-        assert hasattr(lib, s), f"{s} declared in include/spmm_b200.h but not exported"
+        assert hasattr(lib, s), f"{s} declared in include/*.h but not exported"
     assert sorted(pkg.EXPORTS) == syms
 
 
@@ -55,6 +60,16 @@ def test_argument_validation(pkg):
     assert lib.spmm_b200_partition(rp, 10, len(ja), 0, pkg.PART_NNZ, None, 0) == -1
     assert lib.spmm_b200_rows(None) == -1
     lib.spmm_b200_destroy(None)   # must be a no-op
+    # pipeline entry points (include/spmm_b200_pipeline.h)
+    assert lib.spmm_b200_pipeline_create(None, rp, ci, va, 10, len(ja), 8, 0) == -1
+    assert lib.spmm_b200_pipeline_create(C.byref(h), None, ci, va, 10, len(ja), 8, 0) == -1
+    assert lib.spmm_b200_pipeline_create(C.byref(h), rp, ci, va, 10, len(ja), 0, 0) == -1
+    assert lib.spmm_b200_pipeline_create(C.byref(h), rp, ci, va, 10, 2 ** 31, 8, 0) == -5
+    assert lib.spmm_b200_pipeline_sddmm(None, None, 0) == -1
+    assert lib.spmm_b200_pipeline_final(None, None) == -1
+    assert lib.spmm_b200_pipeline_attention(None, None, None, 0, 0) == -1
+    assert lib.spmm_b200_pipeline_launch_count(None) == 0
+    lib.spmm_b200_pipeline_destroy(None)
 
 
 def test_no_cpu_fallback(pkg):
