@@ -24,6 +24,9 @@ void mkl_scsrmm(const char *transa, const MKL_INT *m, const MKL_INT *n, const MK
                 const char *matdescra, const float *val, const MKL_INT *indx, const MKL_INT *pntrb,
                 const MKL_INT *pntre, const float *b, const MKL_INT *ldb, const float *beta, float *c,
                 const MKL_INT *ldc);
+void mkl_set_dynamic(int flag);
+void mkl_set_num_threads(int n);
+int mkl_get_max_threads(void);
 #ifdef __cplusplus
 }
 #endif

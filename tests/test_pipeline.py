@@ -268,3 +268,59 @@ def test_gpu_pipeline_full_size_properties(pkg, L):
     sums = np.add.reduceat(y, mia[:-1])
     assert np.abs(sums - 1).max() < 1e-12
     MF2.close()
+
+
+# ---------------------------------------------------------------- the reference's own pipeline harness
+
+HARNESS_ENV = dict(USE_PROCESSES="0", USE_ARTIFICIAL_MATRICES="0", USE_DLCM_MATRICES="1", COOLDOWN="0", RAPL_REGISTERS="0",
+                   OMP_NUM_THREADS="4", BAND_SIZE="8", SPARSE_ATTENTION_TYPE="band_and_random",
+                   SDDMM_SPARSIFICATION_TYPE="none", SPARSITY="0.05", L_SPARSITY="0.1")
+
+
+def run_pipeline_harness(exe, tmp_path, m, kdim, n, extra_env=None):
+    """Runs pipeline_code_bench/sddmm_bench.cpp's main (built by `make -C oracle pipeline_harness`) on three DLMC
+    weight files; returns (stdout, fields of the CSV line it writes to stderr)."""
+    import subprocess
+    files = []
+    for i, t in enumerate("kqv"):
+        ia, ja, _ = random_csr(m, kdim, 8.0, 50 + i)
+        path = os.path.join(str(tmp_path), f"w_{t}.smtx")
+        with open(path, "w") as f:
+            f.write(f"{m}, {kdim}, {len(ja)}\n" + " ".join(map(str, ia)) + "\n" + " ".join(map(str, ja)) + "\n")
+        files.append(path)
+    env = dict(os.environ, NUM_COLS=str(n), **HARNESS_ENV)
+    env.update(extra_env or {})
+    r = subprocess.run([exe] + files, env=env, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert "failed" not in r.stdout
+    line = [ln for ln in r.stderr.splitlines() if ln.startswith(files[0])]
+    assert len(line) == 1, r.stderr
+    return r.stdout, line[0].split(",")
+
+
+def harness_mask_nnz(m, band=8, fill=0.05):
+    """band_and_random (sddmm_mask.h:47-76): the band |i-j| < band first, then random fill up to fill*m*m."""
+    return max(m * (2 * band - 1) - band * (band - 1), int(fill * m * m))
+
+
+def test_reference_pipeline_harness_runs_on_cpu(tmp_path):
+    exe = os.path.join(os.path.dirname(GOLDEN), "..", "oracle", "_ref", "sddmm_taco_naive_d.exe")
+    if not os.path.exists(exe):
+        pytest.skip("oracle/_ref/sddmm_taco_naive_d.exe not built (make -C oracle pipeline_harness)")
+    out, f = run_pipeline_harness(exe, tmp_path, 256, 192, 16)
+    assert (int(f[2]), int(f[3]), int(f[4])) == (16, 256, 192)           # input_columns, csr_m, csr_k
+    assert (int(f[-3]), int(f[-2]), int(f[-1])) == (256, 16, harness_mask_nnz(256))   # MF->m, MF->n, MF->nnz (the mask)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("mode", ["0", "1"])
+def test_gpu_reference_pipeline_harness_runs_our_plugin(tmp_path, mode):
+    """The UNCHANGED reference harness objects linked with csrc/sddmm_kernel_b200.cpp: csr_to_format(mask),
+    spmm('K'|'Q'|'V'), sddmm, spmm('final') all land in the C ABI."""
+    exe = os.path.join(os.path.dirname(GOLDEN), "..", "oracle", "_ref", "sddmm_b200_d.exe")
+    if not os.path.exists(exe):
+        pytest.skip("oracle/_ref/sddmm_b200_d.exe not built (make -C oracle pipeline_harness)")
+    out, f = run_pipeline_harness(exe, tmp_path, 2048, 1024, 64, {"SPMM_B200_SDDMM_MODE": mode})
+    assert (int(f[2]), int(f[3]), int(f[4])) == (64, 2048, 1024)
+    assert (int(f[-3]), int(f[-2]), int(f[-1])) == (2048, 64, harness_mask_nnz(2048))
+    assert float(f[17]) > 0                                               # gflops of the whole pipeline
