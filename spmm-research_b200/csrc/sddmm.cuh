@@ -88,8 +88,8 @@ sddmm_attention_kernel(const int32_t* __restrict__ ia, const int32_t* __restrict
 // G x G partials are reduced with a transposing butterfly (G-1 shuffle-adds per lane for G results instead of
 // G log G), which leaves nonzero t's sum on lane t -- the y store is coalesced.  The sum order is a tree, not the
 // CPU loop's left-to-right order: results agree with the ordered kernels to rounding (tests: 1e-12, norm-wise).
-template <int G, int V, int U, int THREADS>
-__global__ void __launch_bounds__(THREADS)
+template <int G, int V, int U, int THREADS, int MINB = 1>
+__global__ void __launch_bounds__(THREADS, MINB)
 sddmm_attention_group_kernel(const int32_t* __restrict__ ia, const int32_t* __restrict__ ja, const double* __restrict__ mask_a,
                              const double* __restrict__ Q, const double* __restrict__ K,
                              double* __restrict__ y, int64_t m)

@@ -138,12 +138,17 @@ static int pipe_sddmm_launch(spmm_b200_pipeline* p, int mode)
 			// always in ORDERED mode -- a kernel that keeps the CPU loop's left-to-right order
 			const bool fast = mode == SPMM_B200_SDDMM_ATTENTION && env_int("SPMM_B200_SDDMM_GROUP", 1);
 			const int gw = (int) std::min<int64_t>((p->m + THREADS / 32 - 1) / (THREADS / 32), (int64_t) p->mask->sm_count * 64);
-#define SDDMM_GROUP(G, V, U) sb200::sddmm_attention_group_kernel<G, V, U, THREADS><<<gw, THREADS, 0, p->stream>>>( \
+#define SDDMM_GROUP(G, V, U, MINB) sb200::sddmm_attention_group_kernel<G, V, U, THREADS, MINB><<<gw, THREADS, 0, p->stream>>>( \
 				p->mask->d_ia, p->mask->d_ja, p->d_mask_a, p->w[1].d_out, p->w[0].d_out, p->mask->d_a, p->m)
-			if (fast && p->n == 16) SDDMM_GROUP(4, 4, 4);
-			else if (fast && p->n == 32) SDDMM_GROUP(8, 4, 4);
-			else if (fast && p->n == 64) SDDMM_GROUP(16, 4, 4);
-			else if (fast && p->n == 128) SDDMM_GROUP(16, 8, 2);
+			// U = 2 rows in flight and >= 4 CTAs per SM (64 registers) measured best of {U 2,4,8} x {1..4 CTAs}:
+			// profiles/r1_pipeline_probe.md
+			const int tune = env_int("SPMM_B200_SDDMM_TUNE", 0);     // experiment knob for n = 64: U*10 + min CTAs per SM
+			if (fast && p->n == 16) SDDMM_GROUP(4, 4, 2, 4);
+			else if (fast && p->n == 32) SDDMM_GROUP(8, 4, 2, 4);
+			else if (fast && p->n == 64 && tune == 42) SDDMM_GROUP(16, 4, 4, 2);
+			else if (fast && p->n == 64 && tune == 22) SDDMM_GROUP(16, 4, 2, 2);
+			else if (fast && p->n == 64) SDDMM_GROUP(16, 4, 2, 4);
+			else if (fast && p->n == 128) SDDMM_GROUP(16, 8, 2, 2);
 #undef SDDMM_GROUP
 			else if (p->n % sb200::SDDMM_CH == 0 && p->n <= 1024 && env_int("SPMM_B200_SDDMM_STAGED", 1)) {
 				// K rows staged through shared memory (sddmm.cuh): 4 warps per CTA, 32 x 34 + n doubles per warp
