@@ -29,6 +29,9 @@ struct spmm_b200_pipeline {
 	bool have_y = false, have_final = false;
 	cudaStream_t stream = nullptr;
 	cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+	// attention(): the three projections run side by side, V's overlaps the SDDMM (fork / join on events)
+	cudaStream_t s_side[3] = {nullptr, nullptr, nullptr};
+	cudaEvent_t ev_fork = nullptr, ev_done[3] = {nullptr, nullptr, nullptr};
 	bool timed = false;
 	int64_t own_launches = 0;
 };
@@ -71,6 +74,11 @@ extern "C" void spmm_b200_pipeline_destroy(spmm_b200_pipeline_t* p)
 	if (p->d_part) cudaFree(p->d_part);
 	if (p->ev0) cudaEventDestroy(p->ev0);
 	if (p->ev1) cudaEventDestroy(p->ev1);
+	if (p->ev_fork) cudaEventDestroy(p->ev_fork);
+	for (int i = 0; i < 3; i++) {
+		if (p->ev_done[i]) cudaEventDestroy(p->ev_done[i]);
+		if (p->s_side[i]) { cudaStreamSynchronize(p->s_side[i]); cudaStreamDestroy(p->s_side[i]); }
+	}
 	if (p->stream) cudaStreamDestroy(p->stream);
 	delete p;
 }
@@ -96,6 +104,11 @@ extern "C" int spmm_b200_pipeline_create(spmm_b200_pipeline_t** out,
 	PIPE_TRY(cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking));
 	PIPE_TRY(cudaEventCreate(&p->ev0));
 	PIPE_TRY(cudaEventCreate(&p->ev1));
+	PIPE_TRY(cudaEventCreateWithFlags(&p->ev_fork, cudaEventDisableTiming));
+	for (int i = 0; i < 3; i++) {
+		PIPE_TRY(cudaStreamCreateWithFlags(&p->s_side[i], cudaStreamNonBlocking));
+		PIPE_TRY(cudaEventCreateWithFlags(&p->ev_done[i], cudaEventDisableTiming));
+	}
 	rc = pipe_make_handle(&p->mask, mask_ia, mask_ja, mask_a, m, m, nnz, n, device, true);
 	if (rc) { spmm_b200_pipeline_destroy(p); return rc; }
 	PIPE_TRY(cudaMalloc(&p->d_mask_a, sizeof(double) * std::max<int64_t>(nnz, 1)));
@@ -335,12 +348,23 @@ extern "C" int spmm_b200_pipeline_attention(spmm_b200_pipeline_t* p, const doubl
 	if (rc) return rc;
 	if (k > 0) CU_TRY(cudaMemcpyAsync(p->d_x, x_host, sizeof(double) * k * p->n, cudaMemcpyHostToDevice, p->stream));
 	CU_TRY(cudaEventRecord(p->ev0, p->stream));
-	for (auto& w : p->w) {
+	// K | Q | V on three side streams; the SDDMM waits for K and Q only, the final product for V
+	const bool fork = p->m > 0 && env_int("SPMM_B200_PIPELINE_FORK", 1);
+	if (fork) CU_TRY(cudaEventRecord(p->ev_fork, p->stream));
+	for (int i = 0; i < 3; i++) {
+		auto& w = p->w[i];
 		if (p->m > 0) {
-			rc = spmm_b200_run_device(w.h, p->d_x, w.d_out, p->n, p->stream);
+			cudaStream_t s = fork ? p->s_side[i] : p->stream;
+			if (fork) CU_TRY(cudaStreamWaitEvent(s, p->ev_fork, 0));
+			rc = spmm_b200_run_device(w.h, p->d_x, w.d_out, p->n, s);
 			if (rc) return rc;
+			if (fork) CU_TRY(cudaEventRecord(p->ev_done[i], s));
 		}
 		w.have = true;
+	}
+	if (fork) {
+		CU_TRY(cudaStreamWaitEvent(p->stream, p->ev_done[0], 0));
+		CU_TRY(cudaStreamWaitEvent(p->stream, p->ev_done[1], 0));
 	}
 	rc = pipe_sddmm_launch(p, mode);
 	if (rc) return rc;
@@ -348,6 +372,7 @@ extern "C" int spmm_b200_pipeline_attention(spmm_b200_pipeline_t* p, const doubl
 		rc = pipe_softmax_launch(p, softmax == 2);
 		if (rc) return rc;
 	}
+	if (fork) CU_TRY(cudaStreamWaitEvent(p->stream, p->ev_done[2], 0));
 	if (p->m > 0) {
 		rc = spmm_b200_run_device(p->mask, p->w[2].d_out, p->d_final, p->n, p->stream);
 		if (rc) return rc;
