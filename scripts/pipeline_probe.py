@@ -63,6 +63,11 @@ rows.append(("spmm('final')", ms, nnz * (12 + 8 * n) + 8 * m * n + 4 * m))
 for mode in (0, 1, 2):
     ms = best(lambda: MF.attention(x, yf, mode, 0))
     rows.append((f"attention(), mode {mode}, all kernels", ms, 0))
+for fused in ("1", "0"):
+    os.environ["SPMM_B200_ATTENTION_FUSED"] = fused
+    ms = best(lambda: MF.attention(x, yf, 1, 2))
+    rows.append((f"attention(), mode 1 + row softmax, {'ONE fused kernel' if fused == '1' else 'three kernels'} after the projections", ms, 0))
+os.environ.pop("SPMM_B200_ATTENTION_FUSED")
 print("| stage | kernel ms | algorithmic MB | GB/s |")
 print("|---|---|---|---|")
 for name, ms, byt in rows:

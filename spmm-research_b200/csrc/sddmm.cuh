@@ -157,6 +157,149 @@ sddmm_attention_group_kernel(const int32_t* __restrict__ ia, const int32_t* __re
 	}
 }
 
+// SDDMM -> row-wise softmax -> SpMM in ONE kernel (attention mode; y never leaves the SM).  A warp owns a mask
+// row i and walks its nonzeros 32 at a time:
+//   scores   s_p = mask[p] * Q[i].K[ja[p]]            as in sddmm_attention_group_kernel (lane t ends up with nonzero t's)
+//   softmax  online (running maximum mrun and sum l; the accumulators are rescaled by exp(mrun_old - mrun_new))
+//   product  acc += exp(s_p - mrun) * V[ja[p]]        group g of the warp gathers the V rows of ITS G nonzeros,
+//                                                    lanes own V columns each (the row-split SpMM's mapping)
+// and at the end the 32/G group partials are added and divided by l.  Bytes per nonzero: 2 * 8n (K and V rows)
+// + 12, against 2 * 8n + 12 + 3 * 12 + 48 for the three separate kernels; two launches and the y round trip go.
+// Rounding: tree-ordered dot products, online softmax -- agrees with the step-by-step path to 1e-12 (tested).
+template <int G, int V, int U, int THREADS, int MINB>
+__global__ void __launch_bounds__(THREADS, MINB)
+attention_fused_kernel(const int32_t* __restrict__ ia, const int32_t* __restrict__ ja, const double* __restrict__ mask_a,
+                       const double* __restrict__ Q, const double* __restrict__ K, const double* __restrict__ Vm,
+                       double* __restrict__ out, int64_t m)
+{
+	static_assert(V % 4 == 0 && G % U == 0 && 32 % G == 0, "shape");
+	constexpr int NW = THREADS / 32;
+	constexpr int N = G * V;
+	const int lane = threadIdx.x & 31;
+	const int lig = lane % G;
+	for (int64_t row = (int64_t) blockIdx.x * NW + (threadIdx.x >> 5); row < m; row += (int64_t) gridDim.x * NW) {
+		const int js = __ldg(ia + row), je = __ldg(ia + row + 1);
+		double2* op = reinterpret_cast<double2*>(out + (size_t) row * N);
+		if (js == je) {
+			if (lane < G) {
+				#pragma unroll
+				for (int i = 0; i < V / 2; i++) op[i * G + lig] = make_double2(0.0, 0.0);
+			}
+			continue;
+		}
+		double q[V], acc[V];
+		{
+			const double2* qp = reinterpret_cast<const double2*>(Q + (size_t) row * N);
+			#pragma unroll
+			for (int i = 0; i < V / 2; i++) {
+				const double2 t = __ldg(qp + i * G + lig);
+				q[2 * i] = t.x; q[2 * i + 1] = t.y;
+				acc[2 * i] = 0.0; acc[2 * i + 1] = 0.0;
+			}
+		}
+		double mrun = -DBL_MAX, l = 0.0;
+		for (int p0 = js; p0 < je; p0 += 32) {
+			const int p = p0 + lane;
+			const int col = p < je ? __ldg(ja + p) : -1;
+			// ---- scores
+			double part[G];
+			#pragma unroll
+			for (int t0 = 0; t0 < G; t0 += U) {
+				double2 kv[U][V / 2];
+				int cc[U];
+				#pragma unroll
+				for (int u = 0; u < U; u++) cc[u] = __shfl_sync(0xffffffffu, col, t0 + u, G);
+				#pragma unroll
+				for (int u = 0; u < U; u++) {
+					if (cc[u] >= 0) {
+						const double2* kp = reinterpret_cast<const double2*>(K + (size_t) cc[u] * N);
+						#pragma unroll
+						for (int i = 0; i < V / 2; i++) kv[u][i] = __ldg(kp + i * G + lig);
+					}
+				}
+				#pragma unroll
+				for (int u = 0; u < U; u++) {
+					double s = 0.0;
+					if (cc[u] >= 0) {
+						#pragma unroll
+						for (int i = 0; i < V / 2; i++) {
+							s = fma(q[2 * i], kv[u][i].x, s);
+							s = fma(q[2 * i + 1], kv[u][i].y, s);
+						}
+					}
+					part[t0 + u] = s;
+				}
+			}
+			#pragma unroll
+			for (int off = G / 2; off >= 1; off >>= 1) {
+				const bool up = (lig & off) != 0;
+				#pragma unroll
+				for (int i = 0; i < off; i++) {
+					const double send = up ? part[i] : part[i + off];
+					const double keep = up ? part[i + off] : part[i];
+					part[i] = keep + __shfl_xor_sync(0xffffffffu, send, off, G);
+				}
+			}
+			const double sc = p < je ? part[0] * __ldg(mask_a + p) : -DBL_MAX;
+			// ---- online softmax
+			double bmax = sc;
+			#pragma unroll
+			for (int o = 16; o > 0; o >>= 1) bmax = fmax(bmax, __shfl_xor_sync(0xffffffffu, bmax, o));
+			const double mnew = fmax(mrun, bmax);
+			const double scale = exp(mrun - mnew);          // first batch: exp(-huge) = 0, acc and l are 0 anyway
+			const double pe = p < je ? exp(sc - mnew) : 0.0;
+			double bsum = pe;
+			#pragma unroll
+			for (int o = 16; o > 0; o >>= 1) bsum += __shfl_xor_sync(0xffffffffu, bsum, o);
+			l = l * scale + bsum;
+			mrun = mnew;
+			#pragma unroll
+			for (int v = 0; v < V; v++) acc[v] *= scale;
+			// ---- weighted V rows
+			#pragma unroll
+			for (int t0 = 0; t0 < G; t0 += U) {
+				double2 vv[U][V / 2];
+				int cc[U];
+				double ww[U];
+				#pragma unroll
+				for (int u = 0; u < U; u++) {
+					cc[u] = __shfl_sync(0xffffffffu, col, t0 + u, G);
+					ww[u] = __shfl_sync(0xffffffffu, pe, t0 + u, G);
+				}
+				#pragma unroll
+				for (int u = 0; u < U; u++) {
+					if (cc[u] >= 0) {
+						const double2* vp = reinterpret_cast<const double2*>(Vm + (size_t) cc[u] * N);
+						#pragma unroll
+						for (int i = 0; i < V / 2; i++) vv[u][i] = __ldg(vp + i * G + lig);
+					}
+				}
+				#pragma unroll
+				for (int u = 0; u < U; u++) {
+					if (cc[u] >= 0) {
+						#pragma unroll
+						for (int i = 0; i < V / 2; i++) {
+							acc[2 * i] = fma(ww[u], vv[u][i].x, acc[2 * i]);
+							acc[2 * i + 1] = fma(ww[u], vv[u][i].y, acc[2 * i + 1]);
+						}
+					}
+				}
+			}
+		}
+		// the 32 / G groups hold partial rows: add them, normalise, store from group 0
+		#pragma unroll
+		for (int o = G; o < 32; o <<= 1) {
+			#pragma unroll
+			for (int v = 0; v < V; v++) acc[v] += __shfl_xor_sync(0xffffffffu, acc[v], o);
+		}
+		if (lane < G) {
+			const double inv = 1.0 / l;
+			#pragma unroll
+			for (int i = 0; i < V / 2; i++) op[i * G + lig] = make_double2(acc[2 * i] * inv, acc[2 * i + 1] * inv);
+		}
+	}
+}
+
 // Attention mode for n % 32 == 0: the simple kernel above makes every load instruction touch 32 different
 // 128-byte lines (one K row per lane), which the L1 tag stage serves at ~16 B/clk/SM (3.9 TB/s measured).
 // Here the warp stages the K rows of 32 nonzeros through shared memory in 256-byte column chunks: two rows per

@@ -167,11 +167,8 @@ static int pipe_sddmm_launch(spmm_b200_pipeline* p, int mode)
 				// K rows staged through shared memory (sddmm.cuh): 4 warps per CTA, 32 x 34 + n doubles per warp
 				constexpr int T = 128;
 				const size_t smem = sizeof(double) * (T / 32) * (32 * sb200::SDDMM_LD + p->n);
-				static bool attr_set = false;
-				if (!attr_set) {
-					CU_TRY(cudaFuncSetAttribute(sb200::sddmm_attention_staged_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-					attr_set = true;
-				}
+				if (smem > 48 * 1024)       // per device and cheap: no process-wide flag
+					CU_TRY(cudaFuncSetAttribute(sb200::sddmm_attention_staged_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
 				const int g2 = (int) std::min<int64_t>((p->m + T / 32 - 1) / (T / 32), (int64_t) p->mask->sm_count * 64);
 				sb200::sddmm_attention_staged_kernel<T><<<g2, T, smem, p->stream>>>(p->mask->d_ia, p->mask->d_ja, p->d_mask_a,
 				                                                                  p->w[1].d_out, p->w[0].d_out, p->mask->d_a, p->m, p->n);
@@ -366,16 +363,36 @@ extern "C" int spmm_b200_pipeline_attention(spmm_b200_pipeline_t* p, const doubl
 		CU_TRY(cudaStreamWaitEvent(p->stream, p->ev_done[0], 0));
 		CU_TRY(cudaStreamWaitEvent(p->stream, p->ev_done[1], 0));
 	}
-	rc = pipe_sddmm_launch(p, mode);
-	if (rc) return rc;
-	if (softmax) {
-		rc = pipe_softmax_launch(p, softmax == 2);
+	// attention-mode SDDMM + row-wise softmax + final product as ONE kernel (sddmm.cuh: attention_fused_kernel);
+	// y is not materialised on this path (spmm_b200_pipeline_device_ptr(p, 'y') returns NULL afterwards)
+	const bool fused = mode == SPMM_B200_SDDMM_ATTENTION && softmax == 2 && p->m > 0 && p->nnz > 0
+	                   && (p->n == 32 || p->n == 64 || p->n == 128) && env_int("SPMM_B200_ATTENTION_FUSED", 1);
+	if (fused) {
+		if (fork) CU_TRY(cudaStreamWaitEvent(p->stream, p->ev_done[2], 0));
+		const int gw = (int) std::min<int64_t>((p->m + THREADS / 32 - 1) / (THREADS / 32), (int64_t) p->mask->sm_count * 64);
+#define ATT_FUSED(G, V, U, MINB) sb200::attention_fused_kernel<G, V, U, THREADS, MINB><<<gw, THREADS, 0, p->stream>>>( \
+			p->mask->d_ia, p->mask->d_ja, p->d_mask_a, p->w[1].d_out, p->w[0].d_out, p->w[2].d_out, p->d_final, p->m)
+		// 128 registers (2 CTAs per SM) measured best: tighter caps spill part[], looser ones lose the second CTA;
+		// n = 128 keeps one K / V row in flight per group to stay inside them (profiles/r1_pipeline_probe.md)
+		if (p->n == 32) ATT_FUSED(8, 4, 2, 2);
+		else if (p->n == 64) ATT_FUSED(16, 4, 2, 2);
+		else ATT_FUSED(16, 8, 1, 2);
+#undef ATT_FUSED
+		CU_TRY(cudaGetLastError());
+		p->own_launches += 1;
+		p->have_y = false;
+	} else {
+		rc = pipe_sddmm_launch(p, mode);
 		if (rc) return rc;
-	}
-	if (fork) CU_TRY(cudaStreamWaitEvent(p->stream, p->ev_done[2], 0));
-	if (p->m > 0) {
-		rc = spmm_b200_run_device(p->mask, p->w[2].d_out, p->d_final, p->n, p->stream);
-		if (rc) return rc;
+		if (softmax) {
+			rc = pipe_softmax_launch(p, softmax == 2);
+			if (rc) return rc;
+		}
+		if (fork) CU_TRY(cudaStreamWaitEvent(p->stream, p->ev_done[2], 0));
+		if (p->m > 0) {
+			rc = spmm_b200_run_device(p->mask, p->w[2].d_out, p->d_final, p->n, p->stream);
+			if (rc) return rc;
+		}
 	}
 	p->have_final = true;
 	CU_TRY(cudaEventRecord(p->ev1, p->stream));

@@ -180,9 +180,43 @@ def test_gpu_attention_one_call_equals_the_steps(pkg, mode, softmax):
     yf = np.full(m * n, np.nan)
     before = MF.launch_count()
     MF.attention(x, yf, mode, softmax)
-    assert np.array_equal(yf, steps["y_final"])
-    assert MF.launch_count() - before >= 5 and MF.last_kernel_ms() > 0
-    assert MF.device_ptr("y") and MF.device_ptr("f") and MF.device_ptr("K")
+    if (mode, softmax) == (1, 2):
+        # one fused kernel (SDDMM + row softmax + SpMM, online softmax): rounding differs, y is not materialised
+        assert_close(yf, steps["y_final"], msg="fused attention")
+        assert MF.launch_count() - before == 4 and not MF.device_ptr("y")
+    else:
+        assert np.array_equal(yf, steps["y_final"])
+        assert MF.launch_count() - before >= 5 and MF.device_ptr("y")
+    assert MF.last_kernel_ms() > 0 and MF.device_ptr("f") and MF.device_ptr("K")
+    MF.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n", [32, 64, 128])
+def test_gpu_fused_attention_matches_oracle(pkg, L, n):
+    """attention(mode 1, row-wise softmax) = attention_fused_kernel: against the oracle's three steps, with empty
+    mask rows, rows shorter and longer than one 32-nonzero batch, and non-unit mask values."""
+    m, kdim = 500, 260
+    mask, W, x = pipeline_case(40 + n, m, kdim, n, 3, 0.11, mask_values="random", empty_frac=0.05)
+    mia, mja, ma, _ = mask
+    cut = int(mia[m - 40])
+    mia = mia.copy(); mia[m - 40:] = cut                      # the last 40 rows empty
+    mask = (mia, mja[:cut].copy(), ma[:cut].copy(), m)
+    r = L.pipeline_oracle(mask, W, x, n, 1, 2)
+    MF = pkg.csr_to_pipeline_format(mask[0], mask[1], mask[2], m, cut, n)
+    for t in "KQV":
+        MF.set_weight(t, m, kdim, *W[t])
+    yf = np.full(m * n, np.nan)
+    MF.attention(x, yf, 1, 2)
+    assert_close(yf, r["y_final"], msg=f"fused n={n}")
+    assert (yf.reshape(m, n)[m - 40:] == 0).all()
+    os.environ["SPMM_B200_ATTENTION_FUSED"] = "0"
+    try:
+        yf2 = np.full(m * n, np.nan)
+        MF.attention(x, yf2, 1, 2)
+    finally:
+        del os.environ["SPMM_B200_ATTENTION_FUSED"]
+    assert_close(yf2, r["y_final"], msg=f"unfused n={n}")
     MF.close()
 
 
