@@ -74,7 +74,11 @@ int spmm_b200_pipeline_final(spmm_b200_pipeline_t *p, double *y_final_host);
 
 /* The whole layer with one upload and one download: the three projections of x_host (k x n), sddmm in `mode`,
  * optional softmax (0 none, 1 global, 2 row-wise), final product -> y_final_host (m x n).  The weights must
- * have been registered by earlier spmm('K'|'Q'|'V') calls or spmm_b200_pipeline_set_weight. */
+ * have been registered by earlier spmm('K'|'Q'|'V') calls or spmm_b200_pipeline_set_weight.  The three
+ * projections run side by side.  With mode = SPMM_B200_SDDMM_ATTENTION, softmax = 2 and n = 32, 64 or 128 the
+ * SDDMM, the softmax and the final product are ONE kernel (online softmax); y is then never materialised and
+ * spmm_b200_pipeline_device_ptr(p, 'y') returns NULL afterwards.  SPMM_B200_ATTENTION_FUSED=0 forces the
+ * step-by-step kernels. */
 int spmm_b200_pipeline_set_weight(spmm_b200_pipeline_t *p, char type, int64_t m, int64_t k, int64_t nnz,
                                   const int32_t *ia, const int32_t *ja, const double *a);
 int spmm_b200_pipeline_attention(spmm_b200_pipeline_t *p, const double *x_host, double *y_final_host,

@@ -325,7 +325,7 @@ class PipelineFormat:
     def __init__(self, handle, m, nnz, n, keep):
         self._h = handle
         self.m, self.nnz, self.n = int(m), int(nnz), int(n)
-        self._keep = list(keep)          # the C side remembers host pointers: keep the arrays alive
+        self._keep = {"mask": tuple(keep)}   # the C side remembers host pointers: keep the arrays alive
 
     def spmm(self, type, m, k, n, ia, ja, a, x, y):
         """y = CSR(ia, ja, a; m x k) * x (k x n row-major).  type 'K'|'Q'|'V' also keeps the result on the
@@ -337,7 +337,7 @@ class PipelineFormat:
         if x.size < k * n:
             raise ValueError("x holds fewer than k*n values")
         if t in (b"K", b"Q", b"V"):
-            self._keep += [ia, ja, a]
+            self._keep[t] = (ia, ja, a)
         _check(load_library().spmm_b200_pipeline_spmm(self._h, t, m, k, n, _host(ia, np.int32, "ia"),
                _host(ja, np.int32, "ja") if len(ja) else None, _host(a, np.float64, "a") if len(a) else None,
                _host(x, np.float64, "x") if x.size else None, yp), "spmm_b200_pipeline_spmm")
@@ -358,7 +358,7 @@ class PipelineFormat:
         _check(load_library().spmm_b200_pipeline_final(self._h, _host(y_final, np.float64, "y_final")), "spmm_b200_pipeline_final")
 
     def set_weight(self, type, m, k, ia, ja, a):
-        self._keep += [ia, ja, a]
+        self._keep[type.encode()[:1]] = (ia, ja, a)
         _check(load_library().spmm_b200_pipeline_set_weight(self._h, type.encode()[:1], m, k, len(ja), _host(ia, np.int32, "ia"),
                _host(ja, np.int32, "ja") if len(ja) else None, _host(a, np.float64, "a") if len(a) else None),
                "spmm_b200_pipeline_set_weight")
