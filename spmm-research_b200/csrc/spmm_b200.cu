@@ -108,13 +108,16 @@ static int check_device(int device, int* sm_count)
 		return SPMM_B200_ENODEV;
 	}
 	if (device < 0 || device >= n) return SPMM_B200_EINVAL;
-	cudaDeviceProp p;
-	CU_TRY(cudaGetDeviceProperties(&p, device));
-	if (p.major != 10) {
-		snprintf(g_cuda_err, sizeof(g_cuda_err), "device %d is sm_%d%d; this library holds sm_100a code only", device, p.major, p.minor);
+	// three attributes instead of cudaGetDeviceProperties (which fills ~100 fields and costs milliseconds per call)
+	int major = 0, minor = 0, sms = 0;
+	CU_TRY(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, device));
+	CU_TRY(cudaDeviceGetAttribute(&minor, cudaDevAttrComputeCapabilityMinor, device));
+	CU_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+	if (major != 10) {
+		snprintf(g_cuda_err, sizeof(g_cuda_err), "device %d is sm_%d%d; this library holds sm_100a code only", device, major, minor);
 		return SPMM_B200_ENODEV;
 	}
-	if (sm_count) *sm_count = p.multiProcessorCount;
+	if (sm_count) *sm_count = sms;
 	CU_TRY(cudaSetDevice(device));
 	return SPMM_B200_OK;
 }

@@ -37,10 +37,10 @@ static int device_ok(int device, int* sms)
 	int n = 0;
 	if (cudaGetDeviceCount(&n) != cudaSuccess || n <= 0) { cudaGetLastError(); return SPMM_B200_ENODEV; }
 	if (device < 0 || device >= n) return SPMM_B200_EINVAL;
-	cudaDeviceProp p;
-	CU_TRY(cudaGetDeviceProperties(&p, device));
-	if (p.major != 10) return SPMM_B200_ENODEV;
-	*sms = p.multiProcessorCount;
+	int major = 0;
+	CU_TRY(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, device));
+	if (major != 10) return SPMM_B200_ENODEV;
+	CU_TRY(cudaDeviceGetAttribute(sms, cudaDevAttrMultiProcessorCount, device));
 	CU_TRY(cudaSetDevice(device));
 	return SPMM_B200_OK;
 }
