@@ -98,7 +98,11 @@ int spmm_b200_create_shard(spmm_b200_t **h,
  * copy_back == 0 the result stays on the device (spmm_b200_fetch_c reads it).
  * The call is PCIe-bound; for k >= 32 (k % 16 == 0) and operands of >= 8 MB the columns are cut into
  * 16-column slices so that the upload of slice s+1, the kernel on slice s and the download of
- * C[:, slice s-1] overlap (SPMM_B200_PIPELINE_COLS=0 turns it off).  Results are identical. */
+ * C[:, slice s-1] overlap (SPMM_B200_PIPELINE_COLS=0 turns it off).  Results are identical.
+ * When y_host is page-locked and mapped for the device (cudaHostAlloc / torch pin_memory / spmm_b200_register_host)
+ * and the row-split kernel runs the slices, each slice's kernel stores its part of every C row straight into
+ * y_host (no staging copy; spmm_b200_fetch_c has nothing to fetch afterwards and returns SPMM_B200_EINVAL).
+ * SPMM_B200_DIRECT_STORE=0 keeps the staged download. */
 int spmm_b200_run(spmm_b200_t *h, const double *x_host, double *y_host, int k, int copy_back);
 
 /* Multi-GPU form of the hot call (one process per GPU, handle from spmm_b200_create_shard).  The only

@@ -211,6 +211,11 @@ class MatrixFormat:
         out = dict(zip(self.ACCURACY_LABELS, stats.tolist()))
         return (out, gold[: self.m * k]) if return_gold else out
 
+    def register_host(self, arr):
+        """Page-lock a host array for the lifetime of the handle (full PCIe rate; lets spmm() store C straight
+        into it).  The array must stay alive until close()."""
+        _check(load_library().spmm_b200_register_host(self._h, arr.ctypes.data, arr.nbytes), "spmm_b200_register_host")
+
     def set_b(self, x, k):
         _check(load_library().spmm_b200_set_b(self._h, _host(x, np.float64, "x"), int(k)), "set_b")
 

@@ -885,6 +885,7 @@ extern "C" int spmm_b200_fetch_c(spmm_b200_t* h, double* y_host, int k)
 {
 	if (!h || !y_host || k < 1 || h->cap_C < (size_t) h->m * k) return SPMM_B200_EINVAL;
 	if (h->c_slices > 1 && k % h->c_slices) return SPMM_B200_EINVAL;
+	if (h->c_slices == 0) return SPMM_B200_EINVAL;      // the last run stored C straight into its (mapped) y_host
 	CU_TRY(cudaSetDevice(h->device));
 	int rc = download_c(h, y_host, k, h->stream);
 	if (rc) return rc;
@@ -961,8 +962,36 @@ static int run_pipelined(spmm_b200* h, const double* x_host, double* y_host, int
 		}
 		CU_TRY(cudaEventRecord(h->ev_slice[3 * s], h->s_up));
 	}
+	// Direct store: when y_host is page-locked and mapped into the device's address space, the row-split kernel
+	// writes its w-column slice of every C row (w*8 contiguous bytes, ldc = k) straight into host memory, so the
+	// download of slice s is the kernel itself and overlaps the upload of slice s+1 with no copy-engine pass and no
+	// staging in d_C (profiles/r1_pcie_probe.md: SM stores into mapped host memory run at the 2-D copy's rate).
+	double* y_map = nullptr;
+	if (y_host && h->m > 0 && h->variant == SPMM_B200_ROWSPLIT && (ks == 8 || ks == 16 || ks == 32 || ks == 64)
+	    && env_int("SPMM_B200_DIRECT_STORE", 1)) {
+		cudaPointerAttributes at;
+		if (cudaPointerGetAttributes(&at, y_host) == cudaSuccess && at.type == cudaMemoryTypeHost && at.devicePointer)
+			y_map = (double*) at.devicePointer;
+		else
+			cudaGetLastError();
+	}
 	for (int s = 0; s < S; s++) {
 		CU_TRY(cudaStreamWaitEvent(h->stream, h->ev_slice[3 * s], 0));
+		if (y_map) {
+			const double* Bs = h->d_B + s * bslice;
+			double* Cs = y_map + (size_t) s * ks;
+			CU_TRY(cudaEventRecord(h->ev_slice[3 * s + 1], h->stream));
+			switch (ks) {
+			case 8:  launch_rowsplit_gv<4, 2>(h, Bs, Cs, h->stream, ks, k); break;
+			case 16: launch_rowsplit_gv<8, 2>(h, Bs, Cs, h->stream, ks, k); break;
+			case 32: launch_rowsplit_gv<8, 4>(h, Bs, Cs, h->stream, ks, k); break;
+			default: launch_rowsplit_gv<16, 4>(h, Bs, Cs, h->stream, ks, k); break;
+			}
+			CU_TRY(cudaGetLastError());
+			h->launches += 1;
+			CU_TRY(cudaEventRecord(h->ev_slice[3 * s + 2], h->stream));
+			continue;
+		}
 		rc = run_between(h, h->d_B + s * bslice, h->d_C + s * cslice, ks, h->stream, h->ev_slice[3 * s + 1], h->ev_slice[3 * s + 2]);
 		if (rc) return rc;
 		if (y_host && h->m > 0) {
@@ -971,7 +1000,7 @@ static int run_pipelined(spmm_b200* h, const double* x_host, double* y_host, int
 			                         sizeof(double) * ks, (size_t) h->m, cudaMemcpyDeviceToHost, h->s_down));
 		}
 	}
-	h->c_slices = S;
+	h->c_slices = y_map ? 0 : S;            // 0: C went straight to the host, d_C holds nothing to fetch
 	h->timed = true;
 	h->timed_slices = S;
 	CU_TRY(cudaStreamSynchronize(h->stream));

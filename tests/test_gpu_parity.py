@@ -253,6 +253,38 @@ def test_k_sliced_host_pipeline(pkg, L, layout, monkeypatch):
             mf.close()
 
 
+def test_direct_store_into_page_locked_y(pkg, L, monkeypatch):
+    """With a page-locked (device-mapped) y the sliced row-split kernels store C straight into host memory
+    (no staging copy, DESIGN 5.3).  Same bits as the staged download; fetch_c has nothing to fetch afterwards;
+    untouched guard elements around y stay untouched."""
+    monkeypatch.setenv("SPMM_B200_PIPELINE_MIN_KB", "0")
+    m, c = 4003, 3000
+    ia, ja, a = random_csr(m, c, 11.0, seed=33, empty_frac=0.05)
+    a = np.abs(a) + 0.01                      # no cancellation: the element-wise 1e-12 bound applies
+    for k in (32, 64, 128):
+        x = dense_b(c, k, 6)
+        y_ref = L.spmm_oracle(ia, ja, a, m, c, x, k)
+        mf = pkg.csr_to_format(ia, ja, a, m, c, len(ja), k, variant=pkg.ROWSPLIT)
+        guard = 64
+        buf = np.full(m * k + 2 * guard, -7.0)
+        mf.register_host(buf)
+        y = buf[guard:guard + m * k]
+        before = mf.launch_count()
+        mf.spmm(x, y, k)
+        assert max_rel_err(y, y_ref) <= FP64_TOL, k
+        assert (buf[:guard] == -7.0).all() and (buf[-guard:] == -7.0).all()
+        assert mf.launch_count() - before >= 2                      # at least two slices ran
+        with pytest.raises(pkg.SpmmB200Error):
+            mf.fetch_c(np.empty(m * k), k)
+        monkeypatch.setenv("SPMM_B200_DIRECT_STORE", "0")
+        y2 = np.full(m * k, np.nan); mf.spmm(x, y2, k)
+        monkeypatch.delenv("SPMM_B200_DIRECT_STORE")
+        assert np.array_equal(y2, y)                                 # staged download: the same bits
+        y3 = np.full(m * k, np.nan); mf.fetch_c(y3, k)
+        assert np.array_equal(y3, y)
+        mf.close()
+
+
 def test_kslice_measurement_keeps_results_identical(pkg, L):
     """L2-aware k slicing: a matrix whose touched B window (column span x 8k bytes) exceeds
     192 MB makes the handle time the candidate slice widths on its first 8 device calls.  Every one of those
