@@ -92,14 +92,20 @@ template <int G, int V, int U, int THREADS, int MINB = 1>
 __global__ void __launch_bounds__(THREADS, MINB)
 sddmm_attention_group_kernel(const int32_t* __restrict__ ia, const int32_t* __restrict__ ja, const double* __restrict__ mask_a,
                              const double* __restrict__ Q, const double* __restrict__ K,
-                             double* __restrict__ y, int64_t m)
+                             double* __restrict__ y, int64_t m, int* __restrict__ ticket, int rev)
 {
 	static_assert(V % 4 == 0 && G % U == 0 && 32 % G == 0, "shape");
-	constexpr int NW = THREADS / 32;
 	constexpr int N = G * V;
 	const int lane = threadIdx.x & 31;
 	const int lig = lane % G;
-	for (int64_t row = (int64_t) blockIdx.x * NW + (threadIdx.x >> 5); row < m; row += (int64_t) gridDim.x * NW) {
+	// persistent warps draw rows from a ticket counter, last row first (with causal-shaped masks the late rows are
+	// the long ones): one resident wave, no tail of short CTAs
+	for (;;) {
+		int t = 0;
+		if (lane == 0) t = atomicAdd(ticket, 1);
+		t = __shfl_sync(0xffffffffu, t, 0);
+		if (t >= m) break;
+		const int64_t row = rev ? m - 1 - t : t;
 		const int js = __ldg(ia + row), je = __ldg(ia + row + 1);
 		if (js == je) continue;
 		double q[V];
@@ -170,14 +176,18 @@ template <int G, int V, int U, int THREADS, int MINB>
 __global__ void __launch_bounds__(THREADS, MINB)
 attention_fused_kernel(const int32_t* __restrict__ ia, const int32_t* __restrict__ ja, const double* __restrict__ mask_a,
                        const double* __restrict__ Q, const double* __restrict__ K, const double* __restrict__ Vm,
-                       double* __restrict__ out, int64_t m)
+                       double* __restrict__ out, int64_t m, int* __restrict__ ticket, int rev)
 {
 	static_assert(V % 4 == 0 && G % U == 0 && 32 % G == 0, "shape");
-	constexpr int NW = THREADS / 32;
 	constexpr int N = G * V;
 	const int lane = threadIdx.x & 31;
 	const int lig = lane % G;
-	for (int64_t row = (int64_t) blockIdx.x * NW + (threadIdx.x >> 5); row < m; row += (int64_t) gridDim.x * NW) {
+	for (;;) {                                     // persistent warps, rows by ticket, last row first
+		int t = 0;
+		if (lane == 0) t = atomicAdd(ticket, 1);
+		t = __shfl_sync(0xffffffffu, t, 0);
+		if (t >= m) break;
+		const int64_t row = rev ? m - 1 - t : t;
 		const int js = __ldg(ia + row), je = __ldg(ia + row + 1);
 		double2* op = reinterpret_cast<double2*>(out + (size_t) row * N);
 		if (js == je) {

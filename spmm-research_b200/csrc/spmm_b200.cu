@@ -166,6 +166,11 @@ static int build_rowsplit_plan(spmm_b200* h)
 	const int per_sm = std::max(1, env_int("SPMM_B200_CTAS_PER_SM", dflt));
 	int64_t want = (int64_t) h->sm_count * per_sm;
 	int64_t cap = std::max<int64_t>(1, (h->m + 7) / 8);       // at least ~8 rows per CTA
+	// few rows (the row cap binds): whole waves of the 4 resident CTAs per SM, so that no partial last wave
+	// runs on a fraction of the machine (m = 8192, k = 64, 410 nnz/row: 1024 CTAs 0.141 ms, 592 CTAs 0.123 ms;
+	// profiles/r1_pipeline_probe.md)
+	const int64_t wave = (int64_t) h->sm_count * 4;
+	if (cap < want && h->k >= 64 && cap >= wave && !env_int("SPMM_B200_CTAS_PER_SM", 0)) cap = cap / wave * wave;
 	h->n_ctas = (int) std::max<int64_t>(1, std::min(want, cap));
 	if (h->d_cta_rows) cudaFree(h->d_cta_rows);
 	CU_TRY(cudaMalloc(&h->d_cta_rows, sizeof(int32_t) * (h->n_ctas + 1)));

@@ -26,6 +26,7 @@ struct spmm_b200_pipeline {
 	double* d_tmp = nullptr; size_t cap_tmp = 0;
 	double* d_final = nullptr;
 	double* d_part = nullptr;
+	int* d_ticket = nullptr;                 // row ticket counter of the persistent SDDMM / fused kernels
 	bool have_y = false, have_final = false;
 	cudaStream_t stream = nullptr;
 	cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -72,6 +73,7 @@ extern "C" void spmm_b200_pipeline_destroy(spmm_b200_pipeline_t* p)
 	if (p->d_tmp) cudaFree(p->d_tmp);
 	if (p->d_final) cudaFree(p->d_final);
 	if (p->d_part) cudaFree(p->d_part);
+	if (p->d_ticket) cudaFree(p->d_ticket);
 	if (p->ev0) cudaEventDestroy(p->ev0);
 	if (p->ev1) cudaEventDestroy(p->ev1);
 	if (p->ev_fork) cudaEventDestroy(p->ev_fork);
@@ -115,6 +117,7 @@ extern "C" int spmm_b200_pipeline_create(spmm_b200_pipeline_t** out,
 	if (nnz > 0) PIPE_TRY(cudaMemcpy(p->d_mask_a, mask_a, sizeof(double) * nnz, cudaMemcpyHostToDevice));
 	PIPE_TRY(cudaMalloc(&p->d_final, sizeof(double) * std::max<int64_t>(m * n, 1)));
 	PIPE_TRY(cudaMalloc(&p->d_part, sizeof(double) * (PIPE_PARTS + 2)));
+	PIPE_TRY(cudaMalloc(&p->d_ticket, sizeof(int)));
 #undef PIPE_TRY
 	*out = p;
 	return SPMM_B200_OK;
@@ -151,16 +154,19 @@ static int pipe_sddmm_launch(spmm_b200_pipeline* p, int mode)
 			// always in ORDERED mode -- a kernel that keeps the CPU loop's left-to-right order
 			const bool fast = mode == SPMM_B200_SDDMM_ATTENTION && env_int("SPMM_B200_SDDMM_GROUP", 1);
 			const int gw = (int) std::min<int64_t>((p->m + THREADS / 32 - 1) / (THREADS / 32), (int64_t) p->mask->sm_count * 64);
-#define SDDMM_GROUP(G, V, U, MINB) sb200::sddmm_attention_group_kernel<G, V, U, THREADS, MINB><<<gw, THREADS, 0, p->stream>>>( \
-				p->mask->d_ia, p->mask->d_ja, p->d_mask_a, p->w[1].d_out, p->w[0].d_out, p->mask->d_a, p->m)
-			// U = 2 rows in flight and >= 4 CTAs per SM (64 registers) measured best of {U 2,4,8} x {1..4 CTAs}:
-			// profiles/r1_pipeline_probe.md
-			const int tune = env_int("SPMM_B200_SDDMM_TUNE", 0);     // experiment knob for n = 64: U*10 + min CTAs per SM
+			// one resident wave of persistent CTAs (MINB per SM); rows are handed out by the ticket counter
+#define SDDMM_GROUP(G, V, U, MINB) do { \
+				CU_TRY(cudaMemsetAsync(p->d_ticket, 0, sizeof(int), p->stream)); \
+				sb200::sddmm_attention_group_kernel<G, V, U, THREADS, MINB><<<(int) std::min<int64_t>(gw, (int64_t) p->mask->sm_count * MINB), THREADS, 0, p->stream>>>( \
+				p->mask->d_ia, p->mask->d_ja, p->d_mask_a, p->w[1].d_out, p->w[0].d_out, p->mask->d_a, p->m, p->d_ticket, env_int("SPMM_B200_TICKET_REV", 1)); } while (0)
+			// shapes measured on m = 8192 / 16384 (profiles/r1_pipeline_probe.md): U = 2 rows in flight; with the
+			// persistent ticketed grid n = 64 runs best at 126 registers / 2 CTAs per SM, n = 32 at 64 registers / 4
+			const int tune = env_int("SPMM_B200_SDDMM_TUNE", 0);     // experiment knob for n = 64: U*10 + CTAs per SM
 			if (fast && p->n == 16) SDDMM_GROUP(4, 4, 2, 4);
 			else if (fast && p->n == 32) SDDMM_GROUP(8, 4, 2, 4);
 			else if (fast && p->n == 64 && tune == 42) SDDMM_GROUP(16, 4, 4, 2);
-			else if (fast && p->n == 64 && tune == 22) SDDMM_GROUP(16, 4, 2, 2);
-			else if (fast && p->n == 64) SDDMM_GROUP(16, 4, 2, 4);
+			else if (fast && p->n == 64 && tune == 24) SDDMM_GROUP(16, 4, 2, 4);
+			else if (fast && p->n == 64) SDDMM_GROUP(16, 4, 2, 2);
 			else if (fast && p->n == 128) SDDMM_GROUP(16, 8, 2, 2);
 #undef SDDMM_GROUP
 			else if (p->n % sb200::SDDMM_CH == 0 && p->n <= 1024 && env_int("SPMM_B200_SDDMM_STAGED", 1)) {
@@ -370,8 +376,10 @@ extern "C" int spmm_b200_pipeline_attention(spmm_b200_pipeline_t* p, const doubl
 	if (fused) {
 		if (fork) CU_TRY(cudaStreamWaitEvent(p->stream, p->ev_done[2], 0));
 		const int gw = (int) std::min<int64_t>((p->m + THREADS / 32 - 1) / (THREADS / 32), (int64_t) p->mask->sm_count * 64);
-#define ATT_FUSED(G, V, U, MINB) sb200::attention_fused_kernel<G, V, U, THREADS, MINB><<<gw, THREADS, 0, p->stream>>>( \
-			p->mask->d_ia, p->mask->d_ja, p->d_mask_a, p->w[1].d_out, p->w[0].d_out, p->w[2].d_out, p->d_final, p->m)
+#define ATT_FUSED(G, V, U, MINB) do { \
+			CU_TRY(cudaMemsetAsync(p->d_ticket, 0, sizeof(int), p->stream)); \
+			sb200::attention_fused_kernel<G, V, U, THREADS, MINB><<<(int) std::min<int64_t>(gw, (int64_t) p->mask->sm_count * MINB), THREADS, 0, p->stream>>>( \
+			p->mask->d_ia, p->mask->d_ja, p->d_mask_a, p->w[1].d_out, p->w[0].d_out, p->w[2].d_out, p->d_final, p->m, p->d_ticket, env_int("SPMM_B200_TICKET_REV", 1)); } while (0)
 		// 128 registers (2 CTAs per SM) measured best: tighter caps spill part[], looser ones lose the second CTA;
 		// n = 128 keeps one K / V row in flight per group to stay inside them (profiles/r1_pipeline_probe.md)
 		if (p->n == 32) ATT_FUSED(8, 4, 2, 2);
