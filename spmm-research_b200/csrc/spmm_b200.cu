@@ -65,6 +65,7 @@ struct spmm_b200 {
 	// row-split work list
 	int32_t* d_cta_rows = nullptr;
 	int n_ctas = 0;
+	int* d_ticket = nullptr;              // row-ticket counter of the persistent row-split experiment
 	// row-padded copy of A for the vectorised row-split kernel (rows padded to multiples of 4 entries)
 	int32_t* d_iap = nullptr;
 	int32_t* d_jap = nullptr;
@@ -174,6 +175,7 @@ static int build_rowsplit_plan(spmm_b200* h)
 	h->n_ctas = (int) std::max<int64_t>(1, std::min(want, cap));
 	if (h->d_cta_rows) cudaFree(h->d_cta_rows);
 	CU_TRY(cudaMalloc(&h->d_cta_rows, sizeof(int32_t) * (h->n_ctas + 1)));
+	if (!h->d_ticket) CU_TRY(cudaMalloc(&h->d_ticket, sizeof(int)));
 	const int nb = (h->n_ctas + 1 + 255) / 256;
 	cta_rows_nnz_kernel<<<nb, 256, 0, h->stream>>>(h->d_ia, (int) h->m, h->nnz, h->n_ctas, h->d_cta_rows);
 	h->launches++;
@@ -226,6 +228,31 @@ static void launch_rowsplit_gv(const spmm_b200* h, const double* B, double* C, c
 	// B-row gathers in flight per lane group; tuning knob, default from the ncu study in profiles/
 	static const int unroll = env_int("SPMM_B200_UNROLL", 4);
 	constexpr int K = G * V;
+	// Default: ONE resident wave of persistent warps that draw small row chunks from a ticket counter
+	// (spmm_rowsplit_ticket_kernel).  The whole GPU then sweeps A and C front to back (DRAM / L2 locality of the
+	// A stream) with no tail: cfg2 0.844 -> 0.754 ms on the same box (profiles/r1_ticket_probe.md).  Chunk = 8 rows
+	// (rounded to a multiple of the rows a warp works on at once).  SPMM_B200_TICKET=0 keeps the static
+	// nnz-balanced CTA ranges everywhere, > 0 forces that many rows per ticket.
+	int tick = env_int("SPMM_B200_TICKET", -1);
+	if (tick < 0) {
+		// measured over bench/medium_subset.txt x k in {4, 8, 32, 128} (profiles/r1_ticket_probe.md): rows of >= 50
+		// nonzeros gain 3-15 %, rows of <= 10 lose 3-15 % (a ticket per ~50 nonzeros is too fine, larger chunks lose
+		// the locality), launches of a few tens of microseconds lose to the counter reset and the atomics
+		const double avg = h->m > 0 ? (double) h->nnz / (double) h->m : 1.0;
+		tick = (avg >= 32.0 && h->nnz >= (8 << 20)) ? 8 : 0;
+	}
+	if (tick > 0 && h->d_ticket && unroll == 4) {
+		constexpr int NGW = 32 / G;
+		tick = (tick + NGW - 1) / NGW * NGW;
+		cudaMemsetAsync(h->d_ticket, 0, sizeof(int), s);
+		const int grid = (int) std::min<int64_t>((h->m + tick * (THREADS / 32) - 1) / (tick * (THREADS / 32)) + 1,
+		                                         (int64_t) h->sm_count * std::max(1, env_int("SPMM_B200_TICKET_CTAS", 4)));
+		if (ldb == K && (uint64_t) h->c * K < (1ull << 32) && env_int("SPMM_B200_CONST_LD", 1))
+			spmm_rowsplit_ticket_kernel<G, V, 4, THREADS, K><<<grid, THREADS, 0, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, (int) h->m, tick, h->d_ticket, ldb, ldc);
+		else
+			spmm_rowsplit_ticket_kernel<G, V, 4, THREADS><<<grid, THREADS, 0, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, (int) h->m, tick, h->d_ticket, ldb, ldc);
+		return;
+	}
 	if (unroll >= 8 && G >= 8)
 		spmm_rowsplit_kernel<G, V, 8, THREADS><<<h->n_ctas, THREADS, 0, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, h->d_cta_rows, ldb, ldc);
 	else if (unroll <= 2)
@@ -716,7 +743,7 @@ extern "C" void spmm_b200_destroy(spmm_b200_t* h)
 	cudaFree(h->d_iap); cudaFree(h->d_jap); cudaFree(h->d_ap);
 	cudaFree(h->merge.d_tile); cudaFree(h->merge.d_carry); cudaFree(h->merge.d_carry_row);
 	cudaFree(h->bcsr.d_brow); cudaFree(h->bcsr.d_bcol); cudaFree(h->bcsr.d_bval); cudaFree(h->bcsr.d_bmask);
-	cudaFree(h->d_x); cudaFree(h->d_B); cudaFree(h->d_C);
+	cudaFree(h->d_x); cudaFree(h->d_B); cudaFree(h->d_C); cudaFree(h->d_ticket);
 	if (h->ev0) cudaEventDestroy(h->ev0);
 	if (h->ev1) cudaEventDestroy(h->ev1);
 	for (cudaEvent_t e : h->ev_slice) cudaEventDestroy(e);

@@ -143,6 +143,72 @@ spmm_rowsplit_kernel(const int32_t* __restrict__ ia, const int32_t* __restrict__
 	}
 }
 
+// Experiment (SPMM_B200_TICKET=R): the same row loop on ONE resident wave of persistent warps that draw R-row
+// chunks from a ticket counter instead of owning a fixed nnz-balanced range -- removes the tail of the last wave.
+template <int G, int V, int UNROLL, int THREADS, int LD = 0>
+__global__ void __launch_bounds__(THREADS)
+spmm_rowsplit_ticket_kernel(const int32_t* __restrict__ ia, const int32_t* __restrict__ ja, const double* __restrict__ a,
+                            const double* __restrict__ B, double* __restrict__ C,
+                            int m, int rows_per_ticket, int* __restrict__ ticket, int ldb, int ldc)
+{
+	constexpr int NGW = 32 / G;              // row groups per warp
+	constexpr int U = UNROLL < G ? UNROLL : G;
+	const int lane = threadIdx.x & 31;
+	const int lig = lane % G;
+	const int gid = lane / G;
+	for (;;) {
+		int t = 0;
+		if (lane == 0) t = atomicAdd(ticket, 1);
+		t = __shfl_sync(0xffffffffu, t, 0);
+		const int64_t r0l = (int64_t) t * rows_per_ticket;
+		if (r0l >= m) break;
+		const int r0 = (int) r0l;
+		const int r1 = (int) min((int64_t) m, r0l + rows_per_ticket);
+		for (int base = r0; base < r1; base += NGW) {
+			const int row = base + gid;
+			const bool live = row < r1;
+			int j = 0, je = 0;
+			if (live) { j = __ldg(ia + row); je = __ldg(ia + row + 1); }
+			double acc[V];
+			#pragma unroll
+			for (int v = 0; v < V; v++) acc[v] = 0.0;
+			while (true) {
+				const int rem = je - j;
+				const int rem_warp = __reduce_max_sync(0xffffffffu, rem);
+				if (rem_warp <= 0) break;
+				int cj = 0;
+				double ca = 0.0;
+				if (lig < rem) { cj = __ldg(ja + j + lig); ca = __ldg(a + j + lig); }
+				const int cnt = min(rem_warp, G);
+				#pragma unroll
+				for (int u = 0; u < G; u += U) {
+					if (u >= cnt) break;
+					int cc[U];
+					double vv[U];
+					Frag<V> bb[U];
+					#pragma unroll
+					for (int i = 0; i < U; i++) {
+						cc[i] = __shfl_sync(0xffffffffu, cj, u + i, G);
+						vv[i] = shfl_f64<G>(ca, u + i);
+					}
+					#pragma unroll
+					for (int i = 0; i < U; i++)
+						if (u + i < rem) bb[i] = load_b<G, V, LD>(B, cc[i], lig, ldb);
+					#pragma unroll
+					for (int i = 0; i < U; i++) {
+						if (u + i < rem) {
+							#pragma unroll
+							for (int v = 0; v < V; v++) acc[v] = fma(vv[i], bb[i].v[v], acc[v]);
+						}
+					}
+				}
+				j += G;
+			}
+			if (live) store_c<G, V>(C, (size_t) row, lig, acc, ldc);
+		}
+	}
+}
+
 // Any k: one warp per row, lanes own columns, column chunks of 32 (A re-read per chunk
 // out of L1/L2).  Used for k values without a specialised instantiation.
 template <int THREADS>
