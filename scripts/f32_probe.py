@@ -18,7 +18,10 @@ def main():
     pkg = g.load_package()
     print("| matrix | k | fp32 ms | GFLOP/s | alg. GB/s (8 nnz + 4(m+1) + 4kc + 4km) | frac of %.0f |" % PEAK)
     print("|---|---|---|---|---|---|")
+    only = os.environ.get("F32_ONLY")
     for name, args, ks in CASES:
+        if only and name != only:
+            continue
         ia, ja, a, m, c = L.generate(args)
         a = a.astype(np.float32); nnz = len(ja)
         for k in ks:

@@ -17,6 +17,7 @@ struct spmm_b200_f32 {
 	float* d_a = nullptr;
 	int32_t* d_cta_rows = nullptr;
 	int n_ctas = 0;
+	int* d_ticket = nullptr;
 	float* d_x = nullptr; size_t cap_x = 0;
 	float* d_B = nullptr; size_t cap_B = 0;
 	float* d_C = nullptr; size_t cap_C = 0;
@@ -72,6 +73,7 @@ static int create_slice(spmm_b200_f32** out, const int32_t* ia_slice, const int3
 	const int64_t want = (int64_t) sms * 32, cap = std::max<int64_t>(1, (m + 7) / 8);
 	h->n_ctas = (int) std::max<int64_t>(1, std::min(want, cap));
 	CU_TRY(cudaMalloc(&h->d_cta_rows, sizeof(int32_t) * (h->n_ctas + 1)));
+	CU_TRY(cudaMalloc(&h->d_ticket, sizeof(int)));
 	cta_rows_nnz_kernel<<<(h->n_ctas + 1 + 255) / 256, 256, 0, h->stream>>>(h->d_ia, (int) m, nnz, h->n_ctas, h->d_cta_rows);
 	h->launches++;
 	CU_TRY(cudaGetLastError());
@@ -132,7 +134,7 @@ extern "C" void spmm_b200_destroy_f32(spmm_b200_f32_t* h)
 	if (!h) return;
 	cudaSetDevice(h->device);
 	if (h->stream) cudaStreamSynchronize(h->stream);
-	cudaFree(h->d_ia); cudaFree(h->d_ja); cudaFree(h->d_a); cudaFree(h->d_cta_rows);
+	cudaFree(h->d_ia); cudaFree(h->d_ja); cudaFree(h->d_a); cudaFree(h->d_cta_rows); cudaFree(h->d_ticket);
 	cudaFree(h->d_x); cudaFree(h->d_B); cudaFree(h->d_C);
 	if (h->ev0) cudaEventDestroy(h->ev0);
 	if (h->ev1) cudaEventDestroy(h->ev1);
@@ -143,6 +145,22 @@ extern "C" void spmm_b200_destroy_f32(spmm_b200_f32_t* h)
 template <int G, int V, int U>
 static void launch_gv(const spmm_b200_f32* h, const float* B, float* C, cudaStream_t s)
 {
+	// long rows and enough of them: persistent warps with 8-row tickets, as in the fp64 kernel (launch_rowsplit_gv)
+	int tick = env_int("SPMM_B200_TICKET", -1);
+	if (tick < 0) {
+		const double avg = h->m > 0 ? (double) h->nnz / (double) h->m : 1.0;
+		// measured on cfg2 (profiles/r1_f32_probe.md): k = 64 0.784 -> 0.698 ms, k = 128 1.339 -> 1.267 ms, k = 32 0.466 -> 0.493 ms
+		tick = (avg >= 32.0 && h->nnz >= (8 << 20) && G * V >= 64) ? 8 : 0;
+	}
+	if (tick > 0 && h->d_ticket) {
+		constexpr int NGW = 32 / G;
+		tick = (tick + NGW - 1) / NGW * NGW;
+		cudaMemsetAsync(h->d_ticket, 0, sizeof(int), s);
+		const int grid = (int) std::min<int64_t>((h->m + tick * (THREADS / 32) - 1) / (tick * (THREADS / 32)) + 1, (int64_t) h->sm_count * 4);
+		spmm_rowsplit_f32_kernel<G, V, U, THREADS, true><<<grid, THREADS, 0, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, h->d_cta_rows, G * V, G * V,
+		                                                                         (int) h->m, tick, h->d_ticket);
+		return;
+	}
 	spmm_rowsplit_f32_kernel<G, V, U, THREADS><<<h->n_ctas, THREADS, 0, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, h->d_cta_rows, G * V, G * V);
 }
 

@@ -23,19 +23,35 @@ __device__ __forceinline__ void load_b_f32(const float* __restrict__ B, int col,
 	}
 }
 
-template <int G, int V, int UNROLL, int THREADS>
+// TICKET = false: CTA b owns the fixed row range cta_rows[b..b+1).  TICKET = true: one resident wave of persistent
+// warps draws `rows_per_ticket`-row chunks from an atomic counter (cta_rows is unused) -- the scheduling of
+// spmm_rowsplit_ticket_kernel, same per-row arithmetic.
+template <int G, int V, int UNROLL, int THREADS, bool TICKET = false>
 __global__ void __launch_bounds__(THREADS)
 spmm_rowsplit_f32_kernel(const int32_t* __restrict__ ia, const int32_t* __restrict__ ja, const float* __restrict__ a,
                          const float* __restrict__ B, float* __restrict__ C,
-                         const int32_t* __restrict__ cta_rows, int ldb, int ldc)
+                         const int32_t* __restrict__ cta_rows, int ldb, int ldc,
+                         int m = 0, int rows_per_ticket = 0, int* __restrict__ ticket = nullptr)
 {
-	constexpr int NG = THREADS / G;
+	constexpr int NG = TICKET ? 32 / G : THREADS / G;      // row groups that advance together (warp / CTA)
 	constexpr int U = UNROLL < G ? UNROLL : G;
 	static_assert(G % U == 0, "UNROLL and G must nest");
 	const int lig = threadIdx.x % G;
-	const int gid = threadIdx.x / G;
-	const int r0 = cta_rows[blockIdx.x];
-	const int r1 = cta_rows[blockIdx.x + 1];
+	const int gid = TICKET ? (threadIdx.x & 31) / G : threadIdx.x / G;
+	for (;;) {
+	int r0, r1;
+	if (TICKET) {
+		int t = 0;
+		if ((threadIdx.x & 31) == 0) t = atomicAdd(ticket, 1);
+		t = __shfl_sync(0xffffffffu, t, 0);
+		const int64_t lo = (int64_t) t * rows_per_ticket;
+		if (lo >= m) break;
+		r0 = (int) lo;
+		r1 = (int) min((int64_t) m, lo + rows_per_ticket);
+	} else {
+		r0 = cta_rows[blockIdx.x];
+		r1 = cta_rows[blockIdx.x + 1];
+	}
 	for (int base = r0; base < r1; base += NG) {
 		const int row = base + gid;
 		const bool live = row < r1;
@@ -79,6 +95,8 @@ spmm_rowsplit_f32_kernel(const int32_t* __restrict__ ia, const int32_t* __restri
 			#pragma unroll
 			for (int i = 0; i < V / 4; i++) p[i * G + lig] = make_float4(acc[4 * i], acc[4 * i + 1], acc[4 * i + 2], acc[4 * i + 3]);
 		}
+	}
+	if (!TICKET) break;
 	}
 }
 
