@@ -34,6 +34,8 @@
 extern "C" {
 #endif
 
+/* A handle owns device buffers, streams and a row-ticket counter: calls on ONE handle must not overlap (one host
+ * thread / one stream at a time).  Different handles are independent. */
 typedef struct spmm_b200 spmm_b200_t;
 
 /* kernel variants (north_star (2),(3)) */

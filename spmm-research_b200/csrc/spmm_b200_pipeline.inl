@@ -213,14 +213,6 @@ static int pipe_softmax_launch(spmm_b200_pipeline* p, int rowwise)
 	return SPMM_B200_OK;
 }
 
-static int pipe_finish(spmm_b200_pipeline* p)
-{
-	CU_TRY(cudaEventRecord(p->ev1, p->stream));
-	CU_TRY(cudaStreamSynchronize(p->stream));
-	p->timed = true;
-	return SPMM_B200_OK;
-}
-
 extern "C" int spmm_b200_pipeline_spmm(spmm_b200_pipeline_t* p, char type, int64_t m, int64_t k, int n,
                                        const int32_t* ia, const int32_t* ja, const double* a,
                                        const double* x_host, double* y_host)
