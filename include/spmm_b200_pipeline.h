@@ -7,8 +7,8 @@
  *         csr_to_format(row_ptr, col_ind, values, m, nnz, n)
  * as implemented by pipeline_code_bench/sddmm_taco_naive.cpp and driven by sddmm_bench.cpp:918-936:
  *
- *     K = Wk * x,  Q = Wq * x,  V = Wv * x        spmm('K'|'Q'|'V', ...)      sddmm_taco_naive.cpp:232-275
- *     y[p] = mask[p] * sum_d Q[i][d] * K[i][d]    sddmm(y)                    sddmm_taco_naive.cpp:96-133 (compute2)
+ *     K = Wk * x,  Q = Wq * x,  V = Wv * x        spmm('K'|'Q'|'V', ...)      sddmm_taco_naive.cpp:219-260
+ *     y[p] = mask[p] * sum_d Q[i][d] * K[i][d]    sddmm(y)                    sddmm_taco_naive.cpp:98-140 (compute2)
  *     y_final = Mask(values y) * V                spmm('final', ...)          sddmm_bench.cpp:934-936
  *
  * Wk, Wq, Wv are CSR (m x k), x is dense k x n row-major, K, Q, V and y_final are dense m x n row-major
@@ -37,12 +37,12 @@ extern "C" {
 typedef struct spmm_b200_pipeline spmm_b200_pipeline_t;
 
 enum {
-	SPMM_B200_SDDMM_REFERENCE = 0,  /* both factors at row i (sddmm_taco_naive.cpp:121)           */
+	SPMM_B200_SDDMM_REFERENCE = 0,  /* both factors at row i (sddmm_taco_naive.cpp:128)           */
 	SPMM_B200_SDDMM_ATTENTION = 1,  /* Q at row i, K at row ja[p]; tree-ordered sum for n = 16, 32, 64, 128 */
 	SPMM_B200_SDDMM_ATTENTION_ORDERED = 2  /* same, summed left to right like the CPU loop (bit-reproducible against it) */
 };
 
-/* csr_to_format(row_ptr, col_ind, values, m, nnz, n) of the pipeline bench (sddmm_taco_naive.cpp:278-292):
+/* csr_to_format(row_ptr, col_ind, values, m, nnz, n) of the pipeline bench (sddmm_taco_naive.cpp:263-277):
  * the format is built from the attention mask (m x m CSR); n is the dense width (NUM_COLS).  The mask is
  * copied to `device`; the caller keeps the host arrays. */
 int spmm_b200_pipeline_create(spmm_b200_pipeline_t **p,
@@ -63,7 +63,7 @@ int spmm_b200_pipeline_spmm(spmm_b200_pipeline_t *p, char type, int64_t m, int64
  * SPMM_B200_EINVAL when 'Q' or 'K' has not been computed.  y_host may be NULL (result stays on the device). */
 int spmm_b200_pipeline_sddmm(spmm_b200_pipeline_t *p, double *y_host, int mode);
 
-/* softmax(y, nnz) of the reference (sddmm_taco_naive.cpp:207-225; the call is commented out at :231 and
+/* softmax(y, nnz) of the reference (sddmm_taco_naive.cpp:191-209; the call is commented out at :215 and
  * sddmm_bench.cpp:279): ONE softmax over all nnz values of the resident y.  rowwise != 0 normalises each mask
  * row on its own instead (what attention does; not in the reference). */
 int spmm_b200_pipeline_softmax(spmm_b200_pipeline_t *p, double *y_host, int rowwise);

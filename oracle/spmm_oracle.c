@@ -383,13 +383,13 @@ void oracle_spmm_csr_f32(const int32_t *ia, const int32_t *ja, const float *a,
 /* ---------------------------------------------------------------------------
  * N4: sparse-attention pipeline (benchmark_code/CPU/AMD/pipeline_code_bench).
  *
- * oracle_csrmm_rowmajor -- Matrix_Format::spmm of sddmm_taco_naive.cpp:232-275.  The reference calls
+ * oracle_csrmm_rowmajor -- Matrix_Format::spmm of sddmm_taco_naive.cpp:219-260.  The reference calls
  *   mkl_dcsrmm('N', m, n, k, alpha = 1, "GLNC", a, ja, ia, ia+1, x, ldb = n, beta = 0, y, ldc = n).
  *   Intel MKL (oneMKL Sparse BLAS level 3, deprecated mkl_?csrmm) is a third-party dependency absent from
  *   /root/reference; its published contract: C := alpha*A*B + beta*C, and with matdescra[3] = 'C' zero-based
  *   indices and ROW-major B (k x n) and C (m x n).  The summation order inside MKL is unspecified; this
  *   restatement sums each row left to right like the reference's own gold (spmm_helper, sddmm_bench.cpp:
- *   130-162), so agreement with an MKL build is to rounding (1e-12 relative), not bit for bit.
+ *   141-162), so agreement with an MKL build is to rounding (1e-12 relative), not bit for bit.
  * ------------------------------------------------------------------------- */
 void oracle_csrmm_rowmajor(const int32_t *ia, const int32_t *ja, const double *a,
                            long m, long n, const double *x, double *y)
@@ -405,13 +405,13 @@ void oracle_csrmm_rowmajor(const int32_t *ia, const int32_t *ja, const double *a
 	}
 }
 
-/* oracle_sddmm -- Matrix_Format::sddmm, sddmm_taco_naive.cpp:294-303 (compute_csr: y[] = 0, then compute2) and
- *   compute2, :96-133:
+/* oracle_sddmm -- Matrix_Format::sddmm, sddmm_taco_naive.cpp:280-290 (compute_csr: y[] = 0, then compute2) and
+ *   compute2, :98-140:
  *       for row i, for nonzero p of row i (column kA = ja[p]):
- *           for d < n:  y[p] += Q[i*n + d] * K[i*n + d]          <- BOTH factors at the output row (pO2, :121)
+ *           for d < n:  y[p] += Q[i*n + d] * K[i*n + d]          <- BOTH factors at the output row (pO2, :128)
  *           y[p] *= mask[p]
  *   mode 0 restates exactly that.  mode 1 is the sampled product the variable names describe (pD2 = kA*n + d
- *   is computed at :117 and left unused): K is read at row ja[p].
+ *   is computed at :124 and left unused): K is read at row ja[p].
  *   Rounding: gcc -O3 -mfma vectorises the reference's d loop as rounded products (vmulpd) followed by in-order
  *   adds, i.e. NO fused multiply-add anywhere in the sum (checked against oracle/_ref/libpipeline_ref.so for
  *   widths that are and are not multiples of the vector length); contraction is therefore switched off here. */
@@ -431,8 +431,8 @@ void oracle_sddmm(const int32_t *ia, const int32_t *ja, const double *mask, long
 	}
 }
 
-/* oracle_softmax -- softmax(input, size), sddmm_taco_naive.cpp:207-225 (its call sites are commented out,
- *   :231 and sddmm_bench.cpp:279): one softmax over the whole value array, sequential sums. */
+/* oracle_softmax -- softmax(input, size), sddmm_taco_naive.cpp:191-209 (its call sites are commented out,
+ *   :215 and sddmm_bench.cpp:279): one softmax over the whole value array, sequential sums. */
 #include <math.h>
 void oracle_softmax(double *v, long size)
 {

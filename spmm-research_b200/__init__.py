@@ -322,7 +322,7 @@ SDDMM_REFERENCE, SDDMM_ATTENTION, SDDMM_ATTENTION_ORDERED = 0, 1, 2
 class PipelineFormat:
     """Mirror of the pipeline bench's `struct Matrix_Format` (pipeline_code_bench/sddmm_kernel.h:9-31):
     fields m, n, nnz; methods spmm(type, m, k, n, ia, ja, a, x, y), sddmm(y).  Built from the attention
-    mask by csr_to_pipeline_format (csr_to_format(row_ptr, col_ind, values, m, nnz, n), sddmm_kernel.h:32).
+    mask by csr_to_pipeline_format (csr_to_format(row_ptr, col_ind, values, m, nnz, n), sddmm_kernel.h:31).
     Host numpy arrays in and out; K, Q, V, y stay on the device between calls."""
 
     format_name = "B200_CSR_PIPELINE"
@@ -395,7 +395,7 @@ class PipelineFormat:
 
 
 def csr_to_pipeline_format(row_ptr, col_ind, values, m, nnz, n, *, device=0):
-    """csr_to_format(row_ptr, col_ind, values, m, nnz, n) of the pipeline bench (sddmm_kernel.h:32): the format
+    """csr_to_format(row_ptr, col_ind, values, m, nnz, n) of the pipeline bench (sddmm_kernel.h:31): the format
     is built from the m x m attention mask; n is the dense width."""
     h = _vp()
     _check(load_library().spmm_b200_pipeline_create(C.byref(h), _host(row_ptr, np.int32, "row_ptr"),

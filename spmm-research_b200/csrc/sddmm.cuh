@@ -1,7 +1,7 @@
 // sddmm.cuh -- SDDMM and softmax kernels of the sparse-attention pipeline (SURVEY 8(f) N4;
 // benchmark_code/CPU/AMD/pipeline_code_bench/sddmm_taco_naive.cpp).
 //
-//   reference mode (compute2, sddmm_taco_naive.cpp:96-133):
+//   reference mode (compute2, sddmm_taco_naive.cpp:98-140):
 //       y[p] = ( sum_{d=0..n-1} Q[i*n+d] * K[i*n+d] ) * mask[p]           i = row of nonzero p
 //     the sum starts at 0 and runs left to right.  gcc -O3 -mfma compiles the reference's loop `B[pA2] += O*D`
 //     as rounded products followed by in-order adds (no fused multiply-add), so the chain here is
@@ -376,7 +376,7 @@ sddmm_attention_staged_kernel(const int32_t* __restrict__ ia, const int32_t* __r
 	}
 }
 
-// ---- softmax over ALL nnz values (softmax(), sddmm_taco_naive.cpp:207-225): max, exp(y - max) and its sum,
+// ---- softmax over ALL nnz values (softmax(), sddmm_taco_naive.cpp:191-209): max, exp(y - max) and its sum,
 // divide.  Partials are combined in a fixed order (deterministic); the reference sums left to right on one
 // thread, so the result agrees to rounding, not bit for bit.
 template <int THREADS, bool IS_MAX>

@@ -13,7 +13,7 @@
 // Environment (all optional):
 //   SPMM_B200_DEVICE      = CUDA device ordinal (default 0)
 //   SPMM_B200_SDDMM_MODE  = 0 (default): the reference's SDDMM, both factors at the output row
-//                           (sddmm_taco_naive.cpp:121); 1: K at row ja[p] (tree-ordered sum); 2: same, ordered
+//                           (sddmm_taco_naive.cpp:128); 1: K at row ja[p] (tree-ordered sum); 2: same, ordered
 //   SPMM_B200_RESIDENT    = 1 (default): the harness's last call spmm('final', mask, y, V, y_final) uses the y and V
 //                           that are already on the device when its `a` and `x` arguments are the very buffers the
 //                           preceding sddmm(y) and spmm('V', ..., V) calls wrote; 0: always upload them.

@@ -1,6 +1,6 @@
 // spmm_b200_pipeline.inl -- host side of include/spmm_b200_pipeline.h, included by spmm_b200.cu.
 // The three projections and the final product run on the SpMM handles above (row-major dense operands, the
-// layout mkl_dcsrmm's 'C' indexing gives the reference, sddmm_taco_naive.cpp:232-262); SDDMM and softmax are
+// layout mkl_dcsrmm's 'C' indexing gives the reference, sddmm_taco_naive.cpp:219-260); SDDMM and softmax are
 // the kernels of sddmm.cuh.  y is written straight into the value array of the mask's SpMM handle, so the
 // final product needs no copy.  SDDMM and the final SpMM stay two kernels: fusing them would save one write
 // and one read of y (16 bytes per nonzero) next to the 8n bytes per nonzero the V gather moves.

@@ -54,7 +54,7 @@ def test_oracle_matches_compiled_reference(L):
 
 
 def test_oracle_reference_mode_reads_k_at_the_output_row(L):
-    """sddmm_taco_naive.cpp:121: both factors at row i -- every nonzero of a row gets the same dot product."""
+    """sddmm_taco_naive.cpp:128: both factors at row i -- every nonzero of a row gets the same dot product."""
     mask, W, x = pipeline_case(21, 60, 40, 16, 3, 0.15)
     mia, mja, ma, m = mask
     Q = np.random.default_rng(1).standard_normal((m, 16))
