@@ -91,6 +91,21 @@ double  spmm_b200_pipeline_last_kernel_ms(const spmm_b200_pipeline_t *p);
 int64_t spmm_b200_pipeline_launch_count(const spmm_b200_pipeline_t *p);
 void    spmm_b200_pipeline_destroy(spmm_b200_pipeline_t *p);
 
+/* ---- the same step-by-step interface for the pipeline bench's "_f" build (ValueType = float, mkl_scsrmm +
+ * compute2 on floats): fp32 SpMM handles and ordered fp32 SDDMM kernels (both attention modes keep the loop's
+ * order); no softmax and no fused path in fp32 yet. */
+typedef struct spmm_b200_pipeline_f32 spmm_b200_pipeline_f32_t;
+int spmm_b200_pipeline_create_f32(spmm_b200_pipeline_f32_t **p,
+                                  const int32_t *mask_row_ptr, const int32_t *mask_col_ind, const float *mask_values,
+                                  int64_t m, int64_t nnz, int n, int device);
+int spmm_b200_pipeline_spmm_f32(spmm_b200_pipeline_f32_t *p, char type, int64_t m, int64_t k, int n,
+                                const int32_t *ia, const int32_t *ja, const float *a,
+                                const float *x_host, float *y_host);
+int spmm_b200_pipeline_sddmm_f32(spmm_b200_pipeline_f32_t *p, float *y_host, int mode);
+int spmm_b200_pipeline_final_f32(spmm_b200_pipeline_f32_t *p, float *y_final_host);
+int64_t spmm_b200_pipeline_launch_count_f32(const spmm_b200_pipeline_f32_t *p);
+void    spmm_b200_pipeline_destroy_f32(spmm_b200_pipeline_f32_t *p);
+
 #ifdef __cplusplus
 }
 #endif

@@ -338,3 +338,61 @@ def pipeline_ref(mask, weights, x, n, kdim, softmax=0):
     pipeline_ref_lib().ref_pipeline(mia, mja, ma, m, nnz, n, *weights["K"], *weights["Q"], *weights["V"], kdim,
                                     xx, K, Q, V, y, yf, softmax)
     return {"K": K, "Q": Q, "V": V, "y": y[:nnz], "y_final": yf}
+
+
+# ---- N4 in fp32 (the pipeline bench's "_f" build) -----------------------------------------------------------
+
+_f32p = np.ctypeslib.ndpointer(np.float32, flags="C_CONTIGUOUS")
+
+
+def _pipeline_oracle_f32():
+    lib = oracle()
+    if not hasattr(lib, "_typed_pipeline_f32"):
+        lib.oracle_csrmm_rowmajor_f32.argtypes = [_i32p, _i32p, _f32p, C.c_long, C.c_long, _f32p, _f32p]
+        lib.oracle_csrmm_rowmajor_f32.restype = None
+        lib.oracle_sddmm_f32.argtypes = [_i32p, _i32p, _f32p, C.c_long, C.c_long, _f32p, _f32p, _f32p, C.c_int]
+        lib.oracle_sddmm_f32.restype = None
+        lib._typed_pipeline_f32 = True
+    return lib
+
+
+def pipeline_oracle_f32(mask, weights, x, n, mode=0):
+    """fp32 pipeline without softmax.  mask = (ia, ja, a float32, m); weights values float32; x float32."""
+    mia, mja, ma, m = mask
+    lib = _pipeline_oracle_f32()
+    out = {}
+    xx = np.ascontiguousarray(x, dtype=np.float32).ravel()
+    for t in "KQV":
+        ia, ja, a = weights[t]
+        y = np.empty(m * n, dtype=np.float32)
+        lib.oracle_csrmm_rowmajor_f32(ia, ja, np.ascontiguousarray(a, dtype=np.float32), m, n, xx, y)
+        out[t] = y
+    y = np.empty(max(len(mja), 1), dtype=np.float32)
+    lib.oracle_sddmm_f32(mia, mja, np.ascontiguousarray(ma, dtype=np.float32), m, n, out["Q"], out["K"], y, mode)
+    out["y"] = y[:len(mja)]
+    yf = np.empty(m * n, dtype=np.float32)
+    lib.oracle_csrmm_rowmajor_f32(mia, mja, np.ascontiguousarray(out["y"]), m, n, out["V"], yf)
+    out["y_final"] = yf
+    return out
+
+
+def have_pipeline_ref_f32():
+    return os.path.exists(os.path.join(HERE, "_ref", "libpipeline_ref_f.so"))
+
+
+def pipeline_ref_f32(mask, weights, x, n, kdim):
+    """The reference's own "_f" pipeline TU: csr_to_format / spmm('K','Q','V') / sddmm / spmm('final')."""
+    lib = _load(os.path.join(HERE, "_ref", "libpipeline_ref_f.so"))
+    if not hasattr(lib, "_typed"):
+        csr = [_i32p, _i32p, _f32p]
+        lib.ref_pipeline.argtypes = csr + [C.c_long, C.c_long, C.c_int] + csr * 3 + [C.c_long] + [_f32p] * 6 + [C.c_int]
+        lib.ref_pipeline.restype = None
+        lib._typed = True
+    mia, mja, ma, m = mask
+    nnz = len(mja)
+    K, Q, V, yf = (np.zeros(m * n, np.float32) for _ in range(4))
+    y = np.zeros(max(nnz, 1), np.float32)
+    w = {t: (weights[t][0], weights[t][1], np.ascontiguousarray(weights[t][2], dtype=np.float32)) for t in "KQV"}
+    lib.ref_pipeline(mia, mja, np.ascontiguousarray(ma, dtype=np.float32), m, nnz, n, *w["K"], *w["Q"], *w["V"], kdim,
+                     np.ascontiguousarray(x, dtype=np.float32).ravel(), K, Q, V, y, yf, 0)
+    return {"K": K, "Q": Q, "V": V, "y": y[:nnz], "y_final": yf}

@@ -456,3 +456,35 @@ void oracle_softmax_rows(const int32_t *ia, long m, double *v)
 	for (long i = 0; i < m; i++)
 		oracle_softmax(v + ia[i], ia[i + 1] - ia[i]);
 }
+
+/* N4 in fp32 (the pipeline bench's "_f" build, ValueType = float: mkl_scsrmm + the same compute2 on floats).
+ * Same restatements as above with float sums and float products. */
+void oracle_csrmm_rowmajor_f32(const int32_t *ia, const int32_t *ja, const float *a,
+                               long m, long n, const float *x, float *y)
+{
+	#pragma omp parallel for
+	for (long i = 0; i < m; i++) {
+		for (long d = 0; d < n; d++) {
+			float sum = 0;
+			for (long j = ia[i]; j < ia[i + 1]; j++)
+				sum = __builtin_fmaf(a[j], x[(long) ja[j] * n + d], sum);
+			y[i * n + d] = sum;
+		}
+	}
+}
+
+__attribute__((optimize("-ffp-contract=off")))
+void oracle_sddmm_f32(const int32_t *ia, const int32_t *ja, const float *mask, long m, long n,
+                      const float *Q, const float *K, float *y, int mode)
+{
+	#pragma omp parallel for
+	for (long i = 0; i < m; i++) {
+		for (long p = ia[i]; p < ia[i + 1]; p++) {
+			const float *krow = K + (mode ? (long) ja[p] : i) * n;
+			float s = 0.0f;
+			for (long d = 0; d < n; d++)
+				s += Q[i * n + d] * krow[d];
+			y[p] = s * mask[p];
+		}
+	}
+}

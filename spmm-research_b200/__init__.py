@@ -19,7 +19,7 @@ import numpy as np
 __all__ = ["csr_to_format", "csr_to_format_f32", "MatrixFormatF32", "coo_to_csr", "read_mtx", "read_smtx", "MatrixFormat", "partition", "shard_slices", "statistics_print_labels", "load_library",
            "SpmmB200Error", "ROWSPLIT", "MERGE", "BCSR", "AUTO", "BCSR_FMA", "B_COLMAJOR", "B_ROWMAJOR",
            "PART_ROWS", "PART_NNZ", "PART_MERGE", "LIB_PATH", "EXPORTS",
-           "PipelineFormat", "csr_to_pipeline_format", "SDDMM_REFERENCE", "SDDMM_ATTENTION", "SDDMM_ATTENTION_ORDERED"]
+           "PipelineFormat", "csr_to_pipeline_format", "PipelineFormatF32", "csr_to_pipeline_format_f32", "SDDMM_REFERENCE", "SDDMM_ATTENTION", "SDDMM_ATTENTION_ORDERED"]
 
 ROWSPLIT, MERGE, BCSR, AUTO, BCSR_FMA = 0, 1, 2, 3, 4
 B_COLMAJOR, B_ROWMAJOR = 0, 1
@@ -45,6 +45,8 @@ EXPORTS = [
     "spmm_b200_pipeline_final", "spmm_b200_pipeline_set_weight", "spmm_b200_pipeline_attention",
     "spmm_b200_pipeline_device_ptr", "spmm_b200_pipeline_last_kernel_ms", "spmm_b200_pipeline_launch_count",
     "spmm_b200_pipeline_destroy",
+    "spmm_b200_pipeline_create_f32", "spmm_b200_pipeline_spmm_f32", "spmm_b200_pipeline_sddmm_f32",
+    "spmm_b200_pipeline_final_f32", "spmm_b200_pipeline_launch_count_f32", "spmm_b200_pipeline_destroy_f32",
 ]
 
 _lib = None
@@ -128,6 +130,12 @@ def load_library():
     lib.spmm_b200_pipeline_last_kernel_ms.argtypes = [_vp]; lib.spmm_b200_pipeline_last_kernel_ms.restype = _dbl
     lib.spmm_b200_pipeline_launch_count.argtypes = [_vp]; lib.spmm_b200_pipeline_launch_count.restype = _i64
     lib.spmm_b200_pipeline_destroy.argtypes = [_vp]; lib.spmm_b200_pipeline_destroy.restype = None
+    lib.spmm_b200_pipeline_create_f32.argtypes = lib.spmm_b200_pipeline_create.argtypes
+    lib.spmm_b200_pipeline_spmm_f32.argtypes = lib.spmm_b200_pipeline_spmm.argtypes
+    lib.spmm_b200_pipeline_sddmm_f32.argtypes = [_vp, _vp, _int]
+    lib.spmm_b200_pipeline_final_f32.argtypes = [_vp, _vp]
+    lib.spmm_b200_pipeline_launch_count_f32.argtypes = [_vp]; lib.spmm_b200_pipeline_launch_count_f32.restype = _i64
+    lib.spmm_b200_pipeline_destroy_f32.argtypes = [_vp]; lib.spmm_b200_pipeline_destroy_f32.restype = None
     _lib = lib
     return lib
 
@@ -402,6 +410,64 @@ def csr_to_pipeline_format(row_ptr, col_ind, values, m, nnz, n, *, device=0):
            _host(col_ind, np.int32, "col_ind") if nnz else None, _host(values, np.float64, "values") if nnz else None,
            m, nnz, n, device), "spmm_b200_pipeline_create")
     return PipelineFormat(h, m, nnz, n, (row_ptr, col_ind, values))
+
+
+class PipelineFormatF32:
+    """PipelineFormat for the pipeline bench's "_f" build (float32 arrays): spmm, sddmm, final."""
+
+    format_name = "B200_CSR_PIPELINE_F32"
+
+    def __init__(self, handle, m, nnz, n, keep):
+        self._h = handle
+        self.m, self.nnz, self.n = int(m), int(nnz), int(n)
+        self._keep = {"mask": tuple(keep)}
+
+    def spmm(self, type, m, k, n, ia, ja, a, x, y):
+        t = type.encode()[:1] if isinstance(type, str) else bytes(type)[:1]
+        if y is not None and y.size < m * n:
+            raise ValueError("y holds fewer than m*n values")
+        if x.size < k * n:
+            raise ValueError("x holds fewer than k*n values")
+        if t in (b"K", b"Q", b"V"):
+            self._keep[t] = (ia, ja, a)
+        _check(load_library().spmm_b200_pipeline_spmm_f32(self._h, t, m, k, n, _host(ia, np.int32, "ia"),
+               _host(ja, np.int32, "ja") if len(ja) else None, _host(a, np.float32, "a") if len(a) else None,
+               _host(x, np.float32, "x") if x.size else None, None if y is None else _host(y, np.float32, "y")),
+               "spmm_b200_pipeline_spmm_f32")
+
+    def sddmm(self, y=None, mode=SDDMM_REFERENCE):
+        if y is not None and y.size < self.nnz:
+            raise ValueError("y holds fewer than nnz values")
+        _check(load_library().spmm_b200_pipeline_sddmm_f32(self._h, None if y is None else _host(y, np.float32, "y"), mode),
+               "spmm_b200_pipeline_sddmm_f32")
+
+    def final(self, y_final):
+        if y_final.size < self.m * self.n:
+            raise ValueError("y_final holds fewer than m*n values")
+        _check(load_library().spmm_b200_pipeline_final_f32(self._h, _host(y_final, np.float32, "y_final")),
+               "spmm_b200_pipeline_final_f32")
+
+    def launch_count(self):
+        return load_library().spmm_b200_pipeline_launch_count_f32(self._h)
+
+    def close(self):
+        if self._h:
+            load_library().spmm_b200_pipeline_destroy_f32(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def csr_to_pipeline_format_f32(row_ptr, col_ind, values, m, nnz, n, *, device=0):
+    h = _vp()
+    _check(load_library().spmm_b200_pipeline_create_f32(C.byref(h), _host(row_ptr, np.int32, "row_ptr"),
+           _host(col_ind, np.int32, "col_ind") if nnz else None, _host(values, np.float32, "values") if nnz else None,
+           m, nnz, n, device), "spmm_b200_pipeline_create_f32")
+    return PipelineFormatF32(h, m, nnz, n, (row_ptr, col_ind, values))
 
 
 def csr_to_format_f32(row_ptr, col_ind, values, m, n, nnz, k, *, device=0, b_layout=B_COLMAJOR, rank=None, nranks=None):

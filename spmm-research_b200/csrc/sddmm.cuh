@@ -82,6 +82,47 @@ sddmm_attention_kernel(const int32_t* __restrict__ ia, const int32_t* __restrict
 	}
 }
 
+// fp32 twins of the two ordered kernels above (the pipeline bench's "_f" build, ValueType = float): float
+// products and in-order float adds, a warp per mask row.
+template <int THREADS>
+__global__ void __launch_bounds__(THREADS)
+sddmm_rowdot_f32_kernel(const int32_t* __restrict__ ia, const float* __restrict__ mask_a,
+                        const float* __restrict__ Q, const float* __restrict__ K,
+                        float* __restrict__ y, int64_t m, int n)
+{
+	constexpr int NW = THREADS / 32;
+	const int lane = threadIdx.x & 31;
+	for (int64_t row = (int64_t) blockIdx.x * NW + (threadIdx.x >> 5); row < m; row += (int64_t) gridDim.x * NW) {
+		const int js = __ldg(ia + row), je = __ldg(ia + row + 1);
+		if (js == je) continue;
+		const float* q = Q + (size_t) row * n;
+		const float* kk = K + (size_t) row * n;
+		float s = 0.f;
+		for (int d = 0; d < n; d++) s = __fadd_rn(s, __fmul_rn(__ldg(q + d), __ldg(kk + d)));
+		for (int p = js + lane; p < je; p += 32) y[p] = __fmul_rn(s, __ldg(mask_a + p));
+	}
+}
+
+template <int THREADS>
+__global__ void __launch_bounds__(THREADS)
+sddmm_attention_f32_kernel(const int32_t* __restrict__ ia, const int32_t* __restrict__ ja, const float* __restrict__ mask_a,
+                           const float* __restrict__ Q, const float* __restrict__ K,
+                           float* __restrict__ y, int64_t m, int n)
+{
+	constexpr int NW = THREADS / 32;
+	const int lane = threadIdx.x & 31;
+	for (int64_t row = (int64_t) blockIdx.x * NW + (threadIdx.x >> 5); row < m; row += (int64_t) gridDim.x * NW) {
+		const int js = __ldg(ia + row), je = __ldg(ia + row + 1);
+		const float* q = Q + (size_t) row * n;
+		for (int p = js + lane; p < je; p += 32) {
+			const float* kk = K + (size_t) __ldg(ja + p) * n;
+			float s = 0.f;
+			for (int d = 0; d < n; d++) s = __fadd_rn(s, __fmul_rn(__ldg(q + d), __ldg(kk + d)));
+			y[p] = __fmul_rn(s, __ldg(mask_a + p));
+		}
+	}
+}
+
 // Attention mode, fast path (n = G*V, V a multiple of 4).  Same work mapping as the row-split SpMM: a group of G
 // lanes reads one K row per load instruction (V/2 16-byte chunks per lane, chunk i at i*G + lane-in-group), with
 // U rows in flight.  A lane multiplies its V columns into a partial for each of the group's G nonzeros, then the

@@ -8,7 +8,8 @@
 // (ref: benchmark_code/CPU/AMD/pipeline_code_bench/sddmm_kernel.h:9-33) on top of the C ABI in
 // include/spmm_b200_pipeline.h.  Compiled against the reference's own headers and linked under the UNCHANGED
 // pipeline harness objects exactly like sddmm_taco_naive.cpp (Makefile_in:166); see oracle/Makefile target
-// `pipeline_harness` and INTEGRATION.md.  fp64 builds only (the C ABI of the pipeline is double).
+// `pipeline_harness` and INTEGRATION.md.  "_d" builds use the fp64 entry points, "_f" builds (ValueType = float,
+// DOUBLE == 0) the fp32 ones (spmm_b200_pipeline_*_f32).
 //
 // Environment (all optional):
 //   SPMM_B200_DEVICE      = CUDA device ordinal (default 0)
@@ -26,8 +27,12 @@
 #include "sddmm_kernel.h"
 #include "spmm_b200_pipeline.h"
 
-#if DOUBLE != 1
-	#error "sddmm_kernel_b200.cpp: the pipeline C ABI is fp64; build the _d target"
+#if DOUBLE == 0
+	typedef spmm_b200_pipeline_f32_t pipe_t;
+	#define PIPE(fn) spmm_b200_pipeline_ ## fn ## _f32
+#else
+	typedef spmm_b200_pipeline_t pipe_t;
+	#define PIPE(fn) spmm_b200_pipeline_ ## fn
 #endif
 
 static void die(const char * where, int code)
@@ -39,7 +44,7 @@ static void die(const char * where, int code)
 
 struct B200Pipeline : Matrix_Format
 {
-	spmm_b200_pipeline_t * handle;
+	pipe_t * handle;
 	INT_T * mask_ia;
 	INT_T * mask_ja;
 	ValueType * last_y;      // host buffer the last sddmm() filled
@@ -52,7 +57,7 @@ struct B200Pipeline : Matrix_Format
 
 	~B200Pipeline()
 	{
-		spmm_b200_pipeline_destroy(handle);
+		PIPE(destroy)(handle);
 	}
 
 	void spmm(char type, INT_T m, INT_T k, INT_T n, INT_T * ia, INT_T * ja, ValueType * a, ValueType * x, ValueType * y, int num_threads);
@@ -68,9 +73,9 @@ B200Pipeline::spmm(char type, INT_T m, INT_T k, INT_T n, INT_T * ia, INT_T * ja,
 	int rc;
 	if (resident && type != 'K' && type != 'Q' && type != 'V' && ia == mask_ia && ja == mask_ja && a == last_y && x == last_v
 			&& last_y != NULL && last_v != NULL)
-		rc = spmm_b200_pipeline_final(handle, y);
+		rc = PIPE(final)(handle, y);
 	else
-		rc = spmm_b200_pipeline_spmm(handle, type, m, k, n, ia, ja, a, x, y);
+		rc = PIPE(spmm)(handle, type, m, k, n, ia, ja, a, x, y);
 	if (rc)
 		die("spmm", rc);
 	if (type == 'V')
@@ -80,7 +85,7 @@ B200Pipeline::spmm(char type, INT_T m, INT_T k, INT_T n, INT_T * ia, INT_T * ja,
 void
 B200Pipeline::sddmm(ValueType * y, __attribute__((unused)) int num_threads)
 {
-	int rc = spmm_b200_pipeline_sddmm(handle, y, mode);
+	int rc = PIPE(sddmm)(handle, y, mode);
 	if (rc)
 		die("sddmm", rc);
 	last_y = y;
@@ -98,10 +103,10 @@ csr_to_format(INT_T * row_ptr, INT_T * col_ind, ValueType * values, long m, long
 		p->mode = atoi(s);
 	if ((s = getenv("SPMM_B200_RESIDENT")) != NULL && *s)
 		p->resident = atoi(s);
-	p->format_name = (char *) "B200_CSR_PIPELINE";
+	p->format_name = (char *) (DOUBLE == 0 ? "B200_CSR_PIPELINE_F32" : "B200_CSR_PIPELINE");
 	p->mask_ia = row_ptr;
 	p->mask_ja = col_ind;
-	int rc = spmm_b200_pipeline_create(&p->handle, row_ptr, col_ind, values, m, nnz, (int) n, device);
+	int rc = PIPE(create)(&p->handle, row_ptr, col_ind, values, m, nnz, (int) n, device);
 	if (rc)
 		die("csr_to_format", rc);
 	p->mem_footprint = p->csr_mem_footprint;

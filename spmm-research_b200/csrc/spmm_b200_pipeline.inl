@@ -428,3 +428,177 @@ extern "C" int64_t spmm_b200_pipeline_launch_count(const spmm_b200_pipeline_t* p
 	for (auto& w : p->w) n += w.h ? w.h->launches : 0;
 	return n;
 }
+
+// ------------------------------------------------------------------------------------------
+// fp32 pipeline (the pipeline bench's "_f" build): the step-by-step interface on the fp32 SpMM handles
+// (spmm_b200_f32.inl) and the ordered fp32 SDDMM kernels of sddmm.cuh.  No softmax / fused path yet.
+// ------------------------------------------------------------------------------------------
+struct spmm_b200_pipeline_f32 {
+	int device = 0, n = 0;
+	int64_t m = 0, nnz = 0;
+	const int32_t* mask_ia_host = nullptr;
+	const int32_t* mask_ja_host = nullptr;
+	spmm_b200_f32* mask = nullptr;           // its d_a holds y after sddmm
+	float* d_mask_a = nullptr;
+	struct Weight {
+		spmm_b200_f32* h = nullptr;
+		const int32_t* ia = nullptr; const int32_t* ja = nullptr; const float* a = nullptr;
+		int64_t m = 0, k = 0, nnz = 0;
+		float* d_out = nullptr;
+		bool have = false;
+	} w[3];
+	float* d_x = nullptr; size_t cap_x = 0;
+	float* d_tmp = nullptr; size_t cap_tmp = 0;
+	float* d_final = nullptr;
+	bool have_y = false;
+	cudaStream_t stream = nullptr;
+	int64_t own_launches = 0;
+};
+
+extern "C" void spmm_b200_pipeline_destroy_f32(spmm_b200_pipeline_f32_t* p)
+{
+	if (!p) return;
+	cudaSetDevice(p->device);
+	if (p->stream) cudaStreamSynchronize(p->stream);
+	if (p->mask) spmm_b200_destroy_f32(p->mask);
+	for (auto& w : p->w) {
+		if (w.h) spmm_b200_destroy_f32(w.h);
+		if (w.d_out) cudaFree(w.d_out);
+	}
+	if (p->d_mask_a) cudaFree(p->d_mask_a);
+	if (p->d_x) cudaFree(p->d_x);
+	if (p->d_tmp) cudaFree(p->d_tmp);
+	if (p->d_final) cudaFree(p->d_final);
+	if (p->stream) cudaStreamDestroy(p->stream);
+	delete p;
+}
+
+extern "C" int spmm_b200_pipeline_create_f32(spmm_b200_pipeline_f32_t** out,
+                                             const int32_t* mask_ia, const int32_t* mask_ja, const float* mask_a,
+                                             int64_t m, int64_t nnz, int n, int device)
+{
+	if (!out) return SPMM_B200_EINVAL;
+	*out = nullptr;
+	if (m < 0 || nnz < 0 || n < 1 || !mask_ia || (nnz > 0 && (!mask_ja || !mask_a))) return SPMM_B200_EINVAL;
+	if (m >= INT32_MAX || nnz >= INT32_MAX) return SPMM_B200_ERANGE;
+	int rc = check_device(device, nullptr);
+	if (rc) return rc;
+	spmm_b200_pipeline_f32* p = new (std::nothrow) spmm_b200_pipeline_f32;
+	if (!p) return SPMM_B200_ENOMEM;
+	p->device = device; p->n = n; p->m = m; p->nnz = nnz;
+	p->mask_ia_host = mask_ia; p->mask_ja_host = mask_ja;
+	cudaError_t e = cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking);
+	if (e == cudaSuccess) e = cudaMalloc(&p->d_mask_a, sizeof(float) * std::max<int64_t>(nnz, 1));
+	if (e == cudaSuccess && nnz > 0) e = cudaMemcpy(p->d_mask_a, mask_a, sizeof(float) * nnz, cudaMemcpyHostToDevice);
+	if (e == cudaSuccess) e = cudaMalloc(&p->d_final, sizeof(float) * std::max<int64_t>(m * n, 1));
+	if (e != cudaSuccess) {
+		snprintf(g_cuda_err, sizeof(g_cuda_err), "spmm_b200_pipeline_create_f32: %s", cudaGetErrorString(e));
+		spmm_b200_pipeline_destroy_f32(p);
+		return e == cudaErrorMemoryAllocation ? SPMM_B200_ENOMEM : SPMM_B200_ECUDA;
+	}
+	rc = spmm_b200_create_f32(&p->mask, mask_ia, mask_ja, mask_a, m, m, nnz, n, device, SPMM_B200_B_ROWMAJOR);
+	if (rc) { spmm_b200_pipeline_destroy_f32(p); return rc; }
+	*out = p;
+	return SPMM_B200_OK;
+}
+
+extern "C" int spmm_b200_pipeline_spmm_f32(spmm_b200_pipeline_f32_t* p, char type, int64_t m, int64_t k, int n,
+                                           const int32_t* ia, const int32_t* ja, const float* a,
+                                           const float* x_host, float* y_host)
+{
+	if (!p || !ia || m < 0 || k < 0 || n != p->n) return SPMM_B200_EINVAL;
+	if (k > 0 && !x_host) return SPMM_B200_EINVAL;
+	CU_TRY(cudaSetDevice(p->device));
+	const int idx = pipe_index(type);
+	const int64_t nnz = ia[m];
+	if (nnz > 0 && (!ja || !a)) return SPMM_B200_EINVAL;
+	int rc = ensure32(&p->d_x, &p->cap_x, (size_t) k * n);
+	if (rc) return rc;
+	if (k > 0) CU_TRY(cudaMemcpyAsync(p->d_x, x_host, sizeof(float) * k * n, cudaMemcpyHostToDevice, p->stream));
+	if (idx >= 0) {
+		if (m != p->m) return SPMM_B200_EINVAL;
+		auto& w = p->w[idx];
+		if (!(w.h && w.ia == ia && w.ja == ja && w.a == a && w.m == m && w.k == k && w.nnz == nnz)) {
+			if (w.h) { p->own_launches += w.h->launches; spmm_b200_destroy_f32(w.h); w.h = nullptr; }
+			w.have = false;
+			rc = spmm_b200_create_f32(&w.h, ia, ja, a, m, k, nnz, n, p->device, SPMM_B200_B_ROWMAJOR);
+			if (rc) return rc;
+			if (!w.d_out) CU_TRY(cudaMalloc(&w.d_out, sizeof(float) * std::max<int64_t>(m * n, 1)));
+			w.ia = ia; w.ja = ja; w.a = a; w.m = m; w.k = k; w.nnz = nnz;
+		}
+		if (m > 0) {
+			rc = spmm_b200_run_device_f32(w.h, p->d_x, w.d_out, n, p->stream);
+			if (rc) return rc;
+		}
+		w.have = true;
+		if (y_host && m > 0) CU_TRY(cudaMemcpyAsync(y_host, w.d_out, sizeof(float) * m * n, cudaMemcpyDeviceToHost, p->stream));
+		CU_TRY(cudaStreamSynchronize(p->stream));
+		return SPMM_B200_OK;
+	}
+	if (!y_host && m > 0) return SPMM_B200_EINVAL;
+	if (ia == p->mask_ia_host && ja == p->mask_ja_host && m == p->m && k == p->m && nnz == p->nnz) {
+		// spmm('final', mask, y, V, y_final) with host y and V: only the values and V travel
+		if (nnz > 0) CU_TRY(cudaMemcpyAsync(p->mask->d_a, a, sizeof(float) * nnz, cudaMemcpyHostToDevice, p->stream));
+		p->have_y = true;
+		if (m > 0) {
+			rc = spmm_b200_run_device_f32(p->mask, p->d_x, p->d_final, n, p->stream);
+			if (rc) return rc;
+			CU_TRY(cudaMemcpyAsync(y_host, p->d_final, sizeof(float) * m * n, cudaMemcpyDeviceToHost, p->stream));
+		}
+		CU_TRY(cudaStreamSynchronize(p->stream));
+		return SPMM_B200_OK;
+	}
+	spmm_b200_f32* h = nullptr;
+	rc = spmm_b200_create_f32(&h, ia, ja, a, m, k, nnz, n, p->device, SPMM_B200_B_ROWMAJOR);
+	if (rc) return rc;
+	rc = ensure32(&p->d_tmp, &p->cap_tmp, (size_t) m * n);
+	if (!rc && m > 0) rc = spmm_b200_run_device_f32(h, p->d_x, p->d_tmp, n, p->stream);
+	if (!rc && m > 0 && cudaMemcpyAsync(y_host, p->d_tmp, sizeof(float) * m * n, cudaMemcpyDeviceToHost, p->stream) != cudaSuccess) rc = SPMM_B200_ECUDA;
+	if (cudaStreamSynchronize(p->stream) != cudaSuccess && !rc) rc = SPMM_B200_ECUDA;
+	p->own_launches += h->launches;
+	spmm_b200_destroy_f32(h);
+	return rc;
+}
+
+extern "C" int spmm_b200_pipeline_sddmm_f32(spmm_b200_pipeline_f32_t* p, float* y_host, int mode)
+{
+	if (!p || mode < SPMM_B200_SDDMM_REFERENCE || mode > SPMM_B200_SDDMM_ATTENTION_ORDERED) return SPMM_B200_EINVAL;
+	if (!p->w[0].have || !p->w[1].have) return SPMM_B200_EINVAL;
+	CU_TRY(cudaSetDevice(p->device));
+	if (p->m > 0 && p->nnz > 0) {
+		const int grid = (int) std::min<int64_t>((p->m + THREADS / 32 - 1) / (THREADS / 32), (int64_t) p->mask->sm_count * 64);
+		if (mode == SPMM_B200_SDDMM_REFERENCE)
+			sb200::sddmm_rowdot_f32_kernel<THREADS><<<grid, THREADS, 0, p->stream>>>(p->mask->d_ia, p->d_mask_a, p->w[1].d_out, p->w[0].d_out,
+			                                                                        p->mask->d_a, p->m, p->n);
+		else      // both attention modes: the ordered kernel (no tree-ordered fp32 kernel yet)
+			sb200::sddmm_attention_f32_kernel<THREADS><<<grid, THREADS, 0, p->stream>>>(p->mask->d_ia, p->mask->d_ja, p->d_mask_a,
+			                                                                           p->w[1].d_out, p->w[0].d_out, p->mask->d_a, p->m, p->n);
+		CU_TRY(cudaGetLastError());
+		p->own_launches += 1;
+	}
+	p->have_y = true;
+	if (y_host && p->nnz > 0) CU_TRY(cudaMemcpyAsync(y_host, p->mask->d_a, sizeof(float) * p->nnz, cudaMemcpyDeviceToHost, p->stream));
+	CU_TRY(cudaStreamSynchronize(p->stream));
+	return SPMM_B200_OK;
+}
+
+extern "C" int spmm_b200_pipeline_final_f32(spmm_b200_pipeline_f32_t* p, float* y_final_host)
+{
+	if (!p || !p->have_y || !p->w[2].have) return SPMM_B200_EINVAL;
+	CU_TRY(cudaSetDevice(p->device));
+	if (p->m > 0) {
+		int rc = spmm_b200_run_device_f32(p->mask, p->w[2].d_out, p->d_final, p->n, p->stream);
+		if (rc) return rc;
+		if (y_final_host) CU_TRY(cudaMemcpyAsync(y_final_host, p->d_final, sizeof(float) * p->m * p->n, cudaMemcpyDeviceToHost, p->stream));
+	}
+	CU_TRY(cudaStreamSynchronize(p->stream));
+	return SPMM_B200_OK;
+}
+
+extern "C" int64_t spmm_b200_pipeline_launch_count_f32(const spmm_b200_pipeline_f32_t* p)
+{
+	if (!p) return 0;
+	int64_t n = p->own_launches + (p->mask ? p->mask->launches : 0);
+	for (auto& w : p->w) n += w.h ? w.h->launches : 0;
+	return n;
+}

@@ -34,3 +34,19 @@ for i, (seed, m, kdim, n, band, fill, mv, sm) in enumerate(CASES):
         out[f"case{i}_{k}"] = v
 np.savez_compressed(os.path.join(HERE, "pipeline_reference.npz"), **out)
 print("wrote", len(CASES), "cases")
+
+# the "_f" build of the same TU (ValueType = float): oracle/_ref/libpipeline_ref_f.so
+out32 = {"ncases": 0}
+for i, (seed, m, kdim, n, band, fill, mv, sm) in enumerate(c for c in CASES if c[-1] == 0):
+    mask, W, x = pipeline_case(seed, m, kdim, n, band, fill, mask_values=mv)
+    mask = (mask[0], mask[1], mask[2].astype(np.float32), mask[3])
+    W = {t: (W[t][0], W[t][1], W[t][2].astype(np.float32)) for t in "KQV"}
+    r = L.pipeline_ref_f32(mask, W, x.astype(np.float32), n, kdim)
+    out32[f"case{i}_params"] = np.array([seed, m, kdim, n, band, 0], dtype=np.int64)
+    out32[f"case{i}_fill"] = fill
+    out32[f"case{i}_mask_values"] = mv
+    for k, v in r.items():
+        out32[f"case{i}_{k}"] = v
+    out32["ncases"] = i + 1
+np.savez_compressed(os.path.join(HERE, "pipeline_reference_f32.npz"), **out32)
+print("wrote", out32["ncases"], "fp32 cases")
