@@ -10,7 +10,10 @@
  *   (1) the golden vectors of SURVEY.md section 8(c) (generator FNV hashes,
  *       partition row starts, merge-path coordinates), and
  *   (2) the reference's own code compiled from /root/reference into
- *       oracle/_ref/libspmm_ref.so (see oracle/Makefile, oracle/ref_shim.cpp).
+ *       oracle/_ref/libspmm_ref.so (see oracle/Makefile, oracle/ref_shim.cpp), and for the sparse-attention
+ *       pipeline (N4) into oracle/_ref/libpipeline_ref.so / libpipeline_ref_f.so (oracle/ref_shim_pipeline.cpp;
+ *       the TU's one external dependency, MKL's mkl_?csrmm, is served from its published contract by
+ *       oracle/mkl_stub/ -- so SDDMM and softmax are pinned to reference bits, the projections to that contract).
  *
  * All "ref:" citations are relative to /root/reference.
  */
