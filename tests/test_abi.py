@@ -31,6 +31,21 @@ def test_library_exports_every_declared_symbol(pkg):
     assert sorted(pkg.EXPORTS) == syms
 
 
+def test_headers_are_plain_c99():
+    """The boundary is a C ABI: every header under include/ compiles as C99 (no C++, no torch, no CUDA types)."""
+    import shutil
+    import subprocess
+    if not shutil.which("gcc"):
+        pytest.skip("gcc not on PATH")
+    for name in sorted(os.listdir(os.path.join(ROOT, "include"))):
+        if name.endswith(".h"):
+            r = subprocess.run(["gcc", "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", "-fsyntax-only", "-x", "c",
+                                os.path.join(ROOT, "include", name)], capture_output=True, text=True)
+            assert r.returncode == 0, r.stderr
+            src = open(os.path.join(ROOT, "include", name)).read()
+            assert "torch" not in src and "cudaStream_t" not in re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+
+
 def test_library_is_in_tree_and_sm100(pkg):
     assert os.path.realpath(pkg.LIB_PATH).startswith(os.path.realpath(ROOT))
     blob = open(pkg.LIB_PATH, "rb").read()
