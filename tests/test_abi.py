@@ -85,6 +85,16 @@ def test_argument_validation(pkg):
     assert lib.spmm_b200_pipeline_attention(None, None, None, 0, 0) == -1
     assert lib.spmm_b200_pipeline_launch_count(None) == 0
     lib.spmm_b200_pipeline_destroy(None)
+    # the "_f" pipeline entry points
+    af = a.astype(np.float32)
+    assert lib.spmm_b200_pipeline_create_f32(None, rp, ci, af.ctypes.data, 10, len(ja), 8, 0) == -1
+    assert lib.spmm_b200_pipeline_create_f32(C.byref(h), rp, None, af.ctypes.data, 10, len(ja), 8, 0) == -1
+    assert lib.spmm_b200_pipeline_create_f32(C.byref(h), rp, ci, af.ctypes.data, 10, len(ja), 0, 0) == -1
+    assert lib.spmm_b200_pipeline_create_f32(C.byref(h), rp, ci, af.ctypes.data, 10, 2 ** 31, 8, 0) == -5
+    assert lib.spmm_b200_pipeline_sddmm_f32(None, None, 0) == -1
+    assert lib.spmm_b200_pipeline_final_f32(None, None) == -1
+    assert lib.spmm_b200_pipeline_launch_count_f32(None) == 0
+    lib.spmm_b200_pipeline_destroy_f32(None)
 
 
 def test_no_cpu_fallback(pkg):
