@@ -358,3 +358,33 @@ def test_gpu_reference_pipeline_harness_runs_our_plugin(tmp_path, mode):
     assert (int(f[2]), int(f[3]), int(f[4])) == (64, 2048, 1024)
     assert (int(f[-3]), int(f[-2]), int(f[-1])) == (2048, 64, harness_mask_nnz(2048))
     assert float(f[17]) > 0                                               # gflops of the whole pipeline
+
+
+def test_oracle_sddmm_property_random_shapes(L):
+    """Both SDDMM modes against a dense numpy evaluation over random shapes, including empty rows and n = 1."""
+    from hypothesis import given, settings, strategies as st
+
+    @settings(max_examples=25, deadline=None)
+    @given(st.integers(1, 40), st.integers(1, 33), st.integers(0, 2 ** 16))
+    def check(m, n, seed):
+        rng = np.random.default_rng(seed)
+        ia, ja, a = random_csr(m, m, 3.0, seed, empty_frac=0.3)
+        Q = rng.standard_normal((m, n))
+        K = rng.standard_normal((m, n))
+        rows = np.repeat(np.arange(m), np.diff(ia))
+        for mode in (0, 1):
+            y = L.sddmm_oracle(ia, ja, a, m, n, Q, K, mode)
+            kr = K[rows] if mode == 0 else K[ja]
+            ref = np.einsum("pd,pd->p", Q[rows], kr) * a
+            scale = (np.abs(Q[rows]) * np.abs(kr)).sum(1) * np.abs(a) + 1e-300
+            assert (np.abs(y - ref) <= 1e-13 * scale * n).all()
+
+    check()
+
+
+def test_oracle_softmax_rows_with_empty_rows(L):
+    ia = np.array([0, 0, 4, 4, 9, 9], np.int32)
+    v = np.random.default_rng(5).standard_normal(9) * 3
+    r = L.softmax_oracle(v, ia)
+    assert abs(r[0:4].sum() - 1) < 1e-14 and abs(r[4:9].sum() - 1) < 1e-14
+    assert (r > 0).all()
