@@ -22,6 +22,8 @@ import time
 
 import numpy as np
 
+HOST_CPUS = len(os.sched_getaffinity(0))     # before libgomp may bind the initial thread to one place
+
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
@@ -60,14 +62,36 @@ def measured_peak_gbs():
         return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
-def ncu_traffic(workload, k):
-    """dram bytes per launch of the dominant kernel from the committed ncu capture, or None."""
+def ncu_traffic(workload, k, world, kernel):
+    """dram bytes per launch of the dominant kernel from the committed ncu capture (profiles/traffic.json), or None.
+    Only for the configuration the capture was taken on: one GPU, same workload and k, same kernel family."""
+    if world != 1:
+        return None
     try:
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
             t = json.load(f)
-        return t.get(f"{workload}_k{k}")
+        e = t.get(f"{workload}_k{k}")
+        if isinstance(e, dict):
+            return e.get("dram_bytes") if e.get("kernel", kernel) == kernel else None
+        return e
     except Exception:
         return None
+
+
+def cpu_model():
+    try:
+        with open("/proc/cpuinfo") as f:
+            for line in f:
+                if line.startswith("model name"):
+                    return line.split(":", 1)[1].strip()
+    except OSError:
+        pass
+    return "unknown"
+
+
+# L2 -> SM gather ceiling measured with scripts/gather_probe.cu on this pool's B200 (profiles/r1_gather_probe.log):
+# random 256-byte rows out of an L2-resident window
+L2_GATHER_CEILING_TBS = 21.6
 
 
 class ClockSampler:
@@ -129,7 +153,7 @@ class ClockSampler:
 def use_all_host_threads():
     """torchrun exports OMP_NUM_THREADS=1 to every rank; the CPU arm must use the cores the process may run on."""
     import ctypes
-    n = len(os.sched_getaffinity(0))
+    n = HOST_CPUS
     try:
         ctypes.CDLL("libgomp.so.1").omp_set_num_threads(n)
     except OSError:
@@ -150,18 +174,20 @@ def cpu_spmm_timer(ia, ja, a, m, c, k, x):
     if L.have_ref():
         lib, kind, cores = L.ref(), "reference", L.ref().ref_num_threads()
 
-        def run(rows):
-            nz = int(ia[rows])
+        def run(rows, first=0):
+            # rows [first, first + rows): row_ptr holds absolute offsets into ja / a, so a row window is ia + first
+            nz = int(ia[first + rows])
             t0 = time.perf_counter()
-            lib.ref_spmm_csr_nocopy(ia, ja, a, rows, c, nz, x, y, k)
+            lib.ref_spmm_csr_nocopy(ia[first:], ja, a, rows, c, nz, x, y, k)
             return time.perf_counter() - t0
     else:
         lib, kind, cores = L.oracle(), "port", L.oracle().oracle_num_threads()
 
-        def run(rows):
+        def run(rows, first=0):
             t0 = time.perf_counter()
-            lib.oracle_spmm_csr(ia, ja, a, rows, c, x, y, k)
+            lib.oracle_spmm_csr(ia[first:], ja, a, rows, c, x, y, k)
             return time.perf_counter() - t0
+    run.y = y
     return run, kind, cores
 
 
@@ -178,6 +204,21 @@ def bounded_rows(run, ia, m, k, budget_s):
     return int(max(probe, min(m, np.searchsorted(ia, target_nnz))))
 
 
+def reference_parity(ia, ja, a, c, k, x, y_gpu, first_row, rows):
+    """max_i |y - y_ref| / max(|y_ref|, tiny) of the GPU result (host buffer the e2e call filled) against the
+    reference's own compute_csr (spmm_kernel_csr.cpp:69-97) on the same rows of the same matrix and the same B."""
+    run, kind, _ = cpu_spmm_timer(ia, ja, a, len(ia) - 1, c, k, x)
+    run(rows, first_row)
+    y_ref = run.y[: rows * k]
+    if rows == 0:
+        err = 0.0
+    else:
+        err = float(np.max(np.abs(y_gpu[: rows * k] - y_ref) / np.maximum(np.abs(y_ref), 1e-300)))
+    return {"max_rel_err": err, "tol": 1e-12, "ok": bool(err <= 1e-12), "rows_compared": int(rows), "first_row": int(first_row),
+            "vs": "reference compute_csr (oracle/_ref/libspmm_ref.so)" if kind == "reference" else "oracle port (oracle/liboracle.so)",
+            "against": "y returned by the e2e host-buffer call"}
+
+
 def cpu_baseline(ia, ja, a, m, c, k, x, total_budget_s=20.0):
     run, kind, cores = cpu_spmm_timer(ia, ja, a, m, c, k, x)
     rows = bounded_rows(run, ia, m, k, budget_s=total_budget_s / 4.0)
@@ -189,7 +230,26 @@ def cpu_baseline(ia, ja, a, m, c, k, x, total_budget_s=20.0):
     t = float(np.median(times))
     sample = (f"full matrix ({rows} rows, {int(nz)} nnz)" if rows == m else
               f"first {rows} of {m} rows ({int(nz)} nnz)") + f", {len(times)} timed calls after 1 warm-up, median"
-    return {"value": 2.0 * nz * k / t / 1e9, "unit": UNIT, "cores": int(cores), "kind": kind, "sample": sample}
+    return {"value": 2.0 * nz * k / t / 1e9, "unit": UNIT, "cores": int(cores), "kind": kind, "sample": sample,
+            "cpu_model": cpu_model(), "omp": {v: os.environ.get(v) for v in ("OMP_PROC_BIND", "OMP_PLACES", "OMP_DYNAMIC")}}
+
+
+def cpu_baseline_subprocess(args, k):
+    """The cpu_baseline leg as its own process = `bench.py --impl reference` on the same workload: the reference pins
+    one OpenMP thread per core (OMP_PROC_BIND / OMP_PLACES, run.sh:618-619), which must be in the environment before
+    libgomp starts and would also pin this process's own host thread."""
+    import subprocess
+    cmd = [sys.executable, os.path.abspath(__file__), "--impl", "reference", "--workload", args.workload, "--k", str(k),
+           "--steps", "5", "--warmup", "1"]
+    env = {kk: v for kk, v in os.environ.items() if kk not in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "OMP_NUM_THREADS")}
+    try:
+        r = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=600)
+        for ln in reversed(r.stdout.strip().splitlines()):
+            if ln.startswith("{"):
+                return json.loads(ln)["cpu_baseline"]
+    except Exception:
+        pass
+    return None
 
 
 def reference_arm(args, ia, ja, a, m, c, k, nnz, workload_desc):
@@ -212,7 +272,9 @@ def reference_arm(args, ia, ja, a, m, c, k, nnz, workload_desc):
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": t * 1e3, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": workload_desc,
-            "cpu_baseline": {"value": val, "unit": UNIT, "cores": int(cores), "kind": kind, "sample": sample},
+            "cpu_baseline": {"value": val, "unit": UNIT, "cores": int(cores), "kind": kind, "sample": sample,
+                             "cpu_model": cpu_model(),
+                             "omp": {v: os.environ.get(v) for v in ("OMP_PROC_BIND", "OMP_PLACES", "OMP_DYNAMIC")}},
             "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
@@ -343,6 +405,7 @@ def gpu_arm(args, ia, ja, a, m, c, k, nnz, workload_desc):
     e2e_s = max_over_ranks((time.perf_counter() - t0) / e2e_steps)
     clocks = sampler.stop()
     e2e_val = 2.0 * nnz * k / e2e_s / 1e9
+    timeline = mf.last_timeline()            # event times of the last e2e step on this rank (ms since its first enqueue)
 
     # ---- checksum so that the work cannot be skipped silently -----------------------------------
     csum = float(c_dev[: m_loc * k].sum().item()) if m_loc else 0.0
@@ -352,8 +415,20 @@ def gpu_arm(args, ia, ja, a, m, c, k, nnz, workload_desc):
 
     peak, peak_src = measured_peak_gbs()
     nnz_loc = mf.nnz
-    bytes_launch = algorithmic_bytes(nnz_loc, m_loc, c, k)
+    # Bytes one launch must move.  N = 1: SURVEY 8(d)'s formula (all of B charged once).  N > 1: a shard only reads the
+    # B rows its columns touch (random placement: the same window on every rank), so the per-rank figure charges the
+    # touched window (first..last touched column) instead of all of B -- otherwise the "fraction" exceeds 1.
+    j0, j1 = int(ia[mf.first_row]), int(ia[mf.first_row + m_loc])
+    if j1 > j0:
+        col_lo, col_hi = int(ja[j0:j1].min()), int(ja[j0:j1].max())
+        touched_b = 8.0 * k * (col_hi - col_lo + 1)
+    else:
+        touched_b = 0.0
+    bytes_full = algorithmic_bytes(nnz_loc, m_loc, c, k)
+    bytes_launch = bytes_full if world == 1 else 12.0 * nnz_loc + 4.0 * (m_loc + 1) + touched_b + 8.0 * k * m_loc
     achieved = bytes_launch / (kernel_ms * 1e-3) / 1e9
+    gather_bytes = 8.0 * k * nnz_loc         # one B row per nonzero crosses L2 -> SM
+    gather_tbs = gather_bytes / (kernel_ms * 1e-3) / 1e12
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
@@ -362,19 +437,34 @@ def gpu_arm(args, ia, ja, a, m, c, k, nnz, workload_desc):
                 "ms_per_step": e2e_s * 1e3, "steps": e2e_steps},
         "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": ncu_traffic(args.workload, k), "peak_source": peak_src,
+                     "traffic": ncu_traffic(args.workload, k, world, mf.format_name), "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": bytes_launch, "kernel_ms": kernel_ms,
                      "kernel": mf.format_name, "frac_of_8TBs_nominal": achieved / 8000.0,
+                     "touched_b_bytes": touched_b,
+                     "bytes_model": "12*nnz + 4*(m+1) + 8*k*c + 8*k*m (SURVEY 8(d))" if world == 1 else
+                                    "rank 0 shard: 12*nnz_g + 4*(m_g+1) + touched B window + 8*k*m_g",
+                     "l2_gather": {"bytes": gather_bytes, "achieved_tbs": gather_tbs, "ceiling_tbs": L2_GATHER_CEILING_TBS,
+                                   "frac": gather_tbs / L2_GATHER_CEILING_TBS,
+                                   "note": "nnz*8k bytes of B rows cross L2->SM per launch; ceiling = pure gather of random "
+                                           "256-byte rows from an L2-resident window (scripts/gather_probe.cu); it is the "
+                                           "binding roof when rows share no columns"},
                      "rank0_shard": world > 1},
         "clocks": clocks,
         "checksum_c_rank0": csum, "checksum_c_e2e_rank0": csum_e2e,
         "variant": mf.format_name,
         "bcsr_fill": mf.bcsr_fill(), "kslice": mf.kslice(),
     }
+    line["e2e"]["timeline_ms_last_step_rank0"] = timeline
+    if rank == 0 and not args.no_parity:
+        # the e2e result (host buffer) against the reference's CPU kernel on the same rows: whole matrix at N = 1,
+        # rank 0's shard rows at N > 1
+        line["parity"] = reference_parity(ia, ja, a, c, k, x_host.numpy(), y_host.numpy(), mf.first_row, m_loc)
     if rank == 0 and world == 1 and not args.no_cpu:
-        line["cpu_baseline"] = cpu_baseline(ia, ja, a, m, c, k, x_host.numpy())
+        line["cpu_baseline"] = cpu_baseline_subprocess(args, k) or cpu_baseline(ia, ja, a, m, c, k, x_host.numpy())
     if rank == 0:
         print(json.dumps(line), flush=True)
+        if "parity" in line and not line["parity"]["ok"]:
+            raise SystemExit(f"bench.py: GPU result differs from the reference: {line['parity']}")
     mf.close()
     if world > 1:
         dist.destroy_process_group()
@@ -390,11 +480,17 @@ def main():
     ap.add_argument("--k", type=int, default=None)
     ap.add_argument("--variant", default="auto", choices=["auto", "rowsplit", "merge", "bcsr", "bcsr_fma"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-parity", action="store_true", help="skip the comparison of the e2e result with the reference CPU kernel")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     rank = int(os.environ.get("RANK", 0))
     if args.impl == "reference" and rank != 0:
         return 0
+    if args.impl == "reference":
+        # the reference pins one OpenMP thread per core (run.sh:618-619); must be set before libgomp starts
+        os.environ.setdefault("OMP_PROC_BIND", "true")
+        os.environ.setdefault("OMP_PLACES", "cores")
+        os.environ.setdefault("OMP_DYNAMIC", "false")
 
     from oracle import loader as L          # input generation = the reference's own generator
     gen_args, k = WORKLOADS[args.workload]

@@ -34,8 +34,11 @@
 extern "C" {
 #endif
 
-/* A handle owns device buffers, streams and a row-ticket counter: calls on ONE handle must not overlap (one host
- * thread / one stream at a time).  Different handles are independent. */
+/* A handle owns device buffers, streams and row-ticket counters: calls on ONE handle must not overlap (one host
+ * thread / one stream at a time).  Different handles are independent.
+ * Alignment: the specialised kernels move B and C as 16-byte words.  Device operands handed to
+ * spmm_b200_run_device that are not 16-byte aligned (or whose k is odd) are still accepted -- they run on the
+ * generic kernel (slower, same result); a page-locked y that is not 16-byte aligned takes the staged download. */
 typedef struct spmm_b200 spmm_b200_t;
 
 /* kernel variants (north_star (2),(3)) */
@@ -57,7 +60,9 @@ enum {
 enum {
 	SPMM_B200_PART_ROWS   = 0, /* loop_partitioner_balance_iterations   lib/parallel_util.h:47-93,116-126 : out[2t],out[2t+1] = [start,end) */
 	SPMM_B200_PART_NNZ    = 1, /* loop_partitioner_balance_prefix_sums  lib/parallel_util.h:141-165       : out[0..P] row starts, out[P]=m  */
-	SPMM_B200_PART_MERGE  = 2  /* MergePathSearch at diagonals t*ceil((m+nnz)/P), ARM/spmv_kernel_merge.cpp:214-234,262-272 : out[2t]=row, out[2t+1]=nnz idx, t=0..P */
+	SPMM_B200_PART_MERGE  = 2, /* MergePathSearch at diagonals t*ceil((m+nnz)/P), ARM/spmv_kernel_merge.cpp:214-234,262-272 : out[2t]=row, out[2t+1]=nnz idx, t=0..P */
+	SPMM_B200_PART_NNZ_CARRY = 3 /* perfect nnz balance with row carry, spmv_kernel_csr.cpp:68-80 (CUSTOM_VECTOR_PERFECT_NNZ_BALANCE):
+	                                out[4t..4t+3] = thread_i_s, thread_i_e, thread_j_s, thread_j_e of worker t = 0..P-1 */
 };
 
 enum {
@@ -132,6 +137,16 @@ int spmm_b200_run_replicated(spmm_b200_t *h, const double *x_host, double *y_hos
 int spmm_b200_register_host(spmm_b200_t *h, const void *p, size_t bytes);
 int spmm_b200_unregister_host(spmm_b200_t *h, const void *p);
 
+/* Tuning knobs: every SPMM_B200_<NAME> environment variable is read ONCE, when a handle is
+ * created; afterwards spmm_b200_set_option(h, "<NAME>", value) changes it for that handle ("SPMM_B200_" prefix
+ * optional).  Unknown names: SPMM_B200_EINVAL. */
+int spmm_b200_set_option(spmm_b200_t *h, const char *name, int value);
+
+/* Event-stamped timeline of the last k-sliced host-buffer run (spmm_b200_run / _run_replicated): out[0] = number of
+ * slices S, then per slice six times in ms since the first enqueue: H2D done, replication done, transpose done,
+ * kernel start, kernel end, D2H done.  Returns the number of doubles written. */
+int spmm_b200_last_timeline(const spmm_b200_t *h, double *out, int max_values);
+
 /* Upload B once (x is constant across the reference's timed loop,
  * spmv_bench.cpp:895-903) and run on the resident copy. */
 int spmm_b200_set_b(spmm_b200_t *h, const double *x_host, int k);
@@ -142,14 +157,44 @@ int spmm_b200_fetch_c(spmm_b200_t *h, double *y_host, int k);
  * (bench.py / torch.distributed ranks): b_dev = row-major c x k, c_dev =
  * row-major m_local x k, both on the handle's device; `stream` is a
  * cudaStream_t (NULL = default stream).  Asynchronous -- except that, when the B rows the matrix touches
- * (column span x 8k bytes) are far beyond the 126 MB L2 and k >= 64, the first 8 calls with that k each run and
- * time one candidate column-slice width of the row-split kernel (same bits for every candidate) and block
- * until their kernels finish; the fastest is kept (spmm_b200_kslice).  SPMM_B200_KSLICE=-1 turns this off. */
+ * (column span x 8k bytes) are far beyond the 126 MB L2 and k >= 64, the first 8 calls with a given k each run and
+ * time one candidate column-slice width of the row-split kernel (same bits for every candidate) and BLOCK
+ * until their kernels finish; the fastest is kept per k (spmm_b200_kslice).  The measurement is skipped while
+ * `stream` is being captured into a CUDA graph; SPMM_B200_KSLICE=-1 turns it off. */
 int spmm_b200_run_device(spmm_b200_t *h, const double *b_dev, double *c_dev, int k, void *stream);
 
 /* Column-major (oracle layout) -> row-major transpose of B on the device. */
 int spmm_b200_transpose_b_device(spmm_b200_t *h, const double *x_colmajor_dev, double *b_rowmajor_dev,
                                  int k, void *stream);
+
+/* ---- single-process multi-GPU (csr_to_format(..., ngpus), 8(e)): ONE host thread drives `ngpus`
+ * devices of one box, which is how the reference's C harness reaches more than one GPU.  Rows are cut by
+ * loop_partitioner_balance_prefix_sums with P = ngpus (bit-exact); device g holds shard g of A.  The only exchange is
+ * the replication of B: every device uploads 1/ngpus of each column slice of x over its own PCIe link, then ONE
+ * kernel per device gathers all parts out of its peers' memory over NVLink (peer loads) and writes the row-major
+ * operand -- the all-gather and the layout transpose are the same pass.  C is row-local and lands in rows
+ * [first_row_g, last_row_g) of the caller's single y.  devices == NULL: ordinals 0..ngpus-1.  ngpus <= 16.
+ * Without peer access between a pair of devices every device uploads all of x itself. */
+typedef struct spmm_b200_multi spmm_b200_multi_t;
+int spmm_b200_create_multi(spmm_b200_multi_t **mh,
+                           const int32_t *row_ptr, const int32_t *col_ind, const double *values,
+                           int64_t m, int64_t c, int64_t nnz, int k,
+                           int ngpus, const int *devices, int variant, int b_layout);
+/* Matrix_Format::spmm with HOST buffers over all shards; x: c*k, y: m*k (whole matrix). */
+int spmm_b200_run_multi(spmm_b200_multi_t *mh, const double *x_host, double *y_host, int k, int copy_back);
+/* x constant across calls (spmv_bench.cpp:895-903): replicate once, run on the resident copies, fetch when needed */
+int spmm_b200_set_b_multi(spmm_b200_multi_t *mh, const double *x_host, int k);
+int spmm_b200_run_resident_multi(spmm_b200_multi_t *mh, int k);
+int spmm_b200_fetch_c_multi(spmm_b200_multi_t *mh, double *y_host, int k);
+/* page-lock a caller buffer for every device (cudaHostRegisterPortable | Mapped) */
+int spmm_b200_register_host_multi(spmm_b200_multi_t *mh, const void *p, size_t bytes);
+int spmm_b200_multi_ngpus(const spmm_b200_multi_t *mh);
+spmm_b200_t *spmm_b200_multi_shard(spmm_b200_multi_t *mh, int g);   /* shard handle (introspection, set_option) */
+int64_t spmm_b200_multi_first_row(const spmm_b200_multi_t *mh, int g);  /* g = ngpus: m */
+double  spmm_b200_multi_last_kernel_ms(const spmm_b200_multi_t *mh);    /* max over the shards */
+int64_t spmm_b200_multi_launch_count(const spmm_b200_multi_t *mh);
+int     spmm_b200_multi_peer_access(const spmm_b200_multi_t *mh);      /* 1: B is exchanged over NVLink */
+void    spmm_b200_destroy_multi(spmm_b200_multi_t *mh);
 
 /* ---- partitioning, testable without an SpMM kernel (host pointers in and out,
  * the search itself runs on the device).  `out` sizes: see the enum above. */

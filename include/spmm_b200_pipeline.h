@@ -81,6 +81,14 @@ int spmm_b200_pipeline_final(spmm_b200_pipeline_t *p, double *y_final_host);
  * step-by-step kernels. */
 int spmm_b200_pipeline_set_weight(spmm_b200_pipeline_t *p, char type, int64_t m, int64_t k, int64_t nnz,
                                   const int32_t *ia, const int32_t *ja, const double *a);
+/* Residency hazard: set_weight / spmm('K'|'Q'|'V') keep a weight on the device and take a later call with the SAME host
+ * pointers and sizes for the same weight (after comparing a cheap fingerprint: sizes + ~1024 strided samples of the
+ * arrays).  A caller that rewrites a weight in place should call spmm_b200_pipeline_invalidate(p, type) ('K', 'Q',
+ * 'V' or '*' for all) before handing it over again -- the fingerprint catches a refill, not a single changed entry. */
+int spmm_b200_pipeline_invalidate(spmm_b200_pipeline_t *p, char type);
+/* Tuning knobs (SPMM_B200_SDDMM_GROUP, _SDDMM_STAGED, _SDDMM_TUNE, _TICKET_REV, _PIPELINE_FORK, _ATTENTION_FUSED) are
+ * read once, at creation; this changes one afterwards ("SPMM_B200_" prefix optional). */
+int spmm_b200_pipeline_set_option(spmm_b200_pipeline_t *p, const char *name, int value);
 int spmm_b200_pipeline_attention(spmm_b200_pipeline_t *p, const double *x_host, double *y_final_host,
                                  int mode, int softmax);
 

@@ -44,6 +44,10 @@ def oracle():
         lib.oracle_balance_prefix_sums.argtypes = [_i32p, C.c_long, C.c_long, C.c_long, _i64p]
         lib.oracle_balance_iterations.argtypes = [C.c_long, C.c_long, C.c_long, _i64p]
         lib.oracle_merge_partition.argtypes = [_i32p, C.c_long, C.c_long, C.c_long, _i64p]
+        lib.oracle_nnz_carry_partition.argtypes = [_i32p, C.c_long, C.c_long, C.c_long, _i64p]
+        lib.oracle_nnz_carry_partition.restype = None
+        lib.oracle_spmv_nnz_carry.argtypes = [_i32p, _i32p, _f64p, C.c_long, C.c_long, C.c_long, _f64p, _f64p]
+        lib.oracle_spmv_nnz_carry.restype = None
         lib.oracle_coo_to_csr.argtypes = [_i32p, _i32p, C.c_void_p, C.c_long, C.c_long, C.c_long,
                                           _i32p, _i32p, C.c_void_p, C.c_int, C.c_int]
         lib.oracle_coo_to_csr.restype = None
@@ -93,6 +97,22 @@ def spmm_oracle_f32(ia, ja, a, m, c, x, k):
     y = np.empty(m * k, dtype=np.float32)
     lib.oracle_spmm_csr_f32(ia, ja, a, m, c, x, y, k)
     return y
+
+
+def have_pbv_ref():
+    return os.path.exists(os.path.join(HERE, "_ref", "libpbv_ref.so"))
+
+
+def pbv_ref():
+    """The reference's spmv_kernel_csr.cpp built as Custom_CSR_PBV (perfect nnz balance with row carry, a6)."""
+    lib = _load(os.path.join(HERE, "_ref", "libpbv_ref.so"))
+    if not hasattr(lib, "_typed"):
+        lib.ref_pbv_partition.argtypes = [_i32p, _i32p, _f64p, C.c_long, C.c_long, C.c_long, C.c_int, _i64p]
+        lib.ref_pbv_partition.restype = None
+        lib.ref_pbv_spmv.argtypes = [_i32p, _i32p, _f64p, C.c_long, C.c_long, C.c_long, C.c_int, _f64p, _f64p]
+        lib.ref_pbv_spmv.restype = None
+        lib._typed = True
+    return lib
 
 
 def merge_ref():

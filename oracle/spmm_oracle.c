@@ -144,6 +144,92 @@ void oracle_balance_iterations(long start, long end, long P, int64_t *out)
 }
 
 /* ---------------------------------------------------------------------------
+ * a6: "perfect nnz balance with row carry" (Custom_CSR_PBV).
+ * ref: benchmark_code/CPU/AMD/spmv_code_bench/spmv_kernel_csr.cpp:68-80 (set-up, CUSTOM_VECTOR_PERFECT_NNZ_BALANCE)
+ *      and :625-680 (compute_csr_vector_perfect_nnz_balance).
+ *
+ * Set-up, per worker t of P: [j_s, j_e) = loop_partitioner_balance_iterations over [0, nnz);
+ * i_s = LOWER boundary of binary_search(ia, 0, m, j_s) -- the range is 0..m here (ia has m+1 entries), and the
+ * lower boundary is: the index hit exactly (s first, then e), else s with ia[s] < j_s < ia[s+1];
+ * i_e[t] = i_s[t+1] + 1, last worker: m.   out[4t..4t+3] = i_s, i_e, j_s, j_e.
+ * ------------------------------------------------------------------------- */
+static long lower_boundary(const int32_t *A, long lo, long hi, long T)
+{
+	long s = lo, e = hi, mid;
+	if (T < A[s])
+		return -1;                   /* macrolib.h:481-486: s = -1 */
+	if (T > A[e])
+		return e;                    /* :487-492: s = e */
+	for (;;) {
+		mid = (s + e) / 2;
+		if (mid == s || mid == e)
+			break;
+		if (T > A[mid])
+			s = mid;
+		else
+			e = mid;
+	}
+	if (T == A[s])
+		return s;
+	if (T == A[e])
+		return e;
+	return s;
+}
+
+void oracle_nnz_carry_partition(const int32_t *ia, long m, long nnz, long P, int64_t *out)
+{
+	int64_t *js = (int64_t *) malloc(sizeof(int64_t) * 2 * (size_t) P);
+	oracle_balance_iterations(0, nnz, P, js);
+	for (long t = 0; t < P; t++) {
+		out[4 * t + 2] = js[2 * t];
+		out[4 * t + 3] = js[2 * t + 1];
+		out[4 * t] = lower_boundary(ia, 0, m, js[2 * t]);
+	}
+	for (long t = 0; t < P; t++)
+		out[4 * t + 1] = (t == P - 1) ? m : out[4 * (t + 1)] + 1;
+	free(js);
+}
+
+/* SpMV over that partition, workers run one after the other (the reference runs them in parallel, separated by a
+ * barrier after the zeroing of the shared rows; the arithmetic per worker and the order of the serial fix-up are the
+ * same, so the result is the same bits).  ref: spmv_kernel_csr.cpp:625-680. */
+void oracle_spmv_nnz_carry(const int32_t *ia, const int32_t *ja, const double *a, long m, long nnz, long P,
+                           const double *x, double *y)
+{
+	int64_t *part = (int64_t *) malloc(sizeof(int64_t) * 4 * (size_t) P);
+	double *v_e = (double *) malloc(sizeof(double) * (size_t) P);
+	oracle_nnz_carry_partition(ia, m, nnz, P, part);
+	for (long t = 0; t < P; t++)
+		if (part[4 * t + 1] - 1 >= 0)
+			y[part[4 * t + 1] - 1] = 0;
+	for (long t = 0; t < P; t++) {
+		long i_s = part[4 * t], i_e = part[4 * t + 1], j_s = part[4 * t + 2], j_e = part[4 * t + 3];
+		long i, j = j_s;
+		for (i = i_s; i < i_e - 1; i++) {
+			long je = ia[i + 1];
+			double sum = 0;
+			for (; j < je; j++)
+				sum += a[j] * x[ja[j]];
+			y[i] = sum;
+			j = je;
+		}
+		i = i_e - 1;
+		j = ia[i];
+		if (j_s > j)
+			j = j_s;
+		double sum = 0;
+		for (; j < j_e; j++)
+			sum += a[j] * x[ja[j]];
+		v_e[t] = sum;
+	}
+	for (long t = 0; t < P; t++)
+		if (part[4 * t + 1] - 1 < m)
+			y[part[4 * t + 1] - 1] += v_e[t];
+	free(part);
+	free(v_e);
+}
+
+/* ---------------------------------------------------------------------------
  * a7: merge-path diagonal search.
  * ref: benchmark_code/CPU/ARM/spmv_code_bench/spmv_kernel_merge.cpp:214-234
  *      (MergePathSearch), list A = row_end_offsets = ia+1 (length m),

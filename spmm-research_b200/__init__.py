@@ -18,12 +18,12 @@ import numpy as np
 
 __all__ = ["csr_to_format", "csr_to_format_f32", "MatrixFormatF32", "coo_to_csr", "read_mtx", "read_smtx", "MatrixFormat", "partition", "shard_slices", "statistics_print_labels", "load_library",
            "SpmmB200Error", "ROWSPLIT", "MERGE", "BCSR", "AUTO", "BCSR_FMA", "B_COLMAJOR", "B_ROWMAJOR",
-           "PART_ROWS", "PART_NNZ", "PART_MERGE", "LIB_PATH", "EXPORTS",
+           "PART_ROWS", "PART_NNZ", "PART_MERGE", "PART_NNZ_CARRY", "LIB_PATH", "EXPORTS", "MultiGpuFormat", "csr_to_format_multi",
            "PipelineFormat", "csr_to_pipeline_format", "PipelineFormatF32", "csr_to_pipeline_format_f32", "SDDMM_REFERENCE", "SDDMM_ATTENTION", "SDDMM_ATTENTION_ORDERED"]
 
 ROWSPLIT, MERGE, BCSR, AUTO, BCSR_FMA = 0, 1, 2, 3, 4
 B_COLMAJOR, B_ROWMAJOR = 0, 1
-PART_ROWS, PART_NNZ, PART_MERGE = 0, 1, 2
+PART_ROWS, PART_NNZ, PART_MERGE, PART_NNZ_CARRY = 0, 1, 2, 3
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "lib", "libspmm_b200.so")
@@ -31,7 +31,11 @@ LIB_PATH = os.path.join(HERE, "lib", "libspmm_b200.so")
 # every symbol include/spmm_b200.h declares
 EXPORTS = [
     "spmm_b200_create", "spmm_b200_create_shard", "spmm_b200_run", "spmm_b200_run_replicated", "spmm_b200_set_b",
-    "spmm_b200_register_host", "spmm_b200_unregister_host",
+    "spmm_b200_register_host", "spmm_b200_unregister_host", "spmm_b200_set_option", "spmm_b200_last_timeline",
+    "spmm_b200_create_multi", "spmm_b200_run_multi", "spmm_b200_set_b_multi", "spmm_b200_run_resident_multi",
+    "spmm_b200_fetch_c_multi", "spmm_b200_register_host_multi", "spmm_b200_multi_ngpus", "spmm_b200_multi_shard",
+    "spmm_b200_multi_first_row", "spmm_b200_multi_last_kernel_ms", "spmm_b200_multi_launch_count",
+    "spmm_b200_multi_peer_access", "spmm_b200_destroy_multi",
     "spmm_b200_run_resident", "spmm_b200_fetch_c", "spmm_b200_run_device",
     "spmm_b200_transpose_b_device", "spmm_b200_partition", "spmm_b200_partition_host", "spmm_b200_coo_to_csr", "spmm_b200_rows", "spmm_b200_nnz",
     "spmm_b200_variant", "spmm_b200_bcsr_blocks", "spmm_b200_kslice", "spmm_b200_last_kernel_ms", "spmm_b200_launch_count", "spmm_b200_stats",
@@ -44,7 +48,7 @@ EXPORTS = [
     "spmm_b200_pipeline_create", "spmm_b200_pipeline_spmm", "spmm_b200_pipeline_sddmm", "spmm_b200_pipeline_softmax",
     "spmm_b200_pipeline_final", "spmm_b200_pipeline_set_weight", "spmm_b200_pipeline_attention",
     "spmm_b200_pipeline_device_ptr", "spmm_b200_pipeline_last_kernel_ms", "spmm_b200_pipeline_launch_count",
-    "spmm_b200_pipeline_destroy",
+    "spmm_b200_pipeline_destroy", "spmm_b200_pipeline_invalidate", "spmm_b200_pipeline_set_option",
     "spmm_b200_pipeline_create_f32", "spmm_b200_pipeline_spmm_f32", "spmm_b200_pipeline_sddmm_f32",
     "spmm_b200_pipeline_final_f32", "spmm_b200_pipeline_launch_count_f32", "spmm_b200_pipeline_destroy_f32",
 ]
@@ -84,6 +88,21 @@ def load_library():
     lib.spmm_b200_set_b.argtypes = [_vp, _vp, _int]
     lib.spmm_b200_register_host.argtypes = [_vp, _vp, C.c_size_t]
     lib.spmm_b200_unregister_host.argtypes = [_vp, _vp]
+    lib.spmm_b200_set_option.argtypes = [_vp, C.c_char_p, _int]
+    lib.spmm_b200_last_timeline.argtypes = [_vp, _vp, _int]
+    lib.spmm_b200_create_multi.argtypes = [C.POINTER(_vp), _vp, _vp, _vp, _i64, _i64, _i64, _int, _int, _vp, _int, _int]
+    lib.spmm_b200_run_multi.argtypes = [_vp, _vp, _vp, _int, _int]
+    lib.spmm_b200_set_b_multi.argtypes = [_vp, _vp, _int]
+    lib.spmm_b200_run_resident_multi.argtypes = [_vp, _int]
+    lib.spmm_b200_fetch_c_multi.argtypes = [_vp, _vp, _int]
+    lib.spmm_b200_register_host_multi.argtypes = [_vp, _vp, C.c_size_t]
+    lib.spmm_b200_multi_ngpus.argtypes = [_vp]
+    lib.spmm_b200_multi_shard.argtypes = [_vp, _int]; lib.spmm_b200_multi_shard.restype = _vp
+    lib.spmm_b200_multi_first_row.argtypes = [_vp, _int]; lib.spmm_b200_multi_first_row.restype = _i64
+    lib.spmm_b200_multi_last_kernel_ms.argtypes = [_vp]; lib.spmm_b200_multi_last_kernel_ms.restype = _dbl
+    lib.spmm_b200_multi_launch_count.argtypes = [_vp]; lib.spmm_b200_multi_launch_count.restype = _i64
+    lib.spmm_b200_multi_peer_access.argtypes = [_vp]
+    lib.spmm_b200_destroy_multi.argtypes = [_vp]; lib.spmm_b200_destroy_multi.restype = None
     lib.spmm_b200_run_resident.argtypes = [_vp, _int]
     lib.spmm_b200_fetch_c.argtypes = [_vp, _vp, _int]
     lib.spmm_b200_run_device.argtypes = [_vp, _vp, _vp, _int, _vp]
@@ -126,6 +145,8 @@ def load_library():
     lib.spmm_b200_pipeline_final.argtypes = [_vp, _vp]
     lib.spmm_b200_pipeline_set_weight.argtypes = [_vp, C.c_char, _i64, _i64, _i64, _vp, _vp, _vp]
     lib.spmm_b200_pipeline_attention.argtypes = [_vp, _vp, _vp, _int, _int]
+    lib.spmm_b200_pipeline_invalidate.argtypes = [_vp, C.c_char]
+    lib.spmm_b200_pipeline_set_option.argtypes = [_vp, C.c_char_p, _int]
     lib.spmm_b200_pipeline_device_ptr.argtypes = [_vp, C.c_char]; lib.spmm_b200_pipeline_device_ptr.restype = _vp
     lib.spmm_b200_pipeline_last_kernel_ms.argtypes = [_vp]; lib.spmm_b200_pipeline_last_kernel_ms.restype = _dbl
     lib.spmm_b200_pipeline_launch_count.argtypes = [_vp]; lib.spmm_b200_pipeline_launch_count.restype = _i64
@@ -223,6 +244,20 @@ class MatrixFormat:
         """Page-lock a host array for the lifetime of the handle (full PCIe rate; lets spmm() store C straight
         into it).  The array must stay alive until close()."""
         _check(load_library().spmm_b200_register_host(self._h, arr.ctypes.data, arr.nbytes), "spmm_b200_register_host")
+
+    def set_option(self, name, value):
+        """Change a tuning knob of this handle (the SPMM_B200_<NAME> variables are read once, at creation)."""
+        _check(load_library().spmm_b200_set_option(self._h, name.encode(), int(value)), f"set_option({name})")
+
+    def last_timeline(self):
+        """Event times (ms since the first enqueue) of the last k-sliced host-buffer run:
+        [{h2d, bcast, transpose, kernel_start, kernel_end, d2h}] per slice."""
+        out = np.zeros(1 + 6 * 64)
+        n = load_library().spmm_b200_last_timeline(self._h, out.ctypes.data, out.size)
+        if n < 1:
+            return []
+        keys = ("h2d", "bcast", "transpose", "kernel_start", "kernel_end", "d2h")
+        return [dict(zip(keys, out[1 + 6 * s: 7 + 6 * s].tolist())) for s in range(int(out[0]))]
 
     def set_b(self, x, k):
         _check(load_library().spmm_b200_set_b(self._h, _host(x, np.float64, "x"), int(k)), "set_b")
@@ -376,6 +411,13 @@ class PipelineFormat:
                _host(ja, np.int32, "ja") if len(ja) else None, _host(a, np.float64, "a") if len(a) else None),
                "spmm_b200_pipeline_set_weight")
 
+    def invalidate(self, type="*"):
+        """Forget the resident copy of weight 'K' | 'Q' | 'V' ('*': all): for callers that refill a weight in place."""
+        _check(load_library().spmm_b200_pipeline_invalidate(self._h, type.encode()[:1]), "spmm_b200_pipeline_invalidate")
+
+    def set_option(self, name, value):
+        _check(load_library().spmm_b200_pipeline_set_option(self._h, name.encode(), int(value)), f"pipeline set_option({name})")
+
     def attention(self, x, y_final, mode=SDDMM_REFERENCE, softmax=0):
         """The whole layer, one upload of x and one download of y_final."""
         _check(load_library().spmm_b200_pipeline_attention(self._h, _host(x, np.float64, "x") if x.size else None,
@@ -506,18 +548,102 @@ def csr_to_format(row_ptr, col_ind, values, m, n, nnz, k, *, device=0, variant=A
     return MatrixFormat(h, lib.spmm_b200_rows(h), n, lib.spmm_b200_nnz(h), k, first_row=r0.value, m_global=m)
 
 
+class MultiGpuFormat:
+    """Matrix_Format over `ngpus` devices driven by ONE process (include/spmm_b200.h, "_multi"): rows cut by the
+    reference's nnz-balanced split, B replicated by a peer-memory gather kernel, C row-local in the caller's y."""
+
+    def __init__(self, handle, m, n, nnz, k):
+        self._h = handle
+        self.m, self.n, self.nnz, self.k = int(m), int(n), int(nnz), int(k)
+        lib = load_library()
+        self.ngpus = lib.spmm_b200_multi_ngpus(handle)
+        self.bounds = [lib.spmm_b200_multi_first_row(handle, g) for g in range(self.ngpus + 1)]
+        self.peer_access = bool(lib.spmm_b200_multi_peer_access(handle))
+        self.format_name = f"B200_CSR_x{self.ngpus}"
+        self.csr_mem_footprint = self.nnz * (8 + 4) + (self.m + 1) * 4
+        self.mem_footprint = self.csr_mem_footprint
+
+    def spmm(self, x, y, k, copy_back=True):
+        k = int(k)
+        if x.size != self.n * k:
+            raise ValueError(f"x holds {x.size} values, expected c*k = {self.n * k}")
+        if copy_back and y.size != self.m * k:
+            raise ValueError(f"y holds {y.size} values, expected m*k = {self.m * k}")
+        _check(load_library().spmm_b200_run_multi(self._h, _host(x, np.float64, "x"), _host(y, np.float64, "y") if copy_back else None,
+                                                  k, 1 if copy_back else 0), "spmm(multi)")
+
+    def set_b(self, x, k):
+        _check(load_library().spmm_b200_set_b_multi(self._h, _host(x, np.float64, "x"), int(k)), "set_b(multi)")
+
+    def spmm_resident(self, k):
+        _check(load_library().spmm_b200_run_resident_multi(self._h, int(k)), "spmm_resident(multi)")
+
+    def fetch_c(self, y, k):
+        _check(load_library().spmm_b200_fetch_c_multi(self._h, _host(y, np.float64, "y"), int(k)), "fetch_c(multi)")
+
+    def register_host(self, arr):
+        _check(load_library().spmm_b200_register_host_multi(self._h, arr.ctypes.data, arr.nbytes), "register_host(multi)")
+
+    def set_option(self, name, value):
+        lib = load_library()
+        for g in range(self.ngpus):
+            _check(lib.spmm_b200_set_option(lib.spmm_b200_multi_shard(self._h, g), name.encode(), int(value)), f"set_option({name})")
+
+    def shard_variant(self, g):
+        lib = load_library()
+        return lib.spmm_b200_variant(lib.spmm_b200_multi_shard(self._h, g))
+
+    def last_kernel_ms(self):
+        return load_library().spmm_b200_multi_last_kernel_ms(self._h)
+
+    def launch_count(self):
+        return load_library().spmm_b200_multi_launch_count(self._h)
+
+    def statistics_start(self):
+        pass
+
+    def close(self):
+        if self._h:
+            load_library().spmm_b200_destroy_multi(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def csr_to_format_multi(row_ptr, col_ind, values, m, n, nnz, k, ngpus, *, devices=None, variant=AUTO, b_layout=B_COLMAJOR):
+    """csr_to_format() over `ngpus` devices of this box, one process (`int ngpus`)."""
+    lib = load_library()
+    h = _vp()
+    dv = None
+    if devices is not None:
+        dv = (C.c_int * ngpus)(*[int(d) for d in devices])
+    _check(lib.spmm_b200_create_multi(C.byref(h), _host(row_ptr, np.int32, "row_ptr"),
+                                      _host(col_ind, np.int32, "col_ind") if nnz > 0 else None,
+                                      _host(values, np.float64, "values") if nnz > 0 else None,
+                                      m, n, nnz, k, int(ngpus), C.cast(dv, _vp) if dv is not None else None, variant, b_layout),
+           "csr_to_format_multi")
+    return MultiGpuFormat(h, m, n, nnz, k)
+
+
 def partition(row_ptr, m, nnz, P, mode, device=0, host=False):
     """Bit-exact twins of the reference partitioners (include/spmm_b200.h), searched on the device
     (host=True: the same integer functions on the CPU, for shard planning).
-    PART_NNZ -> int64[P+1] row starts; PART_ROWS -> int64[P,2]; PART_MERGE -> int64[P+1,2]."""
-    n_out = {PART_NNZ: P + 1, PART_ROWS: 2 * P, PART_MERGE: 2 * (P + 1)}[mode]
+    PART_NNZ -> int64[P+1] row starts; PART_ROWS -> int64[P,2]; PART_MERGE -> int64[P+1,2];
+    PART_NNZ_CARRY -> int64[P,4] = (i_s, i_e, j_s, j_e) per worker (spmv_kernel_csr.cpp:68-80)."""
+    n_out = {PART_NNZ: P + 1, PART_ROWS: 2 * P, PART_MERGE: 2 * (P + 1), PART_NNZ_CARRY: 4 * P}[mode]
     out = np.zeros(n_out, dtype=np.int64)
     rp = _host(row_ptr, np.int32, "row_ptr") if row_ptr is not None else None
     if host:
         _check(load_library().spmm_b200_partition_host(rp, m, nnz, P, mode, out.ctypes.data), "partition_host")
     else:
         _check(load_library().spmm_b200_partition(rp, m, nnz, P, mode, out.ctypes.data, device), "partition")
-    return out if mode == PART_NNZ else out.reshape(-1, 2)
+    if mode == PART_NNZ:
+        return out
+    return out.reshape(-1, 4) if mode == PART_NNZ_CARRY else out.reshape(-1, 2)
 
 
 def shard_slices(row_ptr, m, nnz, nranks):

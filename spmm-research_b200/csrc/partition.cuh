@@ -42,6 +42,25 @@ __host__ __device__ inline int64_t nnz_split_start(const int32_t* __restrict__ i
 	return nearest_index(ia, 0, m - 1, target);
 }
 
+// Lower boundary of the reference's binary_search (lib/macros/macrolib.h:471-515) over the inclusive index range
+// [lo, hi] of a non-decreasing array: the index s with A[s] < target < A[s+1], or -- on an exact hit -- the index
+// the bisection ends on (the lowest i in (lo, hi] with A[i] == target, or lo itself when A[lo] == target); -1 when the
+// target is below A[lo], hi when it is above A[hi].
+__host__ __device__ inline int64_t lower_boundary(const int32_t* __restrict__ A, int64_t lo, int64_t hi, int64_t target)
+{
+	int64_t s = lo, e = hi;
+	if (target < (int64_t) A[s]) return -1;
+	if (target > (int64_t) A[e]) return e;
+	while (true) {
+		int64_t mid = (s + e) / 2;
+		if (mid == s || mid == e) break;
+		if (target > (int64_t) A[mid]) s = mid; else e = mid;
+	}
+	if (target == (int64_t) A[s]) return s;
+	if (target == (int64_t) A[e]) return e;
+	return s;
+}
+
 // [start, end) of worker t of P over the iteration space [start, end), step 1.
 __host__ __device__ inline void equal_split(int64_t start, int64_t end, int64_t P, int64_t t, int64_t* s_out, int64_t* e_out)
 {
@@ -73,6 +92,33 @@ __host__ __device__ inline void merge_path_search(int64_t diagonal, const int32_
 	}
 	*row_out = x_min < m ? x_min : m;
 	*nz_out = diagonal - x_min;
+}
+
+// "Perfect nnz balance with row carry" (spmv_kernel_csr.cpp:68-80, CUSTOM_VECTOR_PERFECT_NNZ_BALANCE): worker t
+// owns the nonzeros [j_s, j_e) of an equal split of [0, nnz); its first row i_s is the lower boundary of the search
+// for j_s in ia[0..m] (range 0..m here, not m-1); its row range ends one past the next worker's first row (that row is
+// shared: the worker's partial sum of it is the carry), the last worker's at m.  out4 = {i_s, i_e, j_s, j_e}.
+__host__ __device__ inline void nnz_carry_split(const int32_t* __restrict__ ia, int64_t m, int64_t nnz, int64_t P, int64_t t, int64_t* out4)
+{
+	int64_t js, je;
+	equal_split(0, nnz, P, t, &js, &je);
+	out4[0] = lower_boundary(ia, 0, m, js);
+	if (t == P - 1) {
+		out4[1] = m;
+	} else {
+		int64_t js2, je2;
+		equal_split(0, nnz, P, t + 1, &js2, &je2);
+		out4[1] = lower_boundary(ia, 0, m, js2) + 1;
+	}
+	out4[2] = js;
+	out4[3] = je;
+}
+
+__global__ void partition_nnz_carry_kernel(const int32_t* __restrict__ ia, int64_t m, int64_t nnz, int64_t P, int64_t* __restrict__ out)
+{
+	int64_t t = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+	if (t >= P) return;
+	nnz_carry_split(ia, m, nnz, P, t, out + 4 * t);
 }
 
 __global__ void partition_nnz_kernel(const int32_t* __restrict__ ia, int64_t m, int64_t nnz, int64_t P, int64_t* __restrict__ out)

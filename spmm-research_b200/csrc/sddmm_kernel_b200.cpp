@@ -15,9 +15,12 @@
 //   SPMM_B200_DEVICE      = CUDA device ordinal (default 0)
 //   SPMM_B200_SDDMM_MODE  = 0 (default): the reference's SDDMM, both factors at the output row
 //                           (sddmm_taco_naive.cpp:128); 1: K at row ja[p] (tree-ordered sum); 2: same, ordered
-//   SPMM_B200_RESIDENT    = 1 (default): the harness's last call spmm('final', mask, y, V, y_final) uses the y and V
-//                           that are already on the device when its `a` and `x` arguments are the very buffers the
-//                           preceding sddmm(y) and spmm('V', ..., V) calls wrote; 0: always upload them.
+//   SPMM_B200_RESIDENT    = 0 (default): spmm('final', mask, y, V, y_final) reads its host arguments on every call,
+//                           like the reference's Matrix_Format::spmm.  1 (opt-in): when `a` and `x` are the very
+//                           buffers the preceding sddmm(y) and spmm('V', ..., V) calls wrote, the copies already on
+//                           the device are used -- ONLY valid if the harness does not touch y or V in between (it
+//                           would, e.g., with its commented-out host softmax(y) re-enabled): pointer identity is
+//                           all that is checked.
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
@@ -53,7 +56,7 @@ struct B200Pipeline : Matrix_Format
 	int resident;
 
 	B200Pipeline(long m, long n, long nnz) : Matrix_Format(m, n, nnz),
-		handle(NULL), mask_ia(NULL), mask_ja(NULL), last_y(NULL), last_v(NULL), mode(0), resident(1) {}
+		handle(NULL), mask_ia(NULL), mask_ja(NULL), last_y(NULL), last_v(NULL), mode(0), resident(0) {}
 
 	~B200Pipeline()
 	{

@@ -39,24 +39,74 @@ static thread_local char g_cuda_err[512] = "";
 
 static constexpr int THREADS = 256;
 
+// Tuning knobs.  Read from the environment ONCE per handle (at creation), never on the hot path; a caller changes
+// them afterwards with spmm_b200_set_option(h, "NAME", value).  Names = the SPMM_B200_* variables without prefix.
+struct Options {
+	int ticket = -1;           // TICKET: rows per ticket of the persistent row-split kernel; -1 = rule, 0 = static ranges
+	int ticket_ctas = 4;       // TICKET_CTAS: CTAs per SM of a ticketed grid
+	int ticket_min_nnz = 8 << 20; // TICKET_MIN_NNZ: the rule takes tickets from this many nonzeros on
+	int stage = 0;             // STAGE: 1 = A stream through shared memory by TMA (staged kernel), 0 = off, -1 = rule, 2 = B-row ring experiment
+	int const_ld = 1;          // CONST_LD: compile-time row stride when the operand is whole
+	int unroll = 4;            // UNROLL: B-row gathers in flight per lane group
+	int kslice = 0;            // KSLICE: 0 = measure, -1 = never, w = force
+	int pipeline_cols = -1;    // PIPELINE_COLS: host pipeline slice width; 0 = off, -1 = choose
+	int pipeline_min_kb = 8 << 10;
+	int direct_store = 1;      // DIRECT_STORE
+	int ctas_per_sm = 0;       // CTAS_PER_SM: 0 = by k
+	int merge_maxrow = 256;    // MERGE_MAXROW
+	int bcsr_fill_pct = 30;    // BCSR_FILL_PCT
+	int bcsr_tma = 1, bcsr_stages = 2, bcsr_brw = 0;
+};
+
+static int env_int(const char* name, int dflt)
+{
+	const char* s = getenv(name);
+	return (s && *s) ? atoi(s) : dflt;
+}
+
+struct OptionName { const char* name; int Options::*field; };
+static const OptionName OPTION_TABLE[] = {
+	{"TICKET", &Options::ticket}, {"TICKET_CTAS", &Options::ticket_ctas}, {"TICKET_MIN_NNZ", &Options::ticket_min_nnz}, {"STAGE", &Options::stage},
+	{"CONST_LD", &Options::const_ld}, {"UNROLL", &Options::unroll}, {"KSLICE", &Options::kslice},
+	{"PIPELINE_COLS", &Options::pipeline_cols}, {"PIPELINE_MIN_KB", &Options::pipeline_min_kb},
+	{"DIRECT_STORE", &Options::direct_store}, {"CTAS_PER_SM", &Options::ctas_per_sm},
+	{"MERGE_MAXROW", &Options::merge_maxrow}, {"BCSR_FILL_PCT", &Options::bcsr_fill_pct},
+	{"BCSR_TMA", &Options::bcsr_tma}, {"BCSR_STAGES", &Options::bcsr_stages}, {"BCSR_BRW", &Options::bcsr_brw},
+};
+
+static Options options_from_env()
+{
+	Options o;
+	char name[64];
+	for (const OptionName& e : OPTION_TABLE) {
+		snprintf(name, sizeof(name), "SPMM_B200_%s", e.name);
+		o.*(e.field) = env_int(name, o.*(e.field));
+	}
+	return o;
+}
+
+struct KsliceChoice { int k = 0, best = 0; };     // per-k result of the slice-width measurement
+
 struct spmm_b200 {
 	int device = 0;
 	int variant = SPMM_B200_ROWSPLIT;     // resolved variant
 	int variant_req = SPMM_B200_AUTO;
 	int b_layout = SPMM_B200_B_COLMAJOR;
 	int k = 0;                            // k the work lists were tuned for
-	int sm_count = 148;
+	int sm_count = 0;
+	Options opt;
 	int64_t m = 0, c = 0, nnz = 0;        // this handle's shard
 	int64_t first_row = 0, m_global = 0;
 	int rank = 0, nranks = 1;             // shard identity (spmm_b200_create_shard)
 	int max_row = 0;                      // longest row of the shard
-	int64_t col_span = 0;                 // max column - min column + 1 over the shard's nonzeros
+	int64_t col_min = 0, col_span = 0;    // first touched column, max column - min column + 1 over the shard's nonzeros
 	// L2-aware k slicing of the row-split kernel, chosen by timing the candidates on the first calls
-	int ks_k = 0;                         // k the choice below is for
+	int ks_k = 0;                         // k being measured (or last looked up)
 	int ks_best = 0;                      // chosen slice width (== k: one launch); 0 while still measuring
 	int ks_try = 0;                       // index of the candidate the next call runs
 	int ks_cand[4] = {0, 0, 0, 0};
 	float ks_ms[4] = {0.f, 0.f, 0.f, 0.f};
+	std::vector<KsliceChoice> ks_done;    // finished measurements: alternating k values do not re-tune
 
 	int32_t* d_ia = nullptr;
 	int32_t* d_ja = nullptr;
@@ -65,12 +115,9 @@ struct spmm_b200 {
 	// row-split work list
 	int32_t* d_cta_rows = nullptr;
 	int n_ctas = 0;
-	int* d_ticket = nullptr;              // row-ticket counter of the persistent row-split experiment
-	// row-padded copy of A for the vectorised row-split kernel (rows padded to multiples of 4 entries)
-	int32_t* d_iap = nullptr;
-	int32_t* d_jap = nullptr;
-	double* d_ap = nullptr;
-	int64_t nnz_pad = 0;
+	int* d_ticket = nullptr;              // two row-ticket counters, used alternately (see spmm_rowsplit_ticket_kernel)
+	int ticket_parity = 0;
+	uint32_t smem_attr = 0;               // bit i: dynamic shared-memory limit of kernel family i raised on THIS device/handle
 	// merge-path work list
 	MergePlan merge;
 	// blocked CSR (8x1)
@@ -89,15 +136,24 @@ struct spmm_b200 {
 	// k-sliced host pipeline of spmm_b200_run (upload slice s+1 | kernel slice s | download slice s-1)
 	cudaStream_t s_up = nullptr, s_down = nullptr;
 	std::vector<cudaEvent_t> ev_slice;    // per slice: uploaded, kernel start, kernel end
+	std::vector<cudaEvent_t> ev_tl;       // timeline events of the last pipelined run (spmm_b200_last_timeline)
+	int tl_slices = 0;
 	int c_slices = 1;                     // >1: d_C holds c_slices blocks of m x (k / c_slices)
 	int timed_slices = 0;                 // >0: last_kernel_ms sums the slices' kernel events
 	int64_t launches = 0;
 };
 
-static int env_int(const char* name, int dflt)
+extern "C" int spmm_b200_set_option(spmm_b200_t* h, const char* name, int value)
 {
-	const char* s = getenv(name);
-	return (s && *s) ? atoi(s) : dflt;
+	if (!h || !name) return SPMM_B200_EINVAL;
+	if (!strncmp(name, "SPMM_B200_", 10)) name += 10;
+	for (const OptionName& e : OPTION_TABLE)
+		if (!strcmp(name, e.name)) {
+			h->opt.*(e.field) = value;
+			if (e.field == &Options::kslice) { h->ks_k = 0; h->ks_best = 0; h->ks_done.clear(); }
+			return SPMM_B200_OK;
+		}
+	return SPMM_B200_EINVAL;
 }
 
 static int check_device(int device, int* sm_count)
@@ -164,54 +220,26 @@ static int build_rowsplit_plan(spmm_b200* h)
 	// cfg2 0.787 -> 0.780 ms).  The small-k kernels (32 registers, 8 resident CTAs) keep 4 waves.
 	int dflt = 32;
 	if (h->k == 32) dflt = (h->nnz / ((int64_t) h->sm_count * 8) < 8192) ? 4 : 8;      // k = 64, 128 measured flat-to-better with more CTAs (r1_gvu_probe.md)
-	const int per_sm = std::max(1, env_int("SPMM_B200_CTAS_PER_SM", dflt));
+	const int per_sm = std::max(1, h->opt.ctas_per_sm > 0 ? h->opt.ctas_per_sm : dflt);
 	int64_t want = (int64_t) h->sm_count * per_sm;
 	int64_t cap = std::max<int64_t>(1, (h->m + 7) / 8);       // at least ~8 rows per CTA
 	// few rows (the row cap binds): whole waves of the 4 resident CTAs per SM, so that no partial last wave
 	// runs on a fraction of the machine (m = 8192, k = 64, 410 nnz/row: 1024 CTAs 0.141 ms, 592 CTAs 0.123 ms;
 	// profiles/r1_pipeline_probe.md)
 	const int64_t wave = (int64_t) h->sm_count * 4;
-	if (cap < want && h->k >= 64 && cap >= wave && !env_int("SPMM_B200_CTAS_PER_SM", 0)) cap = cap / wave * wave;
+	if (cap < want && h->k >= 64 && cap >= wave && h->opt.ctas_per_sm <= 0) cap = cap / wave * wave;
 	h->n_ctas = (int) std::max<int64_t>(1, std::min(want, cap));
 	if (h->d_cta_rows) cudaFree(h->d_cta_rows);
 	CU_TRY(cudaMalloc(&h->d_cta_rows, sizeof(int32_t) * (h->n_ctas + 1)));
-	if (!h->d_ticket) CU_TRY(cudaMalloc(&h->d_ticket, sizeof(int)));
+	if (!h->d_ticket) {
+		CU_TRY(cudaMalloc(&h->d_ticket, 2 * sizeof(int)));
+		CU_TRY(cudaMemsetAsync(h->d_ticket, 0, 2 * sizeof(int), h->stream));
+	}
 	const int nb = (h->n_ctas + 1 + 255) / 256;
 	cta_rows_nnz_kernel<<<nb, 256, 0, h->stream>>>(h->d_ia, (int) h->m, h->nnz, h->n_ctas, h->d_cta_rows);
 	h->launches++;
 	CU_TRY(cudaGetLastError());
 	return SPMM_B200_OK;
-}
-
-// Row-padded copy of A for spmm_rowsplit_vec_kernel: iap = exclusive scan of the padded row lengths.
-static int build_padded_plan(spmm_b200* h)
-{
-	if (h->d_iap || h->m == 0) return SPMM_B200_OK;
-	if (h->nnz + 3 * h->m >= INT32_MAX) return SPMM_B200_ENOSUP;
-	const int m = (int) h->m;
-	int32_t* d_tmp = nullptr;
-	CU_TRY(cudaMalloc(&h->d_iap, sizeof(int32_t) * ((size_t) m + 1)));
-	CU_TRY(cudaMalloc(&d_tmp, sizeof(int32_t) * scan_tmp_elems(m + 1)));
-	pad_len_kernel<<<(m + 1 + 255) / 256, 256, 0, h->stream>>>(h->d_ia, m, h->d_iap);
-	h->launches += 1 + exclusive_scan_i32(h->d_iap, (int64_t) m + 1, d_tmp, h->stream);
-	int32_t total = 0;
-	CU_TRY(cudaMemcpyAsync(&total, h->d_iap + m, sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
-	CU_TRY(cudaStreamSynchronize(h->stream));
-	cudaFree(d_tmp);
-	h->nnz_pad = total;
-	CU_TRY(cudaMalloc(&h->d_jap, sizeof(int32_t) * std::max<size_t>((size_t) total, 4)));
-	CU_TRY(cudaMalloc(&h->d_ap, sizeof(double) * std::max<size_t>((size_t) total, 4)));
-	pad_fill_kernel<<<(unsigned) (((int64_t) m * 32 + 255) / 256), 256, 0, h->stream>>>(h->d_ia, h->d_iap, h->d_ja, h->d_a, m, h->d_jap, h->d_ap);
-	h->launches++;
-	CU_TRY(cudaGetLastError());
-	CU_TRY(cudaStreamSynchronize(h->stream));
-	return SPMM_B200_OK;
-}
-
-template <int G, int V>
-static void launch_rowsplit_vec(const spmm_b200* h, const double* B, double* C, cudaStream_t s, int ldb = G * V, int ldc = G * V)
-{
-	spmm_rowsplit_vec_kernel<G, V, THREADS><<<h->n_ctas, THREADS, 0, s>>>(h->d_ia, h->d_iap, h->d_jap, h->d_ap, B, C, h->d_cta_rows, ldb, ldc);
 }
 
 static int pick_small_group(const spmm_b200* h)
@@ -222,43 +250,95 @@ static int pick_small_group(const spmm_b200* h)
 	return g;
 }
 
-template <int G, int V>
-static void launch_rowsplit_gv(const spmm_b200* h, const double* B, double* C, cudaStream_t s, int ldb = G * V, int ldc = G * V)
+// Kernels that need more than 48 KB of dynamic shared memory: the limit is a per-device function attribute, so it is
+// raised once per handle (a handle lives on one device) -- never behind a process-wide flag.
+enum { ATTR_MERGE = 0, ATTR_BCSR_TMA = 8, ATTR_STAGED = 16, ATTR_RING = 24 };
+template <typename Kern>
+static cudaError_t raise_smem_limit(spmm_b200* h, int bit, Kern kern, size_t bytes)
 {
-	// B-row gathers in flight per lane group; tuning knob, default from the ncu study in profiles/
-	static const int unroll = env_int("SPMM_B200_UNROLL", 4);
+	if (bytes <= 48 * 1024 || (h->smem_attr >> bit & 1u)) return cudaSuccess;
+	cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) bytes);
+	if (e == cudaSuccess) h->smem_attr |= 1u << bit;
+	return e;
+}
+
+// The staged kernel holds a ticket's nonzeros in a CAP-entry stage: it is taken when the mean ticket fills at most
+// ~3/4 of it (tickets beyond CAP fall back to global loads inside the kernel, correct but slower).
+static constexpr int STAGED_CAP = 272;
+template <int G, int V> struct StagedShape { static constexpr int PASSES = G >= 16 ? (G == 32 ? 4 : 2) : 1; };
+
+template <int G, int V>
+static void launch_rowsplit_gv(spmm_b200* h, const double* B, double* C, cudaStream_t s, int ldb = G * V, int ldc = G * V)
+{
+	const Options& o = h->opt;
 	constexpr int K = G * V;
-	// Default: ONE resident wave of persistent warps that draw small row chunks from a ticket counter
+	constexpr int NGW = 32 / G;
+	const double avg = h->m > 0 ? (double) h->nnz / (double) h->m : 1.0;
+	const bool whole = ldb == K && (uint64_t) h->c * K < (1ull << 32) && o.const_ld;   // compile-time row stride, 32-bit offsets
+	// Row tickets: ONE resident wave of persistent warps that draw small row chunks from a counter
 	// (spmm_rowsplit_ticket_kernel).  The whole GPU then sweeps A and C front to back (DRAM / L2 locality of the
-	// A stream) with no tail: cfg2 0.844 -> 0.754 ms on the same box (profiles/r1_ticket_probe.md).  Chunk = 8 rows
-	// (rounded to a multiple of the rows a warp works on at once).  SPMM_B200_TICKET=0 keeps the static
-	// nnz-balanced CTA ranges everywhere, > 0 forces that many rows per ticket.
-	int tick = env_int("SPMM_B200_TICKET", -1);
+	// A stream) with no tail: cfg2 0.844 -> 0.754 ms on the same box (profiles/r1_ticket_probe.md).  TICKET=0 keeps
+	// the static nnz-balanced CTA ranges everywhere, > 0 forces that many rows per ticket.
+	int tick = o.ticket;
 	if (tick < 0) {
 		// measured over bench/medium_subset.txt x k in {4, 8, 32, 128} (profiles/r1_ticket_probe.md): rows of >= 50
 		// nonzeros gain 3-15 %, rows of <= 10 lose 3-15 % (a ticket per ~50 nonzeros is too fine, larger chunks lose
-		// the locality), launches of a few tens of microseconds lose to the counter reset and the atomics
-		const double avg = h->m > 0 ? (double) h->nnz / (double) h->m : 1.0;
-		tick = (avg >= 32.0 && h->nnz >= (8 << 20)) ? 8 : 0;
+		// the locality); small launches: profiles/r2_shard_probe.md
+		tick = (avg >= 32.0 && h->nnz >= (int64_t) o.ticket_min_nnz) ? 8 : 0;
 	}
-	if (tick > 0 && h->d_ticket && unroll == 4) {
-		constexpr int NGW = 32 / G;
+	if constexpr (V >= 2 && K >= 32) {
+		// A stream staged through shared memory by TMA bulk copies (spmm_rowsplit_staged_kernel)
+		constexpr int PASSES = StagedShape<G, V>::PASSES;
+		using Cfg = StagedCfg<G, PASSES, STAGED_CAP>;
+		int stage = o.stage;
+		if (stage < 0) stage = (tick > 0 && avg * Cfg::R <= 0.75 * STAGED_CAP) ? 1 : 0;
+		// a row must fit a stage (the kernel copies whole rows): longer rows keep the plain ticketed kernel
+		if (stage == 1 && h->d_ticket && o.unroll == 4 && h->max_row <= STAGED_CAP) {
+			const size_t smem = Cfg::smem(THREADS);
+			const int per_sm = std::max(1, std::min(o.ticket_ctas, (int) ((227 * 1024) / (smem + 1024))));
+			const int grid = (int) std::min<int64_t>((h->m + Cfg::R * (THREADS / 32) - 1) / (Cfg::R * (THREADS / 32)) + 1, (int64_t) h->sm_count * per_sm);
+			h->ticket_parity ^= 1;
+			if (whole) {
+				auto kern = spmm_rowsplit_staged_kernel<G, V, 4, THREADS, PASSES, STAGED_CAP, K>;
+				raise_smem_limit(h, ATTR_STAGED + (K == 32 ? 0 : K == 64 ? 1 : 2), kern, smem);
+				kern<<<grid, THREADS, smem, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, (int) h->m, h->d_ticket, h->ticket_parity, ldb, ldc);
+			} else {
+				auto kern = spmm_rowsplit_staged_kernel<G, V, 4, THREADS, PASSES, STAGED_CAP>;
+				raise_smem_limit(h, ATTR_STAGED + 3 + (K == 32 ? 0 : K == 64 ? 1 : 2), kern, smem);
+				kern<<<grid, THREADS, smem, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, (int) h->m, h->d_ticket, h->ticket_parity, ldb, ldc);
+			}
+			return;
+		}
+		if constexpr (K == 32) {
+			if (stage == 2 && h->d_ticket) {         // experiment: B rows through a cp.async ring (profiles/r2_rowsplit_stage_probe.md)
+				constexpr int H = 4;
+				const size_t smem = (size_t) 2 * H * (V / 2) * THREADS * 16;
+				auto kern = spmm_rowsplit_ring_kernel<G, V, H, THREADS>;
+				raise_smem_limit(h, ATTR_RING, kern, smem);
+				const int rpt = std::max(NGW, (std::max(tick, 1) + NGW - 1) / NGW * NGW);
+				const int grid = (int) std::min<int64_t>((h->m + rpt * (THREADS / 32) - 1) / (rpt * (THREADS / 32)) + 1, (int64_t) h->sm_count * 3);
+				h->ticket_parity ^= 1;
+				kern<<<grid, THREADS, smem, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, (int) h->m, rpt, h->d_ticket, h->ticket_parity, ldb, ldc);
+				return;
+			}
+		}
+	}
+	if (tick > 0 && h->d_ticket && o.unroll == 4) {
 		tick = (tick + NGW - 1) / NGW * NGW;
-		cudaMemsetAsync(h->d_ticket, 0, sizeof(int), s);
 		const int grid = (int) std::min<int64_t>((h->m + tick * (THREADS / 32) - 1) / (tick * (THREADS / 32)) + 1,
-		                                         (int64_t) h->sm_count * std::max(1, env_int("SPMM_B200_TICKET_CTAS", 4)));
-		if (ldb == K && (uint64_t) h->c * K < (1ull << 32) && env_int("SPMM_B200_CONST_LD", 1))
-			spmm_rowsplit_ticket_kernel<G, V, 4, THREADS, K><<<grid, THREADS, 0, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, (int) h->m, tick, h->d_ticket, ldb, ldc);
+		                                         (int64_t) h->sm_count * std::max(1, o.ticket_ctas));
+		h->ticket_parity ^= 1;
+		if (whole)
+			spmm_rowsplit_ticket_kernel<G, V, 4, THREADS, K><<<grid, THREADS, 0, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, (int) h->m, tick, h->d_ticket, h->ticket_parity, ldb, ldc);
 		else
-			spmm_rowsplit_ticket_kernel<G, V, 4, THREADS><<<grid, THREADS, 0, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, (int) h->m, tick, h->d_ticket, ldb, ldc);
+			spmm_rowsplit_ticket_kernel<G, V, 4, THREADS><<<grid, THREADS, 0, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, (int) h->m, tick, h->d_ticket, h->ticket_parity, ldb, ldc);
 		return;
 	}
-	if (unroll >= 8 && G >= 8)
+	if (o.unroll >= 8 && G >= 8)
 		spmm_rowsplit_kernel<G, V, 8, THREADS><<<h->n_ctas, THREADS, 0, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, h->d_cta_rows, ldb, ldc);
-	else if (unroll <= 2)
+	else if (o.unroll <= 2)
 		spmm_rowsplit_kernel<G, V, 2, THREADS><<<h->n_ctas, THREADS, 0, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, h->d_cta_rows, ldb, ldc);
-	else if (ldb == K && (uint64_t) h->c * K < (1ull << 32) && env_int("SPMM_B200_CONST_LD", 1))
-		// whole operand: compile-time row stride, 32-bit element offsets
+	else if (whole)
 		spmm_rowsplit_kernel<G, V, 4, THREADS, K><<<h->n_ctas, THREADS, 0, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, h->d_cta_rows, ldb, ldc);
 	else
 		spmm_rowsplit_kernel<G, V, 4, THREADS><<<h->n_ctas, THREADS, 0, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, h->d_cta_rows, ldb, ldc);
@@ -281,15 +361,11 @@ template <int G, int V, int IPG>
 struct MergeLaunch {
 	using Cfg = MergeCfg<G, V, IPG, THREADS>;
 	static int items() { return Cfg::ITEMS; }
-	static cudaError_t launch(const spmm_b200* h, const double* B, double* C, cudaStream_t s)
+	static cudaError_t launch(spmm_b200* h, const double* B, double* C, cudaStream_t s, int attr_bit)
 	{
 		auto kern = spmm_merge_kernel<G, V, IPG, 4, THREADS>;
-		static bool attr_set = false;
-		if (!attr_set && Cfg::SMEM > 48 * 1024) {
-			cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) Cfg::SMEM);
-			if (e != cudaSuccess) return e;
-			attr_set = true;
-		}
+		cudaError_t e = raise_smem_limit(h, ATTR_MERGE + attr_bit, kern, Cfg::SMEM);
+		if (e != cudaSuccess) return e;
 		kern<<<h->merge.ntiles, THREADS, Cfg::SMEM, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, h->merge.d_tile,
 		                                                h->merge.d_carry, h->merge.d_carry_row);
 		return cudaGetLastError();
@@ -299,21 +375,21 @@ struct MergeLaunch {
 // k -> (G, V, IPG) of the merge kernel; 0 items = no specialised instantiation
 #define MERGE_DISPATCH(k, WHAT)                                    \
 	switch (k) {                                                   \
-	case 1:   WHAT(1, 1, 16); break;                               \
-	case 2:   WHAT(1, 2, 16); break;                               \
-	case 4:   WHAT(2, 2, 16); break;                               \
-	case 8:   WHAT(4, 2, 32); break;                               \
-	case 16:  WHAT(8, 2, 32); break;                               \
-	case 32:  WHAT(8, 4, 64); break;                               \
-	case 64:  WHAT(16, 4, 128); break;                             \
-	case 128: WHAT(32, 4, 128); break;                             \
+	case 1:   WHAT(1, 1, 16, 0); break;                            \
+	case 2:   WHAT(1, 2, 16, 1); break;                            \
+	case 4:   WHAT(2, 2, 16, 2); break;                            \
+	case 8:   WHAT(4, 2, 32, 3); break;                            \
+	case 16:  WHAT(8, 2, 32, 4); break;                            \
+	case 32:  WHAT(8, 4, 64, 5); break;                            \
+	case 64:  WHAT(16, 4, 128, 6); break;                          \
+	case 128: WHAT(32, 4, 128, 7); break;                          \
 	default: break;                                                \
 	}
 
 static int merge_items_for_k(int k)
 {
 	int items = 0;
-#define WHAT(G, V, IPG) items = MergeLaunch<G, V, IPG>::items()
+#define WHAT(G, V, IPG, BIT) items = MergeLaunch<G, V, IPG>::items()
 	MERGE_DISPATCH(k, WHAT)
 #undef WHAT
 	return items;
@@ -347,7 +423,7 @@ static int launch_merge(spmm_b200* h, const double* B, double* C, int k, cudaStr
 	if (rc) return rc;
 	if (h->merge.ntiles == 0) return 0;
 	cudaError_t e = cudaErrorInvalidValue;
-#define WHAT(G, V, IPG) e = MergeLaunch<G, V, IPG>::launch(h, B, C, s)
+#define WHAT(G, V, IPG, BIT) e = MergeLaunch<G, V, IPG>::launch(h, B, C, s, BIT)
 	MERGE_DISPATCH(k, WHAT)
 #undef WHAT
 	if (e != cudaSuccess) {
@@ -433,37 +509,36 @@ static int build_bcsr_plan(spmm_b200* h)
 }
 
 template <int K, int WARPS, int STAGES>
-static void launch_bcsr_tma(const BcsrPlan& p, const double* B, double* C, int m, int brw, unsigned grid, cudaStream_t s)
+static void launch_bcsr_tma(spmm_b200* h, const double* B, double* C, int brw, unsigned grid, cudaStream_t s)
 {
 	using Cfg = BcsrTmaCfg<K, WARPS, STAGES>;
+	const BcsrPlan& p = h->bcsr;
 	auto kern = spmm_bcsr_dmma_tma_kernel<K, WARPS, STAGES>;
-	static bool attr_set = false;
-	if (!attr_set) {
-		cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) Cfg::SMEM);
-		attr_set = true;
-	}
-	kern<<<grid, WARPS * 32, Cfg::SMEM, s>>>(p.d_brow, p.d_bcol, p.d_bval, B, C, m, p.mb, brw);
+	raise_smem_limit(h, ATTR_BCSR_TMA + (STAGES - 2) + 3 * (K == 128 ? 2 : K == 64 ? 1 : 0), kern, Cfg::SMEM);
+	kern<<<grid, WARPS * 32, Cfg::SMEM, s>>>(p.d_brow, p.d_bcol, p.d_bval, B, C, (int) h->m, p.mb, brw);
 }
 
 template <int K>
-static void launch_bcsr_k(const spmm_b200* h, const double* B, double* C, cudaStream_t s)
+static void launch_bcsr_k(spmm_b200* h, const double* B, double* C, cudaStream_t s)
 {
 	constexpr int WARPS = 4;
 	const BcsrPlan& p = h->bcsr;
+	const Options& o = h->opt;
 	const unsigned grid = (unsigned) ((p.mb + WARPS - 1) / WARPS);
-	static const int use_tma = env_int("SPMM_B200_BCSR_TMA", 1);
 	// bulk copies of 8K bytes per B row pay from K = 64 on (cfg4: K=32 0.57 ms fragment loads vs 0.63 ms TMA;
 	// K=128 2.55 ms vs 1.23 ms); 2 stages = most warps per SM, which is what the tensor pipe needs
-	if (h->variant == SPMM_B200_BCSR && (use_tma == 2 || (use_tma == 1 && K >= 64)) && ((uintptr_t) B % 16) == 0) {
-		static const int stages = env_int("SPMM_B200_BCSR_STAGES", 2);
-		static const int brw_env = env_int("SPMM_B200_BCSR_BRW", 0);
-		// block rows per warp: enough to keep the ring flowing, few enough for >= 8 CTAs per SM
-		const int brw = brw_env > 0 ? brw_env : (int) std::max<int64_t>(1, std::min<int64_t>(8, p.mb / ((int64_t) h->sm_count * WARPS * 8)));
-		const unsigned g2 = (unsigned) ((p.mb + (int64_t) WARPS * brw - 1) / ((int64_t) WARPS * brw));
-		if (stages <= 2) launch_bcsr_tma<K, WARPS, 2>(p, B, C, (int) h->m, brw, g2, s);
-		else if (stages == 3) launch_bcsr_tma<K, WARPS, 3>(p, B, C, (int) h->m, brw, g2, s);
-		else launch_bcsr_tma<K, WARPS, 4>(p, B, C, (int) h->m, brw, g2, s);
-	} else if (h->variant == SPMM_B200_BCSR)
+	if (h->variant == SPMM_B200_BCSR && (o.bcsr_tma == 2 || (o.bcsr_tma == 1 && K >= 64))) {
+		if constexpr (K >= 32) {
+			// block rows per warp: enough to keep the ring flowing, few enough for >= 8 CTAs per SM
+			const int brw = o.bcsr_brw > 0 ? o.bcsr_brw : (int) std::max<int64_t>(1, std::min<int64_t>(8, p.mb / ((int64_t) h->sm_count * WARPS * 8)));
+			const unsigned g2 = (unsigned) ((p.mb + (int64_t) WARPS * brw - 1) / ((int64_t) WARPS * brw));
+			if (o.bcsr_stages <= 2) launch_bcsr_tma<K, WARPS, 2>(h, B, C, brw, g2, s);
+			else if (o.bcsr_stages == 3) launch_bcsr_tma<K, WARPS, 3>(h, B, C, brw, g2, s);
+			else launch_bcsr_tma<K, WARPS, 4>(h, B, C, brw, g2, s);
+			return;
+		}
+	}
+	if (h->variant == SPMM_B200_BCSR)
 		spmm_bcsr_dmma_kernel<K, WARPS><<<grid, WARPS * 32, 0, s>>>(p.d_brow, p.d_bcol, p.d_bval, B, C, (int) h->m, p.mb);
 	else if constexpr (K % 32 == 0)
 		spmm_bcsr_simt_kernel<K, WARPS><<<grid, WARPS * 32, 0, s>>>(p.d_brow, p.d_bcol, p.d_bval, p.d_bmask, B, C, (int) h->m, p.mb);
@@ -487,32 +562,56 @@ static int launch_bcsr(spmm_b200* h, const double* B, double* C, int k, cudaStre
 	return 1;
 }
 
-// Launches the SpMM kernel(s) of the handle's variant on stream s.  Returns kernels launched or <0.
-static int launch_spmm(spmm_b200* h, const double* B, double* C, int k, cudaStream_t s)
+// k for which the row-split family has a specialised (double2) kernel
+static bool rowsplit_specialised(int k) { return k == 1 || k == 2 || k == 4 || k == 8 || k == 16 || k == 32 || k == 64 || k == 128; }
+
+static void launch_rowsplit_width(spmm_b200* h, const double* B, double* C, int w, cudaStream_t s, int ldb, int ldc)
+{
+	switch (w) {
+	case 8:  launch_rowsplit_gv<4, 2>(h, B, C, s, ldb, ldc); break;
+	case 16: launch_rowsplit_gv<8, 2>(h, B, C, s, ldb, ldc); break;
+	case 32: launch_rowsplit_gv<8, 4>(h, B, C, s, ldb, ldc); break;
+	default: launch_rowsplit_gv<16, 4>(h, B, C, s, ldb, ldc); break;      // 64
+	}
+}
+
+// Launches the SpMM kernel(s) of the handle's variant on stream s: C (row stride ldc) = A * B (row stride ldb), both
+// row-major with k columns.  Returns kernels launched or <0.
+static int launch_spmm(spmm_b200* h, const double* B, double* C, int k, cudaStream_t s, int ldb = 0, int ldc = 0)
 {
 	if (h->m == 0) return 0;
-	// merge-path has no instantiation for odd k: those run on the row-split generic kernel
-	if (h->variant == SPMM_B200_MERGE && merge_supports_k(k)) return launch_merge(h, B, C, k, s);
-	// blocked variants need k % 16 (tensor pipe) / k % 32 (FMA pipe); other k run on the CSR kernels
-	if ((h->variant == SPMM_B200_BCSR || h->variant == SPMM_B200_BCSR_FMA) && bcsr_supports_k(h->variant, k))
-		return launch_bcsr(h, B, C, k, s);
-	int n = 1;
+	if (ldb <= 0) ldb = k;
+	if (ldc <= 0) ldc = k;
+	// Every specialised kernel moves B and C as double2: operands that are not 16-byte aligned (a tensor view at an
+	// odd offset, an odd row stride) take the generic kernel instead of faulting.
+	const bool aligned = k == 1 || ((((uintptr_t) B | (uintptr_t) C) & 15) == 0 && ldb % 2 == 0 && ldc % 2 == 0);
+	const bool whole = ldb == k && ldc == k;
+	if (aligned && whole) {
+		// merge-path has no instantiation for odd k: those run on the row-split generic kernel
+		if (h->variant == SPMM_B200_MERGE && merge_supports_k(k)) return launch_merge(h, B, C, k, s);
+		// blocked variants need k % 16 (tensor pipe) / k % 32 (FMA pipe); other k run on the CSR kernels
+		if ((h->variant == SPMM_B200_BCSR || h->variant == SPMM_B200_BCSR_FMA) && bcsr_supports_k(h->variant, k))
+			return launch_bcsr(h, B, C, k, s);
+	}
+	if (!aligned || !rowsplit_specialised(k) || (!whole && k < 8)) {
+		spmm_rowsplit_generic_kernel<THREADS><<<h->n_ctas, THREADS, 0, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, h->d_cta_rows, k, ldb, ldc);
+		cudaError_t e = cudaGetLastError();
+		if (e != cudaSuccess) {
+			snprintf(g_cuda_err, sizeof(g_cuda_err), "generic spmm launch (k=%d): %s", k, cudaGetErrorString(e));
+			return SPMM_B200_ECUDA;
+		}
+		h->launches += 1;
+		return 1;
+	}
 	// L2-aware k slicing: run the k columns as k/w launches on w-column slices of the same row-major B and C,
 	// so that the B rows a launch gathers (touched window x 8w bytes) stay in L2.  It pays when the window is
 	// far larger than L2 AND rows are long (every slice re-reads A and pays the per-row overhead again):
-	// profiles/r1_kslice_probe.md, r1_sweep_medium.md.  SPMM_B200_KSLICE=w forces a width, =0 (default) lets the
+	// profiles/r1_kslice_probe.md, r1_sweep_medium.md.  KSLICE=w forces a width, =0 (default) lets the
 	// handle time the candidates on its first calls (spmm_b200_run_device), =-1 turns slicing off.
-	int w = env_int("SPMM_B200_KSLICE", 0);
+	int w = h->opt.kslice;
 	if (w == 0 && h->ks_k == k) w = h->ks_best > 0 ? h->ks_best : h->ks_cand[h->ks_try / 2];
-	if (w > 0 && w < k && k % w == 0 && (w == 8 || w == 16 || w == 32 || w == 64)) {
-		for (int off = 0; off < k; off += w) {
-			switch (w) {
-			case 8:  launch_rowsplit_gv<4, 2>(h, B + off, C + off, s, k, k); break;
-			case 16: launch_rowsplit_gv<8, 2>(h, B + off, C + off, s, k, k); break;
-			case 32: launch_rowsplit_gv<8, 4>(h, B + off, C + off, s, k, k); break;
-			default: launch_rowsplit_gv<16, 4>(h, B + off, C + off, s, k, k); break;
-			}
-		}
+	if (whole && w > 0 && w < k && k % w == 0 && (w == 8 || w == 16 || w == 32 || w == 64)) {
+		for (int off = 0; off < k; off += w) launch_rowsplit_width(h, B + off, C + off, w, s, k, k);
 		cudaError_t e = cudaGetLastError();
 		if (e != cudaSuccess) {
 			snprintf(g_cuda_err, sizeof(g_cuda_err), "sliced spmm launch (k=%d, w=%d): %s", k, w, cudaGetErrorString(e));
@@ -521,64 +620,23 @@ static int launch_spmm(spmm_b200* h, const double* B, double* C, int k, cudaStre
 		h->launches += k / w;
 		return k / w;
 	}
-	const int vec = env_int("SPMM_B200_VEC", 0);
-	if (vec && h->d_iap && (k == 16 || k == 32 || k == 64 || k == 128) && ((uintptr_t) B % 16) == 0) {
-		switch (k) {
-		case 16:  if (vec == 2) launch_rowsplit_vec<8, 2>(h, B, C, s); else launch_rowsplit_vec<4, 4>(h, B, C, s); break;
-		case 32:  if (vec == 2) launch_rowsplit_vec<16, 2>(h, B, C, s); else launch_rowsplit_vec<8, 4>(h, B, C, s); break;
-		case 64:  if (vec == 2) launch_rowsplit_vec<32, 2>(h, B, C, s); else launch_rowsplit_vec<16, 4>(h, B, C, s); break;
-		default:  launch_rowsplit_vec<32, 4>(h, B, C, s); break;
-		}
-		cudaError_t e = cudaGetLastError();
-		if (e != cudaSuccess) {
-			snprintf(g_cuda_err, sizeof(g_cuda_err), "vec spmm launch (k=%d): %s", k, cudaGetErrorString(e));
-			return SPMM_B200_ECUDA;
-		}
-		h->launches += 1;
-		return 1;
-	}
-	// experiment knob: lane-group shape "GxVxU" (G lanes per row, V columns per lane, U gathers in flight)
-	const int gvu = env_int("SPMM_B200_GVU", 0);       // e.g. 842 = G 8, V 4, U 2;  1682 = G 16, V 8, U 2
-	if (gvu > 0) {
-		const int G = gvu / 100, V = (gvu / 10) % 10, U = gvu % 10;
-		bool ok = true;
-#define TRY_GVU(g, v, u) else if (G == g && V == v && U == u && k == g * v) \
-		spmm_rowsplit_kernel<g, v, u, THREADS><<<h->n_ctas, THREADS, 0, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, h->d_cta_rows, k, k)
-		if (false) {}
-		TRY_GVU(8, 4, 2); TRY_GVU(8, 4, 4); TRY_GVU(8, 4, 8);
-		TRY_GVU(8, 8, 2); TRY_GVU(8, 8, 4); TRY_GVU(16, 4, 2); TRY_GVU(16, 4, 4);
-		TRY_GVU(16, 8, 2); TRY_GVU(16, 8, 4); TRY_GVU(32, 4, 2); TRY_GVU(32, 4, 4);
-		TRY_GVU(8, 2, 4); TRY_GVU(8, 2, 8); TRY_GVU(4, 4, 4); TRY_GVU(2, 2, 2); TRY_GVU(4, 1, 4); TRY_GVU(2, 1, 2); TRY_GVU(4, 2, 4); TRY_GVU(2, 4, 2);
-		else ok = false;
-#undef TRY_GVU
-		if (ok) {
-			h->launches += 1;
-			return cudaGetLastError() == cudaSuccess ? 1 : SPMM_B200_ECUDA;
-		}
-	}
 	switch (k) {
 	case 1:   launch_smallk<1>(h, B, C, s); break;
 	case 2:   launch_smallk<2>(h, B, C, s); break;
-	case 4:   launch_rowsplit_gv<2, 2>(h, B, C, s); break;      // 16 rows per warp: cfg2 0.496 -> 0.380 ms, cfg5-large 0.440 -> 0.284 ms vs the small-k kernel
+	case 4:   launch_rowsplit_gv<2, 2>(h, B, C, s, ldb, ldc); break;      // 16 rows per warp: cfg2 0.496 -> 0.380 ms, cfg5-large 0.440 -> 0.284 ms vs the small-k kernel
 	// lane-group shapes from the sweep in profiles/r1_gvu_probe.md: V = 4 columns per lane (two 16-byte loads)
 	// makes a group of 8 lanes cover one 128-byte line per load and halves the shuffle traffic per nonzero
 	// (cfg2: k=32 0.935 -> 0.786 ms, k=64 1.563 -> 1.336 ms); V = 8 costs too many registers
-	case 8:   launch_rowsplit_gv<4, 2>(h, B, C, s); break;
-	case 16:  launch_rowsplit_gv<8, 2>(h, B, C, s); break;
-	case 32:  launch_rowsplit_gv<8, 4>(h, B, C, s); break;
-	case 64:  launch_rowsplit_gv<16, 4>(h, B, C, s); break;
-	case 128: launch_rowsplit_gv<32, 4>(h, B, C, s); break;
-	default:
-		spmm_rowsplit_generic_kernel<THREADS><<<h->n_ctas, THREADS, 0, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, h->d_cta_rows, k);
-		break;
+	case 128: launch_rowsplit_gv<32, 4>(h, B, C, s, ldb, ldc); break;
+	default:  launch_rowsplit_width(h, B, C, k, s, ldb, ldc); break;      // 8, 16, 32, 64
 	}
 	cudaError_t e = cudaGetLastError();
 	if (e != cudaSuccess) {
 		snprintf(g_cuda_err, sizeof(g_cuda_err), "spmm kernel launch (k=%d): %s", k, cudaGetErrorString(e));
 		return SPMM_B200_ECUDA;
 	}
-	h->launches += n;
-	return n;
+	h->launches += 1;
+	return 1;
 }
 
 // ------------------------------------------------------------------------------------------
@@ -593,6 +651,7 @@ static int create_from_slice(spmm_b200_t** out, const int32_t* row_ptr_slice, co
 	if (!h) return SPMM_B200_ENOMEM;
 	h->device = device; h->variant_req = variant; h->b_layout = b_layout; h->k = k;
 	h->sm_count = sm_count;
+	h->opt = options_from_env();
 	h->m = m_local; h->c = c; h->nnz = nnz_local; h->first_row = first_row; h->m_global = m_global;
 	*out = h;   // from here on the caller destroys on error
 
@@ -600,8 +659,11 @@ static int create_from_slice(spmm_b200_t** out, const int32_t* row_ptr_slice, co
 	CU_TRY(cudaEventCreate(&h->ev0));
 	CU_TRY(cudaEventCreate(&h->ev1));
 	CU_TRY(cudaMalloc(&h->d_ia, sizeof(int32_t) * (m_local + 1)));
-	CU_TRY(cudaMalloc(&h->d_ja, sizeof(int32_t) * std::max<int64_t>(nnz_local, 1)));
-	CU_TRY(cudaMalloc(&h->d_a, sizeof(double) * std::max<int64_t>(nnz_local, 1)));
+	// 16 entries of slack: the staged kernel's bulk copies read 16-byte aligned windows that may end past nnz
+	CU_TRY(cudaMalloc(&h->d_ja, sizeof(int32_t) * (nnz_local + 16)));
+	CU_TRY(cudaMalloc(&h->d_a, sizeof(double) * (nnz_local + 16)));
+	CU_TRY(cudaMemsetAsync(h->d_ja + nnz_local, 0, sizeof(int32_t) * 16, h->stream));
+	CU_TRY(cudaMemsetAsync(h->d_a + nnz_local, 0, sizeof(double) * 16, h->stream));
 	CU_TRY(cudaMemcpyAsync(h->d_ia, row_ptr_slice, sizeof(int32_t) * (m_local + 1), cudaMemcpyHostToDevice, h->stream));
 	if (nnz_local > 0) {
 		CU_TRY(cudaMemcpyAsync(h->d_ja, col_ind + base, sizeof(int32_t) * nnz_local, cudaMemcpyHostToDevice, h->stream));
@@ -628,12 +690,13 @@ static int create_from_slice(spmm_b200_t** out, const int32_t* row_ptr_slice, co
 		int mm[2] = {INT32_MAX, -1};
 		CU_TRY(cudaMalloc(&d_mm, 2 * sizeof(int)));
 		CU_TRY(cudaMemcpyAsync(d_mm, mm, sizeof(mm), cudaMemcpyHostToDevice, h->stream));
-		col_span_kernel<<<(unsigned) std::min<int64_t>(148 * 8, (nnz_local + 255) / 256), 256, 0, h->stream>>>(h->d_ja, nnz_local, d_mm, d_mm + 1);
+		col_span_kernel<<<(unsigned) std::min<int64_t>((int64_t) sm_count * 8, (nnz_local + 255) / 256), 256, 0, h->stream>>>(h->d_ja, nnz_local, d_mm, d_mm + 1);
 		h->launches++;
 		CU_TRY(cudaMemcpyAsync(mm, d_mm, sizeof(mm), cudaMemcpyDeviceToHost, h->stream));
 		CU_TRY(cudaStreamSynchronize(h->stream));
 		cudaFree(d_mm);
 		h->col_span = mm[1] >= mm[0] ? (int64_t) mm[1] - mm[0] + 1 : 0;
+		h->col_min = mm[1] >= mm[0] ? mm[0] : 0;
 	}
 	if (variant == SPMM_B200_AUTO) {
 		// row-split serialises a row on one lane group: switch to merge-path when one row is far
@@ -641,17 +704,13 @@ static int create_from_slice(spmm_b200_t** out, const int32_t* row_ptr_slice, co
 		const double avg = m_local > 0 ? (double) nnz_local / (double) m_local : 0.0;
 		// measured (gpurun_out/r2_*): cfg3b (max 866, mean 20) merge 1.24 ms vs row-split 2.03 ms;
 		// cfg2 (max 131, mean 50) row-split 0.91 ms vs merge 0.96 ms
-		const int thr = env_int("SPMM_B200_MERGE_MAXROW", 256);
+		const int thr = h->opt.merge_maxrow;
 		h->variant = (h->max_row >= thr && h->max_row > 8.0 * avg) ? SPMM_B200_MERGE : SPMM_B200_ROWSPLIT;
 	} else {
 		h->variant = variant;
 	}
 	int rc = build_rowsplit_plan(h);        // always: the fallback for k without a specialised instantiation
 	if (rc) return rc;
-	if (env_int("SPMM_B200_VEC", 0) && k >= 16) {
-		rc = build_padded_plan(h);
-		if (rc && rc != SPMM_B200_ENOSUP) return rc;
-	}
 	if (variant == SPMM_B200_AUTO && h->variant == SPMM_B200_ROWSPLIT && k >= 32 && bcsr_supports_k(SPMM_B200_BCSR, k)
 	    && m_local >= 8 && nnz_local > 0) {
 		// "tensor cores only where dense blocks make it a genuine contraction": probe the 8x1 block
@@ -660,7 +719,7 @@ static int create_from_slice(spmm_b200_t** out, const int32_t* row_ptr_slice, co
 		rc = bcsr_count(h);
 		if (rc) return rc;
 		const double fill = h->bcsr.nnzb > 0 ? (double) nnz_local / (8.0 * (double) h->bcsr.nnzb) : 0.0;
-		const double thr = env_int("SPMM_B200_BCSR_FILL_PCT", 30) / 100.0;
+		const double thr = h->opt.bcsr_fill_pct / 100.0;
 		if (fill >= thr) {
 			rc = bcsr_fill(h);
 			if (rc) return rc;
@@ -740,13 +799,13 @@ extern "C" void spmm_b200_destroy(spmm_b200_t* h)
 	for (void* p : h->pinned) cudaHostUnregister(p);
 	cudaFree(h->d_ia); cudaFree(h->d_ja); cudaFree(h->d_a);
 	cudaFree(h->d_cta_rows);
-	cudaFree(h->d_iap); cudaFree(h->d_jap); cudaFree(h->d_ap);
 	cudaFree(h->merge.d_tile); cudaFree(h->merge.d_carry); cudaFree(h->merge.d_carry_row);
 	cudaFree(h->bcsr.d_brow); cudaFree(h->bcsr.d_bcol); cudaFree(h->bcsr.d_bval); cudaFree(h->bcsr.d_bmask);
 	cudaFree(h->d_x); cudaFree(h->d_B); cudaFree(h->d_C); cudaFree(h->d_ticket);
 	if (h->ev0) cudaEventDestroy(h->ev0);
 	if (h->ev1) cudaEventDestroy(h->ev1);
 	for (cudaEvent_t e : h->ev_slice) cudaEventDestroy(e);
+	for (cudaEvent_t e : h->ev_tl) cudaEventDestroy(e);
 	if (h->s_up) cudaStreamDestroy(h->s_up);
 	if (h->s_down) cudaStreamDestroy(h->s_down);
 	if (h->stream) cudaStreamDestroy(h->stream);
@@ -841,11 +900,14 @@ extern "C" int spmm_b200_run_device(spmm_b200_t* h, const double* b_dev, double*
 	CU_TRY(cudaSetDevice(h->device));
 	// L2-aware k slicing: when the touched window of B (col_span x 8k bytes) is far beyond L2, the first calls with
 	// this k run one candidate slice width each and are timed (they block until their kernels finish; every
-	// candidate computes the same bits), then the fastest is kept.
-	const bool tunable = h->variant == SPMM_B200_ROWSPLIT && k >= 64 && k % 16 == 0 && env_int("SPMM_B200_KSLICE", 0) == 0
-	                     && (double) h->col_span * 8.0 * k > 192e6 && h->nnz > 0;
+	// candidate computes the same bits), then the fastest is kept -- per k, so alternating k values do not re-tune.
+	// Never while the stream is being captured into a graph (the measurement synchronises).
+	bool tunable = h->variant == SPMM_B200_ROWSPLIT && k >= 64 && k % 16 == 0 && h->opt.kslice == 0
+	               && (double) h->col_span * 8.0 * k > 192e6 && h->nnz > 0;
 	if (tunable && h->ks_k != k) {
 		h->ks_k = k; h->ks_best = 0; h->ks_try = 0;
+		for (const KsliceChoice& d : h->ks_done)
+			if (d.k == k) h->ks_best = d.best;
 		int n = 0;
 		h->ks_cand[n++] = k;
 		for (int w = 64; w >= 16 && n < 4; w /= 2)
@@ -854,11 +916,17 @@ extern "C" int spmm_b200_run_device(spmm_b200_t* h, const double* b_dev, double*
 	} else if (!tunable && h->ks_k == k) {
 		h->ks_k = 0;
 	}
+	bool measuring = tunable && h->ks_best == 0;
+	if (measuring) {
+		cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+		if (cudaStreamIsCapturing((cudaStream_t) stream, &cap) != cudaSuccess) cudaGetLastError();
+		if (cap != cudaStreamCaptureStatusNone) { measuring = false; h->ks_k = 0; }     // unsliced inside a capture
+	}
 	int rc = run_between(h, b_dev, c_dev, k, (cudaStream_t) stream, h->ev0, h->ev1);
 	if (rc) return rc;
 	h->timed = true;
 	h->timed_slices = 0;
-	if (tunable && h->ks_best == 0) {
+	if (measuring) {
 		float ms = 0.f;
 		CU_TRY(cudaEventSynchronize(h->ev1));
 		CU_TRY(cudaEventElapsedTime(&ms, h->ev0, h->ev1));
@@ -871,6 +939,8 @@ extern "C" int spmm_b200_run_device(spmm_b200_t* h, const double* b_dev, double*
 			for (int i = 1; i < ncand; i++)
 				if (h->ks_ms[i] < h->ks_ms[best]) best = i;
 			h->ks_best = h->ks_cand[best];
+			KsliceChoice d; d.k = k; d.best = h->ks_best;
+			h->ks_done.push_back(d);
 		}
 	}
 	return SPMM_B200_OK;
@@ -933,7 +1003,7 @@ extern "C" int spmm_b200_fetch_c(spmm_b200_t* h, double* y_host, int k)
 // wide 2-D copy, which the copy engine still moves at 52.6 GB/s (64 bytes: 31 GB/s -- hence 16).
 static int slice_width(const spmm_b200* h, int k)
 {
-	int w = env_int("SPMM_B200_PIPELINE_COLS", -1);                  // 0 = off, -1 = choose
+	int w = h->opt.pipeline_cols;                                    // 0 = off, -1 = choose
 	if (w < 0) {
 		// at most 4 slices: every slice re-reads A, and wider slices run the better kernels
 		// (cfg4, k=128: 27.8 ms with 32-column slices, 29.3 ms with 16, 38.8 ms unsliced)
@@ -942,10 +1012,14 @@ static int slice_width(const spmm_b200* h, int k)
 	}
 	if (w <= 0 || k < 2 * w || k % w) return 0;
 	// small operands are latency-bound, not bandwidth-bound: one upload, one kernel, one download
-	const size_t min_bytes = (size_t) env_int("SPMM_B200_PIPELINE_MIN_KB", 8 << 10) << 10;
+	const size_t min_bytes = (size_t) h->opt.pipeline_min_kb << 10;
 	if ((size_t) h->c * k * sizeof(double) < min_bytes) return 0;
 	return w;
 }
+
+// Timeline of the last pipelined run: events t0 (start) and, per slice, {H2D done, replication done, transpose done,
+// kernel start, kernel end, D2H done}; read with spmm_b200_last_timeline.
+enum { TL_H2D = 0, TL_BCAST, TL_TRANSPOSE, TL_K0, TL_K1, TL_D2H, TL_PER_SLICE };
 
 static int run_pipelined(spmm_b200* h, const double* x_host, double* y_host, int k, int ks,
                          spmm_b200_bcast_fn bcast = nullptr, void* bcast_ctx = nullptr, int parts = 1)
@@ -967,8 +1041,16 @@ static int run_pipelined(spmm_b200* h, const double* x_host, double* y_host, int
 		CU_TRY(cudaEventCreate(&e));
 		h->ev_slice.push_back(e);
 	}
+	while (h->ev_tl.size() < (size_t) TL_PER_SLICE * S + 1) {
+		cudaEvent_t e;
+		CU_TRY(cudaEventCreate(&e));
+		h->ev_tl.push_back(e);
+	}
+	cudaEvent_t* tl = h->ev_tl.data() + 1;
+	h->tl_slices = 0;
 	h->resident_k = 0;                       // d_B is about to hold slices, not the c x k operand
 	const size_t bslice = (size_t) h->c * ks, cslice = (size_t) h->m * ks;
+	CU_TRY(cudaEventRecord(h->ev_tl[0], h->s_up));
 	for (int s = 0; s < S; s++) {
 		double* Bs = h->d_B + s * bslice;
 		if (h->b_layout == SPMM_B200_B_COLMAJOR) {
@@ -983,15 +1065,20 @@ static int run_pipelined(spmm_b200* h, const double* x_host, double* y_host, int
 			} else if (x_host) {
 				CU_TRY(cudaMemcpyAsync(h->d_x + s * bslice, x_host + s * bslice, bslice * sizeof(double), cudaMemcpyHostToDevice, h->s_up));
 			}
+			CU_TRY(cudaEventRecord(tl[TL_PER_SLICE * s + TL_H2D], h->s_up));
 			if (bcast && bslice > 0 && bcast(bcast_ctx, h->d_x + s * bslice, bslice, parts, h->s_up)) return SPMM_B200_ECOMM;
+			CU_TRY(cudaEventRecord(tl[TL_PER_SLICE * s + TL_BCAST], h->s_up));
 			rc = spmm_b200_transpose_b_device(h, h->d_x + s * bslice, Bs, ks, h->s_up);
 			if (rc) return rc;
 		} else {
 			if (x_host)
 				CU_TRY(cudaMemcpy2DAsync(Bs, sizeof(double) * ks, x_host + (size_t) s * ks, sizeof(double) * k, sizeof(double) * ks,
 				                         (size_t) h->c, cudaMemcpyHostToDevice, h->s_up));
+			CU_TRY(cudaEventRecord(tl[TL_PER_SLICE * s + TL_H2D], h->s_up));
 			if (bcast && bslice > 0 && bcast(bcast_ctx, Bs, bslice, 1, h->s_up)) return SPMM_B200_ECOMM;
+			CU_TRY(cudaEventRecord(tl[TL_PER_SLICE * s + TL_BCAST], h->s_up));
 		}
+		CU_TRY(cudaEventRecord(tl[TL_PER_SLICE * s + TL_TRANSPOSE], h->s_up));
 		CU_TRY(cudaEventRecord(h->ev_slice[3 * s], h->s_up));
 	}
 	// Direct store: when y_host is page-locked and mapped into the device's address space, the row-split kernel
@@ -1000,44 +1087,61 @@ static int run_pipelined(spmm_b200* h, const double* x_host, double* y_host, int
 	// staging in d_C (profiles/r1_pcie_probe.md: SM stores into mapped host memory run at the 2-D copy's rate).
 	double* y_map = nullptr;
 	if (y_host && h->m > 0 && h->variant == SPMM_B200_ROWSPLIT && (ks == 8 || ks == 16 || ks == 32 || ks == 64)
-	    && env_int("SPMM_B200_DIRECT_STORE", 1)) {
+	    && h->opt.direct_store) {
 		cudaPointerAttributes at;
 		if (cudaPointerGetAttributes(&at, y_host) == cudaSuccess && at.type == cudaMemoryTypeHost && at.devicePointer)
 			y_map = (double*) at.devicePointer;
 		else
 			cudaGetLastError();
+		if (((uintptr_t) y_map & 15) != 0 || k % 2) y_map = nullptr;     // the kernels store C as double2: staged download instead
 	}
 	for (int s = 0; s < S; s++) {
 		CU_TRY(cudaStreamWaitEvent(h->stream, h->ev_slice[3 * s], 0));
 		if (y_map) {
-			const double* Bs = h->d_B + s * bslice;
-			double* Cs = y_map + (size_t) s * ks;
 			CU_TRY(cudaEventRecord(h->ev_slice[3 * s + 1], h->stream));
-			switch (ks) {
-			case 8:  launch_rowsplit_gv<4, 2>(h, Bs, Cs, h->stream, ks, k); break;
-			case 16: launch_rowsplit_gv<8, 2>(h, Bs, Cs, h->stream, ks, k); break;
-			case 32: launch_rowsplit_gv<8, 4>(h, Bs, Cs, h->stream, ks, k); break;
-			default: launch_rowsplit_gv<16, 4>(h, Bs, Cs, h->stream, ks, k); break;
-			}
+			CU_TRY(cudaEventRecord(tl[TL_PER_SLICE * s + TL_K0], h->stream));
+			launch_rowsplit_width(h, h->d_B + s * bslice, y_map + (size_t) s * ks, ks, h->stream, ks, k);
 			CU_TRY(cudaGetLastError());
 			h->launches += 1;
 			CU_TRY(cudaEventRecord(h->ev_slice[3 * s + 2], h->stream));
+			CU_TRY(cudaEventRecord(tl[TL_PER_SLICE * s + TL_K1], h->stream));
+			CU_TRY(cudaEventRecord(tl[TL_PER_SLICE * s + TL_D2H], h->stream));
 			continue;
 		}
+		CU_TRY(cudaEventRecord(tl[TL_PER_SLICE * s + TL_K0], h->stream));
 		rc = run_between(h, h->d_B + s * bslice, h->d_C + s * cslice, ks, h->stream, h->ev_slice[3 * s + 1], h->ev_slice[3 * s + 2]);
 		if (rc) return rc;
+		CU_TRY(cudaEventRecord(tl[TL_PER_SLICE * s + TL_K1], h->stream));
 		if (y_host && h->m > 0) {
 			CU_TRY(cudaStreamWaitEvent(h->s_down, h->ev_slice[3 * s + 2], 0));
 			CU_TRY(cudaMemcpy2DAsync(y_host + (size_t) s * ks, sizeof(double) * k, h->d_C + s * cslice, sizeof(double) * ks,
 			                         sizeof(double) * ks, (size_t) h->m, cudaMemcpyDeviceToHost, h->s_down));
 		}
+		CU_TRY(cudaEventRecord(tl[TL_PER_SLICE * s + TL_D2H], h->s_down));
 	}
 	h->c_slices = y_map ? 0 : S;            // 0: C went straight to the host, d_C holds nothing to fetch
 	h->timed = true;
 	h->timed_slices = S;
 	CU_TRY(cudaStreamSynchronize(h->stream));
 	CU_TRY(cudaStreamSynchronize(h->s_down));
+	h->tl_slices = S;
 	return SPMM_B200_OK;
+}
+
+// out[0] = number of slices S of the last pipelined host-buffer run; then per slice six times in ms since the
+// run's first enqueue: H2D done, replication done, transpose done, kernel start, kernel end, D2H done.
+extern "C" int spmm_b200_last_timeline(const spmm_b200_t* h, double* out, int max_values)
+{
+	if (!h || !out || max_values < 1) return SPMM_B200_EINVAL;
+	const int S = h->tl_slices;
+	out[0] = S;
+	int n = 1;
+	for (int i = 0; i < S * TL_PER_SLICE && n < max_values; i++, n++) {
+		float ms = 0.f;
+		if (cudaEventElapsedTime(&ms, h->ev_tl[0], h->ev_tl[1 + i]) != cudaSuccess) { cudaGetLastError(); ms = -1.f; }
+		out[n] = ms;
+	}
+	return n;
 }
 
 extern "C" int spmm_b200_run(spmm_b200_t* h, const double* x_host, double* y_host, int k, int copy_back)
@@ -1082,14 +1186,24 @@ extern "C" int spmm_b200_run_replicated(spmm_b200_t* h, const double* x_host, do
 // partitioning (device search, host pointers in and out)
 // ------------------------------------------------------------------------------------------
 
+static size_t partition_out_len(int mode, int P)
+{
+	switch (mode) {
+	case SPMM_B200_PART_NNZ:       return (size_t) P + 1;
+	case SPMM_B200_PART_ROWS:      return 2 * (size_t) P;
+	case SPMM_B200_PART_MERGE:     return 2 * ((size_t) P + 1);
+	default:                       return 4 * (size_t) P;        // SPMM_B200_PART_NNZ_CARRY
+	}
+}
+
 extern "C" int spmm_b200_partition(const int32_t* row_ptr, int64_t m, int64_t nnz, int P, int mode, int64_t* out, int device)
 {
 	if (!out || P < 1 || m < 0 || nnz < 0) return SPMM_B200_EINVAL;
 	if (mode != SPMM_B200_PART_ROWS && !row_ptr) return SPMM_B200_EINVAL;
-	if (mode < SPMM_B200_PART_ROWS || mode > SPMM_B200_PART_MERGE) return SPMM_B200_EINVAL;
+	if (mode < SPMM_B200_PART_ROWS || mode > SPMM_B200_PART_NNZ_CARRY) return SPMM_B200_EINVAL;
 	int rc = check_device(device, nullptr);
 	if (rc) return rc;
-	const size_t n_out = (mode == SPMM_B200_PART_NNZ) ? (size_t) P + 1 : (mode == SPMM_B200_PART_ROWS ? 2 * (size_t) P : 2 * ((size_t) P + 1));
+	const size_t n_out = partition_out_len(mode, P);
 	int32_t* d_ia = nullptr;
 	int64_t* d_out = nullptr;
 	CU_TRY(cudaMalloc(&d_out, sizeof(int64_t) * n_out));
@@ -1102,7 +1216,8 @@ extern "C" int spmm_b200_partition(const int32_t* row_ptr, int64_t m, int64_t nn
 	const unsigned nb = (unsigned) ((P + 1 + 255) / 256);
 	if (mode == SPMM_B200_PART_NNZ) partition_nnz_kernel<<<nb, 256>>>(d_ia, m, nnz, P, d_out);
 	else if (mode == SPMM_B200_PART_ROWS) partition_rows_kernel<<<nb, 256>>>(0, m, P, d_out);
-	else partition_merge_kernel<<<nb, 256>>>(d_ia, m, nnz, P, d_out);
+	else if (mode == SPMM_B200_PART_MERGE) partition_merge_kernel<<<nb, 256>>>(d_ia, m, nnz, P, d_out);
+	else partition_nnz_carry_kernel<<<nb, 256>>>(d_ia, m, nnz, P, d_out);
 	cudaError_t e = cudaGetLastError();
 	if (e == cudaSuccess) e = cudaMemcpy(out, d_out, sizeof(int64_t) * n_out, cudaMemcpyDeviceToHost);
 	cudaFree(d_out); cudaFree(d_ia);
@@ -1117,18 +1232,20 @@ extern "C" int spmm_b200_partition(const int32_t* row_ptr, int64_t m, int64_t nn
 extern "C" int spmm_b200_partition_host(const int32_t* row_ptr, int64_t m, int64_t nnz, int P, int mode, int64_t* out)
 {
 	if (!out || P < 1 || m < 0 || nnz < 0) return SPMM_B200_EINVAL;
-	if (mode < SPMM_B200_PART_ROWS || mode > SPMM_B200_PART_MERGE) return SPMM_B200_EINVAL;
+	if (mode < SPMM_B200_PART_ROWS || mode > SPMM_B200_PART_NNZ_CARRY) return SPMM_B200_EINVAL;
 	if (mode != SPMM_B200_PART_ROWS && !row_ptr) return SPMM_B200_EINVAL;
 	if (mode == SPMM_B200_PART_NNZ) {
 		for (int64_t t = 0; t <= P; t++) out[t] = nnz_split_start(row_ptr, m, nnz, P, t);
 	} else if (mode == SPMM_B200_PART_ROWS) {
 		for (int64_t t = 0; t < P; t++) equal_split(0, m, P, t, &out[2 * t], &out[2 * t + 1]);
-	} else {
+	} else if (mode == SPMM_B200_PART_MERGE) {
 		const int64_t L = m + nnz, items = (L + P - 1) / P;
 		for (int64_t t = 0; t <= P; t++) {
 			int64_t d = items * t; if (d > L) d = L;
 			merge_path_search(d, row_ptr + 1, m, nnz, &out[2 * t], &out[2 * t + 1]);
 		}
+	} else {
+		for (int64_t t = 0; t < P; t++) nnz_carry_split(row_ptr, m, nnz, P, t, out + 4 * t);
 	}
 	return SPMM_B200_OK;
 }
@@ -1152,7 +1269,8 @@ extern "C" int spmm_b200_coo_to_csr(const int32_t* R, const int32_t* C, const do
 	if (nnz > 0 && (!R || !C || !col_idx)) return SPMM_B200_EINVAL;
 	if ((V == nullptr) != (values == nullptr) && nnz > 0) return SPMM_B200_EINVAL;
 	if (m >= INT32_MAX || n >= INT32_MAX || nnz >= INT32_MAX) return SPMM_B200_ERANGE;
-	int rc = check_device(device, nullptr);
+	int sms = 0;
+	int rc = check_device(device, &sms);
 	if (rc) return rc;
 	const int64_t nrows = transpose ? n : m;                 // csr_gen.c:170-173
 	const int32_t* h_rows = transpose ? C : R;
@@ -1181,7 +1299,7 @@ extern "C" int spmm_b200_coo_to_csr(const int32_t* R, const int32_t* C, const do
 	}
 	CU_TRY(cudaMemsetAsync(d_ptr.p, 0, ((size_t) nrows + 1) * 4, s));
 	CU_TRY(cudaMemsetAsync(d_nlong.p, 0, 4, s));
-	const unsigned nb = (unsigned) std::min<int64_t>(148 * 16, (nnz + 255) / 256);
+	const unsigned nb = (unsigned) std::min<int64_t>((int64_t) sms * 16, (nnz + 255) / 256);
 	if (nnz > 0) coo_histogram_kernel<<<nb, 256, 0, s>>>(d_rows.as<int32_t>(), nnz, d_ptr.as<int32_t>());
 	exclusive_scan_i32(d_ptr.as<int32_t>(), nrows + 1, d_tmp.as<int32_t>(), s);
 	CU_TRY(cudaMemcpyAsync(d_cursor.p, d_ptr.p, ((size_t) nrows + 1) * 4, cudaMemcpyDeviceToDevice, s));
@@ -1330,6 +1448,11 @@ extern "C" int spmm_b200_device_count(void)
 	if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
 	return n;
 }
+
+// ------------------------------------------------------------------------------------------
+// single-process multi-GPU entry points
+// ------------------------------------------------------------------------------------------
+#include "spmm_b200_multi.inl"
 
 // ------------------------------------------------------------------------------------------
 // fp32 entry points (the reference's "_f" builds)

@@ -1,0 +1,362 @@
+// spmm_b200_multi.inl -- single-process multi-GPU entry points of the C ABI (include/spmm_b200.h, "_multi").
+//
+// the reference's harness is ONE C process (spmv_bench.cpp), so the drop-in reaches 2, 4 or 8 GPUs from
+// one host thread: one shard handle per device (rows cut by the bit-exact loop_partitioner_balance_prefix_sums,
+// partition.cuh), all work enqueued asynchronously on per-device streams, one wait at the end.  The replication of B
+// is the only exchange on the path.  It is not a library broadcast: every device uploads 1/N of a column slice of x
+// over ITS PCIe link into its own staging buffer, and then one kernel per device (gather_transpose_b_kernel) reads all
+// N parts straight out of the peers' memory over NVLink / NVSwitch (peer loads) while writing the row-major operand
+// the SpMM kernels gather from -- all-gather and layout transpose in one pass, no intermediate copy.
+// Included at the end of spmm_b200.cu (one translation unit).
+
+static constexpr int MULTI_MAX = 16;
+
+struct PeerParts {
+	const double* base[MULTI_MAX];   // base[r]: device r's staging copy of the slice (only part r of it is valid there)
+	int64_t per;                     // part length in doubles: part r = [r*per, min((r+1)*per, count))
+};
+
+// B[j*k + n] = x[n*c + j] for one column slice (k columns), where element i = n*c + j of the slice is read from the
+// device that uploaded it: parts.base[i / per][i].  Reads are coalesced along j, writes along n (32x33 tile).
+__global__ void gather_transpose_b_kernel(PeerParts parts, double* __restrict__ B, int64_t c, int k)
+{
+	__shared__ double tile[32][33];
+	const int64_t j0 = (int64_t) blockIdx.x * 32;
+	const int n0 = blockIdx.y * 32;
+	for (int dy = threadIdx.y; dy < 32; dy += blockDim.y) {
+		const int n = n0 + dy;
+		const int64_t j = j0 + threadIdx.x;
+		if (n < k && j < c) {
+			const int64_t i = (int64_t) n * c + j;
+			tile[dy][threadIdx.x] = parts.base[i / parts.per][i];
+		}
+	}
+	__syncthreads();
+	for (int dy = threadIdx.y; dy < 32; dy += blockDim.y) {
+		const int64_t j = j0 + dy;
+		const int n = n0 + threadIdx.x;
+		if (n < k && j < c) B[j * k + n] = tile[threadIdx.x][dy];
+	}
+}
+
+struct spmm_b200_multi {
+	int n = 0;
+	int k = 0, b_layout = SPMM_B200_B_COLMAJOR;
+	int64_t m = 0, c = 0, nnz = 0;
+	bool peer = false;                           // every pair of devices can read each other's memory
+	std::vector<spmm_b200*> sh;                  // shard handle per device
+	std::vector<int> dev;
+	std::vector<int64_t> bounds;                 // n + 1 row starts
+	std::vector<std::vector<cudaEvent_t>> ev_part;   // [device][slice]: that device's part of the slice is uploaded
+	std::vector<void*> pinned;
+	int resident_k = 0;
+};
+
+extern "C" void spmm_b200_destroy_multi(spmm_b200_multi_t* mh)
+{
+	if (!mh) return;
+	for (int g = 0; g < (int) mh->sh.size(); g++) {
+		if (g < (int) mh->ev_part.size()) {
+			cudaSetDevice(mh->dev[g]);
+			for (cudaEvent_t e : mh->ev_part[g]) cudaEventDestroy(e);
+		}
+		spmm_b200_destroy(mh->sh[g]);
+	}
+	for (void* p : mh->pinned) cudaHostUnregister(p);
+	delete mh;
+}
+
+extern "C" int spmm_b200_create_multi(spmm_b200_multi_t** out, const int32_t* row_ptr, const int32_t* col_ind, const double* values,
+                                      int64_t m, int64_t c, int64_t nnz, int k, int ngpus, const int* devices, int variant, int b_layout)
+{
+	if (!out) return SPMM_B200_EINVAL;
+	*out = nullptr;
+	int rc = check_sizes(row_ptr, col_ind, values, m, c, nnz, k);
+	if (rc) return rc;
+	if (ngpus < 1 || ngpus > MULTI_MAX) return SPMM_B200_EINVAL;
+	if (variant < SPMM_B200_ROWSPLIT || variant > SPMM_B200_BCSR_FMA) return SPMM_B200_EINVAL;
+	if (b_layout != SPMM_B200_B_COLMAJOR && b_layout != SPMM_B200_B_ROWMAJOR) return SPMM_B200_EINVAL;
+	int have = 0;
+	if (cudaGetDeviceCount(&have) != cudaSuccess || have <= 0) { cudaGetLastError(); return SPMM_B200_ENODEV; }
+	spmm_b200_multi* mh = new (std::nothrow) spmm_b200_multi();
+	if (!mh) return SPMM_B200_ENOMEM;
+	mh->n = ngpus; mh->k = k; mh->b_layout = b_layout; mh->m = m; mh->c = c; mh->nnz = nnz;
+	for (int g = 0; g < ngpus; g++) {
+		const int d = devices ? devices[g] : g;
+		if (d < 0 || d >= have || std::find(mh->dev.begin(), mh->dev.end(), d) != mh->dev.end()) { delete mh; return SPMM_B200_EINVAL; }
+		mh->dev.push_back(d);
+	}
+	// shard boundaries: the reference's nnz-balanced split with P = ngpus (same integers as spmm_b200_partition)
+	mh->bounds.resize(ngpus + 1);
+	rc = spmm_b200_partition_host(row_ptr, m, nnz, ngpus, SPMM_B200_PART_NNZ, mh->bounds.data());
+	if (rc) { delete mh; return rc; }
+	for (int g = 0; g < ngpus; g++) mh->bounds[g + 1] = std::max(mh->bounds[g + 1], mh->bounds[g]);
+	// peer access: every device reads every other device's staging buffer in the gather kernel
+	mh->peer = ngpus > 1;
+	for (int g = 0; g < ngpus && mh->peer; g++)
+		for (int p = 0; p < ngpus && mh->peer; p++) {
+			if (p == g) continue;
+			int can = 0;
+			if (cudaDeviceCanAccessPeer(&can, mh->dev[g], mh->dev[p]) != cudaSuccess || !can) { cudaGetLastError(); mh->peer = false; }
+		}
+	for (int g = 0; g < ngpus && mh->peer; g++) {
+		if (cudaSetDevice(mh->dev[g]) != cudaSuccess) { cudaGetLastError(); mh->peer = false; break; }
+		for (int p = 0; p < ngpus; p++) {
+			if (p == g) continue;
+			cudaError_t e = cudaDeviceEnablePeerAccess(mh->dev[p], 0);
+			if (e == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError();
+			else if (e != cudaSuccess) { cudaGetLastError(); mh->peer = false; break; }
+		}
+	}
+	mh->sh.assign(ngpus, nullptr);
+	mh->ev_part.resize(ngpus);
+	*out = mh;
+	for (int g = 0; g < ngpus; g++) {
+		int sms = 0;
+		rc = check_device(mh->dev[g], &sms);
+		if (rc) break;
+		const int64_t r0 = mh->bounds[g], r1 = mh->bounds[g + 1];
+		const int32_t base = row_ptr[r0];
+		rc = create_from_slice(&mh->sh[g], row_ptr + r0, col_ind, values, r1 - r0, c, (int64_t) row_ptr[r1] - base, base, k,
+		                       mh->dev[g], variant, b_layout, sms, r0, m);
+		if (rc) break;
+		mh->sh[g]->rank = g; mh->sh[g]->nranks = ngpus;
+	}
+	if (rc) { spmm_b200_destroy_multi(mh); *out = nullptr; }
+	return rc;
+}
+
+extern "C" int spmm_b200_register_host_multi(spmm_b200_multi_t* mh, const void* p, size_t bytes)
+{
+	if (!mh || !p || bytes == 0) return SPMM_B200_EINVAL;
+	if (std::find(mh->pinned.begin(), mh->pinned.end(), (void*) p) != mh->pinned.end()) return SPMM_B200_OK;
+	cudaPointerAttributes at;
+	if (cudaPointerGetAttributes(&at, p) == cudaSuccess && at.type != cudaMemoryTypeUnregistered) return SPMM_B200_OK;
+	cudaGetLastError();
+	CU_TRY(cudaSetDevice(mh->dev[0]));
+	CU_TRY(cudaHostRegister((void*) p, bytes, cudaHostRegisterPortable | cudaHostRegisterMapped));
+	mh->pinned.push_back((void*) p);
+	return SPMM_B200_OK;
+}
+
+// Enqueue upload + exchange + transpose of column slice s (ks columns, of S) on every device's upload stream.
+static int multi_replicate_slice(spmm_b200_multi* mh, const double* x_host, int k, int ks, int s)
+{
+	const int N = mh->n;
+	const size_t bslice = (size_t) mh->c * ks;
+	const bool split = mh->peer && mh->b_layout == SPMM_B200_B_COLMAJOR && N > 1 && bslice >= (size_t) N;
+	const size_t per = split ? (bslice + N - 1) / N : bslice;
+	for (int g = 0; g < N; g++) {
+		spmm_b200* h = mh->sh[g];
+		CU_TRY(cudaSetDevice(h->device));
+		if (mh->b_layout == SPMM_B200_B_COLMAJOR) {
+			const size_t lo = split ? std::min(bslice, per * (size_t) g) : 0, hi = split ? std::min(bslice, lo + per) : bslice;
+			if (hi > lo)
+				CU_TRY(cudaMemcpyAsync(h->d_x + s * bslice + lo, x_host + s * bslice + lo, (hi - lo) * sizeof(double), cudaMemcpyHostToDevice, h->s_up));
+		} else {
+			CU_TRY(cudaMemcpy2DAsync(h->d_B + s * bslice, sizeof(double) * ks, x_host + (size_t) s * ks, sizeof(double) * k, sizeof(double) * ks,
+			                         (size_t) mh->c, cudaMemcpyHostToDevice, h->s_up));
+		}
+		CU_TRY(cudaEventRecord(mh->ev_part[g][s], h->s_up));
+	}
+	for (int g = 0; g < N; g++) {
+		spmm_b200* h = mh->sh[g];
+		CU_TRY(cudaSetDevice(h->device));
+		if (mh->b_layout == SPMM_B200_B_COLMAJOR && mh->c > 0) {
+			PeerParts parts;
+			parts.per = (int64_t) std::max<size_t>(per, 1);
+			for (int p = 0; p < MULTI_MAX; p++) parts.base[p] = mh->sh[split ? std::min(p, N - 1) : g]->d_x + s * bslice;
+			if (split)
+				for (int p = 0; p < N; p++)
+					if (p != g) CU_TRY(cudaStreamWaitEvent(h->s_up, mh->ev_part[p][s], 0));
+			dim3 grid((unsigned) ((mh->c + 31) / 32), (unsigned) ((ks + 31) / 32)), block(32, 8);
+			gather_transpose_b_kernel<<<grid, block, 0, h->s_up>>>(parts, h->d_B + s * bslice, mh->c, ks);
+			h->launches++;
+			CU_TRY(cudaGetLastError());
+		}
+		CU_TRY(cudaEventRecord(h->ev_slice[3 * s], h->s_up));
+	}
+	return SPMM_B200_OK;
+}
+
+static int multi_prepare(spmm_b200_multi* mh, int k, int S)
+{
+	for (int g = 0; g < mh->n; g++) {
+		spmm_b200* h = mh->sh[g];
+		CU_TRY(cudaSetDevice(h->device));
+		const size_t nb = (size_t) h->c * k;
+		int rc = ensure(&h->d_B, &h->cap_B, nb);
+		if (rc) return rc;
+		if (mh->b_layout == SPMM_B200_B_COLMAJOR) {
+			rc = ensure(&h->d_x, &h->cap_x, nb);
+			if (rc) return rc;
+		}
+		rc = ensure(&h->d_C, &h->cap_C, (size_t) h->m * k);
+		if (rc) return rc;
+		if (!h->s_up) CU_TRY(cudaStreamCreateWithFlags(&h->s_up, cudaStreamNonBlocking));
+		if (!h->s_down) CU_TRY(cudaStreamCreateWithFlags(&h->s_down, cudaStreamNonBlocking));
+		while (h->ev_slice.size() < (size_t) 3 * S) {
+			cudaEvent_t e;
+			CU_TRY(cudaEventCreate(&e));
+			h->ev_slice.push_back(e);
+		}
+		while (mh->ev_part[g].size() < (size_t) S) {
+			cudaEvent_t e;
+			CU_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+			mh->ev_part[g].push_back(e);
+		}
+		h->resident_k = 0;
+		h->tl_slices = 0;
+	}
+	mh->resident_k = 0;
+	return SPMM_B200_OK;
+}
+
+// A staging buffer (d_x) may only be refilled once every peer has finished reading the previous contents: the
+// run ends with all streams of all devices synchronised, so consecutive calls are ordered by the host.
+static int multi_sync(spmm_b200_multi* mh)
+{
+	for (int g = 0; g < mh->n; g++) {
+		spmm_b200* h = mh->sh[g];
+		CU_TRY(cudaSetDevice(h->device));
+		if (h->s_up) CU_TRY(cudaStreamSynchronize(h->s_up));
+		CU_TRY(cudaStreamSynchronize(h->stream));
+		if (h->s_down) CU_TRY(cudaStreamSynchronize(h->s_down));
+	}
+	return SPMM_B200_OK;
+}
+
+extern "C" int spmm_b200_run_multi(spmm_b200_multi_t* mh, const double* x_host, double* y_host, int k, int copy_back)
+{
+	if (!mh || !x_host || k < 1 || (copy_back && !y_host)) return SPMM_B200_EINVAL;
+	int ks = slice_width(mh->sh[0], k);
+	if (ks <= 0) ks = k;
+	const int S = k / ks;
+	int rc = multi_prepare(mh, k, S);
+	if (rc) return rc;
+	for (int s = 0; s < S; s++) {
+		rc = multi_replicate_slice(mh, x_host, k, ks, s);
+		if (rc) return rc;
+	}
+	const size_t bslice = (size_t) mh->c * ks;
+	// y_host mapped for the devices (page-locked + portable): the sliced row-split kernels store C straight into it
+	double* y_map = nullptr;
+	if (copy_back && S > 1 && mh->sh[0]->opt.direct_store) {
+		cudaPointerAttributes at;
+		if (cudaPointerGetAttributes(&at, y_host) == cudaSuccess && at.type == cudaMemoryTypeHost && at.devicePointer)
+			y_map = (double*) at.devicePointer;
+		else
+			cudaGetLastError();
+		if (((uintptr_t) y_map & 15) != 0 || k % 2) y_map = nullptr;
+	}
+	for (int s = 0; s < S; s++) {
+		for (int g = 0; g < mh->n; g++) {
+			spmm_b200* h = mh->sh[g];
+			CU_TRY(cudaSetDevice(h->device));
+			CU_TRY(cudaStreamWaitEvent(h->stream, h->ev_slice[3 * s], 0));
+			if (h->m == 0) continue;
+			const size_t cslice = (size_t) h->m * ks;
+			double* y_rows = copy_back ? y_host + (size_t) h->first_row * k : nullptr;
+			const bool direct = y_map && h->variant == SPMM_B200_ROWSPLIT && (ks == 8 || ks == 16 || ks == 32 || ks == 64);
+			if (direct) {
+				CU_TRY(cudaEventRecord(h->ev_slice[3 * s + 1], h->stream));
+				launch_rowsplit_width(h, h->d_B + s * bslice, y_map + (size_t) h->first_row * k + (size_t) s * ks, ks, h->stream, ks, k);
+				CU_TRY(cudaGetLastError());
+				h->launches += 1;
+				CU_TRY(cudaEventRecord(h->ev_slice[3 * s + 2], h->stream));
+				h->c_slices = 0;
+				continue;
+			}
+			rc = run_between(h, h->d_B + s * bslice, h->d_C + s * cslice, ks, h->stream, h->ev_slice[3 * s + 1], h->ev_slice[3 * s + 2]);
+			if (rc) return rc;
+			h->c_slices = S;
+			if (y_rows) {
+				CU_TRY(cudaStreamWaitEvent(h->s_down, h->ev_slice[3 * s + 2], 0));
+				if (S == 1)
+					CU_TRY(cudaMemcpyAsync(y_rows, h->d_C, sizeof(double) * h->m * k, cudaMemcpyDeviceToHost, h->s_down));
+				else
+					CU_TRY(cudaMemcpy2DAsync(y_rows + (size_t) s * ks, sizeof(double) * k, h->d_C + s * cslice, sizeof(double) * ks,
+					                         sizeof(double) * ks, (size_t) h->m, cudaMemcpyDeviceToHost, h->s_down));
+			}
+		}
+	}
+	for (int g = 0; g < mh->n; g++) { mh->sh[g]->timed = true; mh->sh[g]->timed_slices = mh->sh[g]->m > 0 ? S : 0; }
+	rc = multi_sync(mh);
+	if (rc) return rc;
+	if (S == 1) {
+		for (int g = 0; g < mh->n; g++) mh->sh[g]->resident_k = k;
+		mh->resident_k = k;
+	}
+	return SPMM_B200_OK;
+}
+
+extern "C" int spmm_b200_set_b_multi(spmm_b200_multi_t* mh, const double* x_host, int k)
+{
+	if (!mh || !x_host || k < 1) return SPMM_B200_EINVAL;
+	int rc = multi_prepare(mh, k, 1);
+	if (rc) return rc;
+	rc = multi_replicate_slice(mh, x_host, k, k, 0);
+	if (rc) return rc;
+	rc = multi_sync(mh);
+	if (rc) return rc;
+	for (int g = 0; g < mh->n; g++) mh->sh[g]->resident_k = k;
+	mh->resident_k = k;
+	return SPMM_B200_OK;
+}
+
+extern "C" int spmm_b200_run_resident_multi(spmm_b200_multi_t* mh, int k)
+{
+	if (!mh || k < 1 || mh->resident_k != k) return SPMM_B200_EINVAL;
+	for (int g = 0; g < mh->n; g++) {
+		spmm_b200* h = mh->sh[g];
+		h->c_slices = 1;
+		int rc = spmm_b200_run_device(h, h->d_B, h->d_C, k, h->stream);     // asynchronous: all devices run side by side
+		if (rc) return rc;
+	}
+	for (int g = 0; g < mh->n; g++) {
+		CU_TRY(cudaSetDevice(mh->sh[g]->device));
+		CU_TRY(cudaStreamSynchronize(mh->sh[g]->stream));
+	}
+	return SPMM_B200_OK;
+}
+
+extern "C" int spmm_b200_fetch_c_multi(spmm_b200_multi_t* mh, double* y_host, int k)
+{
+	if (!mh || !y_host || k < 1) return SPMM_B200_EINVAL;
+	for (int g = 0; g < mh->n; g++) {
+		spmm_b200* h = mh->sh[g];
+		if (h->cap_C < (size_t) h->m * k || h->c_slices == 0 || (h->c_slices > 1 && k % h->c_slices)) return SPMM_B200_EINVAL;
+		CU_TRY(cudaSetDevice(h->device));
+		int rc = download_c(h, y_host + (size_t) h->first_row * k, k, h->stream);
+		if (rc) return rc;
+	}
+	for (int g = 0; g < mh->n; g++) {
+		CU_TRY(cudaSetDevice(mh->sh[g]->device));
+		CU_TRY(cudaStreamSynchronize(mh->sh[g]->stream));
+	}
+	return SPMM_B200_OK;
+}
+
+extern "C" int spmm_b200_multi_ngpus(const spmm_b200_multi_t* mh) { return mh ? mh->n : SPMM_B200_EINVAL; }
+extern "C" int spmm_b200_multi_peer_access(const spmm_b200_multi_t* mh) { return mh ? (mh->peer ? 1 : 0) : SPMM_B200_EINVAL; }
+extern "C" spmm_b200_t* spmm_b200_multi_shard(spmm_b200_multi_t* mh, int g) { return (mh && g >= 0 && g < mh->n) ? mh->sh[g] : nullptr; }
+extern "C" int64_t spmm_b200_multi_first_row(const spmm_b200_multi_t* mh, int g) { return (mh && g >= 0 && g <= mh->n) ? mh->bounds[g] : -1; }
+
+extern "C" double spmm_b200_multi_last_kernel_ms(const spmm_b200_multi_t* mh)
+{
+	if (!mh) return -1.0;
+	double worst = -1.0;
+	for (int g = 0; g < mh->n; g++) {
+		cudaSetDevice(mh->sh[g]->device);
+		worst = std::max(worst, spmm_b200_last_kernel_ms(mh->sh[g]));
+	}
+	return worst;
+}
+
+extern "C" int64_t spmm_b200_multi_launch_count(const spmm_b200_multi_t* mh)
+{
+	if (!mh) return -1;
+	int64_t n = 0;
+	for (int g = 0; g < mh->n; g++) n += mh->sh[g]->launches;
+	return n;
+}

@@ -19,6 +19,7 @@ struct spmm_b200_pipeline {
 		spmm_b200* h = nullptr;
 		const int32_t* ia = nullptr; const int32_t* ja = nullptr; const double* a = nullptr;
 		int64_t m = 0, k = 0, nnz = 0;
+		uint64_t sig = 0;                    // pipe_weight_signature of the arrays that were uploaded
 		double* d_out = nullptr;             // K, Q or V: m x n row-major
 		bool have = false;
 	} w[3];
@@ -35,7 +36,42 @@ struct spmm_b200_pipeline {
 	cudaEvent_t ev_fork = nullptr, ev_done[3] = {nullptr, nullptr, nullptr};
 	bool timed = false;
 	int64_t own_launches = 0;
+	// knobs, read from the environment once at creation (spmm_b200_pipeline_set_option changes them afterwards)
+	struct Opt { int sddmm_group = 1, ticket_rev = 1, sddmm_tune = 0, sddmm_staged = 1, fork = 1, fused = 1; } opt;
 };
+
+struct PipeOptionName { const char* name; int spmm_b200_pipeline::Opt::*field; };
+static const PipeOptionName PIPE_OPTION_TABLE[] = {
+	{"SDDMM_GROUP", &spmm_b200_pipeline::Opt::sddmm_group}, {"TICKET_REV", &spmm_b200_pipeline::Opt::ticket_rev},
+	{"SDDMM_TUNE", &spmm_b200_pipeline::Opt::sddmm_tune}, {"SDDMM_STAGED", &spmm_b200_pipeline::Opt::sddmm_staged},
+	{"PIPELINE_FORK", &spmm_b200_pipeline::Opt::fork}, {"ATTENTION_FUSED", &spmm_b200_pipeline::Opt::fused},
+};
+
+extern "C" int spmm_b200_pipeline_set_option(spmm_b200_pipeline_t* p, const char* name, int value)
+{
+	if (!p || !name) return SPMM_B200_EINVAL;
+	if (!strncmp(name, "SPMM_B200_", 10)) name += 10;
+	for (const PipeOptionName& e : PIPE_OPTION_TABLE)
+		if (!strcmp(name, e.name)) { p->opt.*(e.field) = value; return SPMM_B200_OK; }
+	return SPMM_B200_EINVAL;
+}
+
+// Cheap fingerprint of a host CSR weight (sizes + up to 1024 strided samples of the arrays): a weight that was refilled
+// in place behind the same pointers is then uploaded again instead of being taken for the resident copy.
+static uint64_t pipe_weight_signature(const int32_t* ia, const int32_t* ja, const double* a, int64_t m, int64_t nnz)
+{
+	uint64_t h = 1469598103934665603ull;
+	auto mix = [&h](uint64_t v) { h = (h ^ v) * 1099511628211ull; };
+	mix((uint64_t) m); mix((uint64_t) nnz);
+	const int64_t sm = std::max<int64_t>(1, (m + 1) / 1024), sn = std::max<int64_t>(1, nnz / 1024);
+	for (int64_t i = 0; i <= m; i += sm) mix((uint64_t) (uint32_t) ia[i]);
+	for (int64_t j = 0; j < nnz; j += sn) {
+		uint64_t bits;
+		memcpy(&bits, a + j, sizeof(bits));
+		mix(bits); mix((uint64_t) (uint32_t) ja[j]);
+	}
+	return h;
+}
 
 static constexpr int PIPE_PARTS = 1184;      // 148 SMs x 8 blocks: partials of the global softmax
 
@@ -118,6 +154,13 @@ extern "C" int spmm_b200_pipeline_create(spmm_b200_pipeline_t** out,
 	PIPE_TRY(cudaMalloc(&p->d_final, sizeof(double) * std::max<int64_t>(m * n, 1)));
 	PIPE_TRY(cudaMalloc(&p->d_part, sizeof(double) * (PIPE_PARTS + 2)));
 	PIPE_TRY(cudaMalloc(&p->d_ticket, sizeof(int)));
+	{
+		char name[64];
+		for (const PipeOptionName& e : PIPE_OPTION_TABLE) {
+			snprintf(name, sizeof(name), "SPMM_B200_%s", e.name);
+			p->opt.*(e.field) = env_int(name, p->opt.*(e.field));
+		}
+	}
 #undef PIPE_TRY
 	*out = p;
 	return SPMM_B200_OK;
@@ -129,14 +172,26 @@ extern "C" int spmm_b200_pipeline_set_weight(spmm_b200_pipeline_t* p, char type,
 	const int idx = pipe_index(type);
 	if (!p || idx < 0 || !ia || m != p->m || k < 0 || nnz < 0 || (nnz > 0 && (!ja || !a))) return SPMM_B200_EINVAL;
 	auto& w = p->w[idx];
-	if (w.h && w.ia == ia && w.ja == ja && w.a == a && w.m == m && w.k == k && w.nnz == nnz) return SPMM_B200_OK;
+	const uint64_t sig = pipe_weight_signature(ia, ja, a, m, nnz);
+	if (w.h && w.ia == ia && w.ja == ja && w.a == a && w.m == m && w.k == k && w.nnz == nnz && w.sig == sig) return SPMM_B200_OK;
 	CU_TRY(cudaSetDevice(p->device));
 	if (w.h) { p->own_launches += w.h->launches; spmm_b200_destroy(w.h); w.h = nullptr; }
 	w.have = false;
 	int rc = pipe_make_handle(&w.h, ia, ja, a, m, k, nnz, p->n, p->device, false);
 	if (rc) return rc;
 	if (!w.d_out) CU_TRY(cudaMalloc(&w.d_out, sizeof(double) * std::max<int64_t>(m * p->n, 1)));
-	w.ia = ia; w.ja = ja; w.a = a; w.m = m; w.k = k; w.nnz = nnz;
+	w.ia = ia; w.ja = ja; w.a = a; w.m = m; w.k = k; w.nnz = nnz; w.sig = sig;
+	return SPMM_B200_OK;
+}
+
+// Forget what is resident for `type` ('K', 'Q', 'V'; '*': all three): the next spmm / set_weight with the same
+// host pointers uploads the arrays again.  For callers that refill a weight in place.
+extern "C" int spmm_b200_pipeline_invalidate(spmm_b200_pipeline_t* p, char type)
+{
+	if (!p) return SPMM_B200_EINVAL;
+	if (type != '*' && pipe_index(type) < 0) return SPMM_B200_EINVAL;
+	for (int i = 0; i < 3; i++)
+		if (type == '*' || pipe_index(type) == i) { p->w[i].ia = nullptr; p->w[i].ja = nullptr; p->w[i].a = nullptr; p->w[i].sig = 0; }
 	return SPMM_B200_OK;
 }
 
@@ -152,16 +207,16 @@ static int pipe_sddmm_launch(spmm_b200_pipeline* p, int mode)
 		else {
 			// attention mode: the group kernel for the widths it is instantiated for (tree-ordered sum), else -- and
 			// always in ORDERED mode -- a kernel that keeps the CPU loop's left-to-right order
-			const bool fast = mode == SPMM_B200_SDDMM_ATTENTION && env_int("SPMM_B200_SDDMM_GROUP", 1);
+			const bool fast = mode == SPMM_B200_SDDMM_ATTENTION && p->opt.sddmm_group;
 			const int gw = (int) std::min<int64_t>((p->m + THREADS / 32 - 1) / (THREADS / 32), (int64_t) p->mask->sm_count * 64);
 			// one resident wave of persistent CTAs (MINB per SM); rows are handed out by the ticket counter
 #define SDDMM_GROUP(G, V, U, MINB) do { \
 				CU_TRY(cudaMemsetAsync(p->d_ticket, 0, sizeof(int), p->stream)); \
 				sb200::sddmm_attention_group_kernel<G, V, U, THREADS, MINB><<<(int) std::min<int64_t>(gw, (int64_t) p->mask->sm_count * MINB), THREADS, 0, p->stream>>>( \
-				p->mask->d_ia, p->mask->d_ja, p->d_mask_a, p->w[1].d_out, p->w[0].d_out, p->mask->d_a, p->m, p->d_ticket, env_int("SPMM_B200_TICKET_REV", 1)); } while (0)
+				p->mask->d_ia, p->mask->d_ja, p->d_mask_a, p->w[1].d_out, p->w[0].d_out, p->mask->d_a, p->m, p->d_ticket, p->opt.ticket_rev); } while (0)
 			// shapes measured on m = 8192 / 16384 (profiles/r1_pipeline_probe.md): U = 2 rows in flight; with the
 			// persistent ticketed grid n = 64 runs best at 126 registers / 2 CTAs per SM, n = 32 at 64 registers / 4
-			const int tune = env_int("SPMM_B200_SDDMM_TUNE", 0);     // experiment knob for n = 64: U*10 + CTAs per SM
+			const int tune = p->opt.sddmm_tune;     // experiment knob for n = 64: U*10 + CTAs per SM
 			if (fast && p->n == 16) SDDMM_GROUP(4, 4, 2, 4);
 			else if (fast && p->n == 32) SDDMM_GROUP(8, 4, 2, 4);
 			else if (fast && p->n == 64 && tune == 42) SDDMM_GROUP(16, 4, 4, 2);
@@ -169,7 +224,7 @@ static int pipe_sddmm_launch(spmm_b200_pipeline* p, int mode)
 			else if (fast && p->n == 64) SDDMM_GROUP(16, 4, 2, 2);
 			else if (fast && p->n == 128) SDDMM_GROUP(16, 8, 2, 2);
 #undef SDDMM_GROUP
-			else if (p->n % sb200::SDDMM_CH == 0 && p->n <= 1024 && env_int("SPMM_B200_SDDMM_STAGED", 1)) {
+			else if (p->n % sb200::SDDMM_CH == 0 && p->n <= 1024 && p->opt.sddmm_staged) {
 				// K rows staged through shared memory (sddmm.cuh): 4 warps per CTA, 32 x 34 + n doubles per warp
 				constexpr int T = 128;
 				const size_t smem = sizeof(double) * (T / 32) * (32 * sb200::SDDMM_LD + p->n);
@@ -344,7 +399,7 @@ extern "C" int spmm_b200_pipeline_attention(spmm_b200_pipeline_t* p, const doubl
 	if (k > 0) CU_TRY(cudaMemcpyAsync(p->d_x, x_host, sizeof(double) * k * p->n, cudaMemcpyHostToDevice, p->stream));
 	CU_TRY(cudaEventRecord(p->ev0, p->stream));
 	// K | Q | V on three side streams; the SDDMM waits for K and Q only, the final product for V
-	const bool fork = p->m > 0 && env_int("SPMM_B200_PIPELINE_FORK", 1);
+	const bool fork = p->m > 0 && p->opt.fork;
 	if (fork) CU_TRY(cudaEventRecord(p->ev_fork, p->stream));
 	for (int i = 0; i < 3; i++) {
 		auto& w = p->w[i];
@@ -364,14 +419,14 @@ extern "C" int spmm_b200_pipeline_attention(spmm_b200_pipeline_t* p, const doubl
 	// attention-mode SDDMM + row-wise softmax + final product as ONE kernel (sddmm.cuh: attention_fused_kernel);
 	// y is not materialised on this path (spmm_b200_pipeline_device_ptr(p, 'y') returns NULL afterwards)
 	const bool fused = mode == SPMM_B200_SDDMM_ATTENTION && softmax == 2 && p->m > 0 && p->nnz > 0
-	                   && (p->n == 32 || p->n == 64 || p->n == 128) && env_int("SPMM_B200_ATTENTION_FUSED", 1);
+	                   && (p->n == 32 || p->n == 64 || p->n == 128) && p->opt.fused;
 	if (fused) {
 		if (fork) CU_TRY(cudaStreamWaitEvent(p->stream, p->ev_done[2], 0));
 		const int gw = (int) std::min<int64_t>((p->m + THREADS / 32 - 1) / (THREADS / 32), (int64_t) p->mask->sm_count * 64);
 #define ATT_FUSED(G, V, U, MINB) do { \
 			CU_TRY(cudaMemsetAsync(p->d_ticket, 0, sizeof(int), p->stream)); \
 			sb200::attention_fused_kernel<G, V, U, THREADS, MINB><<<(int) std::min<int64_t>(gw, (int64_t) p->mask->sm_count * MINB), THREADS, 0, p->stream>>>( \
-			p->mask->d_ia, p->mask->d_ja, p->d_mask_a, p->w[1].d_out, p->w[0].d_out, p->w[2].d_out, p->d_final, p->m, p->d_ticket, env_int("SPMM_B200_TICKET_REV", 1)); } while (0)
+			p->mask->d_ia, p->mask->d_ja, p->d_mask_a, p->w[1].d_out, p->w[0].d_out, p->w[2].d_out, p->d_final, p->m, p->d_ticket, p->opt.ticket_rev); } while (0)
 		// 128 registers (2 CTAs per SM) measured best: tighter caps spill part[], looser ones lose the second CTA;
 		// n = 128 keeps one K / V row in flight per group to stay inside them (profiles/r1_pipeline_probe.md)
 		if (p->n == 32) ATT_FUSED(8, 4, 2, 2);

@@ -28,6 +28,7 @@
 #include <limits.h>
 #include <cuda_runtime.h>
 #include "spmm_rowsplit.cuh"
+#include "ptx.cuh"
 
 namespace sb200 {
 
@@ -141,29 +142,6 @@ spmm_bcsr_dmma_kernel(const int32_t* __restrict__ brow, const int32_t* __restric
 // completion on an mbarrier, and fragments are read from shared memory without bank conflicts
 // (row stride = 8K + 32 bytes).  A warp owns `brw` consecutive block rows and keeps the ring
 // flowing across their boundaries; no CTA-wide barrier is used.
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t) __cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count)
-{
-	asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes)
-{
-	asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity)
-{
-	uint32_t ok;
-	asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}"
-	             : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
-	return ok != 0;
-}
-__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar)
-{
-	asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-	             ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
-}
-
 template <int K, int WARPS, int STAGES>
 struct BcsrTmaCfg {
 	static constexpr int ROW_BYTES = K * 8;

@@ -12,6 +12,9 @@
 // Environment (all optional):
 //   SPMM_B200_VARIANT  = rowsplit | merge | bcsr | auto (default auto)
 //   SPMM_B200_DEVICE   = CUDA device ordinal (default 0)
+//   SPMM_B200_NGPUS    = N > 1: this ONE process drives devices 0..N-1 (csr_to_format(..., ngpus)):
+//                        rows are cut by the reference's nnz-balanced split, B is replicated inside the library by a
+//                        peer-memory gather kernel over NVLink, C lands row-local in the harness's single y
 //   SPMM_B200_COPYBACK = 1 (default): every spmm() uploads x and downloads y, i.e. the call has
 //                        the reference's host-buffer semantics; 0: x is uploaded on the first
 //                        call only (it never changes, spmv_bench.cpp:895-903) and y is fetched
@@ -47,18 +50,29 @@ struct B200Arrays : Matrix_Format
 	INT_T * ja;
 	ValueType * a;
 	b200_handle_t * handle;
+#if DOUBLE != 0
+	spmm_b200_multi_t * multi;     // SPMM_B200_NGPUS > 1: one shard per device, handle stays NULL
+#endif
 	int copy_back;
 	int x_resident;
 	int registered;
 	ValueType * last_y;
 	INT_T last_k;
+	INT_T last_k_seen;
 	char name[64];
 
 	B200Arrays(long m, long n, long nnz) : Matrix_Format(m, n, nnz),
-		ia(NULL), ja(NULL), a(NULL), handle(NULL), copy_back(1), x_resident(0), registered(0), last_y(NULL), last_k(0) {}
+		ia(NULL), ja(NULL), a(NULL), handle(NULL),
+#if DOUBLE != 0
+		multi(NULL),
+#endif
+		copy_back(1), x_resident(0), registered(0), last_y(NULL), last_k(0), last_k_seen(0) {}
 
 	~B200Arrays()
 	{
+#if DOUBLE != 0
+		spmm_b200_destroy_multi(multi);
+#endif
 		B200_DESTROY(handle);
 		free(a);
 		free(ia);
@@ -84,25 +98,34 @@ struct B200Arrays : Matrix_Format
 	void spmm(ValueType * x, ValueType * y, INT_T k)
 	{
 		int rc;
+		last_k_seen = k;
 		if (!registered)
 		{
 			// the harness's x and y live for the whole run (spmv_bench.cpp:896-907): page-lock them once
 			// (best effort; a refusal only slows the copies down)
-			spmm_b200_register_host(handle, x, sizeof(ValueType) * (size_t) n * k);
-			spmm_b200_register_host(handle, y, sizeof(ValueType) * (size_t) m * k);
+			if (multi)
+			{
+				spmm_b200_register_host_multi(multi, x, sizeof(ValueType) * (size_t) n * k);
+				spmm_b200_register_host_multi(multi, y, sizeof(ValueType) * (size_t) m * k);
+			}
+			else
+			{
+				spmm_b200_register_host(handle, x, sizeof(ValueType) * (size_t) n * k);
+				spmm_b200_register_host(handle, y, sizeof(ValueType) * (size_t) m * k);
+			}
 			registered = 1;
 		}
 		if (copy_back)
-			rc = spmm_b200_run(handle, x, y, k, 1);
+			rc = multi ? spmm_b200_run_multi(multi, x, y, k, 1) : spmm_b200_run(handle, x, y, k, 1);
 		else
 		{
 			if (!x_resident)
 			{
-				rc = spmm_b200_set_b(handle, x, k);
+				rc = multi ? spmm_b200_set_b_multi(multi, x, k) : spmm_b200_set_b(handle, x, k);
 				if (rc) die("set_b", rc);
 				x_resident = 1;
 			}
-			rc = spmm_b200_run_resident(handle, k);
+			rc = multi ? spmm_b200_run_resident_multi(multi, k) : spmm_b200_run_resident(handle, k);
 			last_y = y;
 			last_k = k;
 		}
@@ -113,7 +136,7 @@ struct B200Arrays : Matrix_Format
 	{
 		if (!copy_back && last_y != NULL)
 		{
-			int rc = spmm_b200_fetch_c(handle, last_y, last_k);
+			int rc = multi ? spmm_b200_fetch_c_multi(multi, last_y, last_k) : spmm_b200_fetch_c(handle, last_y, last_k);
 			if (rc) die("fetch_c", rc);
 		}
 	}
@@ -123,6 +146,12 @@ struct B200Arrays : Matrix_Format
 	int statistics_print_data(char * buf, long buf_n)
 	{
 		sync_y();
+		if (multi)      // the columns of spmm_b200_stats_labels: variant, ctas -> devices, max_row, kernel_ms (slowest shard), gflops, roofline
+		{
+			const double ms = spmm_b200_multi_last_kernel_ms(multi);
+			return snprintf(buf, buf_n, ",multi,%d,0,%g,%g,0", spmm_b200_multi_ngpus(multi), ms,
+				ms > 0 ? 2.0 * nnz * last_k_seen / (ms * 1e6) : 0.0);
+		}
 		return spmm_b200_stats(handle, buf, buf_n);
 	}
 #endif
@@ -154,11 +183,24 @@ csr_to_format(INT_T * row_ptr, INT_T * col_ind, ValueType * values, long m, long
 	if (rc) die("csr_to_format", rc);
 	snprintf(f->name, sizeof(f->name), "B200_CSR_ROWSPLIT_F32");
 #else
-	int rc = spmm_b200_create(&f->handle, row_ptr, col_ind, values, m, n, nnz, k, d ? atoi(d) : 0, variant, SPMM_B200_B_COLMAJOR);
-	if (rc) die("csr_to_format", rc);
 	static const char * names[] = {"B200_CSR_ROWSPLIT", "B200_CSR_MERGE", "B200_BCSR_DMMA", "B200_CSR", "B200_BCSR_FMA"};
-	int vr = spmm_b200_variant(f->handle);
-	snprintf(f->name, sizeof(f->name), "%s", names[(vr >= 0 && vr <= 4) ? vr : 3]);
+	const char * ng = getenv("SPMM_B200_NGPUS");
+	const int ngpus = (ng != NULL && *ng) ? atoi(ng) : 1;
+	int rc, vr;
+	if (ngpus > 1)
+	{
+		rc = spmm_b200_create_multi(&f->multi, row_ptr, col_ind, values, m, n, nnz, k, ngpus, NULL, variant, SPMM_B200_B_COLMAJOR);
+		if (rc) die("csr_to_format (multi-GPU)", rc);
+		vr = spmm_b200_variant(spmm_b200_multi_shard(f->multi, 0));
+		snprintf(f->name, sizeof(f->name), "%s_x%d", names[(vr >= 0 && vr <= 4) ? vr : 3], ngpus);
+	}
+	else
+	{
+		rc = spmm_b200_create(&f->handle, row_ptr, col_ind, values, m, n, nnz, k, d ? atoi(d) : 0, variant, SPMM_B200_B_COLMAJOR);
+		if (rc) die("csr_to_format", rc);
+		vr = spmm_b200_variant(f->handle);
+		snprintf(f->name, sizeof(f->name), "%s", names[(vr >= 0 && vr <= 4) ? vr : 3]);
+	}
 #endif
 	f->format_name = f->name;
 	f->mem_footprint = f->csr_mem_footprint;

@@ -8,18 +8,26 @@
 // all k columns at once.  The per-row sum runs left to right like the oracle's.
 //
 // Work mapping
-//   * CTA b owns the contiguous rows [cta_rows[b], cta_rows[b+1]) of the nnz-balanced
-//     split (partition.cuh: cta_rows_nnz_kernel, bit-exact with lib/parallel_util.h:141-165).
-//   * Inside a CTA a group of G lanes owns one row at a time; a lane owns V of the k = G*V
-//     dense columns, so one group-wide load of a B row is k*8 contiguous bytes
-//     (k=32: 16 lanes x 16 B = 256 B = two full 128-B lines).
-//   * (col, val) of a nonzero are read once per group as same-address (broadcast) loads
-//     through L1; UNROLL nonzeros are in flight per group so that each warp keeps
-//     UNROLL * 32/G independent B gathers outstanding (the kernel is bound by L2->SM
-//     gather bandwidth, not by HBM).
+//   * a group of G lanes owns one row at a time; a lane owns V of the k = G*V dense columns, so one
+//     group-wide load of a B row is k*8 contiguous bytes (k=32: G=8, V=4: every 16-byte load
+//     instruction of a group covers exactly one 128-byte line);
+//   * who owns which rows is the scheduling, and there are three:
+//       spmm_rowsplit_kernel         CTA b owns the rows [cta_rows[b], cta_rows[b+1]) of the reference's
+//                                    nnz-balanced split (partition.cuh: cta_rows_nnz_kernel, bit-exact with
+//                                    lib/parallel_util.h:141-165);
+//       spmm_rowsplit_ticket_kernel  one resident wave of persistent warps draws small row chunks from an
+//                                    atomic counter: the GPU sweeps A and C front to back, no tail wave;
+//       spmm_rowsplit_staged_kernel  the ticketed kernel with the (col, val) stream of a ticket brought into a
+//                                    per-warp, double-buffered shared-memory stage by 1-D bulk copies (TMA,
+//                                    SASS UBLKCP + mbarrier) one ticket ahead, so that a warp never waits on
+//                                    the HBM latency of the A stream and spends no registers or shuffles on it;
+//   * spmm_rowsplit_ring_kernel is the experiment VERDICT r1 asked for: gathered B rows land in a per-lane
+//     shared-memory ring through cp.async (LDGSTS) so that the gathers in flight are not paid in registers.
+//   All of them run the same per-row arithmetic: same bits.
 #pragma once
 #include <stdint.h>
 #include <cuda_runtime.h>
+#include "ptx.cuh"
 
 namespace sb200 {
 
@@ -74,30 +82,19 @@ __device__ __forceinline__ double shfl_f64(double v, int src)
 	return __hiloint2double(hi, lo);
 }
 
-// (col, val) staging: the G lanes of a group read G consecutive nonzeros of their row with ONE
-// coalesced load each (the 32/G groups of a warp own consecutive rows, so the warp's loads are
-// contiguous in ja / a) and hand them round with shuffles.  The previous version read every
-// (col, val) as a same-address load per group; ncu (profiles/r1_rowsplit_cfg2.md) showed those
-// broadcast loads were half of the L1 data-pipe wavefronts, the busiest unit of the kernel.
-// The per-row sum still runs strictly left to right.
-template <int G, int V, int UNROLL, int THREADS, int LD = 0>
-__global__ void __launch_bounds__(THREADS)
-spmm_rowsplit_kernel(const int32_t* __restrict__ ia, const int32_t* __restrict__ ja, const double* __restrict__ a,
-                     const double* __restrict__ B, double* __restrict__ C,
-                     const int32_t* __restrict__ cta_rows, int ldb, int ldc)
+// The row loop the static and the ticketed kernel share: rows r0 + gid, r0 + gid + stride, ... below r1.
+// (col, val) staging: the G lanes of a group read G consecutive nonzeros of their row with ONE coalesced load each
+// (the groups of a warp own consecutive rows, so the warp's loads are contiguous in ja / a) and hand them round
+// with shuffles; UNROLL B-row gathers are in flight per group.  All lanes of a warp run the same trip counts (the
+// shuffles need the full warp).  The per-row sum runs strictly left to right.
+template <int G, int V, int UNROLL, int LD>
+__device__ __forceinline__ void row_sweep(const int32_t* __restrict__ ia, const int32_t* __restrict__ ja, const double* __restrict__ a,
+                                          const double* __restrict__ B, double* __restrict__ C,
+                                          int r0, int r1, int stride, int gid, int lig, int ldb, int ldc)
 {
-	// ldb / ldc = row strides of B and C in doubles (G*V for a whole operand; larger when the launch
-	// works on a column slice of a wider B / C, see launch_spmm's L2-aware k slicing)
-	constexpr int NG = THREADS / G;          // row groups per CTA
 	static_assert(G % UNROLL == 0 || UNROLL % G == 0, "UNROLL and G must nest");
 	constexpr int U = UNROLL < G ? UNROLL : G;
-	const int lig = threadIdx.x % G;         // lane in group
-	const int gid = threadIdx.x / G;
-	const int r0 = cta_rows[blockIdx.x];
-	const int r1 = cta_rows[blockIdx.x + 1];
-
-	// all lanes of a warp run the same trip counts (the shuffles need the full warp)
-	for (int base = r0; base < r1; base += NG) {
+	for (int base = r0; base < r1; base += stride) {
 		const int row = base + gid;
 		const bool live = row < r1;
 		int j = 0, je = 0;
@@ -143,27 +140,237 @@ spmm_rowsplit_kernel(const int32_t* __restrict__ ia, const int32_t* __restrict__
 	}
 }
 
-// Experiment (SPMM_B200_TICKET=R): the same row loop on ONE resident wave of persistent warps that draw R-row
-// chunks from a ticket counter instead of owning a fixed nnz-balanced range -- removes the tail of the last wave.
+// ldb / ldc = row strides of B and C in doubles (G*V for a whole operand; larger when the launch
+// works on a column slice of a wider B / C, see launch_spmm's L2-aware k slicing)
+template <int G, int V, int UNROLL, int THREADS, int LD = 0>
+__global__ void __launch_bounds__(THREADS)
+spmm_rowsplit_kernel(const int32_t* __restrict__ ia, const int32_t* __restrict__ ja, const double* __restrict__ a,
+                     const double* __restrict__ B, double* __restrict__ C,
+                     const int32_t* __restrict__ cta_rows, int ldb, int ldc)
+{
+	row_sweep<G, V, UNROLL, LD>(ia, ja, a, B, C, cta_rows[blockIdx.x], cta_rows[blockIdx.x + 1], THREADS / G,
+	                            threadIdx.x / G, threadIdx.x % G, ldb, ldc);
+}
+
+// Row tickets.  `ticket` points at TWO counters: this launch draws from ticket[parity] and zeroes ticket[parity ^ 1]
+// for the next launch of the handle (launches of one handle are stream-ordered), so no memset node sits between
+// back-to-back launches.
 template <int G, int V, int UNROLL, int THREADS, int LD = 0>
 __global__ void __launch_bounds__(THREADS)
 spmm_rowsplit_ticket_kernel(const int32_t* __restrict__ ia, const int32_t* __restrict__ ja, const double* __restrict__ a,
                             const double* __restrict__ B, double* __restrict__ C,
-                            int m, int rows_per_ticket, int* __restrict__ ticket, int ldb, int ldc)
+                            int m, int rows_per_ticket, int* __restrict__ ticket, int parity, int ldb, int ldc)
 {
 	constexpr int NGW = 32 / G;              // row groups per warp
-	constexpr int U = UNROLL < G ? UNROLL : G;
 	const int lane = threadIdx.x & 31;
-	const int lig = lane % G;
-	const int gid = lane / G;
+	if (blockIdx.x == 0 && threadIdx.x == 0) ticket[parity ^ 1] = 0;
+	int* const counter = ticket + parity;
 	for (;;) {
 		int t = 0;
-		if (lane == 0) t = atomicAdd(ticket, 1);
+		if (lane == 0) t = atomicAdd(counter, 1);
 		t = __shfl_sync(0xffffffffu, t, 0);
 		const int64_t r0l = (int64_t) t * rows_per_ticket;
 		if (r0l >= m) break;
-		const int r0 = (int) r0l;
-		const int r1 = (int) min((int64_t) m, r0l + rows_per_ticket);
+		row_sweep<G, V, UNROLL, LD>(ia, ja, a, B, C, (int) r0l, (int) min((int64_t) m, r0l + rows_per_ticket), NGW,
+		                            lane / G, lane % G, ldb, ldc);
+	}
+}
+
+// ------------------------------------------------------------------------------------------------
+// Row tickets with the A stream staged through shared memory by TMA bulk copies.
+//
+// A ticket = R = (32/G)*PASSES consecutive rows; its nonzeros [ia[r0], ia[r0+R]) are one contiguous range of ja and
+// of a.  Each warp runs a four-stage software pipeline over ITS tickets:
+//     A  draw a ticket number (atomicAdd; the value is needed an iteration later)
+//     B  load the R+1 row pointers of the ticket drawn one iteration ago (lane l holds ia[r0+l])
+//     C  lane 0 issues two cp.async.bulk copies (col_ind range, value range; 16-byte aligned windows) of the ticket
+//        whose row pointers arrived, into the warp's free stage, completion on that stage's mbarrier
+//     D  wait for the stage of the ticket issued one iteration ago and run its rows out of shared memory:
+//        every lane of a group reads (col, val) of the same nonzero (a shared-memory broadcast), gathers its V
+//        columns of that B row and multiplies; no shuffles, no warp votes, lane groups advance independently.
+// The latency of the counter, of ia and of the (ja, a) stream (HBM) is therefore never on a warp's critical path;
+// what remains is the L2 gather of B rows.  A ticket whose nonzeros exceed CAP (or an unaligned operand) runs the
+// same loop on global-memory loads.  Same per-row arithmetic and order as row_sweep: same bits.
+// ------------------------------------------------------------------------------------------------
+template <int G, int PASSES, int CAP>
+struct StagedCfg {
+	static constexpr int R = (32 / G) * PASSES;                      // rows per ticket
+	static constexpr int SJ = CAP + 8, SA = CAP + 4;                 // slack: the copy windows are aligned outwards
+	static constexpr int BUF_BYTES = SA * 8 + SJ * 4;
+	static_assert(CAP % 4 == 0 && R + 1 <= 32, "CAP must keep the stages 16-byte aligned; row pointers live in one warp");
+	static constexpr size_t smem(int threads) { return (size_t) (threads / 32) * (2 * BUF_BYTES + 16); }
+};
+
+// sj[jj - offj], sa[jj - offa] hold (col, val) of nonzero jj in the warp's shared-memory stage (offsets = start of the
+// copy windows).  Every lane of a group reads the same word: a broadcast.
+template <int G, int V, int UNROLL, int LD>
+__device__ __forceinline__ void staged_row(const int32_t* __restrict__ sj, const double* __restrict__ sa, const int offj, const int offa,
+                                           int j, const int je, const double* __restrict__ B, int lig, int ldb, double (&acc)[V])
+{
+	constexpr int U = UNROLL;
+	for (; j < je; j += U) {
+		int cc[U];
+		Frag<V> bb[U];
+		#pragma unroll
+		for (int i = 0; i < U; i++)
+			if (j + i < je) cc[i] = sj[j + i - offj];
+		// all U gathers are issued before the first multiply (predicated like row_sweep: with unconditional loads
+		// the compiler re-used the destination registers and kept only two B rows in flight)
+		#pragma unroll
+		for (int i = 0; i < U; i++)
+			if (j + i < je) bb[i] = load_b<G, V, LD>(B, cc[i], lig, ldb);
+		// the values are read while the gathers fly: they are not live across the issue of the loads
+		#pragma unroll
+		for (int i = 0; i < U; i++) {
+			if (j + i < je) {
+				const double vv = sa[j + i - offa];
+				#pragma unroll
+				for (int v = 0; v < V; v++) acc[v] = fma(vv, bb[i].v[v], acc[v]);
+			}
+		}
+	}
+}
+
+template <int G, int V, int UNROLL, int THREADS, int PASSES, int CAP, int LD = 0>
+__global__ void __launch_bounds__(THREADS, 4)      // 64 registers
+spmm_rowsplit_staged_kernel(const int32_t* __restrict__ ia, const int32_t* __restrict__ ja, const double* __restrict__ a,
+                            const double* __restrict__ B, double* __restrict__ C,
+                            int m, int* __restrict__ ticket, int parity, int ldb, int ldc)
+{
+	using Cfg = StagedCfg<G, PASSES, CAP>;
+	constexpr int NW = THREADS / 32, NGW = 32 / G, R = Cfg::R;
+	extern __shared__ __align__(128) unsigned char staged_smem[];
+	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	const int lig = lane % G, gid = lane / G;
+	unsigned char* const wbuf = staged_smem + (size_t) warp * 2 * Cfg::BUF_BYTES;
+	const uint32_t wbuf_u = smem_u32(wbuf);
+	const uint32_t bar_u = smem_u32(staged_smem + (size_t) NW * 2 * Cfg::BUF_BYTES) + warp * 16;
+	if (blockIdx.x == 0 && threadIdx.x == 0) ticket[parity ^ 1] = 0;
+	int* const counter = ticket + parity;
+	if (lane == 0) {
+		mbar_init(bar_u, 1);
+		mbar_init(bar_u + 8, 1);
+		asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+		asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+	}
+	__syncwarp();
+
+	int tA = 0;                                  // lane 0: the ticket drawn this iteration
+	int tB = -1, tC = -1, tD = -1;               // warp-uniform ticket numbers in stages B, C, D (-1: pipeline filling)
+	int iaB = 0, iaC = 0, iaD = 0;               // lane l <= R: ia[min(r0 + l, m)] of that ticket
+	bool stagedC = false, stagedD = false;
+	uint32_t phase = 0;                          // bit b: parity the next wait on stage b uses
+	const int ntickets = (m + R - 1) / R;
+	for (int it = 0;; it++) {
+		tD = tC; iaD = iaC; stagedD = stagedC;
+		tC = tB; iaC = iaB;
+		tB = it >= 1 ? __shfl_sync(0xffffffffu, tA, 0) : -1;
+		// A
+		if (lane == 0) tA = atomicAdd(counter, 1);
+		// B
+		iaB = 0;
+		if (tB >= 0 && tB < ntickets && lane <= R) iaB = __ldg(ia + min(tB * R + lane, m));
+		// C
+		stagedC = false;
+		if (tC >= 0 && tC < ntickets) {
+			const int j0 = __shfl_sync(0xffffffffu, iaC, 0), j1 = __shfl_sync(0xffffffffu, iaC, R);
+			const int n = j1 - j0;
+			if (n > 0 && n <= CAP) {
+				stagedC = true;
+				if (lane == 0) {
+					const int b = it & 1;
+					const int jj = j0 & ~3, ja_n = ((j1 + 3) & ~3) - jj;        // col_ind window, multiples of 4 entries
+					const int jv = j0 & ~1, a_n = ((j1 + 1) & ~1) - jv;         // value window, multiples of 2 entries
+					const uint32_t dst = wbuf_u + b * Cfg::BUF_BYTES;
+					mbar_expect_tx(bar_u + b * 8, (uint32_t) (a_n * 8 + ja_n * 4));
+					bulk_g2s(dst, a + jv, (uint32_t) a_n * 8, bar_u + b * 8);
+					bulk_g2s(dst + Cfg::SA * 8, ja + jj, (uint32_t) ja_n * 4, bar_u + b * 8);
+				}
+			}
+		}
+		// D
+		if (tD < 0) continue;
+		if (tD >= ntickets) break;
+		const int b = (it - 1) & 1;
+		const int r0 = tD * R;
+		const uint32_t bar = bar_u + b * 8;
+		const double* sa = reinterpret_cast<const double*>(wbuf + (size_t) b * Cfg::BUF_BYTES);
+		const int32_t* sj = reinterpret_cast<const int32_t*>(wbuf + (size_t) b * Cfg::BUF_BYTES + Cfg::SA * 8);
+		// Common case: the whole ticket [0, R) is in flight since stage C.  A ticket of more than CAP nonzeros (or of
+		// none) was not prefetched: it goes through the same stage in greedy sub-ranges of whole rows that fit
+		// (the launcher guarantees max_row <= CAP), copied here and waited for on the spot.
+		int rs = 0, re = R;
+		bool ready = stagedD;
+		do {
+			const int j0 = __shfl_sync(0xffffffffu, iaD, rs);
+			if (!ready) {
+				const unsigned fit = __ballot_sync(0xffffffffu, lane > rs && lane <= R && iaD - j0 <= CAP);
+				re = fit ? 31 - __clz(fit) : rs + 1;
+				const int j1 = __shfl_sync(0xffffffffu, iaD, re);
+				ready = j1 > j0;
+				if (ready && lane == 0) {
+					const int jj = j0 & ~3, ja_n = ((j1 + 3) & ~3) - jj;
+					const int jv = j0 & ~1, a_n = ((j1 + 1) & ~1) - jv;
+					const uint32_t dst = wbuf_u + b * Cfg::BUF_BYTES;
+					mbar_expect_tx(bar, (uint32_t) (a_n * 8 + ja_n * 4));
+					bulk_g2s(dst, a + jv, (uint32_t) a_n * 8, bar);
+					bulk_g2s(dst + Cfg::SA * 8, ja + jj, (uint32_t) ja_n * 4, bar);
+				}
+			}
+			if (ready) {
+				while (!mbar_try_wait(bar, (phase >> b) & 1)) {}
+				phase ^= 1u << b;
+			}
+			#pragma unroll 1
+			for (int p = rs; p < re; p += NGW) {
+				const int lr = min(p + gid, R);                      // ticket-local row of my group (R: none)
+				const int js = __shfl_sync(0xffffffffu, iaD, lr);
+				const int je = lr < re ? __shfl_sync(0xffffffffu, iaD, min(lr + 1, R)) : js;
+				double acc[V];
+				#pragma unroll
+				for (int v = 0; v < V; v++) acc[v] = 0.0;
+				staged_row<G, V, UNROLL, LD>(sj, sa, j0 & ~3, j0 & ~1, js, je, B, lig, ldb, acc);
+				if (lr < re && r0 + lr < m) store_c<G, V>(C, (size_t) (r0 + lr), lig, acc, ldc);
+				__syncwarp();
+			}
+			rs = re;
+			ready = false;
+		} while (rs < R);
+		__syncwarp();                            // every lane is done with stage b before iteration it+1 refills it
+	}
+}
+
+// ------------------------------------------------------------------------------------------------
+// Experiment: gathered B rows through a shared-memory ring ("the one experiment not yet run").
+// The ticketed row loop, but a group's gathers are cp.async (LDGSTS, 16 bytes per lane and piece) into a per-lane
+// ring of 2 stages x H nonzeros instead of loads into registers: a stage is being filled while the previous one is
+// consumed, so 4..8 B rows are in flight per group with 8 fewer live doubles per lane.  Each lane reads back exactly
+// the bytes it copied, so cp.async.wait_group is all the synchronisation needed.  The ring is drained at the end
+// of every row.  Same arithmetic and order: same bits.
+// ------------------------------------------------------------------------------------------------
+template <int G, int V, int H, int THREADS>
+__global__ void __launch_bounds__(THREADS)
+spmm_rowsplit_ring_kernel(const int32_t* __restrict__ ia, const int32_t* __restrict__ ja, const double* __restrict__ a,
+                          const double* __restrict__ B, double* __restrict__ C,
+                          int m, int rows_per_ticket, int* __restrict__ ticket, int parity, int ldb, int ldc)
+{
+	static_assert(G % H == 0 && V % 2 == 0, "a chunk of G nonzeros is a whole number of stages");
+	constexpr int NGW = 32 / G, P = V / 2;                  // 16-byte pieces per lane and B row
+	extern __shared__ __align__(128) unsigned char ring_smem[];
+	const int lane = threadIdx.x & 31, lig = lane % G, gid = lane / G;
+	// layout [stage][slot][piece][thread] of 16 bytes: consecutive threads, consecutive 16-byte words (no bank conflicts)
+	double2* const ring = reinterpret_cast<double2*>(ring_smem) + threadIdx.x;
+	const uint32_t ring_u = smem_u32(ring);
+	auto slot_off = [](int stage, int i, int p) { return ((stage * H + i) * P + p) * THREADS; };
+	if (blockIdx.x == 0 && threadIdx.x == 0) ticket[parity ^ 1] = 0;
+	int* const counter = ticket + parity;
+	for (;;) {
+		int t = 0;
+		if (lane == 0) t = atomicAdd(counter, 1);
+		t = __shfl_sync(0xffffffffu, t, 0);
+		const int64_t r0l = (int64_t) t * rows_per_ticket;
+		if (r0l >= m) break;
+		const int r0 = (int) r0l, r1 = (int) min((int64_t) m, r0l + rows_per_ticket);
 		for (int base = r0; base < r1; base += NGW) {
 			const int row = base + gid;
 			const bool live = row < r1;
@@ -172,6 +379,23 @@ spmm_rowsplit_ticket_kernel(const int32_t* __restrict__ ia, const int32_t* __res
 			double acc[V];
 			#pragma unroll
 			for (int v = 0; v < V; v++) acc[v] = 0.0;
+			double pv[H];                                        // values of the stage in flight
+			int pn = 0;                                          // its live nonzeros for my row (0: nothing in flight)
+			int stage = 0;
+			auto consume = [&](int st) {
+				#pragma unroll
+				for (int i = 0; i < H; i++) {
+					if (i < pn) {
+						#pragma unroll
+						for (int p = 0; p < P; p++) {
+							const double2 bb = ring[slot_off(st, i, p)];
+							acc[2 * p] = fma(pv[i], bb.x, acc[2 * p]);
+							acc[2 * p + 1] = fma(pv[i], bb.y, acc[2 * p + 1]);
+						}
+					}
+				}
+			};
+			bool inflight = false;                               // warp-uniform: a stage has been committed and not consumed
 			while (true) {
 				const int rem = je - j;
 				const int rem_warp = __reduce_max_sync(0xffffffffu, rem);
@@ -181,28 +405,40 @@ spmm_rowsplit_ticket_kernel(const int32_t* __restrict__ ia, const int32_t* __res
 				if (lig < rem) { cj = __ldg(ja + j + lig); ca = __ldg(a + j + lig); }
 				const int cnt = min(rem_warp, G);
 				#pragma unroll
-				for (int u = 0; u < G; u += U) {
-					if (u >= cnt) break;
-					int cc[U];
-					double vv[U];
-					Frag<V> bb[U];
+				for (int u = 0; u < G; u += H) {
+					if (u >= cnt) break;                             // warp-uniform
+					int cc[H];
+					double vv[H];
 					#pragma unroll
-					for (int i = 0; i < U; i++) {
+					for (int i = 0; i < H; i++) {
 						cc[i] = __shfl_sync(0xffffffffu, cj, u + i, G);
 						vv[i] = shfl_f64<G>(ca, u + i);
 					}
 					#pragma unroll
-					for (int i = 0; i < U; i++)
-						if (u + i < rem) bb[i] = load_b<G, V, LD>(B, cc[i], lig, ldb);
-					#pragma unroll
-					for (int i = 0; i < U; i++) {
+					for (int i = 0; i < H; i++) {
 						if (u + i < rem) {
+							const double2* src = reinterpret_cast<const double2*>(B + (size_t) cc[i] * ldb) + lig;
 							#pragma unroll
-							for (int v = 0; v < V; v++) acc[v] = fma(vv[i], bb[i].v[v], acc[v]);
+							for (int p = 0; p < P; p++)
+								cp_async16(ring_u + (uint32_t) slot_off(stage, i, p) * 16, src + p * G);
 						}
 					}
+					cp_async_commit();
+					if (inflight) {                                  // the other stage: everything but the newest group is done
+						cp_async_wait<1>();
+						consume(stage ^ 1);
+					}
+					#pragma unroll
+					for (int i = 0; i < H; i++) pv[i] = vv[i];
+					pn = max(0, min(H, rem - u));
+					inflight = true;
+					stage ^= 1;
 				}
 				j += G;
+			}
+			if (inflight) {
+				cp_async_wait<0>();
+				consume(stage ^ 1);
 			}
 			if (live) store_c<G, V>(C, (size_t) row, lig, acc, ldc);
 		}
@@ -210,12 +446,13 @@ spmm_rowsplit_ticket_kernel(const int32_t* __restrict__ ia, const int32_t* __res
 }
 
 // Any k: one warp per row, lanes own columns, column chunks of 32 (A re-read per chunk
-// out of L1/L2).  Used for k values without a specialised instantiation.
+// out of L1/L2).  Used for k values without a specialised instantiation and for operands that are
+// not 16-byte aligned (the specialised kernels move B and C as double2).
 template <int THREADS>
 __global__ void __launch_bounds__(THREADS)
 spmm_rowsplit_generic_kernel(const int32_t* __restrict__ ia, const int32_t* __restrict__ ja, const double* __restrict__ a,
                              const double* __restrict__ B, double* __restrict__ C,
-                             const int32_t* __restrict__ cta_rows, int k)
+                             const int32_t* __restrict__ cta_rows, int k, int ldb, int ldc)
 {
 	constexpr int NW = THREADS / 32;
 	const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -227,8 +464,8 @@ spmm_rowsplit_generic_kernel(const int32_t* __restrict__ ia, const int32_t* __re
 			double acc = 0.0;
 			if (n < k) {
 				for (int j = js; j < je; j++)
-					acc = fma(__ldg(a + j), __ldg(B + (size_t) __ldg(ja + j) * k + n), acc);
-				C[(size_t) row * k + n] = acc;
+					acc = fma(__ldg(a + j), __ldg(B + (size_t) __ldg(ja + j) * ldb + n), acc);
+				C[(size_t) row * ldc + n] = acc;
 			}
 		}
 	}
@@ -301,97 +538,6 @@ __global__ void transpose_b_kernel(const double* __restrict__ x, double* __restr
 		const int64_t j = j0 + dy;
 		const int n = n0 + threadIdx.x;
 		if (n < k && j < c) B[j * k + n] = tile[threadIdx.x][dy];
-	}
-}
-
-} // namespace sb200
-
-namespace sb200 {
-
-// ------------------------------------------------------------------------------------------------
-// Row-split on a row-PADDED copy of A ("vec" variant).
-//
-// ncu on spmm_rowsplit_kernel (profiles/r1_rowsplit_cfg2_v2.md) shows 13.9 warp instructions and ~3.5 L1
-// data-pipe wavefronts per nonzero (2 for the 256-byte B row, the rest for handing (col, val) round a lane
-// group with shuffles), issue slots 67 % and the L1 data pipe 78 % busy -- while a pure gather of the same B
-// rows reaches 21.6 TB/s against the kernel's 14.6 (scripts/gather_probe.cu).  The cure is fewer
-// instructions and wavefronts per nonzero, not more loads in flight:
-//   * every row of A is padded to a multiple of 4 entries (col = the row's last column, val = 0), so a
-//     lane reads 4 column indices with ONE 16-byte load and 4 values with TWO, as same-address loads of
-//     its lane group (one wavefront per group and load, no shuffles, no per-step warp votes);
-//   * lane groups are independent: no shuffle means no warp-synchronous trip counts;
-//   * 4 B-row gathers (V doubles each) are in flight per lane and step.
-// The row sum still runs left to right; padded entries are skipped by a predicate, never multiplied.
-// ------------------------------------------------------------------------------------------------
-template <int G, int V, int THREADS>
-__global__ void __launch_bounds__(THREADS)
-spmm_rowsplit_vec_kernel(const int32_t* __restrict__ ia, const int32_t* __restrict__ iap,
-                         const int32_t* __restrict__ jap, const double* __restrict__ ap,
-                         const double* __restrict__ B, double* __restrict__ C,
-                         const int32_t* __restrict__ cta_rows, int ldb, int ldc)
-{
-	constexpr int NG = THREADS / G;
-	const int lig = threadIdx.x % G;
-	const int gid = threadIdx.x / G;
-	const int r0 = cta_rows[blockIdx.x];
-	const int r1 = cta_rows[blockIdx.x + 1];
-	for (int row = r0 + gid; row < r1; row += NG) {
-		const int len = __ldg(ia + row + 1) - __ldg(ia + row);
-		const int p = __ldg(iap + row);
-		const int4* cp = reinterpret_cast<const int4*>(jap + p);
-		const double2* vp = reinterpret_cast<const double2*>(ap + p);
-		double acc[V];
-		#pragma unroll
-		for (int v = 0; v < V; v++) acc[v] = 0.0;
-		for (int u = 0; u < len; u += 4) {
-			const int4 c4 = __ldg(cp + (u >> 2));
-			const double2 v01 = __ldg(vp + (u >> 1));
-			const double2 v23 = __ldg(vp + (u >> 1) + 1);
-			const Frag<V> b0 = load_b<G, V>(B, c4.x, lig, ldb);
-			const Frag<V> b1 = load_b<G, V>(B, c4.y, lig, ldb);
-			const Frag<V> b2 = load_b<G, V>(B, c4.z, lig, ldb);
-			const Frag<V> b3 = load_b<G, V>(B, c4.w, lig, ldb);
-			const int rem = len - u;
-			#pragma unroll
-			for (int v = 0; v < V; v++) acc[v] = fma(v01.x, b0.v[v], acc[v]);
-			if (rem > 1) {
-				#pragma unroll
-				for (int v = 0; v < V; v++) acc[v] = fma(v01.y, b1.v[v], acc[v]);
-			}
-			if (rem > 2) {
-				#pragma unroll
-				for (int v = 0; v < V; v++) acc[v] = fma(v23.x, b2.v[v], acc[v]);
-			}
-			if (rem > 3) {
-				#pragma unroll
-				for (int v = 0; v < V; v++) acc[v] = fma(v23.y, b3.v[v], acc[v]);
-			}
-		}
-		store_c<G, V>(C, (size_t) row, lig, acc, ldc);
-	}
-}
-
-// padded row lengths: out[i] = (len_i + 3) & ~3 for i < m, out[m] = 0 (then exclusive scan -> iap)
-__global__ void pad_len_kernel(const int32_t* __restrict__ ia, int m, int32_t* __restrict__ out)
-{
-	const int i = blockIdx.x * blockDim.x + threadIdx.x;
-	if (i < m) out[i] = (ia[i + 1] - ia[i] + 3) & ~3;
-	else if (i == m) out[i] = 0;
-}
-
-// one thread per padded slot of a row group of 4: copies (col, val), pads with (last col of the row, 0)
-__global__ void pad_fill_kernel(const int32_t* __restrict__ ia, const int32_t* __restrict__ iap,
-                                const int32_t* __restrict__ ja, const double* __restrict__ a, int m,
-                                int32_t* __restrict__ jap, double* __restrict__ ap)
-{
-	const int lane = threadIdx.x & 31;
-	const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;      // a warp per row
-	if (row >= m) return;
-	const int s = ia[row], len = ia[row + 1] - s, p = iap[row], plen = iap[row + 1] - p;
-	const int last = len > 0 ? ja[s + len - 1] : 0;
-	for (int u = lane; u < plen; u += 32) {
-		jap[p + u] = u < len ? ja[s + u] : last;
-		ap[p + u] = u < len ? a[s + u] : 0.0;
 	}
 }
 

@@ -246,9 +246,9 @@ def test_k_sliced_host_pipeline(pkg, L, layout, monkeypatch):
             assert mf.last_kernel_ms() > 0
             y2 = np.full(m * k, np.nan); mf.spmm(xin, None, k, copy_back=False); mf.fetch_c(y2, k)
             assert np.array_equal(y, y2)
-            monkeypatch.setenv("SPMM_B200_PIPELINE_COLS", "0")          # one-shot path on the same handle
+            mf.set_option("PIPELINE_COLS", 0)                            # one-shot path on the same handle
             y3 = np.full(m * k, np.nan); mf.spmm(xin, y3, k)
-            monkeypatch.delenv("SPMM_B200_PIPELINE_COLS")
+            mf.set_option("PIPELINE_COLS", -1)
             assert max_rel_err(y3, y_ref) <= FP64_TOL
             mf.close()
 
@@ -276,9 +276,9 @@ def test_direct_store_into_page_locked_y(pkg, L, monkeypatch):
         assert mf.launch_count() - before >= 2                      # at least two slices ran
         with pytest.raises(pkg.SpmmB200Error):
             mf.fetch_c(np.empty(m * k), k)
-        monkeypatch.setenv("SPMM_B200_DIRECT_STORE", "0")
+        mf.set_option("DIRECT_STORE", 0)
         y2 = np.full(m * k, np.nan); mf.spmm(x, y2, k)
-        monkeypatch.delenv("SPMM_B200_DIRECT_STORE")
+        mf.set_option("DIRECT_STORE", 1)
         assert np.array_equal(y2, y)                                 # staged download: the same bits
         y3 = np.full(m * k, np.nan); mf.fetch_c(y3, k)
         assert np.array_equal(y3, y)

@@ -210,12 +210,10 @@ def test_gpu_fused_attention_matches_oracle(pkg, L, n):
     MF.attention(x, yf, 1, 2)
     assert_close(yf, r["y_final"], msg=f"fused n={n}")
     assert (yf.reshape(m, n)[m - 40:] == 0).all()
-    os.environ["SPMM_B200_ATTENTION_FUSED"] = "0"
-    try:
-        yf2 = np.full(m * n, np.nan)
-        MF.attention(x, yf2, 1, 2)
-    finally:
-        del os.environ["SPMM_B200_ATTENTION_FUSED"]
+    MF.set_option("ATTENTION_FUSED", 0)
+    yf2 = np.full(m * n, np.nan)
+    MF.attention(x, yf2, 1, 2)
+    MF.set_option("ATTENTION_FUSED", 1)
     assert_close(yf2, r["y_final"], msg=f"unfused n={n}")
     MF.close()
 
