@@ -249,18 +249,29 @@ int spmm_b200_check_accuracy(spmm_b200_t *h, const double *x_host, const double 
                              double *stats, double *y_gold_host);
 
 /* ---- fp32 ("_f" builds of the reference, make.sh:98-108: ValueType = float).  Same plug-in interface
- * (spmv_kernel.h:9-30) and layouts as the fp64 entry points above, int32 indices, fp32 values / x / y;
- * row-split CSR kernels, the same bit-exact partitioners for CTA work lists and shards.  The row sum runs
- * left to right in fp32 with fused multiply-add. */
+ * (spmv_kernel.h:9-30) and layouts as the fp64 entry points above, int32 indices, fp32 values / x / y, the same
+ * bit-exact partitioners for CTA work lists, merge tiles and shards.  `variant`:
+ *   SPMM_B200_ROWSPLIT  row-split CSR, the row sum runs left to right in fp32 with fused multiply-add
+ *                       (bit-identical to the reference's _f build of compute_csr);
+ *   SPMM_B200_MERGE     merge-path tiles with k-wide carries (skewed rows; sums are re-associated at the carries);
+ *   SPMM_B200_AUTO      merge-path when one row is far longer than the mean, else row-split;
+ *   SPMM_B200_BCSR      blocked tensor-core kernel for BANDED matrices: 128-row slabs x their column window as dense
+ *                       TF32 products on tcgen05.mma with fp32 accumulators in TMEM (k = 32, 64, 128; other k fall back
+ *                       to row-split).  A and B are rounded to TF32 (10 mantissa bits): results agree with the fp32
+ *                       reference to ~1e-3 relative, NOT bit for bit -- which is why AUTO never picks it
+ *                       (the stand-in for mkl_sparse_s_mm-class kernels, spmm_kernel_mkl_ie.cpp:143-146).
+ *   SPMM_B200_BCSR_FMA  = SPMM_B200_ROWSPLIT (no fp32 FMA-pipe blocked kernel). */
 typedef struct spmm_b200_f32 spmm_b200_f32_t;
 int spmm_b200_create_f32(spmm_b200_f32_t **h, const int32_t *row_ptr, const int32_t *col_ind, const float *values,
-                         int64_t m, int64_t c, int64_t nnz, int k, int device, int b_layout);
+                         int64_t m, int64_t c, int64_t nnz, int k, int device, int variant, int b_layout);
 int spmm_b200_create_shard_f32(spmm_b200_f32_t **h, const int32_t *row_ptr, const int32_t *col_ind, const float *values,
-                               int64_t m, int64_t c, int64_t nnz, int k, int device, int b_layout,
+                               int64_t m, int64_t c, int64_t nnz, int k, int device, int variant, int b_layout,
                                int rank, int nranks, int64_t *first_row, int64_t *last_row);
 int spmm_b200_run_f32(spmm_b200_f32_t *h, const float *x_host, float *y_host, int k, int copy_back);
 int spmm_b200_run_device_f32(spmm_b200_f32_t *h, const float *b_dev, float *c_dev, int k, void *stream);
 int spmm_b200_fetch_c_f32(spmm_b200_f32_t *h, float *y_host, int k);
+int     spmm_b200_variant_f32(const spmm_b200_f32_t *h);      /* the variant the handle resolved to */
+int     spmm_b200_set_option_f32(spmm_b200_f32_t *h, const char *name, int value);
 int64_t spmm_b200_rows_f32(const spmm_b200_f32_t *h);
 int64_t spmm_b200_nnz_f32(const spmm_b200_f32_t *h);
 int64_t spmm_b200_launch_count_f32(const spmm_b200_f32_t *h);

@@ -41,7 +41,7 @@ EXPORTS = [
     "spmm_b200_variant", "spmm_b200_bcsr_blocks", "spmm_b200_kslice", "spmm_b200_last_kernel_ms", "spmm_b200_launch_count", "spmm_b200_stats",
     "spmm_b200_stats_labels", "spmm_b200_destroy", "spmm_b200_strerror", "spmm_b200_last_cuda_error",
     "spmm_b200_create_f32", "spmm_b200_create_shard_f32", "spmm_b200_run_f32", "spmm_b200_run_device_f32",
-    "spmm_b200_fetch_c_f32", "spmm_b200_rows_f32", "spmm_b200_nnz_f32", "spmm_b200_launch_count_f32",
+    "spmm_b200_fetch_c_f32", "spmm_b200_variant_f32", "spmm_b200_set_option_f32", "spmm_b200_rows_f32", "spmm_b200_nnz_f32", "spmm_b200_launch_count_f32",
     "spmm_b200_last_kernel_ms_f32", "spmm_b200_destroy_f32",
     "spmm_b200_device_count", "spmm_b200_read_mtx", "spmm_b200_read_smtx", "spmm_b200_free", "spmm_b200_check_accuracy",
     # include/spmm_b200_pipeline.h
@@ -128,7 +128,9 @@ def load_library():
     lib.spmm_b200_read_smtx.argtypes = [C.c_char_p, C.c_uint64, C.POINTER(_i64), C.POINTER(_i64), C.POINTER(_i64), _pp, _pp, _pp]
     lib.spmm_b200_free.argtypes = [_vp]; lib.spmm_b200_free.restype = None
     lib.spmm_b200_check_accuracy.argtypes = [_vp, _vp, _vp, _int, _vp, _vp]
-    lib.spmm_b200_create_f32.argtypes = [C.POINTER(_vp), _vp, _vp, _vp, _i64, _i64, _i64, _int, _int, _int]
+    lib.spmm_b200_create_f32.argtypes = [C.POINTER(_vp), _vp, _vp, _vp, _i64, _i64, _i64, _int, _int, _int, _int]
+    lib.spmm_b200_variant_f32.argtypes = [_vp]
+    lib.spmm_b200_set_option_f32.argtypes = [_vp, C.c_char_p, _int]
     lib.spmm_b200_create_shard_f32.argtypes = lib.spmm_b200_create_f32.argtypes + [_int, _int, C.POINTER(_i64), C.POINTER(_i64)]
     lib.spmm_b200_run_f32.argtypes = [_vp, _vp, _vp, _int, _int]
     lib.spmm_b200_run_device_f32.argtypes = [_vp, _vp, _vp, _int, _vp]
@@ -319,7 +321,8 @@ class MatrixFormatF32:
     def __init__(self, handle, m, n, nnz, k, first_row=0):
         self._h = handle
         self.m, self.n, self.nnz, self.k, self.first_row = int(m), int(n), int(nnz), int(k), int(first_row)
-        self.format_name = "B200_CSR_ROWSPLIT_F32"
+        self.variant = load_library().spmm_b200_variant_f32(handle)
+        self.format_name = {ROWSPLIT: "B200_CSR_ROWSPLIT_F32", MERGE: "B200_CSR_MERGE_F32", BCSR: "B200_BLOCKED_TF32"}.get(self.variant, "B200_CSR_F32")
         self.csr_mem_footprint = self.nnz * (4 + 4) + (self.m + 1) * 4
         self.mem_footprint = self.csr_mem_footprint
 
@@ -334,6 +337,9 @@ class MatrixFormatF32:
 
     def spmm_device(self, b_ptr, c_ptr, k, stream=0):
         _check(load_library().spmm_b200_run_device_f32(self._h, b_ptr, c_ptr, int(k), stream or None), "spmm_device(f32)")
+
+    def set_option(self, name, value):
+        _check(load_library().spmm_b200_set_option_f32(self._h, name.encode(), int(value)), f"set_option_f32({name})")
 
     def fetch_c(self, y, k):
         _check(load_library().spmm_b200_fetch_c_f32(self._h, _host(y, np.float32, "y"), int(k)), "fetch_c(f32)")
@@ -512,18 +518,19 @@ def csr_to_pipeline_format_f32(row_ptr, col_ind, values, m, nnz, n, *, device=0)
     return PipelineFormatF32(h, m, nnz, n, (row_ptr, col_ind, values))
 
 
-def csr_to_format_f32(row_ptr, col_ind, values, m, n, nnz, k, *, device=0, b_layout=B_COLMAJOR, rank=None, nranks=None):
-    """csr_to_format() of an "_f" build: values float32."""
+def csr_to_format_f32(row_ptr, col_ind, values, m, n, nnz, k, *, device=0, variant=AUTO, b_layout=B_COLMAJOR, rank=None, nranks=None):
+    """csr_to_format() of an "_f" build: values float32.  variant: ROWSPLIT | MERGE | AUTO | BCSR (= the TF32
+    tensor-core kernel for banded matrices, ~1e-3 relative accuracy; never picked by AUTO)."""
     lib = load_library()
     h = _vp()
     rp = _host(row_ptr, np.int32, "row_ptr")
     ci = _host(col_ind, np.int32, "col_ind") if nnz > 0 else None
     va = _host(values, np.float32, "values") if nnz > 0 else None
     if nranks is None:
-        _check(lib.spmm_b200_create_f32(C.byref(h), rp, ci, va, m, n, nnz, k, device, b_layout), "csr_to_format_f32")
+        _check(lib.spmm_b200_create_f32(C.byref(h), rp, ci, va, m, n, nnz, k, device, variant, b_layout), "csr_to_format_f32")
         return MatrixFormatF32(h, m, n, nnz, k)
     r0, r1 = _i64(), _i64()
-    _check(lib.spmm_b200_create_shard_f32(C.byref(h), rp, ci, va, m, n, nnz, k, device, b_layout, int(rank), int(nranks),
+    _check(lib.spmm_b200_create_shard_f32(C.byref(h), rp, ci, va, m, n, nnz, k, device, variant, b_layout, int(rank), int(nranks),
                                           C.byref(r0), C.byref(r1)), "csr_to_format_f32(shard)")
     return MatrixFormatF32(h, lib.spmm_b200_rows_f32(h), n, lib.spmm_b200_nnz_f32(h), k, first_row=r0.value)
 

@@ -44,7 +44,7 @@ static constexpr int THREADS = 256;
 struct Options {
 	int ticket = -1;           // TICKET: rows per ticket of the persistent row-split kernel; -1 = rule, 0 = static ranges
 	int ticket_ctas = 4;       // TICKET_CTAS: CTAs per SM of a ticketed grid
-	int ticket_min_nnz = 8 << 20; // TICKET_MIN_NNZ: the rule takes tickets from this many nonzeros on
+	int ticket_min_nnz = 2 << 20; // TICKET_MIN_NNZ: the rule takes tickets from this many nonzeros on
 	int stage = 0;             // STAGE: 1 = A stream through shared memory by TMA (staged kernel), 0 = off, -1 = rule, 2 = B-row ring experiment
 	int const_ld = 1;          // CONST_LD: compile-time row stride when the operand is whole
 	int unroll = 4;            // UNROLL: B-row gathers in flight per lane group
@@ -284,7 +284,9 @@ static void launch_rowsplit_gv(spmm_b200* h, const double* B, double* C, cudaStr
 		// measured over bench/medium_subset.txt x k in {4, 8, 32, 128} (profiles/r1_ticket_probe.md): rows of >= 50
 		// nonzeros gain 3-15 %, rows of <= 10 lose 3-15 % (a ticket per ~50 nonzeros is too fine, larger chunks lose
 		// the locality); small launches: profiles/r2_shard_probe.md
-		tick = (avg >= 32.0 && h->nnz >= (int64_t) o.ticket_min_nnz) ? 8 : 0;
+		// k = 32 (4 rows per warp): 4-row tickets = one row per lane group; same time on a whole matrix (cfg2 0.764 vs
+		// 0.767 ms), better on the 1/8 shards of the 8-GPU run (0.114 vs 0.120 ms, static ranges 0.124 ms)
+		tick = (avg >= 32.0 && h->nnz >= (int64_t) o.ticket_min_nnz) ? (K == 32 ? 4 : 8) : 0;
 	}
 	if constexpr (V >= 2 && K >= 32) {
 		// A stream staged through shared memory by TMA bulk copies (spmm_rowsplit_staged_kernel)
@@ -367,7 +369,7 @@ struct MergeLaunch {
 		cudaError_t e = raise_smem_limit(h, ATTR_MERGE + attr_bit, kern, Cfg::SMEM);
 		if (e != cudaSuccess) return e;
 		kern<<<h->merge.ntiles, THREADS, Cfg::SMEM, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, h->merge.d_tile,
-		                                                h->merge.d_carry, h->merge.d_carry_row);
+		                                                (double*) h->merge.d_carry, h->merge.d_carry_row);
 		return cudaGetLastError();
 	}
 };
@@ -432,7 +434,7 @@ static int launch_merge(spmm_b200* h, const double* B, double* C, int k, cudaStr
 	}
 	const int64_t n = (int64_t) h->merge.ntiles * k;
 	spmm_merge_fixup_kernel<THREADS><<<(unsigned) ((n + THREADS - 1) / THREADS), THREADS, 0, s>>>(
-		h->merge.d_carry, h->merge.d_carry_row, h->merge.ntiles, (int) h->m, k, C);
+		(const double*) h->merge.d_carry, h->merge.d_carry_row, h->merge.ntiles, (int) h->m, k, C);
 	e = cudaGetLastError();
 	if (e != cudaSuccess) {
 		snprintf(g_cuda_err, sizeof(g_cuda_err), "merge fixup launch (k=%d): %s", k, cudaGetErrorString(e));

@@ -2,15 +2,24 @@
 //
 // The reference builds every kernel twice, "_d" (ValueType = double) and "_f" (ValueType = float,
 // make.sh:98-108); this file is the "_f" side of the drop-in: same plug-in interface
-// (spmv_kernel.h:9-30), int32 CSR indices, fp32 values / B / C.  Row-split CSR kernels only
-// (spmm_f32.cuh); CTA work lists and shard boundaries come from the same bit-exact partitioners as the
-// fp64 path (partition.cuh).  No CPU fallback.
+// (spmv_kernel.h:9-30), int32 CSR indices, fp32 values / B / C.  Variants: row-split (spmm_f32.cuh), merge-path
+// (the kernel of spmm_merge.cuh instantiated for float: skewed rows no longer serialise on one lane group), and the
+// TF32 blocked kernel on tcgen05 / TMEM for banded matrices (spmm_tf32_blocked.cuh, explicit request only: it
+// rounds the operands to TF32).  CTA work lists, merge tiles and shard boundaries come from the same bit-exact
+// partitioners as the fp64 path (partition.cuh).  No CPU fallback.
 // Included at the end of spmm_b200.cu (one translation unit: the kernels of partition.cuh must not be
 // defined twice, and CU_TRY / g_cuda_err are shared).
 #include "spmm_f32.cuh"
+#include "spmm_tf32_blocked.cuh"
 
 struct spmm_b200_f32 {
-	int device = 0, b_layout = SPMM_B200_B_COLMAJOR, k = 0, sm_count = 148;
+	int device = 0, b_layout = SPMM_B200_B_COLMAJOR, k = 0, sm_count = 0;
+	int variant = SPMM_B200_ROWSPLIT, variant_req = SPMM_B200_AUTO;
+	int max_row = 0;
+	Options opt;
+	MergePlan merge;
+	Tf32Plan tf32;
+	uint32_t smem_attr = 0;
 	int64_t m = 0, c = 0, nnz = 0, first_row = 0;
 	int32_t* d_ia = nullptr;
 	int32_t* d_ja = nullptr;
@@ -46,13 +55,151 @@ static int device_ok(int device, int* sms)
 	return SPMM_B200_OK;
 }
 
+// ---- TF32 blocked kernel (tcgen05 / TMEM): per-slab column windows + launch --------------------------------
+static int tf32_build_plan(spmm_b200_f32* h)
+{
+	Tf32Plan& p = h->tf32;
+	p.nslabs = (int) ((h->m + TF32_M - 1) / TF32_M);
+	if (p.nslabs == 0) return SPMM_B200_OK;
+	unsigned long long* d_total = nullptr;
+	unsigned long long total = 0;
+	CU_TRY(cudaMalloc(&p.d_win, sizeof(int2) * p.nslabs));
+	CU_TRY(cudaMalloc(&d_total, sizeof(unsigned long long)));
+	CU_TRY(cudaMemsetAsync(d_total, 0, sizeof(unsigned long long), h->stream));
+	tf32_window_kernel<<<p.nslabs, TF32_M, 0, h->stream>>>(h->d_ia, h->d_ja, (int) h->m, p.d_win, d_total);
+	h->launches++;
+	CU_TRY(cudaGetLastError());
+	CU_TRY(cudaMemcpyAsync(&total, d_total, sizeof(total), cudaMemcpyDeviceToHost, h->stream));
+	CU_TRY(cudaStreamSynchronize(h->stream));
+	cudaFree(d_total);
+	p.window_cols = (double) total;
+	return SPMM_B200_OK;
+}
+
+static void tf32_release_plan(spmm_b200_f32* h)
+{
+	cudaFree(h->tf32.d_win);
+	h->tf32 = Tf32Plan();
+}
+
+static bool tf32_supports(const spmm_b200_f32* h, int k) { return h->tf32.d_win && (k == 32 || k == 64 || k == 128); }
+
+template <int N>
+static cudaError_t tf32_launch_n(spmm_b200_f32* h, const float* B, float* C, cudaStream_t s, int bit)
+{
+	constexpr int STAGES = 2;
+	using Cfg = Tf32Cfg<N, STAGES>;
+	auto kern = spmm_tf32_blocked_kernel<N, STAGES>;
+	if (Cfg::SMEM > 48 * 1024 && !(h->smem_attr >> bit & 1u)) {
+		cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) Cfg::SMEM);
+		if (e != cudaSuccess) return e;
+		h->smem_attr |= 1u << bit;
+	}
+	kern<<<h->tf32.nslabs, TF32_M, Cfg::SMEM, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, h->tf32.d_win, (int) h->m, (int) h->c);
+	return cudaGetLastError();
+}
+
+static int tf32_launch(spmm_b200_f32* h, const float* B, float* C, int k, cudaStream_t s)
+{
+	cudaError_t e = k == 32 ? tf32_launch_n<32>(h, B, C, s, 16) : k == 64 ? tf32_launch_n<64>(h, B, C, s, 17) : tf32_launch_n<128>(h, B, C, s, 18);
+	if (e != cudaSuccess) {
+		snprintf(g_cuda_err, sizeof(g_cuda_err), "tf32 blocked launch (k=%d): %s", k, cudaGetErrorString(e));
+		return SPMM_B200_ECUDA;
+	}
+	h->launches += 1;
+	return 1;
+}
+
+// k -> (G, V, IPG) of the float merge kernel (V = 4 floats = one 16-byte piece per lane and load)
+#define MERGE_F32_DISPATCH(k, WHAT)                                \
+	switch (k) {                                                   \
+	case 1:   WHAT(1, 1, 16, 0); break;                            \
+	case 2:   WHAT(1, 2, 16, 1); break;                            \
+	case 4:   WHAT(1, 4, 16, 2); break;                            \
+	case 8:   WHAT(2, 4, 16, 3); break;                            \
+	case 16:  WHAT(4, 4, 32, 4); break;                            \
+	case 32:  WHAT(8, 4, 64, 5); break;                            \
+	case 64:  WHAT(16, 4, 128, 6); break;                          \
+	case 128: WHAT(32, 4, 128, 7); break;                          \
+	default: break;                                                \
+	}
+
+static int merge_items_f32(int k)
+{
+	int items = 0;
+#define WHAT(G, V, IPG, BIT) items = MergeCfg<G, V, IPG, THREADS, float>::ITEMS
+	MERGE_F32_DISPATCH(k, WHAT)
+#undef WHAT
+	return items;
+}
+
+static int build_merge_plan_f32(spmm_b200_f32* h, int k, cudaStream_t s)
+{
+	const int items = merge_items_f32(k);
+	if (items <= 0) return SPMM_B200_ENOSUP;
+	MergePlan& p = h->merge;
+	if (p.items == items && p.carry_k >= k && p.d_tile) return SPMM_B200_OK;
+	const int64_t L = h->m + h->nnz;
+	const int ntiles = (int) ((L + items - 1) / items);
+	cudaFree(p.d_tile); cudaFree(p.d_carry); cudaFree(p.d_carry_row);
+	p.d_tile = nullptr; p.d_carry = nullptr; p.d_carry_row = nullptr;
+	CU_TRY(cudaMalloc(&p.d_tile, sizeof(int2) * ((size_t) ntiles + 1)));
+	CU_TRY(cudaMalloc(&p.d_carry, sizeof(float) * std::max<size_t>((size_t) ntiles * k, 1)));
+	CU_TRY(cudaMalloc(&p.d_carry_row, sizeof(int32_t) * std::max(ntiles, 1)));
+	p.ntiles = ntiles; p.items = items; p.carry_k = k;
+	tile_merge_kernel<<<(ntiles + 1 + 255) / 256, 256, 0, s>>>(h->d_ia, (int) h->m, h->nnz, items, ntiles, p.d_tile);
+	h->launches++;
+	CU_TRY(cudaGetLastError());
+	return SPMM_B200_OK;
+}
+
+template <int G, int V, int IPG>
+static cudaError_t launch_merge_f32_gv(spmm_b200_f32* h, const float* B, float* C, cudaStream_t s, int bit)
+{
+	using Cfg = MergeCfg<G, V, IPG, THREADS, float>;
+	auto kern = spmm_merge_kernel<G, V, IPG, 4, THREADS, float>;
+	if (Cfg::SMEM > 48 * 1024 && !(h->smem_attr >> bit & 1u)) {
+		cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) Cfg::SMEM);
+		if (e != cudaSuccess) return e;
+		h->smem_attr |= 1u << bit;
+	}
+	kern<<<h->merge.ntiles, THREADS, Cfg::SMEM, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, h->merge.d_tile,
+	                                                (float*) h->merge.d_carry, h->merge.d_carry_row);
+	return cudaGetLastError();
+}
+
+static int launch_merge_f32(spmm_b200_f32* h, const float* B, float* C, int k, cudaStream_t s)
+{
+	int rc = build_merge_plan_f32(h, k, s);
+	if (rc) return rc;
+	if (h->merge.ntiles == 0) return 0;
+	cudaError_t e = cudaErrorInvalidValue;
+#define WHAT(G, V, IPG, BIT) e = launch_merge_f32_gv<G, V, IPG>(h, B, C, s, BIT)
+	MERGE_F32_DISPATCH(k, WHAT)
+#undef WHAT
+	if (e == cudaSuccess) {
+		const int64_t n = (int64_t) h->merge.ntiles * k;
+		spmm_merge_fixup_kernel<THREADS, float><<<(unsigned) ((n + THREADS - 1) / THREADS), THREADS, 0, s>>>(
+			(const float*) h->merge.d_carry, h->merge.d_carry_row, h->merge.ntiles, (int) h->m, k, C);
+		e = cudaGetLastError();
+	}
+	if (e != cudaSuccess) {
+		snprintf(g_cuda_err, sizeof(g_cuda_err), "fp32 merge launch (k=%d): %s", k, cudaGetErrorString(e));
+		return SPMM_B200_ECUDA;
+	}
+	h->launches += 2;
+	return 2;
+}
+
 static int create_slice(spmm_b200_f32** out, const int32_t* ia_slice, const int32_t* ja, const float* a, int64_t m, int64_t c,
-                        int64_t nnz, int32_t base, int k, int device, int b_layout, int sms, int64_t first_row)
+                        int64_t nnz, int32_t base, int k, int device, int variant, int b_layout, int sms, int64_t first_row)
 {
 	spmm_b200_f32* h = new (std::nothrow) spmm_b200_f32();
 	if (!h) return SPMM_B200_ENOMEM;
 	*out = h;
 	h->device = device; h->b_layout = b_layout; h->k = k; h->sm_count = sms;
+	h->variant_req = variant;
+	h->opt = options_from_env();
 	h->m = m; h->c = c; h->nnz = nnz; h->first_row = first_row;
 	CU_TRY(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
 	CU_TRY(cudaEventCreate(&h->ev0));
@@ -77,6 +224,32 @@ static int create_slice(spmm_b200_f32** out, const int32_t* ia_slice, const int3
 	cta_rows_nnz_kernel<<<(h->n_ctas + 1 + 255) / 256, 256, 0, h->stream>>>(h->d_ia, (int) m, nnz, h->n_ctas, h->d_cta_rows);
 	h->launches++;
 	CU_TRY(cudaGetLastError());
+	if (m > 0) {
+		int* d_max = nullptr;
+		CU_TRY(cudaMalloc(&d_max, sizeof(int)));
+		CU_TRY(cudaMemsetAsync(d_max, 0, sizeof(int), h->stream));
+		max_row_kernel<<<(unsigned) std::min<int64_t>(1024, (m + 255) / 256), 256, 0, h->stream>>>(h->d_ia, (int) m, d_max);
+		h->launches++;
+		CU_TRY(cudaMemcpyAsync(&h->max_row, d_max, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+		CU_TRY(cudaStreamSynchronize(h->stream));
+		cudaFree(d_max);
+	}
+	if (variant == SPMM_B200_AUTO) {
+		// the fp64 rule (create_from_slice): merge-path when one row is far longer than the mean.  AUTO never picks the
+		// TF32 blocked kernel: it rounds A and B to 10 mantissa bits, which the caller has to ask for.
+		const double avg = m > 0 ? (double) nnz / (double) m : 0.0;
+		h->variant = (h->max_row >= h->opt.merge_maxrow && h->max_row > 8.0 * avg) ? SPMM_B200_MERGE : SPMM_B200_ROWSPLIT;
+	} else {
+		h->variant = variant == SPMM_B200_BCSR_FMA ? SPMM_B200_ROWSPLIT : variant;
+	}
+	if (h->variant == SPMM_B200_MERGE && merge_items_f32(k) > 0) {
+		int rc = build_merge_plan_f32(h, k, h->stream);
+		if (rc) return rc;
+	}
+	if (h->variant == SPMM_B200_BCSR) {
+		int rc = tf32_build_plan(h);
+		if (rc) return rc;
+	}
 	CU_TRY(cudaStreamSynchronize(h->stream));
 	return SPMM_B200_OK;
 }
@@ -91,28 +264,30 @@ static int check_args(const void* rp, const void* ci, const void* va, int64_t m,
 }
 
 extern "C" int spmm_b200_create_f32(spmm_b200_f32_t** h, const int32_t* row_ptr, const int32_t* col_ind, const float* values,
-                                    int64_t m, int64_t c, int64_t nnz, int k, int device, int b_layout)
+                                    int64_t m, int64_t c, int64_t nnz, int k, int device, int variant, int b_layout)
 {
 	if (!h) return SPMM_B200_EINVAL;
 	*h = nullptr;
 	int rc = check_args(row_ptr, col_ind, values, m, c, nnz, k, b_layout);
 	if (rc) return rc;
+	if (variant < SPMM_B200_ROWSPLIT || variant > SPMM_B200_BCSR_FMA) return SPMM_B200_EINVAL;
 	int sms = 0;
 	rc = device_ok(device, &sms);
 	if (rc) return rc;
-	rc = create_slice(h, row_ptr, col_ind, values, m, c, nnz, 0, k, device, b_layout, sms, 0);
+	rc = create_slice(h, row_ptr, col_ind, values, m, c, nnz, 0, k, device, variant, b_layout, sms, 0);
 	if (rc) { spmm_b200_destroy_f32(*h); *h = nullptr; }
 	return rc;
 }
 
 extern "C" int spmm_b200_create_shard_f32(spmm_b200_f32_t** h, const int32_t* row_ptr, const int32_t* col_ind, const float* values,
-                                          int64_t m, int64_t c, int64_t nnz, int k, int device, int b_layout,
+                                          int64_t m, int64_t c, int64_t nnz, int k, int device, int variant, int b_layout,
                                           int rank, int nranks, int64_t* first_row, int64_t* last_row)
 {
 	if (!h) return SPMM_B200_EINVAL;
 	*h = nullptr;
 	int rc = check_args(row_ptr, col_ind, values, m, c, nnz, k, b_layout);
 	if (rc) return rc;
+	if (variant < SPMM_B200_ROWSPLIT || variant > SPMM_B200_BCSR_FMA) return SPMM_B200_EINVAL;
 	if (nranks < 1 || rank < 0 || rank >= nranks) return SPMM_B200_EINVAL;
 	int sms = 0;
 	rc = device_ok(device, &sms);
@@ -124,7 +299,7 @@ extern "C" int spmm_b200_create_shard_f32(spmm_b200_f32_t** h, const int32_t* ro
 	if (first_row) *first_row = r0;
 	if (last_row) *last_row = r1;
 	const int32_t base = row_ptr[r0];
-	rc = create_slice(h, row_ptr + r0, col_ind, values, r1 - r0, c, (int64_t) row_ptr[r1] - base, base, k, device, b_layout, sms, r0);
+	rc = create_slice(h, row_ptr + r0, col_ind, values, r1 - r0, c, (int64_t) row_ptr[r1] - base, base, k, device, variant, b_layout, sms, r0);
 	if (rc) { spmm_b200_destroy_f32(*h); *h = nullptr; }
 	return rc;
 }
@@ -136,6 +311,8 @@ extern "C" void spmm_b200_destroy_f32(spmm_b200_f32_t* h)
 	if (h->stream) cudaStreamSynchronize(h->stream);
 	cudaFree(h->d_ia); cudaFree(h->d_ja); cudaFree(h->d_a); cudaFree(h->d_cta_rows); cudaFree(h->d_ticket);
 	cudaFree(h->d_x); cudaFree(h->d_B); cudaFree(h->d_C);
+	cudaFree(h->merge.d_tile); cudaFree(h->merge.d_carry); cudaFree(h->merge.d_carry_row);
+	tf32_release_plan(h);
 	if (h->ev0) cudaEventDestroy(h->ev0);
 	if (h->ev1) cudaEventDestroy(h->ev1);
 	if (h->stream) cudaStreamDestroy(h->stream);
@@ -146,7 +323,7 @@ template <int G, int V, int U>
 static void launch_gv(const spmm_b200_f32* h, const float* B, float* C, cudaStream_t s)
 {
 	// long rows and enough of them: persistent warps with 8-row tickets, as in the fp64 kernel (launch_rowsplit_gv)
-	int tick = env_int("SPMM_B200_TICKET", -1);
+	int tick = h->opt.ticket;
 	if (tick < 0) {
 		const double avg = h->m > 0 ? (double) h->nnz / (double) h->m : 1.0;
 		// measured on cfg2 (profiles/r1_f32_probe.md): k = 64 0.784 -> 0.698 ms, k = 128 1.339 -> 1.267 ms, k = 32 0.466 -> 0.493 ms
@@ -171,7 +348,15 @@ extern "C" int spmm_b200_run_device_f32(spmm_b200_f32_t* h, const float* b_dev, 
 	CU_TRY(cudaSetDevice(h->device));
 	cudaStream_t s = (cudaStream_t) stream;
 	CU_TRY(cudaEventRecord(h->ev0, s));
-	if (h->m > 0) {
+	if (h->m > 0 && h->variant == SPMM_B200_MERGE && merge_items_f32(k) > 0
+	    && (k < 4 || (((uintptr_t) b_dev | (uintptr_t) c_dev) % 16) == 0)) {
+		int n = launch_merge_f32(h, b_dev, c_dev, k, s);
+		if (n < 0) return n;
+	} else if (h->m > 0 && h->variant == SPMM_B200_BCSR && tf32_supports(h, k)
+	           && (((uintptr_t) b_dev | (uintptr_t) c_dev) % 16) == 0) {
+		int n = tf32_launch(h, b_dev, c_dev, k, s);
+		if (n < 0) return n;
+	} else if (h->m > 0) {
 		const bool aligned = ((uintptr_t) b_dev % 16) == 0 && ((uintptr_t) c_dev % 16) == 0;
 		// a group of 8 lanes covers one 128-byte line per 16-byte load (see profiles/r1_gvu_probe.md)
 		if (aligned && k == 16) launch_gv<4, 4, 4>(h, b_dev, c_dev, s);
@@ -237,6 +422,16 @@ extern "C" int spmm_b200_fetch_c_f32(spmm_b200_f32_t* h, float* y_host, int k)
 }
 
 extern "C" int64_t spmm_b200_rows_f32(const spmm_b200_f32_t* h) { return h ? h->m : -1; }
+extern "C" int spmm_b200_variant_f32(const spmm_b200_f32_t* h) { return h ? h->variant : SPMM_B200_EINVAL; }
+
+extern "C" int spmm_b200_set_option_f32(spmm_b200_f32_t* h, const char* name, int value)
+{
+	if (!h || !name) return SPMM_B200_EINVAL;
+	if (!strncmp(name, "SPMM_B200_", 10)) name += 10;
+	for (const OptionName& e : OPTION_TABLE)
+		if (!strcmp(name, e.name)) { h->opt.*(e.field) = value; return SPMM_B200_OK; }
+	return SPMM_B200_EINVAL;
+}
 extern "C" int64_t spmm_b200_nnz_f32(const spmm_b200_f32_t* h) { return h ? h->nnz : -1; }
 extern "C" int64_t spmm_b200_launch_count_f32(const spmm_b200_f32_t* h) { return h ? h->launches : -1; }
 

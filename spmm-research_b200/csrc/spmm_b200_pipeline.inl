@@ -551,7 +551,7 @@ extern "C" int spmm_b200_pipeline_create_f32(spmm_b200_pipeline_f32_t** out,
 		spmm_b200_pipeline_destroy_f32(p);
 		return e == cudaErrorMemoryAllocation ? SPMM_B200_ENOMEM : SPMM_B200_ECUDA;
 	}
-	rc = spmm_b200_create_f32(&p->mask, mask_ia, mask_ja, mask_a, m, m, nnz, n, device, SPMM_B200_B_ROWMAJOR);
+	rc = spmm_b200_create_f32(&p->mask, mask_ia, mask_ja, mask_a, m, m, nnz, n, device, SPMM_B200_ROWSPLIT, SPMM_B200_B_ROWMAJOR);
 	if (rc) { spmm_b200_pipeline_destroy_f32(p); return rc; }
 	*out = p;
 	return SPMM_B200_OK;
@@ -576,7 +576,7 @@ extern "C" int spmm_b200_pipeline_spmm_f32(spmm_b200_pipeline_f32_t* p, char typ
 		if (!(w.h && w.ia == ia && w.ja == ja && w.a == a && w.m == m && w.k == k && w.nnz == nnz)) {
 			if (w.h) { p->own_launches += w.h->launches; spmm_b200_destroy_f32(w.h); w.h = nullptr; }
 			w.have = false;
-			rc = spmm_b200_create_f32(&w.h, ia, ja, a, m, k, nnz, n, p->device, SPMM_B200_B_ROWMAJOR);
+			rc = spmm_b200_create_f32(&w.h, ia, ja, a, m, k, nnz, n, p->device, SPMM_B200_ROWSPLIT, SPMM_B200_B_ROWMAJOR);
 			if (rc) return rc;
 			if (!w.d_out) CU_TRY(cudaMalloc(&w.d_out, sizeof(float) * std::max<int64_t>(m * n, 1)));
 			w.ia = ia; w.ja = ja; w.a = a; w.m = m; w.k = k; w.nnz = nnz;
@@ -604,7 +604,7 @@ extern "C" int spmm_b200_pipeline_spmm_f32(spmm_b200_pipeline_f32_t* p, char typ
 		return SPMM_B200_OK;
 	}
 	spmm_b200_f32* h = nullptr;
-	rc = spmm_b200_create_f32(&h, ia, ja, a, m, k, nnz, n, p->device, SPMM_B200_B_ROWMAJOR);
+	rc = spmm_b200_create_f32(&h, ia, ja, a, m, k, nnz, n, p->device, SPMM_B200_ROWSPLIT, SPMM_B200_B_ROWMAJOR);
 	if (rc) return rc;
 	rc = ensure32(&p->d_tmp, &p->cap_tmp, (size_t) m * n);
 	if (!rc && m > 0) rc = spmm_b200_run_device_f32(h, p->d_x, p->d_tmp, n, p->stream);

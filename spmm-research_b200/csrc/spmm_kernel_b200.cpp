@@ -178,10 +178,11 @@ csr_to_format(INT_T * row_ptr, INT_T * col_ind, ValueType * values, long m, long
 	f->ja = col_ind;
 	f->a = values;
 #if DOUBLE == 0
-	(void) variant;
-	int rc = spmm_b200_create_f32(&f->handle, row_ptr, col_ind, values, m, n, nnz, k, d ? atoi(d) : 0, SPMM_B200_B_COLMAJOR);
+	// SPMM_B200_VARIANT=bcsr in an "_f" build = the TF32 tensor-core kernel for banded matrices (~1e-3 relative accuracy)
+	int rc = spmm_b200_create_f32(&f->handle, row_ptr, col_ind, values, m, n, nnz, k, d ? atoi(d) : 0, variant, SPMM_B200_B_COLMAJOR);
 	if (rc) die("csr_to_format", rc);
-	snprintf(f->name, sizeof(f->name), "B200_CSR_ROWSPLIT_F32");
+	const int vr = spmm_b200_variant_f32(f->handle);
+	snprintf(f->name, sizeof(f->name), "%s", vr == SPMM_B200_MERGE ? "B200_CSR_MERGE_F32" : vr == SPMM_B200_BCSR ? "B200_BLOCKED_TF32" : "B200_CSR_ROWSPLIT_F32");
 #else
 	static const char * names[] = {"B200_CSR_ROWSPLIT", "B200_CSR_MERGE", "B200_BCSR_DMMA", "B200_CSR", "B200_BCSR_FMA"};
 	const char * ng = getenv("SPMM_B200_NGPUS");

@@ -26,35 +26,81 @@
 
 namespace sb200 {
 
+// A lane's V columns of one dense row, for double and float operands alike: 16-byte pieces where V allows
+// (piece i of the group covers the contiguous bytes [i*G*16, (i+1)*G*16) of the row), scalar loads otherwise.
+template <typename T, int V> struct FragT { T v[V]; };
+
+template <typename T, int G, int V>
+__device__ __forceinline__ FragT<T, V> load_row_t(const T* __restrict__ B, int col, int lig, int ldb)
+{
+	constexpr int E = 16 / sizeof(T);            // elements per 16-byte piece
+	FragT<T, V> f;
+	const T* p = B + (size_t) col * ldb;
+	if constexpr (V % E == 0) {
+		#pragma unroll
+		for (int i = 0; i < V / E; i++) {
+			const uint4 t = __ldg(reinterpret_cast<const uint4*>(p) + i * G + lig);
+			memcpy(&f.v[i * E], &t, 16);
+		}
+	} else {
+		#pragma unroll
+		for (int v = 0; v < V; v++) f.v[v] = __ldg(p + lig * V + v);
+	}
+	return f;
+}
+
+template <typename T, int G, int V>
+__device__ __forceinline__ void store_row_t(T* __restrict__ C, size_t row, int lig, const T (&acc)[V], int ldc)
+{
+	constexpr int E = 16 / sizeof(T);
+	T* p = C + row * ldc;
+	if constexpr (V % E == 0) {
+		#pragma unroll
+		for (int i = 0; i < V / E; i++) {
+			uint4 t;
+			memcpy(&t, &acc[i * E], 16);
+			reinterpret_cast<uint4*>(p)[i * G + lig] = t;
+		}
+	} else {
+		#pragma unroll
+		for (int v = 0; v < V; v++) p[lig * V + v] = acc[v];
+	}
+}
+
+template <typename T> __device__ __forceinline__ T fma_t(T a, T b, T c);
+template <> __device__ __forceinline__ double fma_t<double>(double a, double b, double c) { return fma(a, b, c); }
+template <> __device__ __forceinline__ float fma_t<float>(float a, float b, float c) { return fmaf(a, b, c); }
+
 struct MergePlan {
 	int ntiles = 0;            // CTAs of the main kernel
 	int items = 0;             // merge items per tile
 	int2* d_tile = nullptr;    // [ntiles+1] (row, nnz) start coordinate of each tile
-	double* d_carry = nullptr; // [ntiles][k]
+	void* d_carry = nullptr;   // [ntiles][k] values (double or float)
 	int32_t* d_carry_row = nullptr; // [ntiles]
 	int carry_k = 0;
 };
 
-template <int G, int V, int IPG, int THREADS>
+template <int G, int V, int IPG, int THREADS, typename T = double>
 struct MergeCfg {
 	static constexpr int K = G * V;
 	static constexpr int NG = THREADS / G;
 	static constexpr int ITEMS = NG * IPG;
-	static constexpr size_t SMEM = (size_t) ITEMS * (sizeof(double) + 2 * sizeof(int32_t))
-	                               + (size_t) NG * K * sizeof(double) + (size_t) NG * sizeof(int32_t);
+	static constexpr size_t SMEM = (size_t) ITEMS * (sizeof(T) + 2 * sizeof(int32_t))
+	                               + (size_t) NG * K * sizeof(T) + (size_t) NG * sizeof(int32_t);
 };
 
-template <int G, int V, int IPG, int UNROLL, int THREADS>
+template <int G, int V, int IPG, int UNROLL, int THREADS, typename T = double>
 __global__ void __launch_bounds__(THREADS)
-spmm_merge_kernel(const int32_t* __restrict__ ia, const int32_t* __restrict__ ja, const double* __restrict__ a,
-                  const double* __restrict__ B, double* __restrict__ C,
-                  const int2* __restrict__ tile_coord, double* __restrict__ tile_carry, int32_t* __restrict__ tile_carry_row)
+spmm_merge_kernel(const int32_t* __restrict__ ia, const int32_t* __restrict__ ja, const T* __restrict__ a,
+                  const T* __restrict__ B, T* __restrict__ C,
+                  const int2* __restrict__ tile_coord, T* __restrict__ tile_carry, int32_t* __restrict__ tile_carry_row)
 {
-	using Cfg = MergeCfg<G, V, IPG, THREADS>;
+	using Cfg = MergeCfg<G, V, IPG, THREADS, T>;
 	constexpr int K = Cfg::K, NG = Cfg::NG, ITEMS = Cfg::ITEMS;
+	static_assert((ITEMS * sizeof(T)) % 16 == 0 && (NG * K * sizeof(T)) % 4 == 0, "shared-memory carve-up alignment");
 	extern __shared__ __align__(16) unsigned char smem_raw[];
-	double* s_a = reinterpret_cast<double*>(smem_raw);                 // [ITEMS]
-	double* s_carry = s_a + ITEMS;                                     // [NG][K]
+	T* s_a = reinterpret_cast<T*>(smem_raw);                           // [ITEMS]
+	T* s_carry = s_a + ITEMS;                                          // [NG][K]
 	int32_t* s_ja = reinterpret_cast<int32_t*>(s_carry + NG * K);      // [ITEMS]
 	int32_t* s_end = s_ja + ITEMS;                                     // [ITEMS] row ends, tile-local rows
 	int32_t* s_crow = s_end + ITEMS;                                   // [NG]
@@ -88,42 +134,42 @@ spmm_merge_kernel(const int32_t* __restrict__ ia, const int32_t* __restrict__ ja
 	const int row_e = gr[1];
 	const int je = gj[1];
 	int next_end = (row < row_e) ? s_end[row] - j0 : INT_MAX;
-	double acc[V];
+	T acc[V];
 	#pragma unroll
-	for (int v = 0; v < V; v++) acc[v] = 0.0;
+	for (int v = 0; v < V; v++) acc[v] = T(0);
 
 	for (int j = gj[0]; j < je; j += UNROLL) {
-		Frag<V> bb[UNROLL];
-		double vv[UNROLL];
+		FragT<T, V> bb[UNROLL];
+		T vv[UNROLL];
 		#pragma unroll
 		for (int u = 0; u < UNROLL; u++) {
 			const bool live = j + u < je;
 			const int jj = live ? j + u : je - 1;
-			vv[u] = live ? s_a[jj] : 0.0;
-			bb[u] = load_b<G, V>(B, s_ja[jj], lig, G * V);
+			vv[u] = live ? s_a[jj] : T(0);
+			bb[u] = load_row_t<T, G, V>(B, s_ja[jj], lig, G * V);
 		}
 		#pragma unroll
 		for (int u = 0; u < UNROLL; u++) {
 			if (j + u < je) {
 				while (j + u >= next_end) {      // rows that ended before this nonzero
-					store_c<G, V>(C, (size_t) (r0 + row), lig, acc, G * V);
+					store_row_t<T, G, V>(C, (size_t) (r0 + row), lig, acc, G * V);
 					#pragma unroll
-					for (int v = 0; v < V; v++) acc[v] = 0.0;
+					for (int v = 0; v < V; v++) acc[v] = T(0);
 					row++;
 					next_end = (row < row_e) ? s_end[row] - j0 : INT_MAX;
 				}
 				#pragma unroll
-				for (int v = 0; v < V; v++) acc[v] = fma(vv[u], bb[u].v[v], acc[v]);
+				for (int v = 0; v < V; v++) acc[v] = fma_t<T>(vv[u], bb[u].v[v], acc[v]);
 			}
 		}
 	}
 	for (; row < row_e; row++) {                 // row ends after the group's last nonzero
-		store_c<G, V>(C, (size_t) (r0 + row), lig, acc, G * V);
+		store_row_t<T, G, V>(C, (size_t) (r0 + row), lig, acc, G * V);
 		#pragma unroll
-		for (int v = 0; v < V; v++) acc[v] = 0.0;
+		for (int v = 0; v < V; v++) acc[v] = T(0);
 	}
 	// what is left belongs to tile-local row row_e, which ends in a later group or tile
-	store_c<G, V>(s_carry, (size_t) gid, lig, acc, G * V);
+	store_row_t<T, G, V>(s_carry, (size_t) gid, lig, acc, G * V);
 	if (lig == 0) s_crow[gid] = row_e;
 	__syncthreads();
 
@@ -131,7 +177,7 @@ spmm_merge_kernel(const int32_t* __restrict__ ia, const int32_t* __restrict__ ja
 		const int g = idx / K, n = idx % K;
 		const int crow = s_crow[g];
 		if (g > 0 && s_crow[g - 1] == crow) continue;        // not the head of its run
-		double sum = 0.0;
+		T sum = T(0);
 		for (int g2 = g; g2 < NG && s_crow[g2] == crow; g2++) sum += s_carry[g2 * K + n];
 		if (crow < nr) C[(size_t) (r0 + crow) * K + n] += sum; // row ended inside this tile
 		else tile_carry[(size_t) tile * K + n] = sum;          // crow == nr: leaves the tile
@@ -141,10 +187,10 @@ spmm_merge_kernel(const int32_t* __restrict__ ia, const int32_t* __restrict__ ja
 
 // Adds the tile carries to the rows they belong to.  A run of tiles with the same carry row
 // (a row longer than a tile) is summed in tile order by the thread group of its first tile.
-template <int THREADS>
+template <int THREADS, typename T = double>
 __global__ void __launch_bounds__(THREADS)
-spmm_merge_fixup_kernel(const double* __restrict__ tile_carry, const int32_t* __restrict__ tile_carry_row,
-                        int ntiles, int m, int k, double* __restrict__ C)
+spmm_merge_fixup_kernel(const T* __restrict__ tile_carry, const int32_t* __restrict__ tile_carry_row,
+                        int ntiles, int m, int k, T* __restrict__ C)
 {
 	const int64_t idx = (int64_t) blockIdx.x * THREADS + threadIdx.x;
 	if (idx >= (int64_t) ntiles * k) return;
@@ -152,7 +198,7 @@ spmm_merge_fixup_kernel(const double* __restrict__ tile_carry, const int32_t* __
 	const int row = tile_carry_row[t];
 	if (row >= m) return;
 	if (t > 0 && tile_carry_row[t - 1] == row) return;
-	double sum = 0.0;
+	T sum = T(0);
 	for (int t2 = t; t2 < ntiles && tile_carry_row[t2] == row; t2++) sum += tile_carry[(size_t) t2 * k + n];
 	C[(size_t) row * k + n] += sum;
 }

@@ -325,7 +325,8 @@ spmm_rowsplit_staged_kernel(const int32_t* __restrict__ ia, const int32_t* __res
 			for (int p = rs; p < re; p += NGW) {
 				const int lr = min(p + gid, R);                      // ticket-local row of my group (R: none)
 				const int js = __shfl_sync(0xffffffffu, iaD, lr);
-				const int je = lr < re ? __shfl_sync(0xffffffffu, iaD, min(lr + 1, R)) : js;
+				const int je_row = __shfl_sync(0xffffffffu, iaD, min(lr + 1, R));      // every lane shuffles: lr differs per group
+				const int je = lr < re ? je_row : js;
 				double acc[V];
 				#pragma unroll
 				for (int v = 0; v < V; v++) acc[v] = 0.0;

@@ -1,0 +1,247 @@
+// spmm_tf32_blocked.cuh -- fp32 SpMM for BANDED matrices on the 5th-generation tensor cores (tcgen05.mma kind::tf32,
+// accumulators in TMEM).  SURVEY 8(f) N3 / north_star kernel (3): "tensor cores only where dense blocks make it a
+// genuine contraction" -- this is the one place on the SpMM path where tcgen05 / TMEM applies (there is no FP64 kind).
+//
+// Idea.  A slab of 128 consecutive rows of a banded matrix (diagonal placement, SURVEY cfg 4) touches one narrow
+// window of columns [lo, hi].  Inside that window the slab is treated as a DENSE 128 x W matrix:
+//     C[slab, :] = A_dense[128 x W] * B[lo .. hi, :]          (W ~ band width + 128)
+// and B[lo .. hi, :] is a contiguous block of the row-major dense operand.  One CTA per slab walks the window in
+// chunks of KT = 32 columns:
+//   * the 128 threads (one per row) zero a 128 x KT stage and scatter their row's nonzeros of the chunk into it as TF32
+//     (cvt.rna), in the UMMA K-major core-matrix layout (8 rows x 16 bytes);
+//   * the matching KT rows of B (KT x N floats, contiguous in global memory) land in shared memory through cp.async
+//     (LDGSTS) in the UMMA MN-major core-matrix layout (8 k x 16 bytes) -- B is consumed in place, no transpose pass;
+//   * one thread issues KT/8 tcgen05.mma (M = 128, N = k, K = 8) that accumulate into N fp32 columns of TMEM, and
+//     tcgen05.commit releases the stage through an mbarrier when the tensor core has read it;
+//   * chunks no row has a nonzero in are skipped (block-wide min of the rows' next columns), so the cost follows the
+//     occupied part of the window;
+//   * epilogue: tcgen05.ld (32 lanes x 32 bit, 16 columns per instruction) -> registers -> C.
+// Several CTAs are resident per SM (32 KB of shared memory per stage, N of the 512 TMEM columns each), so one slab's
+// scatter / epilogue overlaps another's tensor work without warp specialisation.
+//
+// Numerics: A is rounded to TF32 (10 mantissa bits, round to nearest), B is read by the tensor core as TF32
+// (low 13 mantissa bits ignored), products are exact, accumulation is fp32 in TMEM.  Relative error ~1e-3 per term:
+// the tests state 4e-3 against the fp32 reference.  Therefore never chosen by AUTO: variant SPMM_B200_BCSR on an fp32 handle.
+#pragma once
+#include <stdint.h>
+#include <limits.h>
+#include <cuda_runtime.h>
+#include "ptx.cuh"
+
+namespace sb200 {
+
+struct Tf32Plan {
+	int2* d_win = nullptr;      // [nslabs] (first, last) column of the slab; first > last: the slab has no nonzero
+	int nslabs = 0;
+	double window_cols = 0;     // sum of the slabs' window widths (dense work = 128 * window_cols * k multiply-adds)
+};
+
+constexpr int TF32_M = 128;     // rows per slab = UMMA M
+constexpr int TF32_KT = 32;     // columns of A (rows of B) per stage
+
+__global__ void __launch_bounds__(TF32_M)
+tf32_window_kernel(const int32_t* __restrict__ ia, const int32_t* __restrict__ ja, int m, int2* __restrict__ win,
+                   unsigned long long* __restrict__ total)
+{
+	__shared__ int s_lo[4], s_hi[4];
+	const int r = blockIdx.x * TF32_M + threadIdx.x;
+	int lo = INT_MAX, hi = -1;
+	if (r < m) {
+		const int js = ia[r], je = ia[r + 1];
+		if (je > js) { lo = ja[js]; hi = ja[je - 1]; }      // columns are sorted inside a row
+	}
+	lo = __reduce_min_sync(0xffffffffu, lo);
+	hi = __reduce_max_sync(0xffffffffu, hi);
+	if ((threadIdx.x & 31) == 0) { s_lo[threadIdx.x >> 5] = lo; s_hi[threadIdx.x >> 5] = hi; }
+	__syncthreads();
+	if (threadIdx.x == 0) {
+		lo = min(min(s_lo[0], s_lo[1]), min(s_lo[2], s_lo[3]));
+		hi = max(max(s_hi[0], s_hi[1]), max(s_hi[2], s_hi[3]));
+		win[blockIdx.x] = make_int2(lo, hi);
+		if (hi >= lo) atomicAdd(total, (unsigned long long) (hi - lo + 1));
+	}
+}
+
+// ---- tcgen05 / TMEM wrappers ------------------------------------------------------------------------------------
+__device__ __forceinline__ void tmem_alloc(uint32_t smem_slot, uint32_t ncols)       // whole warp
+{
+	asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_slot), "r"(ncols) : "memory");
+	asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols)         // whole warp
+{
+	asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+// arrive on an mbarrier once every tcgen05.mma issued so far by this thread has completed (and released its operands)
+__device__ __forceinline__ void tc_commit(uint32_t bar)
+{
+	asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+// D[tmem] (+)= A[smem desc] * B[smem desc], TF32 inputs, fp32 accumulate; one thread issues for the CTA
+__device__ __forceinline__ void tc_mma_tf32(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate)
+{
+	asm volatile("{\n .reg .pred p;\n setp.ne.b32 p, %4, 0;\n"
+	             " tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n}"
+	             ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
+}
+// 16 consecutive fp32 columns of this thread's TMEM lane (warp w owns lanes 32w .. 32w+31)
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16])
+{
+	uint32_t r[16];
+	asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+	             : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+	               "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+	             : "r"(taddr));
+	asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+	#pragma unroll
+	for (int i = 0; i < 16; i++) v[i] = __uint_as_float(r[i]);
+}
+// 16-byte cp.async with zero fill: src_bytes = 0 writes zeros (rows of B beyond the matrix)
+__device__ __forceinline__ void cp_async16_zfill(uint32_t dst, const void* src, uint32_t src_bytes)
+{
+	asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
+}
+// bounded spin: a broken pipeline traps instead of hanging the GPU
+__device__ __forceinline__ void mbar_wait_bounded(uint32_t bar, uint32_t parity)
+{
+	for (uint32_t spin = 0; !mbar_try_wait(bar, parity); spin++)
+		if (spin > (1u << 24)) __trap();
+}
+
+// shared-memory matrix descriptor, no swizzle ("interleave"): 8 x 16-byte core matrices;
+// lbo / sbo = byte strides between core matrices (which one is which depends on the operand's major, see below)
+__device__ __forceinline__ uint64_t umma_desc(uint32_t smem_addr, uint32_t lbo, uint32_t sbo)
+{
+	return (uint64_t) ((smem_addr >> 4) & 0x3FFF) | ((uint64_t) ((lbo >> 4) & 0x3FFF) << 16)
+	       | ((uint64_t) ((sbo >> 4) & 0x3FFF) << 32) | (1ull << 46);      // bits 46-47: descriptor version 1 (sm_100)
+}
+
+template <int N, int STAGES>
+struct Tf32Cfg {
+	// A stage, K-major: element (r, kk) at (r/8)*SBO_A + (kk/4)*LBO_A + (r%8)*16 + (kk%4)*4
+	static constexpr int LBO_A = 128, SBO_A = (TF32_KT / 4) * 128, A_BYTES = TF32_M * TF32_KT * 4;
+	// B stage, MN-major: element (n, kk) at (n/4)*SBO_B + (kk/8)*LBO_B + (kk%8)*16 + (n%4)*4
+	static constexpr int LBO_B = 128, SBO_B = (TF32_KT / 8) * 128, B_BYTES = TF32_KT * N * 4;
+	static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+	static constexpr size_t SMEM = (size_t) STAGES * STAGE_BYTES + 128;          // + barriers, TMEM slot, chunk minima
+	// instruction descriptor: D = F32 (bits 4-5 = 1), A = B = TF32 (bits 7-9, 10-12 = 2), A K-major (bit 15 = 0),
+	// B MN-major (bit 16 = 1), N >> 3 at bits 17-22, M >> 4 at bits 24-28
+	static constexpr uint32_t IDESC = (1u << 4) | (2u << 7) | (2u << 10) | (1u << 16) | ((uint32_t) (N >> 3) << 17) | ((uint32_t) (TF32_M >> 4) << 24);
+};
+
+template <int N, int STAGES>
+__global__ void __launch_bounds__(TF32_M)
+spmm_tf32_blocked_kernel(const int32_t* __restrict__ ia, const int32_t* __restrict__ ja, const float* __restrict__ a,
+                         const float* __restrict__ B, float* __restrict__ C, const int2* __restrict__ win, int m, int c)
+{
+	using Cfg = Tf32Cfg<N, STAGES>;
+	constexpr int KT = TF32_KT;
+	extern __shared__ __align__(128) unsigned char tf_smem[];
+	const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+	const int slab = blockIdx.x;
+	const int row = slab * TF32_M + tid;
+	unsigned char* const ctl = tf_smem + (size_t) STAGES * Cfg::STAGE_BYTES;
+	const uint32_t smem_u = smem_u32(tf_smem), ctl_u = smem_u32(ctl);
+	const uint32_t bar_free = ctl_u;                 // STAGES barriers: stage consumed by the tensor core
+	const uint32_t bar_done = ctl_u + 8 * STAGES;    // accumulator complete
+	volatile uint32_t* const tmem_slot = reinterpret_cast<volatile uint32_t*>(ctl + 8 * STAGES + 8);
+	volatile int* const s_min = reinterpret_cast<volatile int*>(ctl + 8 * STAGES + 16);      // [2][4]
+
+	if (warp == 0) tmem_alloc(smem_u32(ctl + 8 * STAGES + 8), N);
+	if (tid == 0) {
+		#pragma unroll
+		for (int s = 0; s < STAGES; s++) mbar_init(bar_free + 8 * s, 1);
+		mbar_init(bar_done, 1);
+		asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+	}
+	tc_fence_before();
+	__syncthreads();
+	tc_fence_after();
+	const uint32_t tmem = *tmem_slot;
+
+	int j = 0, jend = 0;
+	if (row < m) { j = __ldg(ia + row); jend = __ldg(ia + row + 1); }
+	const int2 w = win[slab];
+	int kc = w.x;                                    // first column of the current chunk
+	int it = 0;
+	const bool any = w.y >= w.x;
+	while (any) {
+		const int stage = it % STAGES;
+		if (it >= STAGES) mbar_wait_bounded(bar_free + 8 * stage, (uint32_t) ((it / STAGES) - 1) & 1u);
+		unsigned char* const sA = tf_smem + (size_t) stage * Cfg::STAGE_BYTES;
+		const uint32_t sA_u = smem_u + stage * Cfg::STAGE_BYTES, sB_u = sA_u + Cfg::A_BYTES;
+		// B rows kc .. kc+KT-1: 16-byte pieces, a warp covers 8 rows x 64 bytes per instruction
+		#pragma unroll
+		for (int i = 0; i < KT * N / 4 / TF32_M; i++) {
+			const int q = i * TF32_M + tid;
+			const int t = q >> 5;
+			const int kk = (t % (KT / 8)) * 8 + (q & 7);
+			const int nc = (t / (KT / 8)) * 4 + ((q >> 3) & 3);
+			const int brow = kc + kk;
+			const bool ok = brow < c;
+			cp_async16_zfill(sB_u + nc * Cfg::SBO_B + (kk >> 3) * Cfg::LBO_B + (kk & 7) * 16,
+			                 B + (size_t) (ok ? brow : 0) * N + nc * 4, ok ? 16u : 0u);
+		}
+		cp_async_commit();
+		// my row of the A stage: zero, then scatter this chunk's nonzeros (TF32, round to nearest)
+		unsigned char* const myrow = sA + (tid >> 3) * Cfg::SBO_A + (tid & 7) * 16;
+		#pragma unroll
+		for (int q = 0; q < KT / 4; q++) *reinterpret_cast<uint4*>(myrow + q * Cfg::LBO_A) = make_uint4(0, 0, 0, 0);
+		int col = j < jend ? __ldg(ja + j) : INT_MAX;
+		while (col < kc + KT) {
+			const int kk = col - kc;
+			uint32_t bits;
+			asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(bits) : "f"(__ldg(a + j)));
+			*reinterpret_cast<uint32_t*>(myrow + (kk >> 2) * Cfg::LBO_A + (kk & 3) * 4) = bits;
+			j++;
+			col = j < jend ? __ldg(ja + j) : INT_MAX;
+		}
+		const int wmin = __reduce_min_sync(0xffffffffu, col);            // next column any row of the warp still has
+		if (lane == 0) s_min[(it & 1) * 4 + warp] = wmin;
+		cp_async_wait<0>();
+		asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // st.shared / cp.async data -> visible to the tensor core
+		tc_fence_before();
+		__syncthreads();
+		if (tid == 0) {
+			tc_fence_after();
+			#pragma unroll
+			for (int ks = 0; ks < KT / 8; ks++)
+				tc_mma_tf32(tmem, umma_desc(sA_u + ks * 2 * Cfg::LBO_A, Cfg::LBO_A, Cfg::SBO_A),
+				            umma_desc(sB_u + ks * Cfg::LBO_B, Cfg::LBO_B, Cfg::SBO_B), Cfg::IDESC, (it > 0 || ks > 0) ? 1u : 0u);
+			tc_commit(bar_free + 8 * stage);
+		}
+		const int nxt = min(min(s_min[(it & 1) * 4], s_min[(it & 1) * 4 + 1]), min(s_min[(it & 1) * 4 + 2], s_min[(it & 1) * 4 + 3]));
+		it++;
+		if (nxt == INT_MAX) break;
+		kc = nxt;
+	}
+	if (any) {
+		if (tid == 0) tc_commit(bar_done);
+		mbar_wait_bounded(bar_done, 0);
+		tc_fence_after();
+	}
+	// epilogue: thread = row, 16 columns per TMEM load
+	if (any) {
+		#pragma unroll 1
+		for (int c0 = 0; c0 < N; c0 += 16) {
+			float v[16];
+			tmem_ld16(tmem + ((uint32_t) (warp * 32) << 16) + c0, v);
+			if (row < m) {
+				float4* dst = reinterpret_cast<float4*>(C + (size_t) row * N + c0);
+				#pragma unroll
+				for (int q = 0; q < 4; q++) dst[q] = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+			}
+		}
+	} else if (row < m) {
+		float4* dst = reinterpret_cast<float4*>(C + (size_t) row * N);
+		#pragma unroll 1
+		for (int q = 0; q < N / 4; q++) dst[q] = make_float4(0.f, 0.f, 0.f, 0.f);
+	}
+	tc_fence_before();
+	__syncthreads();
+	if (warp == 0) tmem_dealloc(tmem, N);
+}
+
+} // namespace sb200

@@ -46,7 +46,7 @@ def test_gpu_f32_all_k(pkg, L, k):
     m, c = 4000, 3500
     ia, ja, a, x = case(m, c, 9.0, k, k, long_row=1500)
     y_ref = L.spmm_oracle_f32(ia, ja, a, m, c, x, k).astype(np.float64)
-    mf = pkg.csr_to_format_f32(ia, ja, a, m, c, len(ja), k)
+    mf = pkg.csr_to_format_f32(ia, ja, a, m, c, len(ja), k, variant=pkg.ROWSPLIT)
     y = np.full(m * k, np.nan, np.float32); mf.spmm(x, y, k)
     assert mf.last_kernel_ms() > 0 and mf.launch_count() >= 2
     mf.close()
@@ -54,7 +54,7 @@ def test_gpu_f32_all_k(pkg, L, k):
     assert rel_err(y, y_ref) <= F32_TOL, k
     # row-major B gives the same result
     x_rm = np.ascontiguousarray(x.reshape(k, c).T).ravel()
-    mf = pkg.csr_to_format_f32(ia, ja, a, m, c, len(ja), k, b_layout=pkg.B_ROWMAJOR)
+    mf = pkg.csr_to_format_f32(ia, ja, a, m, c, len(ja), k, variant=pkg.ROWSPLIT, b_layout=pkg.B_ROWMAJOR)
     y2 = np.full(m * k, np.nan, np.float32); mf.spmm(x_rm, y2, k); mf.close()
     assert np.array_equal(y, y2)
 
@@ -108,3 +108,84 @@ def test_reference_harness_dropin_f_build(pkg):
     row = r.stderr.strip().splitlines()[-1].split(",")
     assert row[0] == "synthetic" and row[6] == "999475" and row[23] == "B200_CSR_ROWSPLIT_F32"
     assert float(row[25]) > 0
+
+
+F32_MERGE_TOL = 2e-5     # merge-path re-associates a row's sum at the carries: fp32, rows of up to 1500 positive terms
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("k", [1, 2, 4, 8, 16, 32, 64, 128, 20])
+def test_gpu_f32_merge_path(pkg, L, k):
+    """fp32 merge-path (a skewed matrix in an "_f" build serialised on one lane group): the merge kernel of
+    spmm_merge.cuh instantiated for float.  AUTO takes it for the skewed matrix; k without an instantiation (20) falls
+    back to row-split."""
+    m, c = 4000, 3500
+    ia, ja, a, x = case(m, c, 9.0, 50 + k, k, long_row=1500)
+    y_ref = L.spmm_oracle_f32(ia, ja, a, m, c, x, k).astype(np.float64)
+    for variant in (pkg.MERGE, pkg.AUTO):
+        mf = pkg.csr_to_format_f32(ia, ja, a, m, c, len(ja), k, variant=variant)
+        assert mf.format_name == "B200_CSR_MERGE_F32"
+        y = np.full(m * k, np.nan, np.float32); mf.spmm(x, y, k); mf.close()
+        assert not np.isnan(y).any()
+        assert rel_err(y, y_ref) <= F32_MERGE_TOL, (k, variant)
+    # ragged shapes: no rows, no nonzeros, one huge row
+    for ia2, ja2, a2, m2, c2 in ((np.zeros(1, np.int32), np.zeros(0, np.int32), np.zeros(0, np.float32), 0, 5),
+                                 (np.zeros(8, np.int32), np.zeros(0, np.int32), np.zeros(0, np.float32), 7, 5),
+                                 (np.array([0, 3000], np.int32), np.arange(3000, dtype=np.int32), np.ones(3000, np.float32), 1, 3000)):
+        x2 = np.random.default_rng(1).random(c2 * k, dtype=np.float32)
+        mf = pkg.csr_to_format_f32(ia2, ja2, a2, m2, c2, len(ja2), k, variant=pkg.MERGE)
+        y = np.full(m2 * k, np.nan, np.float32); mf.spmm(x2, y, k); mf.close()
+        y_ref2 = L.spmm_oracle_f32(ia2, ja2, a2, m2, c2, x2, k).astype(np.float64)
+        assert rel_err(y, y_ref2) <= 1e-4 and not np.isnan(y).any()
+
+
+TF32_TOL = 4e-3          # TF32 operands (10 mantissa bits: A rounded to nearest, B truncated by the tensor core), fp32 accumulate
+
+
+def banded(m, c, band, per_row, seed, empty_rows=()):
+    """rows with `per_row` nonzeros inside a band of `band` columns around the diagonal (cfg4's structure, small)"""
+    rng = np.random.default_rng(seed)
+    cols = []
+    for i in range(m):
+        if i in empty_rows:
+            cols.append(np.zeros(0, np.int64))
+            continue
+        centre = i * c // max(m, 1)
+        lo = max(0, min(c - band, centre - band // 2))
+        cols.append(lo + np.sort(rng.choice(band, min(per_row, band), replace=False)))
+    ia = np.zeros(m + 1, np.int32); ia[1:] = np.cumsum([len(x) for x in cols])
+    ja = np.concatenate(cols).astype(np.int32) if m else np.zeros(0, np.int32)
+    a = (rng.random(len(ja)) + 0.05).astype(np.float32)
+    return ia, ja, a
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("k", [32, 64, 128])
+def test_gpu_tf32_blocked_kernel(pkg, L, k):
+    """N3: the TF32 blocked kernel (tcgen05.mma kind::tf32, accumulators in TMEM) on banded matrices, against the fp32
+    reference restatement with the stated TF32 tolerance.  Shapes: m not a multiple of the 128-row slab, empty rows, a
+    slab with no nonzero at all, windows that touch the last column, a window far wider than a stage (chunk skipping)."""
+    cases = [banded(5003, 4000, 200, 40, 1, empty_rows=set(range(256, 384)) | {5, 77, 5002}),
+             banded(300, 300, 64, 20, 2),
+             banded(128, 5000, 48, 48, 3)]
+    ia, ja, a = random_csr(700, 20000, 6.0, seed=4)                    # not banded: windows of ~20000 columns, mostly empty chunks
+    cases.append((ia, ja, (np.abs(a) + 0.05).astype(np.float32)))
+    for ia, ja, a in cases:
+        m = len(ia) - 1
+        c = int(ja.max()) + 1
+        x = np.random.default_rng(k).random(c * k, dtype=np.float32)
+        y_ref = L.spmm_oracle_f32(ia, ja, a, m, c, x, k).astype(np.float64)
+        mf = pkg.csr_to_format_f32(ia, ja, a, m, c, len(ja), k, variant=pkg.BCSR)
+        assert mf.format_name == "B200_BLOCKED_TF32"
+        for rep in range(2):
+            y = np.full(m * k, np.nan, np.float32); mf.spmm(x, y, k)
+            assert not np.isnan(y).any()
+            assert rel_err(y, y_ref) <= TF32_TOL, (k, m, rep)
+        mf.close()
+    # AUTO never rounds to TF32; k without an instantiation runs the fp32 row-split kernel (bit-exact again)
+    ia, ja, a = cases[1]
+    x = np.random.default_rng(0).random(300 * 16, dtype=np.float32)
+    mf = pkg.csr_to_format_f32(ia, ja, a, 300, 300, len(ja), 16, variant=pkg.BCSR)
+    y = np.full(300 * 16, np.nan, np.float32); mf.spmm(x, y, 16); mf.close()
+    assert rel_err(y, L.spmm_oracle_f32(ia, ja, a, 300, 300, x, 16).astype(np.float64)) <= F32_TOL
+    assert pkg.csr_to_format_f32(ia, ja, a, 300, 300, len(ja), 32).format_name == "B200_CSR_ROWSPLIT_F32"
