@@ -59,7 +59,7 @@ __device__ __forceinline__ void store_row_t(T* __restrict__ C, size_t row, int l
 		for (int i = 0; i < V / E; i++) {
 			uint4 t;
 			memcpy(&t, &acc[i * E], 16);
-			reinterpret_cast<uint4*>(p)[i * G + lig] = t;
+			reinterpret_cast<uint4*>(p)[i * G + lig] = t;      // (also used for the shared-memory carries: plain store)
 		}
 	} else {
 		#pragma unroll
@@ -70,6 +70,10 @@ __device__ __forceinline__ void store_row_t(T* __restrict__ C, size_t row, int l
 template <typename T> __device__ __forceinline__ T fma_t(T a, T b, T c);
 template <> __device__ __forceinline__ double fma_t<double>(double a, double b, double c) { return fma(a, b, c); }
 template <> __device__ __forceinline__ float fma_t<float>(float a, float b, float c) { return fmaf(a, b, c); }
+
+#ifndef MERGE_MIN_CTAS
+#define MERGE_MIN_CTAS 4      // 64 registers: 4 resident CTAs per SM (ncu r2b: 72 registers = 3 CTAs, 36 % warps active)
+#endif
 
 struct MergePlan {
 	int ntiles = 0;            // CTAs of the main kernel
@@ -90,7 +94,7 @@ struct MergeCfg {
 };
 
 template <int G, int V, int IPG, int UNROLL, int THREADS, typename T = double>
-__global__ void __launch_bounds__(THREADS)
+__global__ void __launch_bounds__(THREADS, MERGE_MIN_CTAS)
 spmm_merge_kernel(const int32_t* __restrict__ ia, const int32_t* __restrict__ ja, const T* __restrict__ a,
                   const T* __restrict__ B, T* __restrict__ C,
                   const int2* __restrict__ tile_coord, T* __restrict__ tile_carry, int32_t* __restrict__ tile_carry_row)
@@ -110,10 +114,11 @@ spmm_merge_kernel(const int32_t* __restrict__ ia, const int32_t* __restrict__ ja
 	const int r0 = c0.x, j0 = c0.y, r1 = c1.x, j1 = c1.y;
 	const int nr = r1 - r0, nn = j1 - j0;                              // nr + nn <= ITEMS
 
-	for (int i = threadIdx.x; i < nr; i += THREADS) s_end[i] = __ldg(ia + r0 + 1 + i);
+	// the A stream is read once: streaming loads keep it from displacing the gathered B rows in L2
+	for (int i = threadIdx.x; i < nr; i += THREADS) s_end[i] = __ldcs(ia + r0 + 1 + i);
 	for (int i = threadIdx.x; i < nn; i += THREADS) {
-		s_ja[i] = __ldg(ja + j0 + i);
-		s_a[i] = __ldg(a + j0 + i);
+		s_ja[i] = __ldcs(ja + j0 + i);
+		s_a[i] = __ldcs(a + j0 + i);
 	}
 	__syncthreads();
 

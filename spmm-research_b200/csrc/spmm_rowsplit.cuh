@@ -66,9 +66,11 @@ __device__ __forceinline__ void store_c(double* __restrict__ C, size_t row, int 
 	if constexpr (V == 1) {
 		p[lig] = acc[0];
 	} else {
+		// streaming store (st.global.cs): C is written once and never read by the kernel -- it must not evict the B rows
+		// the gathers want to find in L2 (cfg5-large: 2.1 GB of C per 32-column slice against a 107 MB window of B)
 		#pragma unroll
 		for (int i = 0; i < V / 2; i++)
-			reinterpret_cast<double2*>(p)[i * G + lig] = make_double2(acc[2 * i], acc[2 * i + 1]);
+			__stcs(reinterpret_cast<double2*>(p) + i * G + lig, make_double2(acc[2 * i], acc[2 * i + 1]));
 	}
 }
 
@@ -109,7 +111,8 @@ __device__ __forceinline__ void row_sweep(const int32_t* __restrict__ ia, const 
 			if (rem_warp <= 0) break;
 			int cj = 0;
 			double ca = 0.0;
-			if (lig < rem) { cj = __ldg(ja + j + lig); ca = __ldg(a + j + lig); }
+			// the A stream is read exactly once: streaming loads (ld.global.cs, evict-first) keep it from displacing B in L2
+			if (lig < rem) { cj = __ldcs(ja + j + lig); ca = __ldcs(a + j + lig); }
 			const int cnt = min(rem_warp, G);
 			// at most G/U steps: unrolled so that the shuffle source lanes are immediates
 			#pragma unroll
@@ -214,8 +217,9 @@ __device__ __forceinline__ void staged_row(const int32_t* __restrict__ sj, const
 		#pragma unroll
 		for (int i = 0; i < U; i++)
 			if (j + i < je) cc[i] = sj[j + i - offj];
-		// all U gathers are issued before the first multiply (predicated like row_sweep: with unconditional loads
-		// the compiler re-used the destination registers and kept only two B rows in flight)
+		// all U gathers are issued before the first multiply.  Predicated like row_sweep: with unconditional loads (an
+		// unpredicated main loop + tail was tried) ptxas interleaves the multiplies with the loads under the 64-register
+		// cap and a group keeps only ~2 B rows in flight.
 		#pragma unroll
 		for (int i = 0; i < U; i++)
 			if (j + i < je) bb[i] = load_b<G, V, LD>(B, cc[i], lig, ldb);

@@ -89,6 +89,11 @@ def test_gpu_f32_generated_matrix(pkg, L):
         y_ref = L.spmm_oracle_f32(ia, ja, a, m, c, x, k).astype(np.float64)
         mf = pkg.csr_to_format_f32(ia, ja, a, m, c, len(ja), k)
         y = np.empty(m * k, np.float32); mf.spmm(x, y, k); mf.close()
+        # max row 20 040 against a mean of 20: AUTO takes merge-path, which re-associates the long rows' sums
+        assert mf.format_name == "B200_CSR_MERGE_F32"
+        assert rel_err(y, y_ref) <= 2e-5
+        mf = pkg.csr_to_format_f32(ia, ja, a, m, c, len(ja), k, variant=pkg.ROWSPLIT)
+        y = np.empty(m * k, np.float32); mf.spmm(x, y, k); mf.close()
         assert rel_err(y, y_ref) <= F32_TOL
 
 
