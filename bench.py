@@ -443,7 +443,7 @@ def gpu_arm(args, ia, ja, a, m, c, k, nnz, workload_desc):
                      "touched_b_bytes": touched_b,
                      "bytes_model": "12*nnz + 4*(m+1) + 8*k*c + 8*k*m (SURVEY 8(d))" if world == 1 else
                                     "rank 0 shard: 12*nnz_g + 4*(m_g+1) + touched B window + 8*k*m_g",
-                     "l2_gather": {"bytes": gather_bytes, "achieved_tbs": gather_tbs, "ceiling_tbs": L2_GATHER_CEILING_TBS,
+                     "l2_gather": None if "BCSR" in mf.format_name else {"bytes": gather_bytes, "achieved_tbs": gather_tbs, "ceiling_tbs": L2_GATHER_CEILING_TBS,
                                    "frac": gather_tbs / L2_GATHER_CEILING_TBS,
                                    "note": "nnz*8k bytes of B rows cross L2->SM per launch; ceiling = pure gather of random "
                                            "256-byte rows from an L2-resident window (scripts/gather_probe.cu); it is the "

@@ -11,8 +11,10 @@
 using namespace sb200;
 #define CK(x) do { cudaError_t e = (x); if (e != cudaSuccess) { printf("%s:%d %s\n", __FILE__, __LINE__, cudaGetErrorString(e)); exit(1); } } while (0)
 
-// variant bits: 1 = swap LBO/SBO in the A descriptor, 2 = swap in the B descriptor, 4 = B stored K-major (b_major = 0),
-// 8 = no K advance inside the stage (one MMA only, K = 8)
+// variant bits: 1 = swap LBO/SBO in the A descriptor, 2 = swap in the B descriptor, 4 = B stored MN-major (b_major = 1,
+// element (n, kk) at (n/4)*512 + (kk/8)*128 + (kk%8)*16 + (n%4)*4 -- the form cp.async could fill without a transpose),
+// 8 = no K advance inside the stage (one MMA only, K = 8).  Variant 0 is the product kernel's layout.
+// Result on B200 (profiles/r2_tf32_probe.md): K-major B exact; every MN-major variant returns all zeros.
 template <int N>
 __global__ void __launch_bounds__(128) probe(const float* __restrict__ A, const float* __restrict__ B, float* __restrict__ D, int variant)
 {
@@ -27,19 +29,20 @@ __global__ void __launch_bounds__(128) probe(const float* __restrict__ A, const 
 	if (tid == 0) { mbar_init(bar, 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
 	tc_fence_before(); __syncthreads(); tc_fence_after();
 	const uint32_t tmem = *slot;
-	const bool b_kmajor = variant & 4;
+	const bool b_kmajor = !(variant & 4);
+	constexpr int MN_LBO = 128, MN_SBO = (TF32_KT / 8) * 128;
 	// A: row tid
 	for (int kk = 0; kk < KT; kk++) {
 		uint32_t bits;
 		asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(bits) : "f"(A[tid * KT + kk]));
-		*reinterpret_cast<uint32_t*>(sm + (tid >> 3) * Cfg::SBO_A + (kk >> 2) * Cfg::LBO_A + (tid & 7) * 16 + (kk & 3) * 4) = bits;
+		*reinterpret_cast<uint32_t*>(sm + (tid >> 3) * Cfg::SBO_A + (kk >> 2) * Cfg::LBO + (tid & 7) * 16 + (kk & 3) * 4) = bits;
 	}
 	// B: element (kk, n)
 	for (int e = tid; e < KT * N; e += 128) {
 		const int kk = e / N, n = e % N;
 		uint32_t off;
-		if (!b_kmajor) off = (n >> 2) * Cfg::SBO_B + (kk >> 3) * Cfg::LBO_B + (kk & 7) * 16 + (n & 3) * 4;
-		else off = (n >> 3) * ((KT / 4) * 128) + (kk >> 2) * 128 + (n & 7) * 16 + (kk & 3) * 4;       // K-major like A
+		if (!b_kmajor) off = (n >> 2) * MN_SBO + (kk >> 3) * MN_LBO + (kk & 7) * 16 + (n & 3) * 4;
+		else off = (n >> 3) * Cfg::SBO_B + (kk >> 2) * Cfg::LBO + (n & 7) * 16 + (kk & 3) * 4;       // K-major like A
 		*reinterpret_cast<float*>(sm + Cfg::A_BYTES + off) = B[e];
 	}
 	asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -47,17 +50,15 @@ __global__ void __launch_bounds__(128) probe(const float* __restrict__ A, const 
 	if (tid == 0) {
 		tc_fence_after();
 		uint32_t idesc = Cfg::IDESC;
-		if (b_kmajor) idesc &= ~(1u << 16);
+		if (!b_kmajor) idesc |= 1u << 16;
 		const int nk = (variant & 8) ? 1 : KT / 8;
 		for (int ks = 0; ks < nk; ks++) {
-			const uint32_t a_lbo = (variant & 1) ? Cfg::SBO_A : Cfg::LBO_A, a_sbo = (variant & 1) ? Cfg::LBO_A : Cfg::SBO_A;
-			uint64_t ad = umma_desc(sA_u + ks * 2 * Cfg::LBO_A, a_lbo, a_sbo), bd;
+			const uint32_t a_lbo = (variant & 1) ? Cfg::SBO_A : Cfg::LBO, a_sbo = (variant & 1) ? Cfg::LBO : Cfg::SBO_A;
+			uint64_t ad = umma_desc(sA_u + ks * 2 * Cfg::LBO, a_lbo, a_sbo), bd;
 			if (!b_kmajor) {
-				const uint32_t b_lbo = (variant & 2) ? Cfg::SBO_B : Cfg::LBO_B, b_sbo = (variant & 2) ? Cfg::LBO_B : Cfg::SBO_B;
-				bd = umma_desc(sB_u + ks * Cfg::LBO_B, b_lbo, b_sbo);
+				bd = umma_desc(sB_u + ks * MN_LBO, (variant & 2) ? MN_SBO : MN_LBO, (variant & 2) ? MN_LBO : MN_SBO);
 			} else {
-				const uint32_t l = 128, sb = (KT / 4) * 128;
-				bd = umma_desc(sB_u + ks * 2 * 128, (variant & 2) ? sb : l, (variant & 2) ? l : sb);
+				bd = umma_desc(sB_u + ks * 2 * Cfg::LBO, (variant & 2) ? Cfg::SBO_B : Cfg::LBO, (variant & 2) ? Cfg::LBO : Cfg::SBO_B);
 			}
 			tc_mma_tf32(tmem, ad, bd, idesc, ks > 0 ? 1u : 0u);
 		}
@@ -95,7 +96,7 @@ void run(int variant)
 	CK(cudaMemcpy(D.data(), dD, D.size() * 4, cudaMemcpyDeviceToHost));
 	int bad = 0, zero = 0; double worst = 0;
 	for (size_t i = 0; i < D.size(); i++) { if (D[i] != R[i]) bad++; if (D[i] == 0.f) zero++; worst = fmax(worst, fabs((double) D[i] - R[i])); }
-	printf("N=%3d variant=%2d (a_swap=%d b_swap=%d b_kmajor=%d oneK=%d): mismatches %5d / %d, zeros %d, max abs diff %.1f | D[0..3]=%.0f %.0f %.0f %.0f ref %.0f %.0f %.0f %.0f | D[row1]=%.0f ref %.0f\n",
+	printf("N=%3d variant=%2d (a_swap=%d b_swap=%d b_mnmajor=%d oneK=%d): mismatches %5d / %d, zeros %d, max abs diff %.1f | D[0..3]=%.0f %.0f %.0f %.0f ref %.0f %.0f %.0f %.0f | D[row1]=%.0f ref %.0f\n",
 	       N, variant, variant & 1, (variant >> 1) & 1, (variant >> 2) & 1, (variant >> 3) & 1, bad, (int) D.size(), zero, worst,
 	       D[0], D[1], D[2], D[3], R[0], R[1], R[2], R[3], D[N], R[N]);
 	cudaFree(dA); cudaFree(dB); cudaFree(dD);
@@ -104,7 +105,7 @@ void run(int variant)
 int main()
 {
 	for (int v = 0; v < 16; v++) run<128>(v);
-	for (int v = 0; v < 4; v++) run<32>(v);
+	run<32>(0); run<32>(4);
 	run<64>(0);
 	return 0;
 }

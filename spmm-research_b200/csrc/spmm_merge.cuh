@@ -72,7 +72,7 @@ template <> __device__ __forceinline__ double fma_t<double>(double a, double b, 
 template <> __device__ __forceinline__ float fma_t<float>(float a, float b, float c) { return fmaf(a, b, c); }
 
 #ifndef MERGE_MIN_CTAS
-#define MERGE_MIN_CTAS 4      // 64 registers: 4 resident CTAs per SM (ncu r2b: 72 registers = 3 CTAs, 36 % warps active)
+#define MERGE_MIN_CTAS 1      // 4 (64 registers, 4 CTAs per SM instead of 3) together with streaming loads measured 4-7 % slower on cfg3a / cfg3b (r2c)
 #endif
 
 struct MergePlan {
@@ -114,11 +114,10 @@ spmm_merge_kernel(const int32_t* __restrict__ ia, const int32_t* __restrict__ ja
 	const int r0 = c0.x, j0 = c0.y, r1 = c1.x, j1 = c1.y;
 	const int nr = r1 - r0, nn = j1 - j0;                              // nr + nn <= ITEMS
 
-	// the A stream is read once: streaming loads keep it from displacing the gathered B rows in L2
-	for (int i = threadIdx.x; i < nr; i += THREADS) s_end[i] = __ldcs(ia + r0 + 1 + i);
+	for (int i = threadIdx.x; i < nr; i += THREADS) s_end[i] = __ldg(ia + r0 + 1 + i);
 	for (int i = threadIdx.x; i < nn; i += THREADS) {
-		s_ja[i] = __ldcs(ja + j0 + i);
-		s_a[i] = __ldcs(a + j0 + i);
+		s_ja[i] = __ldg(ja + j0 + i);
+		s_a[i] = __ldg(a + j0 + i);
 	}
 	__syncthreads();
 

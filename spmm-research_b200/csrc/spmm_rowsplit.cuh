@@ -66,11 +66,11 @@ __device__ __forceinline__ void store_c(double* __restrict__ C, size_t row, int 
 	if constexpr (V == 1) {
 		p[lig] = acc[0];
 	} else {
-		// streaming store (st.global.cs): C is written once and never read by the kernel -- it must not evict the B rows
-		// the gathers want to find in L2 (cfg5-large: 2.1 GB of C per 32-column slice against a 107 MB window of B)
+		// (streaming stores / loads -- st.global.cs for C, ld.global.cs for the A stream -- were measured in round 2 to keep
+		// B in L2 on the large-window workloads: no gain on cfg5-large, 5-8 % slower on cfg2 bw 0.3 / 1; plain accesses stay)
 		#pragma unroll
 		for (int i = 0; i < V / 2; i++)
-			__stcs(reinterpret_cast<double2*>(p) + i * G + lig, make_double2(acc[2 * i], acc[2 * i + 1]));
+			reinterpret_cast<double2*>(p)[i * G + lig] = make_double2(acc[2 * i], acc[2 * i + 1]);
 	}
 }
 
@@ -111,8 +111,7 @@ __device__ __forceinline__ void row_sweep(const int32_t* __restrict__ ia, const 
 			if (rem_warp <= 0) break;
 			int cj = 0;
 			double ca = 0.0;
-			// the A stream is read exactly once: streaming loads (ld.global.cs, evict-first) keep it from displacing B in L2
-			if (lig < rem) { cj = __ldcs(ja + j + lig); ca = __ldcs(a + j + lig); }
+			if (lig < rem) { cj = __ldg(ja + j + lig); ca = __ldg(a + j + lig); }
 			const int cnt = min(rem_warp, G);
 			// at most G/U steps: unrolled so that the shuffle source lanes are immediates
 			#pragma unroll

@@ -9,8 +9,10 @@
 // chunks of KT = 32 columns:
 //   * the 128 threads (one per row) zero a 128 x KT stage and scatter their row's nonzeros of the chunk into it as TF32
 //     (cvt.rna), in the UMMA K-major core-matrix layout (8 rows x 16 bytes);
-//   * the matching KT rows of B (KT x N floats, contiguous in global memory) land in shared memory through cp.async
-//     (LDGSTS) in the UMMA MN-major core-matrix layout (8 k x 16 bytes) -- B is consumed in place, no transpose pass;
+//   * the matching KT rows of B (KT x N floats, contiguous in global memory) are read with coalesced 16-byte loads and
+//     transposed 4 x 4 in registers into the same K-major core-matrix layout (the tensor core takes B as N x K, K
+//     contiguous; the MN-major form, which would let cp.async drop B rows in unchanged, returned zeros for kind::tf32 with
+//     un-swizzled core matrices on this hardware -- scripts/umma_probe.cu, profiles/r2_tf32_probe.md);
 //   * one thread issues KT/8 tcgen05.mma (M = 128, N = k, K = 8) that accumulate into N fp32 columns of TMEM, and
 //     tcgen05.commit releases the stage through an mbarrier when the tensor core has read it;
 //   * chunks no row has a nonzero in are skipped (block-wide min of the rows' next columns), so the cost follows the
@@ -120,15 +122,18 @@ __device__ __forceinline__ uint64_t umma_desc(uint32_t smem_addr, uint32_t lbo, 
 
 template <int N, int STAGES>
 struct Tf32Cfg {
-	// A stage, K-major: element (r, kk) at (r/8)*SBO_A + (kk/4)*LBO_A + (r%8)*16 + (kk%4)*4
-	static constexpr int LBO_A = 128, SBO_A = (TF32_KT / 4) * 128, A_BYTES = TF32_M * TF32_KT * 4;
-	// B stage, MN-major: element (n, kk) at (n/4)*SBO_B + (kk/8)*LBO_B + (kk%8)*16 + (n%4)*4
-	static constexpr int LBO_B = 128, SBO_B = (TF32_KT / 8) * 128, B_BYTES = TF32_KT * N * 4;
+	// Both operands K-major, un-swizzled 8 x 16-byte core matrices:
+	//   A stage: element (r, kk) at (r/8)*SBO_A + (kk/4)*LBO + (r%8)*16 + (kk%4)*4        (r = row of the slab)
+	//   B stage: element (n, kk) at (n/8)*SBO_B + (kk/4)*LBO + (n%8)*16 + (kk%4)*4        (n = dense column)
+	// SBO_B is 16 bytes more than a packed group so that the transposing 16-byte stores of a quarter-warp hit 8 different
+	// bank groups.
+	static constexpr int LBO = 128, SBO_A = (TF32_KT / 4) * 128, SBO_B = (TF32_KT / 4) * 128 + 16;
+	static constexpr int A_BYTES = (TF32_M / 8) * SBO_A, B_BYTES = (N / 8) * SBO_B;
 	static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
 	static constexpr size_t SMEM = (size_t) STAGES * STAGE_BYTES + 128;          // + barriers, TMEM slot, chunk minima
-	// instruction descriptor: D = F32 (bits 4-5 = 1), A = B = TF32 (bits 7-9, 10-12 = 2), A K-major (bit 15 = 0),
-	// B MN-major (bit 16 = 1), N >> 3 at bits 17-22, M >> 4 at bits 24-28
-	static constexpr uint32_t IDESC = (1u << 4) | (2u << 7) | (2u << 10) | (1u << 16) | ((uint32_t) (N >> 3) << 17) | ((uint32_t) (TF32_M >> 4) << 24);
+	// instruction descriptor: D = F32 (bits 4-5 = 1), A = B = TF32 (bits 7-9, 10-12 = 2), both K-major (bits 15, 16 = 0),
+	// N >> 3 at bits 17-22, M >> 4 at bits 24-28
+	static constexpr uint32_t IDESC = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t) (N >> 3) << 17) | ((uint32_t) (TF32_M >> 4) << 24);
 };
 
 template <int N, int STAGES>
@@ -138,6 +143,7 @@ spmm_tf32_blocked_kernel(const int32_t* __restrict__ ia, const int32_t* __restri
 {
 	using Cfg = Tf32Cfg<N, STAGES>;
 	constexpr int KT = TF32_KT;
+	static_assert(Cfg::STAGE_BYTES % 16 == 0, "stages stay 16-byte aligned");
 	extern __shared__ __align__(128) unsigned char tf_smem[];
 	const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 	const int slab = blockIdx.x;
@@ -171,45 +177,75 @@ spmm_tf32_blocked_kernel(const int32_t* __restrict__ ia, const int32_t* __restri
 		const int stage = it % STAGES;
 		if (it >= STAGES) mbar_wait_bounded(bar_free + 8 * stage, (uint32_t) ((it / STAGES) - 1) & 1u);
 		unsigned char* const sA = tf_smem + (size_t) stage * Cfg::STAGE_BYTES;
+		unsigned char* const sB = sA + Cfg::A_BYTES;
 		const uint32_t sA_u = smem_u + stage * Cfg::STAGE_BYTES, sB_u = sA_u + Cfg::A_BYTES;
-		// B rows kc .. kc+KT-1: 16-byte pieces, a warp covers 8 rows x 64 bytes per instruction
+		// ---- B rows kc .. kc+KT-1: unit = 4 rows x 4 columns; a warp reads 512 contiguous bytes of a row per load
+		constexpr int UNITS = (KT / 4) * (N / 4), PER_THREAD = (UNITS + TF32_M - 1) / TF32_M;
+		float4 br[PER_THREAD][4];
 		#pragma unroll
-		for (int i = 0; i < KT * N / 4 / TF32_M; i++) {
-			const int q = i * TF32_M + tid;
-			const int t = q >> 5;
-			const int kk = (t % (KT / 8)) * 8 + (q & 7);
-			const int nc = (t / (KT / 8)) * 4 + ((q >> 3) & 3);
-			const int brow = kc + kk;
-			const bool ok = brow < c;
-			cp_async16_zfill(sB_u + nc * Cfg::SBO_B + (kk >> 3) * Cfg::LBO_B + (kk & 7) * 16,
-			                 B + (size_t) (ok ? brow : 0) * N + nc * 4, ok ? 16u : 0u);
+		for (int u = 0; u < PER_THREAD; u++) {
+			const int unit = u * TF32_M + tid;
+			const int n4 = unit % (N / 4), kk4 = unit / (N / 4);
+			#pragma unroll
+			for (int r = 0; r < 4; r++) {
+				const int brow = kc + kk4 * 4 + r;
+				br[u][r] = (unit < UNITS && brow < c) ? __ldg(reinterpret_cast<const float4*>(B + (size_t) brow * N) + n4) : make_float4(0.f, 0.f, 0.f, 0.f);
+			}
 		}
-		cp_async_commit();
-		// my row of the A stage: zero, then scatter this chunk's nonzeros (TF32, round to nearest)
+		// ---- my row of the A stage: zero, then scatter this chunk's nonzeros (TF32, round to nearest); the (col, val)
+		// pairs are fetched four at a time with independent loads (columns are sorted: the ones of this chunk are a prefix)
 		unsigned char* const myrow = sA + (tid >> 3) * Cfg::SBO_A + (tid & 7) * 16;
 		#pragma unroll
-		for (int q = 0; q < KT / 4; q++) *reinterpret_cast<uint4*>(myrow + q * Cfg::LBO_A) = make_uint4(0, 0, 0, 0);
-		int col = j < jend ? __ldg(ja + j) : INT_MAX;
-		while (col < kc + KT) {
-			const int kk = col - kc;
-			uint32_t bits;
-			asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(bits) : "f"(__ldg(a + j)));
-			*reinterpret_cast<uint32_t*>(myrow + (kk >> 2) * Cfg::LBO_A + (kk & 3) * 4) = bits;
-			j++;
-			col = j < jend ? __ldg(ja + j) : INT_MAX;
+		for (int q = 0; q < KT / 4; q++) *reinterpret_cast<uint4*>(myrow + q * Cfg::LBO) = make_uint4(0, 0, 0, 0);
+		const int kend = kc + KT;
+		for (;;) {
+			int cols[4];
+			float vals[4];
+			#pragma unroll
+			for (int q = 0; q < 4; q++) {
+				const bool ok = j + q < jend;
+				cols[q] = ok ? __ldg(ja + j + q) : INT_MAX;
+				vals[q] = ok ? __ldg(a + j + q) : 0.f;
+			}
+			int used = 0;
+			#pragma unroll
+			for (int q = 0; q < 4; q++) {
+				if (cols[q] < kend) {
+					const int kk = cols[q] - kc;
+					uint32_t bits;
+					asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(bits) : "f"(vals[q]));
+					*reinterpret_cast<uint32_t*>(myrow + (kk >> 2) * Cfg::LBO + (kk & 3) * 4) = bits;
+					used++;
+				}
+			}
+			j += used;
+			if (used < 4) break;
 		}
+		const int col = j < jend ? __ldg(ja + j) : INT_MAX;
 		const int wmin = __reduce_min_sync(0xffffffffu, col);            // next column any row of the warp still has
 		if (lane == 0) s_min[(it & 1) * 4 + warp] = wmin;
-		cp_async_wait<0>();
-		asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // st.shared / cp.async data -> visible to the tensor core
+		// ---- B: 4 x 4 transpose in registers, four 16-byte stores = half a core matrix (4 columns x 4 k)
+		#pragma unroll
+		for (int u = 0; u < PER_THREAD; u++) {
+			const int unit = u * TF32_M + tid;
+			if (unit < UNITS) {
+				const int n4 = unit % (N / 4), kk4 = unit / (N / 4);
+				unsigned char* const dst = sB + (n4 >> 1) * Cfg::SBO_B + kk4 * Cfg::LBO + (n4 & 1) * 64;
+				*reinterpret_cast<float4*>(dst) = make_float4(br[u][0].x, br[u][1].x, br[u][2].x, br[u][3].x);
+				*reinterpret_cast<float4*>(dst + 16) = make_float4(br[u][0].y, br[u][1].y, br[u][2].y, br[u][3].y);
+				*reinterpret_cast<float4*>(dst + 32) = make_float4(br[u][0].z, br[u][1].z, br[u][2].z, br[u][3].z);
+				*reinterpret_cast<float4*>(dst + 48) = make_float4(br[u][0].w, br[u][1].w, br[u][2].w, br[u][3].w);
+			}
+		}
+		asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // st.shared data -> visible to the tensor core
 		tc_fence_before();
 		__syncthreads();
 		if (tid == 0) {
 			tc_fence_after();
 			#pragma unroll
 			for (int ks = 0; ks < KT / 8; ks++)
-				tc_mma_tf32(tmem, umma_desc(sA_u + ks * 2 * Cfg::LBO_A, Cfg::LBO_A, Cfg::SBO_A),
-				            umma_desc(sB_u + ks * Cfg::LBO_B, Cfg::LBO_B, Cfg::SBO_B), Cfg::IDESC, (it > 0 || ks > 0) ? 1u : 0u);
+				tc_mma_tf32(tmem, umma_desc(sA_u + ks * 2 * Cfg::LBO, Cfg::LBO, Cfg::SBO_A),
+				            umma_desc(sB_u + ks * 2 * Cfg::LBO, Cfg::LBO, Cfg::SBO_B), Cfg::IDESC, (it > 0 || ks > 0) ? 1u : 0u);
 			tc_commit(bar_free + 8 * stage);
 		}
 		const int nxt = min(min(s_min[(it & 1) * 4], s_min[(it & 1) * 4 + 1]), min(s_min[(it & 1) * 4 + 2], s_min[(it & 1) * 4 + 3]));
