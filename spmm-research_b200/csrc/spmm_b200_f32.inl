@@ -95,7 +95,7 @@ static cudaError_t tf32_launch_n(spmm_b200_f32* h, const float* B, float* C, cud
 		if (e != cudaSuccess) return e;
 		h->smem_attr |= 1u << bit;
 	}
-	kern<<<h->tf32.nslabs, TF32_M, Cfg::SMEM, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, h->tf32.d_win, (int) h->m, (int) h->c);
+	kern<<<h->tf32.nslabs, TF32_THREADS, Cfg::SMEM, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, h->tf32.d_win, (int) h->m, (int) h->c);
 	return cudaGetLastError();
 }
 

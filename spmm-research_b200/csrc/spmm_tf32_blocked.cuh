@@ -136,18 +136,50 @@ struct Tf32Cfg {
 	static constexpr uint32_t IDESC = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t) (N >> 3) << 17) | ((uint32_t) (TF32_M >> 4) << 24);
 };
 
+constexpr int TF32_THREADS = 256;   // threads 0..127 own a row of the slab each (A scatter); all 256 move B and read TMEM
+
+// 4 rows x 4 columns of B for chunk `kc` into registers: unit = (kk4, n4); a warp reads 512 contiguous bytes of a row
+template <int N, int PER_THREAD>
+__device__ __forceinline__ void tf32_load_b(const float* __restrict__ B, int kc, int c, int tid, float4 (&br)[PER_THREAD][4])
+{
+	constexpr int UNITS = (TF32_KT / 4) * (N / 4);
+	#pragma unroll
+	for (int u = 0; u < PER_THREAD; u++) {
+		const int unit = u * TF32_THREADS + tid;
+		const int n4 = unit % (N / 4), kk4 = unit / (N / 4);
+		#pragma unroll
+		for (int r = 0; r < 4; r++) {
+			const int brow = kc + kk4 * 4 + r;
+			br[u][r] = (unit < UNITS && brow < c) ? __ldg(reinterpret_cast<const float4*>(B + (size_t) brow * N) + n4) : make_float4(0.f, 0.f, 0.f, 0.f);
+		}
+	}
+}
+
+// up to four (col, val) pairs of a row starting at nonzero j, with independent loads
+__device__ __forceinline__ void tf32_load_a(const int32_t* __restrict__ ja, const float* __restrict__ a, int j, int jend, int (&cols)[4], float (&vals)[4])
+{
+	#pragma unroll
+	for (int q = 0; q < 4; q++) {
+		const bool ok = j + q < jend;
+		cols[q] = ok ? __ldg(ja + j + q) : INT_MAX;
+		vals[q] = ok ? __ldg(a + j + q) : 0.f;
+	}
+}
+
 template <int N, int STAGES>
-__global__ void __launch_bounds__(TF32_M)
+__global__ void __launch_bounds__(TF32_THREADS)
 spmm_tf32_blocked_kernel(const int32_t* __restrict__ ia, const int32_t* __restrict__ ja, const float* __restrict__ a,
                          const float* __restrict__ B, float* __restrict__ C, const int2* __restrict__ win, int m, int c)
 {
 	using Cfg = Tf32Cfg<N, STAGES>;
 	constexpr int KT = TF32_KT;
+	constexpr int UNITS = (KT / 4) * (N / 4), PER_THREAD = (UNITS + TF32_THREADS - 1) / TF32_THREADS;
 	static_assert(Cfg::STAGE_BYTES % 16 == 0, "stages stay 16-byte aligned");
 	extern __shared__ __align__(128) unsigned char tf_smem[];
 	const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+	const bool row_thread = tid < TF32_M;
 	const int slab = blockIdx.x;
-	const int row = slab * TF32_M + tid;
+	const int row = slab * TF32_M + (tid & (TF32_M - 1));
 	unsigned char* const ctl = tf_smem + (size_t) STAGES * Cfg::STAGE_BYTES;
 	const uint32_t smem_u = smem_u32(tf_smem), ctl_u = smem_u32(ctl);
 	const uint32_t bar_free = ctl_u;                 // STAGES barriers: stage consumed by the tensor core
@@ -168,66 +200,30 @@ spmm_tf32_blocked_kernel(const int32_t* __restrict__ ia, const int32_t* __restri
 	const uint32_t tmem = *tmem_slot;
 
 	int j = 0, jend = 0;
-	if (row < m) { j = __ldg(ia + row); jend = __ldg(ia + row + 1); }
+	if (row_thread && row < m) { j = __ldg(ia + row); jend = __ldg(ia + row + 1); }
 	const int2 w = win[slab];
 	int kc = w.x;                                    // first column of the current chunk
 	int it = 0;
 	const bool any = w.y >= w.x;
+	// operands of the chunk about to be staged, already on their way: the loads of chunk it+1 are issued before the
+	// barrier of chunk it, so their latency hides behind the barrier, the MMA issue and the wait for the stage
+	float4 br[PER_THREAD][4];
+	int qc[4];
+	float qv[4];
+	if (any) {
+		tf32_load_b<N, PER_THREAD>(B, kc, c, tid, br);
+		tf32_load_a(ja, a, j, jend, qc, qv);
+	}
 	while (any) {
 		const int stage = it % STAGES;
 		if (it >= STAGES) mbar_wait_bounded(bar_free + 8 * stage, (uint32_t) ((it / STAGES) - 1) & 1u);
 		unsigned char* const sA = tf_smem + (size_t) stage * Cfg::STAGE_BYTES;
 		unsigned char* const sB = sA + Cfg::A_BYTES;
 		const uint32_t sA_u = smem_u + stage * Cfg::STAGE_BYTES, sB_u = sA_u + Cfg::A_BYTES;
-		// ---- B rows kc .. kc+KT-1: unit = 4 rows x 4 columns; a warp reads 512 contiguous bytes of a row per load
-		constexpr int UNITS = (KT / 4) * (N / 4), PER_THREAD = (UNITS + TF32_M - 1) / TF32_M;
-		float4 br[PER_THREAD][4];
-		#pragma unroll
-		for (int u = 0; u < PER_THREAD; u++) {
-			const int unit = u * TF32_M + tid;
-			const int n4 = unit % (N / 4), kk4 = unit / (N / 4);
-			#pragma unroll
-			for (int r = 0; r < 4; r++) {
-				const int brow = kc + kk4 * 4 + r;
-				br[u][r] = (unit < UNITS && brow < c) ? __ldg(reinterpret_cast<const float4*>(B + (size_t) brow * N) + n4) : make_float4(0.f, 0.f, 0.f, 0.f);
-			}
-		}
-		// ---- my row of the A stage: zero, then scatter this chunk's nonzeros (TF32, round to nearest); the (col, val)
-		// pairs are fetched four at a time with independent loads (columns are sorted: the ones of this chunk are a prefix)
-		unsigned char* const myrow = sA + (tid >> 3) * Cfg::SBO_A + (tid & 7) * 16;
-		#pragma unroll
-		for (int q = 0; q < KT / 4; q++) *reinterpret_cast<uint4*>(myrow + q * Cfg::LBO) = make_uint4(0, 0, 0, 0);
-		const int kend = kc + KT;
-		for (;;) {
-			int cols[4];
-			float vals[4];
-			#pragma unroll
-			for (int q = 0; q < 4; q++) {
-				const bool ok = j + q < jend;
-				cols[q] = ok ? __ldg(ja + j + q) : INT_MAX;
-				vals[q] = ok ? __ldg(a + j + q) : 0.f;
-			}
-			int used = 0;
-			#pragma unroll
-			for (int q = 0; q < 4; q++) {
-				if (cols[q] < kend) {
-					const int kk = cols[q] - kc;
-					uint32_t bits;
-					asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(bits) : "f"(vals[q]));
-					*reinterpret_cast<uint32_t*>(myrow + (kk >> 2) * Cfg::LBO + (kk & 3) * 4) = bits;
-					used++;
-				}
-			}
-			j += used;
-			if (used < 4) break;
-		}
-		const int col = j < jend ? __ldg(ja + j) : INT_MAX;
-		const int wmin = __reduce_min_sync(0xffffffffu, col);            // next column any row of the warp still has
-		if (lane == 0) s_min[(it & 1) * 4 + warp] = wmin;
 		// ---- B: 4 x 4 transpose in registers, four 16-byte stores = half a core matrix (4 columns x 4 k)
 		#pragma unroll
 		for (int u = 0; u < PER_THREAD; u++) {
-			const int unit = u * TF32_M + tid;
+			const int unit = u * TF32_THREADS + tid;
 			if (unit < UNITS) {
 				const int n4 = unit % (N / 4), kk4 = unit / (N / 4);
 				unsigned char* const dst = sB + (n4 >> 1) * Cfg::SBO_B + kk4 * Cfg::LBO + (n4 & 1) * 64;
@@ -237,6 +233,36 @@ spmm_tf32_blocked_kernel(const int32_t* __restrict__ ia, const int32_t* __restri
 				*reinterpret_cast<float4*>(dst + 48) = make_float4(br[u][0].w, br[u][1].w, br[u][2].w, br[u][3].w);
 			}
 		}
+		// ---- A: my row of the stage: zero, then scatter this chunk's nonzeros (TF32, round to nearest).  Columns are
+		// sorted, so the ones of this chunk are a prefix of the queue; a full queue is refilled on the spot.
+		int nextcol = INT_MAX;
+		if (row_thread) {
+			unsigned char* const myrow = sA + (tid >> 3) * Cfg::SBO_A + (tid & 7) * 16;
+			#pragma unroll
+			for (int q = 0; q < KT / 4; q++) *reinterpret_cast<uint4*>(myrow + q * Cfg::LBO) = make_uint4(0, 0, 0, 0);
+			const int kend = kc + KT;
+			for (;;) {
+				int used = 0;
+				#pragma unroll
+				for (int q = 0; q < 4; q++) {
+					if (qc[q] < kend) {
+						const int kk = qc[q] - kc;
+						uint32_t bits;
+						asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(bits) : "f"(qv[q]));
+						*reinterpret_cast<uint32_t*>(myrow + (kk >> 2) * Cfg::LBO + (kk & 3) * 4) = bits;
+						used++;
+					}
+				}
+				j += used;
+				if (used < 4) { nextcol = used == 0 ? qc[0] : used == 1 ? qc[1] : used == 2 ? qc[2] : qc[3]; break; }
+				tf32_load_a(ja, a, j, jend, qc, qv);
+			}
+			const int wmin = __reduce_min_sync(0xffffffffu, nextcol);       // next column any row of the warp still has
+			if (lane == 0) s_min[(it & 1) * 4 + warp] = wmin;
+			tf32_load_a(ja, a, j, jend, qc, qv);                           // the queue for the next chunk
+		}
+		// B of the chunk that follows unless a whole chunk is empty (then it is re-loaded below)
+		tf32_load_b<N, PER_THREAD>(B, kc + KT, c, tid, br);
 		asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // st.shared data -> visible to the tensor core
 		tc_fence_before();
 		__syncthreads();
@@ -251,19 +277,26 @@ spmm_tf32_blocked_kernel(const int32_t* __restrict__ ia, const int32_t* __restri
 		const int nxt = min(min(s_min[(it & 1) * 4], s_min[(it & 1) * 4 + 1]), min(s_min[(it & 1) * 4 + 2], s_min[(it & 1) * 4 + 3]));
 		it++;
 		if (nxt == INT_MAX) break;
-		kc = nxt;
+		if (nxt < kc + 2 * KT) {
+			kc += KT;                                   // the usual case: the next chunk follows on (it need not start on a nonzero)
+		} else {
+			kc = nxt;                                   // at least one whole chunk without a nonzero: skip it, fetch B again
+			tf32_load_b<N, PER_THREAD>(B, kc, c, tid, br);
+		}
 	}
 	if (any) {
 		if (tid == 0) tc_commit(bar_done);
 		mbar_wait_bounded(bar_done, 0);
 		tc_fence_after();
 	}
-	// epilogue: thread = row, 16 columns per TMEM load
+	// epilogue: warps 0-3 read the lower half of the columns, warps 4-7 the upper half; thread = row, 16 columns per TMEM load
+	constexpr int HALF = N / 2;
+	const int cbase = (warp >> 2) * HALF;
 	if (any) {
 		#pragma unroll 1
-		for (int c0 = 0; c0 < N; c0 += 16) {
+		for (int c0 = cbase; c0 < cbase + HALF; c0 += 16) {
 			float v[16];
-			tmem_ld16(tmem + ((uint32_t) (warp * 32) << 16) + c0, v);
+			tmem_ld16(tmem + ((uint32_t) ((warp & 3) * 32) << 16) + c0, v);
 			if (row < m) {
 				float4* dst = reinterpret_cast<float4*>(C + (size_t) row * N + c0);
 				#pragma unroll
@@ -271,9 +304,9 @@ spmm_tf32_blocked_kernel(const int32_t* __restrict__ ia, const int32_t* __restri
 			}
 		}
 	} else if (row < m) {
-		float4* dst = reinterpret_cast<float4*>(C + (size_t) row * N);
+		float4* dst = reinterpret_cast<float4*>(C + (size_t) row * N + cbase);
 		#pragma unroll 1
-		for (int q = 0; q < N / 4; q++) dst[q] = make_float4(0.f, 0.f, 0.f, 0.f);
+		for (int q = 0; q < HALF / 4; q++) dst[q] = make_float4(0.f, 0.f, 0.f, 0.f);
 	}
 	tc_fence_before();
 	__syncthreads();
