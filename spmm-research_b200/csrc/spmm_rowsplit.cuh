@@ -167,14 +167,17 @@ spmm_rowsplit_ticket_kernel(const int32_t* __restrict__ ia, const int32_t* __res
 	const int lane = threadIdx.x & 31;
 	if (blockIdx.x == 0 && threadIdx.x == 0) ticket[parity ^ 1] = 0;
 	int* const counter = ticket + parity;
+	// a warp's first ticket is its own number (no atomic: the whole wave would otherwise start with one atomic each on
+	// the same address); later tickets are drawn from the counter, offset by the number of warps
+	const int nwarps = gridDim.x * (THREADS / 32);
+	int t = blockIdx.x * (THREADS / 32) + (threadIdx.x >> 5);
 	for (;;) {
-		int t = 0;
-		if (lane == 0) t = atomicAdd(counter, 1);
-		t = __shfl_sync(0xffffffffu, t, 0);
 		const int64_t r0l = (int64_t) t * rows_per_ticket;
 		if (r0l >= m) break;
 		row_sweep<G, V, UNROLL, LD>(ia, ja, a, B, C, (int) r0l, (int) min((int64_t) m, r0l + rows_per_ticket), NGW,
 		                            lane / G, lane % G, ldb, ldc);
+		if (lane == 0) t = atomicAdd(counter, 1) + nwarps;
+		t = __shfl_sync(0xffffffffu, t, 0);
 	}
 }
 

@@ -15,8 +15,9 @@
 //     un-swizzled core matrices on this hardware -- scripts/umma_probe.cu, profiles/r2_tf32_probe.md);
 //   * one thread issues KT/8 tcgen05.mma (M = 128, N = k, K = 8) that accumulate into N fp32 columns of TMEM, and
 //     tcgen05.commit releases the stage through an mbarrier when the tensor core has read it;
-//   * chunks no row has a nonzero in are skipped (block-wide min of the rows' next columns), so the cost follows the
-//     occupied part of the window;
+//   * producers (8 warps) and the MMA thread (a 9th warp) hand stages over through mbarriers (full: 256 arrivals after a
+//     fence.proxy.async; free: tcgen05.commit) -- no CTA-wide barrier in the chunk loop, and the global loads of chunk
+//     it+1 are in flight while chunk it is staged;
 //   * epilogue: tcgen05.ld (32 lanes x 32 bit, 16 columns per instruction) -> registers -> C.
 // Several CTAs are resident per SM (32 KB of shared memory per stage, N of the 512 TMEM columns each), so one slab's
 // scatter / epilogue overlaps another's tensor work without warp specialisation.
@@ -136,7 +137,13 @@ struct Tf32Cfg {
 	static constexpr uint32_t IDESC = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t) (N >> 3) << 17) | ((uint32_t) (TF32_M >> 4) << 24);
 };
 
-constexpr int TF32_THREADS = 256;   // threads 0..127 own a row of the slab each (A scatter); all 256 move B and read TMEM
+constexpr int TF32_PRODUCERS = 256;               // warps 0..7: threads 0..127 own a row of the slab each (A scatter); all 256 move B and read TMEM
+constexpr int TF32_THREADS = TF32_PRODUCERS + 32;  // + warp 8: one lane issues the MMAs
+
+__device__ __forceinline__ void mbar_arrive(uint32_t bar)
+{
+	asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
 
 // 4 rows x 4 columns of B for chunk `kc` into registers: unit = (kk4, n4); a warp reads 512 contiguous bytes of a row
 template <int N, int PER_THREAD>
@@ -145,7 +152,7 @@ __device__ __forceinline__ void tf32_load_b(const float* __restrict__ B, int kc,
 	constexpr int UNITS = (TF32_KT / 4) * (N / 4);
 	#pragma unroll
 	for (int u = 0; u < PER_THREAD; u++) {
-		const int unit = u * TF32_THREADS + tid;
+		const int unit = u * TF32_PRODUCERS + tid;
 		const int n4 = unit % (N / 4), kk4 = unit / (N / 4);
 		#pragma unroll
 		for (int r = 0; r < 4; r++) {
@@ -173,24 +180,25 @@ spmm_tf32_blocked_kernel(const int32_t* __restrict__ ia, const int32_t* __restri
 {
 	using Cfg = Tf32Cfg<N, STAGES>;
 	constexpr int KT = TF32_KT;
-	constexpr int UNITS = (KT / 4) * (N / 4), PER_THREAD = (UNITS + TF32_THREADS - 1) / TF32_THREADS;
+	constexpr int UNITS = (KT / 4) * (N / 4), PER_THREAD = (UNITS + TF32_PRODUCERS - 1) / TF32_PRODUCERS;
 	static_assert(Cfg::STAGE_BYTES % 16 == 0, "stages stay 16-byte aligned");
 	extern __shared__ __align__(128) unsigned char tf_smem[];
-	const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-	const bool row_thread = tid < TF32_M;
+	const int tid = threadIdx.x, warp = tid >> 5;
+	const bool producer = tid < TF32_PRODUCERS, row_thread = tid < TF32_M;
 	const int slab = blockIdx.x;
 	const int row = slab * TF32_M + (tid & (TF32_M - 1));
 	unsigned char* const ctl = tf_smem + (size_t) STAGES * Cfg::STAGE_BYTES;
 	const uint32_t smem_u = smem_u32(tf_smem), ctl_u = smem_u32(ctl);
-	const uint32_t bar_free = ctl_u;                 // STAGES barriers: stage consumed by the tensor core
-	const uint32_t bar_done = ctl_u + 8 * STAGES;    // accumulator complete
-	volatile uint32_t* const tmem_slot = reinterpret_cast<volatile uint32_t*>(ctl + 8 * STAGES + 8);
-	volatile int* const s_min = reinterpret_cast<volatile int*>(ctl + 8 * STAGES + 16);      // [2][4]
+	// no CTA-wide barrier inside the chunk loop: stages are handed over through mbarriers
+	const uint32_t bar_full = ctl_u;                  // STAGES barriers, 256 arrivals: every producer has written its part
+	const uint32_t bar_free = ctl_u + 8 * STAGES;     // STAGES barriers, tcgen05.commit: the tensor core has read the stage
+	const uint32_t bar_done = ctl_u + 16 * STAGES;    // accumulator complete
+	volatile uint32_t* const tmem_slot = reinterpret_cast<volatile uint32_t*>(ctl + 16 * STAGES + 8);
 
-	if (warp == 0) tmem_alloc(smem_u32(ctl + 8 * STAGES + 8), N);
+	if (warp == 0) tmem_alloc(smem_u32(ctl + 16 * STAGES + 8), N);
 	if (tid == 0) {
 		#pragma unroll
-		for (int s = 0; s < STAGES; s++) mbar_init(bar_free + 8 * s, 1);
+		for (int s = 0; s < STAGES; s++) { mbar_init(bar_full + 8 * s, TF32_PRODUCERS); mbar_init(bar_free + 8 * s, 1); }
 		mbar_init(bar_done, 1);
 		asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
 	}
@@ -199,114 +207,109 @@ spmm_tf32_blocked_kernel(const int32_t* __restrict__ ia, const int32_t* __restri
 	tc_fence_after();
 	const uint32_t tmem = *tmem_slot;
 
-	int j = 0, jend = 0;
-	if (row_thread && row < m) { j = __ldg(ia + row); jend = __ldg(ia + row + 1); }
 	const int2 w = win[slab];
-	int kc = w.x;                                    // first column of the current chunk
-	int it = 0;
 	const bool any = w.y >= w.x;
-	// operands of the chunk about to be staged, already on their way: the loads of chunk it+1 are issued before the
-	// barrier of chunk it, so their latency hides behind the barrier, the MMA issue and the wait for the stage
-	float4 br[PER_THREAD][4];
-	int qc[4];
-	float qv[4];
-	if (any) {
-		tf32_load_b<N, PER_THREAD>(B, kc, c, tid, br);
-		tf32_load_a(ja, a, j, jend, qc, qv);
-	}
-	while (any) {
-		const int stage = it % STAGES;
-		if (it >= STAGES) mbar_wait_bounded(bar_free + 8 * stage, (uint32_t) ((it / STAGES) - 1) & 1u);
-		unsigned char* const sA = tf_smem + (size_t) stage * Cfg::STAGE_BYTES;
-		unsigned char* const sB = sA + Cfg::A_BYTES;
-		const uint32_t sA_u = smem_u + stage * Cfg::STAGE_BYTES, sB_u = sA_u + Cfg::A_BYTES;
-		// ---- B: 4 x 4 transpose in registers, four 16-byte stores = half a core matrix (4 columns x 4 k)
-		#pragma unroll
-		for (int u = 0; u < PER_THREAD; u++) {
-			const int unit = u * TF32_THREADS + tid;
-			if (unit < UNITS) {
-				const int n4 = unit % (N / 4), kk4 = unit / (N / 4);
-				unsigned char* const dst = sB + (n4 >> 1) * Cfg::SBO_B + kk4 * Cfg::LBO + (n4 & 1) * 64;
-				*reinterpret_cast<float4*>(dst) = make_float4(br[u][0].x, br[u][1].x, br[u][2].x, br[u][3].x);
-				*reinterpret_cast<float4*>(dst + 16) = make_float4(br[u][0].y, br[u][1].y, br[u][2].y, br[u][3].y);
-				*reinterpret_cast<float4*>(dst + 32) = make_float4(br[u][0].z, br[u][1].z, br[u][2].z, br[u][3].z);
-				*reinterpret_cast<float4*>(dst + 48) = make_float4(br[u][0].w, br[u][1].w, br[u][2].w, br[u][3].w);
-			}
+	// every chunk of the window is processed (no skipping: in a band nearly every column is occupied); all threads
+	// derive the same chunk sequence from the window alone, so nothing has to be agreed on inside the loop
+	const int nchunks = any ? (w.y - w.x) / KT + 1 : 0;
+
+	if (producer) {
+		int j = 0, jend = 0;
+		if (row_thread && row < m) { j = __ldg(ia + row); jend = __ldg(ia + row + 1); }
+		int kc = w.x;
+		// operands of the chunk about to be staged are already on their way: the loads of chunk it+1 are issued before
+		// chunk it is handed over
+		float4 br[PER_THREAD][4];
+		int qc[4];
+		float qv[4];
+		if (any) {
+			tf32_load_b<N, PER_THREAD>(B, kc, c, tid, br);
+			if (row_thread) tf32_load_a(ja, a, j, jend, qc, qv);
 		}
-		// ---- A: my row of the stage: zero, then scatter this chunk's nonzeros (TF32, round to nearest).  Columns are
-		// sorted, so the ones of this chunk are a prefix of the queue; a full queue is refilled on the spot.
-		int nextcol = INT_MAX;
-		if (row_thread) {
-			unsigned char* const myrow = sA + (tid >> 3) * Cfg::SBO_A + (tid & 7) * 16;
+		for (int it = 0; it < nchunks; it++, kc += KT) {
+			const int stage = it % STAGES;
+			if (it >= STAGES) mbar_wait_bounded(bar_free + 8 * stage, (uint32_t) ((it / STAGES) - 1) & 1u);
+			unsigned char* const sA = tf_smem + (size_t) stage * Cfg::STAGE_BYTES;
+			unsigned char* const sB = sA + Cfg::A_BYTES;
+			// ---- B: 4 x 4 transpose in registers, four 16-byte stores = half a core matrix (4 columns x 4 k)
 			#pragma unroll
-			for (int q = 0; q < KT / 4; q++) *reinterpret_cast<uint4*>(myrow + q * Cfg::LBO) = make_uint4(0, 0, 0, 0);
-			const int kend = kc + KT;
-			for (;;) {
-				int used = 0;
-				#pragma unroll
-				for (int q = 0; q < 4; q++) {
-					if (qc[q] < kend) {
-						const int kk = qc[q] - kc;
-						uint32_t bits;
-						asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(bits) : "f"(qv[q]));
-						*reinterpret_cast<uint32_t*>(myrow + (kk >> 2) * Cfg::LBO + (kk & 3) * 4) = bits;
-						used++;
-					}
+			for (int u = 0; u < PER_THREAD; u++) {
+				const int unit = u * TF32_PRODUCERS + tid;
+				if (unit < UNITS) {
+					const int n4 = unit % (N / 4), kk4 = unit / (N / 4);
+					unsigned char* const dst = sB + (n4 >> 1) * Cfg::SBO_B + kk4 * Cfg::LBO + (n4 & 1) * 64;
+					*reinterpret_cast<float4*>(dst) = make_float4(br[u][0].x, br[u][1].x, br[u][2].x, br[u][3].x);
+					*reinterpret_cast<float4*>(dst + 16) = make_float4(br[u][0].y, br[u][1].y, br[u][2].y, br[u][3].y);
+					*reinterpret_cast<float4*>(dst + 32) = make_float4(br[u][0].z, br[u][1].z, br[u][2].z, br[u][3].z);
+					*reinterpret_cast<float4*>(dst + 48) = make_float4(br[u][0].w, br[u][1].w, br[u][2].w, br[u][3].w);
 				}
-				j += used;
-				if (used < 4) { nextcol = used == 0 ? qc[0] : used == 1 ? qc[1] : used == 2 ? qc[2] : qc[3]; break; }
-				tf32_load_a(ja, a, j, jend, qc, qv);
 			}
-			const int wmin = __reduce_min_sync(0xffffffffu, nextcol);       // next column any row of the warp still has
-			if (lane == 0) s_min[(it & 1) * 4 + warp] = wmin;
-			tf32_load_a(ja, a, j, jend, qc, qv);                           // the queue for the next chunk
+			if (it + 1 < nchunks) tf32_load_b<N, PER_THREAD>(B, kc + KT, c, tid, br);
+			// ---- A: my row of the stage: zero, then scatter this chunk's nonzeros (TF32, round to nearest).  Columns are
+			// sorted, so the ones of this chunk are a prefix of the queue; a full queue is refilled on the spot.
+			if (row_thread) {
+				unsigned char* const myrow = sA + (tid >> 3) * Cfg::SBO_A + (tid & 7) * 16;
+				#pragma unroll
+				for (int q = 0; q < KT / 4; q++) *reinterpret_cast<uint4*>(myrow + q * Cfg::LBO) = make_uint4(0, 0, 0, 0);
+				const int kend = kc + KT;
+				for (;;) {
+					int used = 0;
+					#pragma unroll
+					for (int q = 0; q < 4; q++) {
+						if (qc[q] < kend) {
+							const int kk = qc[q] - kc;
+							uint32_t bits;
+							asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(bits) : "f"(qv[q]));
+							*reinterpret_cast<uint32_t*>(myrow + (kk >> 2) * Cfg::LBO + (kk & 3) * 4) = bits;
+							used++;
+						}
+					}
+					j += used;
+					if (used == 0) break;                              // the queue still starts at nonzero j: nothing to reload
+					tf32_load_a(ja, a, j, jend, qc, qv);               // refill (for this chunk if the queue was used up, else for the next)
+					if (used < 4) break;
+				}
+			}
+			asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // st.shared data -> visible to the tensor core
+			mbar_arrive(bar_full + 8 * stage);
 		}
-		// B of the chunk that follows unless a whole chunk is empty (then it is re-loaded below)
-		tf32_load_b<N, PER_THREAD>(B, kc + KT, c, tid, br);
-		asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // st.shared data -> visible to the tensor core
-		tc_fence_before();
-		__syncthreads();
-		if (tid == 0) {
+	} else if (tid == TF32_PRODUCERS) {
+		// ---- the MMA thread
+		for (int it = 0; it < nchunks; it++) {
+			const int stage = it % STAGES;
+			mbar_wait_bounded(bar_full + 8 * stage, (uint32_t) (it / STAGES) & 1u);
 			tc_fence_after();
+			const uint32_t sA_u = smem_u + stage * Cfg::STAGE_BYTES, sB_u = sA_u + Cfg::A_BYTES;
 			#pragma unroll
 			for (int ks = 0; ks < KT / 8; ks++)
 				tc_mma_tf32(tmem, umma_desc(sA_u + ks * 2 * Cfg::LBO, Cfg::LBO, Cfg::SBO_A),
 				            umma_desc(sB_u + ks * 2 * Cfg::LBO, Cfg::LBO, Cfg::SBO_B), Cfg::IDESC, (it > 0 || ks > 0) ? 1u : 0u);
 			tc_commit(bar_free + 8 * stage);
 		}
-		const int nxt = min(min(s_min[(it & 1) * 4], s_min[(it & 1) * 4 + 1]), min(s_min[(it & 1) * 4 + 2], s_min[(it & 1) * 4 + 3]));
-		it++;
-		if (nxt == INT_MAX) break;
-		if (nxt < kc + 2 * KT) {
-			kc += KT;                                   // the usual case: the next chunk follows on (it need not start on a nonzero)
-		} else {
-			kc = nxt;                                   // at least one whole chunk without a nonzero: skip it, fetch B again
-			tf32_load_b<N, PER_THREAD>(B, kc, c, tid, br);
-		}
-	}
-	if (any) {
-		if (tid == 0) tc_commit(bar_done);
-		mbar_wait_bounded(bar_done, 0);
-		tc_fence_after();
+		if (any) tc_commit(bar_done);
 	}
 	// epilogue: warps 0-3 read the lower half of the columns, warps 4-7 the upper half; thread = row, 16 columns per TMEM load
-	constexpr int HALF = N / 2;
-	const int cbase = (warp >> 2) * HALF;
-	if (any) {
-		#pragma unroll 1
-		for (int c0 = cbase; c0 < cbase + HALF; c0 += 16) {
-			float v[16];
-			tmem_ld16(tmem + ((uint32_t) ((warp & 3) * 32) << 16) + c0, v);
-			if (row < m) {
-				float4* dst = reinterpret_cast<float4*>(C + (size_t) row * N + c0);
-				#pragma unroll
-				for (int q = 0; q < 4; q++) dst[q] = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+	if (producer) {
+		constexpr int HALF = N / 2;
+		const int cbase = (warp >> 2) * HALF;
+		if (any) {
+			mbar_wait_bounded(bar_done, 0);
+			tc_fence_after();
+			#pragma unroll 1
+			for (int c0 = cbase; c0 < cbase + HALF; c0 += 16) {
+				float v[16];
+				tmem_ld16(tmem + ((uint32_t) ((warp & 3) * 32) << 16) + c0, v);
+				if (row < m) {
+					float4* dst = reinterpret_cast<float4*>(C + (size_t) row * N + c0);
+					#pragma unroll
+					for (int q = 0; q < 4; q++) dst[q] = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+				}
 			}
+		} else if (row < m) {
+			float4* dst = reinterpret_cast<float4*>(C + (size_t) row * N + cbase);
+			#pragma unroll 1
+			for (int q = 0; q < HALF / 4; q++) dst[q] = make_float4(0.f, 0.f, 0.f, 0.f);
 		}
-	} else if (row < m) {
-		float4* dst = reinterpret_cast<float4*>(C + (size_t) row * N + cbase);
-		#pragma unroll 1
-		for (int q = 0; q < HALF / 4; q++) dst[q] = make_float4(0.f, 0.f, 0.f, 0.f);
 	}
 	tc_fence_before();
 	__syncthreads();
