@@ -23,6 +23,7 @@ def main():
     ap.add_argument("--workload", default="cfg4")
     ap.add_argument("--ks", default="32,64,128")
     ap.add_argument("--variants", default="rowsplit,merge,bcsr")
+    ap.add_argument("--set", default="", help="comma-separated NAME=VALUE handle options (e.g. TF32_STAGES=3)")
     args = ap.parse_args()
     pkg = g.load_package()
     gen, _ = WORKLOADS[args.workload]
@@ -39,6 +40,9 @@ def main():
         for vname in args.variants.split(","):
             variant = {"rowsplit": pkg.ROWSPLIT, "merge": pkg.MERGE, "bcsr": pkg.BCSR, "auto": pkg.AUTO}[vname]
             mf = pkg.csr_to_format_f32(ia, ja, a, m, c, nnz, k, variant=variant)
+            for kv in args.set.split(","):
+                if kv:
+                    mf.set_option(kv.split("=")[0], int(kv.split("=")[1]))
             c_dev = torch.empty(m * k, dtype=torch.float32, device="cuda")
             ts = []
             for i in range(25):
@@ -49,7 +53,7 @@ def main():
             y = c_dev[: check_rows * k].cpu().numpy().astype(np.float64)
             err = float(np.max(np.abs(y - y_ref) / np.maximum(np.abs(y_ref), 1e-30)))
             t = float(np.median(ts))
-            print(json.dumps({"workload": args.workload, "k": k, "kernel": mf.format_name, "ms": round(t, 4),
+            print(json.dumps({"workload": args.workload, "k": k, "kernel": mf.format_name + (" " + args.set if args.set else ""), "ms": round(t, 4),
                               "gflops": round(2.0 * nnz * k / t / 1e6, 1), "frac_hbm": round(bytes_ / (t * 1e-3) / 1e9 / peak, 4),
                               "max_rel_err_vs_fp32_oracle": err, "rows_checked": check_rows}), flush=True)
             mf.close()

@@ -56,6 +56,7 @@ struct Options {
 	int merge_maxrow = 256;    // MERGE_MAXROW
 	int bcsr_fill_pct = 30;    // BCSR_FILL_PCT
 	int bcsr_tma = 1, bcsr_stages = 2, bcsr_brw = 0;
+	int tf32_stages = 2;       // TF32_STAGES: shared-memory stages of the TF32 blocked kernel (2 or 3)
 };
 
 static int env_int(const char* name, int dflt)
@@ -71,7 +72,7 @@ static const OptionName OPTION_TABLE[] = {
 	{"PIPELINE_COLS", &Options::pipeline_cols}, {"PIPELINE_MIN_KB", &Options::pipeline_min_kb},
 	{"DIRECT_STORE", &Options::direct_store}, {"CTAS_PER_SM", &Options::ctas_per_sm},
 	{"MERGE_MAXROW", &Options::merge_maxrow}, {"BCSR_FILL_PCT", &Options::bcsr_fill_pct},
-	{"BCSR_TMA", &Options::bcsr_tma}, {"BCSR_STAGES", &Options::bcsr_stages}, {"BCSR_BRW", &Options::bcsr_brw},
+	{"TF32_STAGES", &Options::tf32_stages}, {"BCSR_TMA", &Options::bcsr_tma}, {"BCSR_STAGES", &Options::bcsr_stages}, {"BCSR_BRW", &Options::bcsr_brw},
 };
 
 static Options options_from_env()
@@ -115,8 +116,7 @@ struct spmm_b200 {
 	// row-split work list
 	int32_t* d_cta_rows = nullptr;
 	int n_ctas = 0;
-	int* d_ticket = nullptr;              // two row-ticket counters, used alternately (see spmm_rowsplit_ticket_kernel)
-	int ticket_parity = 0;
+	int* d_ticket = nullptr;              // {ticket counter, warps that left}: reset by the last warp of a launch (spmm_rowsplit_ticket_kernel)
 	uint32_t smem_attr = 0;               // bit i: dynamic shared-memory limit of kernel family i raised on THIS device/handle
 	// merge-path work list
 	MergePlan merge;
@@ -299,15 +299,14 @@ static void launch_rowsplit_gv(spmm_b200* h, const double* B, double* C, cudaStr
 			const size_t smem = Cfg::smem(THREADS);
 			const int per_sm = std::max(1, std::min(o.ticket_ctas, (int) ((227 * 1024) / (smem + 1024))));
 			const int grid = (int) std::min<int64_t>((h->m + Cfg::R * (THREADS / 32) - 1) / (Cfg::R * (THREADS / 32)) + 1, (int64_t) h->sm_count * per_sm);
-			h->ticket_parity ^= 1;
 			if (whole) {
 				auto kern = spmm_rowsplit_staged_kernel<G, V, 4, THREADS, PASSES, STAGED_CAP, K>;
 				raise_smem_limit(h, ATTR_STAGED + (K == 32 ? 0 : K == 64 ? 1 : 2), kern, smem);
-				kern<<<grid, THREADS, smem, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, (int) h->m, h->d_ticket, h->ticket_parity, ldb, ldc);
+				kern<<<grid, THREADS, smem, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, (int) h->m, h->d_ticket, ldb, ldc);
 			} else {
 				auto kern = spmm_rowsplit_staged_kernel<G, V, 4, THREADS, PASSES, STAGED_CAP>;
 				raise_smem_limit(h, ATTR_STAGED + 3 + (K == 32 ? 0 : K == 64 ? 1 : 2), kern, smem);
-				kern<<<grid, THREADS, smem, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, (int) h->m, h->d_ticket, h->ticket_parity, ldb, ldc);
+				kern<<<grid, THREADS, smem, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, (int) h->m, h->d_ticket, ldb, ldc);
 			}
 			return;
 		}
@@ -319,8 +318,7 @@ static void launch_rowsplit_gv(spmm_b200* h, const double* B, double* C, cudaStr
 				raise_smem_limit(h, ATTR_RING, kern, smem);
 				const int rpt = std::max(NGW, (std::max(tick, 1) + NGW - 1) / NGW * NGW);
 				const int grid = (int) std::min<int64_t>((h->m + rpt * (THREADS / 32) - 1) / (rpt * (THREADS / 32)) + 1, (int64_t) h->sm_count * 3);
-				h->ticket_parity ^= 1;
-				kern<<<grid, THREADS, smem, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, (int) h->m, rpt, h->d_ticket, h->ticket_parity, ldb, ldc);
+					kern<<<grid, THREADS, smem, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, (int) h->m, rpt, h->d_ticket, ldb, ldc);
 				return;
 			}
 		}
@@ -329,11 +327,10 @@ static void launch_rowsplit_gv(spmm_b200* h, const double* B, double* C, cudaStr
 		tick = (tick + NGW - 1) / NGW * NGW;
 		const int grid = (int) std::min<int64_t>((h->m + tick * (THREADS / 32) - 1) / (tick * (THREADS / 32)) + 1,
 		                                         (int64_t) h->sm_count * std::max(1, o.ticket_ctas));
-		h->ticket_parity ^= 1;
 		if (whole)
-			spmm_rowsplit_ticket_kernel<G, V, 4, THREADS, K><<<grid, THREADS, 0, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, (int) h->m, tick, h->d_ticket, h->ticket_parity, ldb, ldc);
+			spmm_rowsplit_ticket_kernel<G, V, 4, THREADS, K><<<grid, THREADS, 0, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, (int) h->m, tick, h->d_ticket, ldb, ldc);
 		else
-			spmm_rowsplit_ticket_kernel<G, V, 4, THREADS><<<grid, THREADS, 0, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, (int) h->m, tick, h->d_ticket, h->ticket_parity, ldb, ldc);
+			spmm_rowsplit_ticket_kernel<G, V, 4, THREADS><<<grid, THREADS, 0, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, (int) h->m, tick, h->d_ticket, ldb, ldc);
 		return;
 	}
 	if (o.unroll >= 8 && G >= 8)

@@ -84,10 +84,9 @@ static void tf32_release_plan(spmm_b200_f32* h)
 
 static bool tf32_supports(const spmm_b200_f32* h, int k) { return h->tf32.d_win && (k == 32 || k == 64 || k == 128); }
 
-template <int N>
-static cudaError_t tf32_launch_n(spmm_b200_f32* h, const float* B, float* C, cudaStream_t s, int bit)
+template <int N, int STAGES>
+static cudaError_t tf32_launch_ns(spmm_b200_f32* h, const float* B, float* C, cudaStream_t s, int bit)
 {
-	constexpr int STAGES = 2;
 	using Cfg = Tf32Cfg<N, STAGES>;
 	auto kern = spmm_tf32_blocked_kernel<N, STAGES>;
 	if (Cfg::SMEM > 48 * 1024 && !(h->smem_attr >> bit & 1u)) {
@@ -97,6 +96,13 @@ static cudaError_t tf32_launch_n(spmm_b200_f32* h, const float* B, float* C, cud
 	}
 	kern<<<h->tf32.nslabs, TF32_THREADS, Cfg::SMEM, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, h->tf32.d_win, (int) h->m, (int) h->c);
 	return cudaGetLastError();
+}
+
+template <int N>
+static cudaError_t tf32_launch_n(spmm_b200_f32* h, const float* B, float* C, cudaStream_t s, int bit)
+{
+	// 2 stages = 3 resident slabs per SM at k = 128 (the default); 3 stages = deeper hand-over, 2 slabs per SM
+	return h->opt.tf32_stages >= 3 ? tf32_launch_ns<N, 3>(h, B, C, s, bit + 3) : tf32_launch_ns<N, 2>(h, B, C, s, bit);
 }
 
 static int tf32_launch(spmm_b200_f32* h, const float* B, float* C, int k, cudaStream_t s)

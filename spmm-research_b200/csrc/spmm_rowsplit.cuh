@@ -154,31 +154,35 @@ spmm_rowsplit_kernel(const int32_t* __restrict__ ia, const int32_t* __restrict__
 	                            threadIdx.x / G, threadIdx.x % G, ldb, ldc);
 }
 
-// Row tickets.  `ticket` points at TWO counters: this launch draws from ticket[parity] and zeroes ticket[parity ^ 1]
-// for the next launch of the handle (launches of one handle are stream-ordered), so no memset node sits between
-// back-to-back launches.
+// Row tickets.  `ticket` points at two integers: [0] the ticket counter, [1] the number of warps that have left the
+// kernel.  The last warp to leave zeroes both, so the next launch of the handle (stream-ordered) -- or the next replay of
+// a CUDA graph that captured this launch -- starts from zero without a memset node in between.
+__device__ __forceinline__ void ticket_leave(int* __restrict__ ticket, int lane, int nwarps)
+{
+	if (lane == 0) {
+		const int left = atomicAdd(ticket + 1, 1);
+		if (left == nwarps - 1) { ticket[0] = 0; ticket[1] = 0; }      // every warp has drawn its last ticket before it counts itself out
+	}
+}
+
 template <int G, int V, int UNROLL, int THREADS, int LD = 0>
 __global__ void __launch_bounds__(THREADS)
 spmm_rowsplit_ticket_kernel(const int32_t* __restrict__ ia, const int32_t* __restrict__ ja, const double* __restrict__ a,
                             const double* __restrict__ B, double* __restrict__ C,
-                            int m, int rows_per_ticket, int* __restrict__ ticket, int parity, int ldb, int ldc)
+                            int m, int rows_per_ticket, int* __restrict__ ticket, int ldb, int ldc)
 {
 	constexpr int NGW = 32 / G;              // row groups per warp
 	const int lane = threadIdx.x & 31;
-	if (blockIdx.x == 0 && threadIdx.x == 0) ticket[parity ^ 1] = 0;
-	int* const counter = ticket + parity;
-	// a warp's first ticket is its own number (no atomic: the whole wave would otherwise start with one atomic each on
-	// the same address); later tickets are drawn from the counter, offset by the number of warps
-	const int nwarps = gridDim.x * (THREADS / 32);
-	int t = blockIdx.x * (THREADS / 32) + (threadIdx.x >> 5);
 	for (;;) {
+		int t = 0;
+		if (lane == 0) t = atomicAdd(ticket, 1);
+		t = __shfl_sync(0xffffffffu, t, 0);
 		const int64_t r0l = (int64_t) t * rows_per_ticket;
 		if (r0l >= m) break;
 		row_sweep<G, V, UNROLL, LD>(ia, ja, a, B, C, (int) r0l, (int) min((int64_t) m, r0l + rows_per_ticket), NGW,
 		                            lane / G, lane % G, ldb, ldc);
-		if (lane == 0) t = atomicAdd(counter, 1) + nwarps;
-		t = __shfl_sync(0xffffffffu, t, 0);
 	}
+	ticket_leave(ticket, lane, gridDim.x * (THREADS / 32));
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -241,7 +245,7 @@ template <int G, int V, int UNROLL, int THREADS, int PASSES, int CAP, int LD = 0
 __global__ void __launch_bounds__(THREADS, 4)      // 64 registers
 spmm_rowsplit_staged_kernel(const int32_t* __restrict__ ia, const int32_t* __restrict__ ja, const double* __restrict__ a,
                             const double* __restrict__ B, double* __restrict__ C,
-                            int m, int* __restrict__ ticket, int parity, int ldb, int ldc)
+                            int m, int* __restrict__ ticket, int ldb, int ldc)
 {
 	using Cfg = StagedCfg<G, PASSES, CAP>;
 	constexpr int NW = THREADS / 32, NGW = 32 / G, R = Cfg::R;
@@ -251,8 +255,7 @@ spmm_rowsplit_staged_kernel(const int32_t* __restrict__ ia, const int32_t* __res
 	unsigned char* const wbuf = staged_smem + (size_t) warp * 2 * Cfg::BUF_BYTES;
 	const uint32_t wbuf_u = smem_u32(wbuf);
 	const uint32_t bar_u = smem_u32(staged_smem + (size_t) NW * 2 * Cfg::BUF_BYTES) + warp * 16;
-	if (blockIdx.x == 0 && threadIdx.x == 0) ticket[parity ^ 1] = 0;
-	int* const counter = ticket + parity;
+	int* const counter = ticket;
 	if (lane == 0) {
 		mbar_init(bar_u, 1);
 		mbar_init(bar_u + 8, 1);
@@ -345,6 +348,7 @@ spmm_rowsplit_staged_kernel(const int32_t* __restrict__ ia, const int32_t* __res
 		} while (rs < R);
 		__syncwarp();                            // every lane is done with stage b before iteration it+1 refills it
 	}
+	ticket_leave(ticket, lane, gridDim.x * (THREADS / 32));
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -359,7 +363,7 @@ template <int G, int V, int H, int THREADS>
 __global__ void __launch_bounds__(THREADS)
 spmm_rowsplit_ring_kernel(const int32_t* __restrict__ ia, const int32_t* __restrict__ ja, const double* __restrict__ a,
                           const double* __restrict__ B, double* __restrict__ C,
-                          int m, int rows_per_ticket, int* __restrict__ ticket, int parity, int ldb, int ldc)
+                          int m, int rows_per_ticket, int* __restrict__ ticket, int ldb, int ldc)
 {
 	static_assert(G % H == 0 && V % 2 == 0, "a chunk of G nonzeros is a whole number of stages");
 	constexpr int NGW = 32 / G, P = V / 2;                  // 16-byte pieces per lane and B row
@@ -369,8 +373,7 @@ spmm_rowsplit_ring_kernel(const int32_t* __restrict__ ia, const int32_t* __restr
 	double2* const ring = reinterpret_cast<double2*>(ring_smem) + threadIdx.x;
 	const uint32_t ring_u = smem_u32(ring);
 	auto slot_off = [](int stage, int i, int p) { return ((stage * H + i) * P + p) * THREADS; };
-	if (blockIdx.x == 0 && threadIdx.x == 0) ticket[parity ^ 1] = 0;
-	int* const counter = ticket + parity;
+	int* const counter = ticket;
 	for (;;) {
 		int t = 0;
 		if (lane == 0) t = atomicAdd(counter, 1);
@@ -450,6 +453,7 @@ spmm_rowsplit_ring_kernel(const int32_t* __restrict__ ia, const int32_t* __restr
 			if (live) store_c<G, V>(C, (size_t) row, lig, acc, ldc);
 		}
 	}
+	ticket_leave(ticket, lane, gridDim.x * (THREADS / 32));
 }
 
 // Any k: one warp per row, lanes own columns, column chunks of 32 (A re-read per chunk

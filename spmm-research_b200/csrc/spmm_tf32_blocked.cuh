@@ -137,7 +137,8 @@ struct Tf32Cfg {
 	static constexpr uint32_t IDESC = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t) (N >> 3) << 17) | ((uint32_t) (TF32_M >> 4) << 24);
 };
 
-constexpr int TF32_PRODUCERS = 256;               // warps 0..7: threads 0..127 own a row of the slab each (A scatter); all 256 move B and read TMEM
+constexpr int TF32_PRODUCERS = 256;               // warps 0..3: threads 0..127 own a row of the slab each (A scatter); warps 4..7 move B; all 8 read TMEM
+constexpr int TF32_BTHREADS = 128;
 constexpr int TF32_THREADS = TF32_PRODUCERS + 32;  // + warp 8: one lane issues the MMAs
 
 __device__ __forceinline__ void mbar_arrive(uint32_t bar)
@@ -152,7 +153,7 @@ __device__ __forceinline__ void tf32_load_b(const float* __restrict__ B, int kc,
 	constexpr int UNITS = (TF32_KT / 4) * (N / 4);
 	#pragma unroll
 	for (int u = 0; u < PER_THREAD; u++) {
-		const int unit = u * TF32_PRODUCERS + tid;
+		const int unit = u * TF32_BTHREADS + tid;
 		const int n4 = unit % (N / 4), kk4 = unit / (N / 4);
 		#pragma unroll
 		for (int r = 0; r < 4; r++) {
@@ -180,7 +181,7 @@ spmm_tf32_blocked_kernel(const int32_t* __restrict__ ia, const int32_t* __restri
 {
 	using Cfg = Tf32Cfg<N, STAGES>;
 	constexpr int KT = TF32_KT;
-	constexpr int UNITS = (KT / 4) * (N / 4), PER_THREAD = (UNITS + TF32_PRODUCERS - 1) / TF32_PRODUCERS;
+	constexpr int UNITS = (KT / 4) * (N / 4), PER_THREAD = (UNITS + TF32_BTHREADS - 1) / TF32_BTHREADS;
 	static_assert(Cfg::STAGE_BYTES % 16 == 0, "stages stay 16-byte aligned");
 	extern __shared__ __align__(128) unsigned char tf_smem[];
 	const int tid = threadIdx.x, warp = tid >> 5;
@@ -219,35 +220,38 @@ spmm_tf32_blocked_kernel(const int32_t* __restrict__ ia, const int32_t* __restri
 		int kc = w.x;
 		// operands of the chunk about to be staged are already on their way: the loads of chunk it+1 are issued before
 		// chunk it is handed over
+		// warps 0..3 stage A (one row per thread), warps 4..7 stage B: the two run side by side and meet at the stage's barrier
 		float4 br[PER_THREAD][4];
 		int qc[4];
 		float qv[4];
+		const int btid = tid - TF32_M;
 		if (any) {
-			tf32_load_b<N, PER_THREAD>(B, kc, c, tid, br);
 			if (row_thread) tf32_load_a(ja, a, j, jend, qc, qv);
+			else tf32_load_b<N, PER_THREAD>(B, kc, c, btid, br);
 		}
 		for (int it = 0; it < nchunks; it++, kc += KT) {
 			const int stage = it % STAGES;
 			if (it >= STAGES) mbar_wait_bounded(bar_free + 8 * stage, (uint32_t) ((it / STAGES) - 1) & 1u);
 			unsigned char* const sA = tf_smem + (size_t) stage * Cfg::STAGE_BYTES;
 			unsigned char* const sB = sA + Cfg::A_BYTES;
-			// ---- B: 4 x 4 transpose in registers, four 16-byte stores = half a core matrix (4 columns x 4 k)
-			#pragma unroll
-			for (int u = 0; u < PER_THREAD; u++) {
-				const int unit = u * TF32_PRODUCERS + tid;
-				if (unit < UNITS) {
-					const int n4 = unit % (N / 4), kk4 = unit / (N / 4);
-					unsigned char* const dst = sB + (n4 >> 1) * Cfg::SBO_B + kk4 * Cfg::LBO + (n4 & 1) * 64;
-					*reinterpret_cast<float4*>(dst) = make_float4(br[u][0].x, br[u][1].x, br[u][2].x, br[u][3].x);
-					*reinterpret_cast<float4*>(dst + 16) = make_float4(br[u][0].y, br[u][1].y, br[u][2].y, br[u][3].y);
-					*reinterpret_cast<float4*>(dst + 32) = make_float4(br[u][0].z, br[u][1].z, br[u][2].z, br[u][3].z);
-					*reinterpret_cast<float4*>(dst + 48) = make_float4(br[u][0].w, br[u][1].w, br[u][2].w, br[u][3].w);
+			if (!row_thread) {
+				// ---- B: 4 x 4 transpose in registers, four 16-byte stores = half a core matrix (4 columns x 4 k)
+				#pragma unroll
+				for (int u = 0; u < PER_THREAD; u++) {
+					const int unit = u * TF32_BTHREADS + btid;
+					if (unit < UNITS) {
+						const int n4 = unit % (N / 4), kk4 = unit / (N / 4);
+						unsigned char* const dst = sB + (n4 >> 1) * Cfg::SBO_B + kk4 * Cfg::LBO + (n4 & 1) * 64;
+						*reinterpret_cast<float4*>(dst) = make_float4(br[u][0].x, br[u][1].x, br[u][2].x, br[u][3].x);
+						*reinterpret_cast<float4*>(dst + 16) = make_float4(br[u][0].y, br[u][1].y, br[u][2].y, br[u][3].y);
+						*reinterpret_cast<float4*>(dst + 32) = make_float4(br[u][0].z, br[u][1].z, br[u][2].z, br[u][3].z);
+						*reinterpret_cast<float4*>(dst + 48) = make_float4(br[u][0].w, br[u][1].w, br[u][2].w, br[u][3].w);
+					}
 				}
-			}
-			if (it + 1 < nchunks) tf32_load_b<N, PER_THREAD>(B, kc + KT, c, tid, br);
-			// ---- A: my row of the stage: zero, then scatter this chunk's nonzeros (TF32, round to nearest).  Columns are
-			// sorted, so the ones of this chunk are a prefix of the queue; a full queue is refilled on the spot.
-			if (row_thread) {
+				if (it + 1 < nchunks) tf32_load_b<N, PER_THREAD>(B, kc + KT, c, btid, br);
+			} else {
+				// ---- A: my row of the stage: zero, then scatter this chunk's nonzeros (TF32, round to nearest).  Columns
+				// are sorted, so the ones of this chunk are a prefix of the queue; a full queue is refilled on the spot.
 				unsigned char* const myrow = sA + (tid >> 3) * Cfg::SBO_A + (tid & 7) * 16;
 				#pragma unroll
 				for (int q = 0; q < KT / 4; q++) *reinterpret_cast<uint4*>(myrow + q * Cfg::LBO) = make_uint4(0, 0, 0, 0);

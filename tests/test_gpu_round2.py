@@ -223,3 +223,72 @@ def test_reference_harness_multi_gpu(pkg):
     if n >= 2:
         assert row[23].endswith("_x2")
     assert float(row[25]) > 0
+
+
+def test_run_device_inside_graph_capture(pkg, L):
+    """spmm_b200_run_device must not synchronise while the caller's stream is being captured.  A matrix whose
+    touched B window triggers the k-slice measurement (which blocks) is launched inside a CUDA-graph capture: the
+    measurement is skipped there, the capture succeeds, and replaying the graph gives the oracle's result."""
+    import torch
+    m, c, k = 3000, 210000, 128
+    rng = np.random.default_rng(12)
+    deg = rng.integers(1, 9, m)
+    ia = np.zeros(m + 1, np.int32); ia[1:] = np.cumsum(deg)
+    ja = np.concatenate([np.sort(rng.choice(c, d, replace=False)) for d in deg]).astype(np.int32)
+    ja[0], ja[-1] = 0, c - 1
+    ja[: deg[0]].sort(); ja[-deg[-1]:].sort()
+    a = rng.random(len(ja)) + 0.05
+    x = dense_b(c, k, 4)
+    y_ref = L.spmm_oracle(ia, ja, a, m, c, x, k)
+    mf = pkg.csr_to_format(ia, ja, a, m, c, len(ja), k, variant=pkg.ROWSPLIT)
+    b = torch.from_numpy(np.ascontiguousarray(x.reshape(k, c).T)).cuda().contiguous()
+    out = torch.full((m * k,), float("nan"), dtype=torch.float64, device="cuda")
+    s = torch.cuda.Stream()
+    graph = torch.cuda.CUDAGraph()
+    torch.cuda.synchronize()
+    with torch.cuda.graph(graph, stream=s):
+        mf.spmm_device(b.data_ptr(), out.data_ptr(), k, torch.cuda.current_stream().cuda_stream)
+    assert mf.kslice() == 0                      # nothing was measured during the capture
+    for _ in range(2):
+        out.fill_(float("nan"))
+        graph.replay()
+        torch.cuda.synchronize()
+        assert max_rel_err(out.cpu().numpy(), y_ref) <= FP64_TOL
+    # outside a capture the same handle still measures and settles on a width
+    for _ in range(10):
+        mf.spmm_device(b.data_ptr(), out.data_ptr(), k)
+    torch.cuda.synchronize()
+    assert mf.kslice() in (16, 32, 64, 128)
+    assert max_rel_err(out.cpu().numpy(), y_ref) <= FP64_TOL
+    mf.close()
+
+
+def test_ticket_kernel_replays_in_a_graph(pkg, L):
+    """The ticketed row-split kernel resets its own counters (last warp out), so a captured launch can be replayed:
+    every replay must produce the full result (a stale counter would leave all but the first wave of rows unwritten)."""
+    import torch
+    m, c, k = 60000, 3000, 32
+    ia, ja, a = random_csr(m, c, 40.0, seed=77)
+    assert len(ja) >= (2 << 20)                  # large enough for the ticket rule (avg >= 32, nnz >= 2 Mi)
+    x = dense_b(c, k, 9)
+    y_ref = L.spmm_oracle(ia, ja, a, m, c, x, k)
+    mf = pkg.csr_to_format(ia, ja, a, m, c, len(ja), k, variant=pkg.ROWSPLIT)
+    b = torch.from_numpy(np.ascontiguousarray(x.reshape(k, c).T)).cuda().contiguous()
+    out = torch.full((m * k,), float("nan"), dtype=torch.float64, device="cuda")
+    mf.spmm_device(b.data_ptr(), out.data_ptr(), k)          # a plain launch first
+    torch.cuda.synchronize()
+    assert max_rel_err(out.cpu().numpy(), y_ref) <= FP64_TOL
+    s = torch.cuda.Stream()
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph, stream=s):
+        mf.spmm_device(b.data_ptr(), out.data_ptr(), k, torch.cuda.current_stream().cuda_stream)
+    for _ in range(3):
+        out.fill_(float("nan"))
+        graph.replay()
+        torch.cuda.synchronize()
+        assert max_rel_err(out.cpu().numpy(), y_ref) <= FP64_TOL
+    out.fill_(float("nan"))
+    mf.spmm_device(b.data_ptr(), out.data_ptr(), k)          # and a plain launch after the replays
+    torch.cuda.synchronize()
+    assert max_rel_err(out.cpu().numpy(), y_ref) <= FP64_TOL
+    mf.close()
