@@ -216,7 +216,15 @@ spmm_tf32_blocked_kernel(const int32_t* __restrict__ ia, const int32_t* __restri
 
 	if (producer) {
 		int j = 0, jend = 0;
-		if (row_thread && row < m) { j = __ldg(ia + row); jend = __ldg(ia + row + 1); }
+		if (row_thread && row < m) {
+			j = __ldg(ia + row); jend = __ldg(ia + row + 1);
+			// the row's (col, val) range is walked four entries per chunk: pull its lines into L2 now, so that the
+			// per-chunk queue loads find them there instead of paying an HBM round trip each
+			for (int q = j; q < jend; q += 32) {
+				asm volatile("prefetch.global.L2 [%0];" ::"l"(ja + q));
+				asm volatile("prefetch.global.L2 [%0];" ::"l"(a + q));
+			}
+		}
 		int kc = w.x;
 		// operands of the chunk about to be staged are already on their way: the loads of chunk it+1 are issued before
 		// chunk it is handed over
@@ -253,11 +261,16 @@ spmm_tf32_blocked_kernel(const int32_t* __restrict__ ia, const int32_t* __restri
 				// ---- A: my row of the stage: zero, then scatter this chunk's nonzeros (TF32, round to nearest).  Columns
 				// are sorted, so the ones of this chunk are a prefix of the queue; a full queue is refilled on the spot.
 				unsigned char* const myrow = sA + (tid >> 3) * Cfg::SBO_A + (tid & 7) * 16;
+				const int kend = kc + KT;
+				// how much of the queue belongs to this chunk is known from registers: the refill (entries j + used ...)
+				// is issued FIRST and has the whole chunk to arrive
+				int used = (qc[0] < kend) + (qc[1] < kend) + (qc[2] < kend) + (qc[3] < kend);
+				int nqc[4];
+				float nqv[4];
+				tf32_load_a(ja, a, j + used, jend, nqc, nqv);
 				#pragma unroll
 				for (int q = 0; q < KT / 4; q++) *reinterpret_cast<uint4*>(myrow + q * Cfg::LBO) = make_uint4(0, 0, 0, 0);
-				const int kend = kc + KT;
 				for (;;) {
-					int used = 0;
 					#pragma unroll
 					for (int q = 0; q < 4; q++) {
 						if (qc[q] < kend) {
@@ -265,13 +278,14 @@ spmm_tf32_blocked_kernel(const int32_t* __restrict__ ia, const int32_t* __restri
 							uint32_t bits;
 							asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(bits) : "f"(qv[q]));
 							*reinterpret_cast<uint32_t*>(myrow + (kk >> 2) * Cfg::LBO + (kk & 3) * 4) = bits;
-							used++;
 						}
 					}
 					j += used;
-					if (used == 0) break;                              // the queue still starts at nonzero j: nothing to reload
-					tf32_load_a(ja, a, j, jend, qc, qv);               // refill (for this chunk if the queue was used up, else for the next)
-					if (used < 4) break;
+					#pragma unroll
+					for (int q = 0; q < 4; q++) { qc[q] = nqc[q]; qv[q] = nqv[q]; }
+					if (used < 4) break;                               // the usual case: the new queue is for later chunks
+					used = (qc[0] < kend) + (qc[1] < kend) + (qc[2] < kend) + (qc[3] < kend);
+					tf32_load_a(ja, a, j + used, jend, nqc, nqv);
 				}
 			}
 			asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // st.shared data -> visible to the tensor core
