@@ -56,6 +56,13 @@ static int device_ok(int device, int* sms)
 }
 
 // ---- TF32 blocked kernel (tcgen05 / TMEM): per-slab column windows + launch --------------------------------
+static void tf32_release_plan(spmm_b200_f32* h)
+{
+	cudaFree(h->tf32.d_win); cudaFree(h->tf32.d_chunk0); cudaFree(h->tf32.d_eptr); cudaFree(h->tf32.d_ent);
+	h->tf32 = Tf32Plan();
+}
+
+// Per-slab column windows, then the chunk-major copy of A (count -> scan -> place), all on the device.
 static int tf32_build_plan(spmm_b200_f32* h)
 {
 	Tf32Plan& p = h->tf32;
@@ -63,26 +70,46 @@ static int tf32_build_plan(spmm_b200_f32* h)
 	if (p.nslabs == 0) return SPMM_B200_OK;
 	unsigned long long* d_total = nullptr;
 	unsigned long long total = 0;
+	int32_t* d_tmp = nullptr;
+	int32_t* d_cursor = nullptr;
+	int32_t nchunks = 0;
 	CU_TRY(cudaMalloc(&p.d_win, sizeof(int2) * p.nslabs));
+	CU_TRY(cudaMalloc(&p.d_chunk0, sizeof(int32_t) * ((size_t) p.nslabs + 1)));
 	CU_TRY(cudaMalloc(&d_total, sizeof(unsigned long long)));
 	CU_TRY(cudaMemsetAsync(d_total, 0, sizeof(unsigned long long), h->stream));
-	tf32_window_kernel<<<p.nslabs, TF32_M, 0, h->stream>>>(h->d_ia, h->d_ja, (int) h->m, p.d_win, d_total);
+	tf32_window_kernel<<<p.nslabs, TF32_M, 0, h->stream>>>(h->d_ia, h->d_ja, (int) h->m, p.d_win, p.d_chunk0, d_total);
 	h->launches++;
 	CU_TRY(cudaGetLastError());
 	CU_TRY(cudaMemcpyAsync(&total, d_total, sizeof(total), cudaMemcpyDeviceToHost, h->stream));
 	CU_TRY(cudaStreamSynchronize(h->stream));
 	cudaFree(d_total);
 	p.window_cols = (double) total;
+	// a matrix whose windows add up to more chunks than fit an int32 (or a few hundred MB of pointers) is not banded:
+	// the handle then stays on the row-split kernel (tf32_supports() is false without a plan)
+	if (p.window_cols / TF32_KT + p.nslabs > 64e6) { tf32_release_plan(h); return SPMM_B200_OK; }
+	CU_TRY(cudaMalloc(&d_tmp, sizeof(int32_t) * scan_tmp_elems((int64_t) p.nslabs + 1)));
+	h->launches += exclusive_scan_i32(p.d_chunk0, (int64_t) p.nslabs + 1, d_tmp, h->stream);
+	CU_TRY(cudaMemcpyAsync(&nchunks, p.d_chunk0 + p.nslabs, sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
+	CU_TRY(cudaStreamSynchronize(h->stream));
+	cudaFree(d_tmp); d_tmp = nullptr;
+	p.total_chunks = nchunks;
+	CU_TRY(cudaMalloc(&p.d_eptr, sizeof(int32_t) * ((size_t) nchunks + 1)));
+	CU_TRY(cudaMalloc(&d_cursor, sizeof(int32_t) * ((size_t) nchunks + 1)));
+	CU_TRY(cudaMalloc(&p.d_ent, sizeof(uint2) * std::max<int64_t>(h->nnz, 1)));
+	CU_TRY(cudaMalloc(&d_tmp, sizeof(int32_t) * scan_tmp_elems((int64_t) nchunks + 1)));
+	CU_TRY(cudaMemsetAsync(p.d_eptr, 0, sizeof(int32_t) * ((size_t) nchunks + 1), h->stream));
+	tf32_bucket_kernel<false><<<p.nslabs, TF32_M, 0, h->stream>>>(h->d_ia, h->d_ja, h->d_a, (int) h->m, p.d_win, p.d_chunk0, p.d_eptr, nullptr);
+	h->launches += 1 + exclusive_scan_i32(p.d_eptr, (int64_t) nchunks + 1, d_tmp, h->stream);
+	CU_TRY(cudaMemcpyAsync(d_cursor, p.d_eptr, sizeof(int32_t) * ((size_t) nchunks + 1), cudaMemcpyDeviceToDevice, h->stream));
+	tf32_bucket_kernel<true><<<p.nslabs, TF32_M, 0, h->stream>>>(h->d_ia, h->d_ja, h->d_a, (int) h->m, p.d_win, p.d_chunk0, d_cursor, p.d_ent);
+	h->launches++;
+	CU_TRY(cudaGetLastError());
+	CU_TRY(cudaStreamSynchronize(h->stream));
+	cudaFree(d_tmp); cudaFree(d_cursor);
 	return SPMM_B200_OK;
 }
 
-static void tf32_release_plan(spmm_b200_f32* h)
-{
-	cudaFree(h->tf32.d_win);
-	h->tf32 = Tf32Plan();
-}
-
-static bool tf32_supports(const spmm_b200_f32* h, int k) { return h->tf32.d_win && (k == 32 || k == 64 || k == 128); }
+static bool tf32_supports(const spmm_b200_f32* h, int k) { return h->tf32.d_ent && (k == 32 || k == 64 || k == 128); }
 
 template <int N, int STAGES>
 static cudaError_t tf32_launch_ns(spmm_b200_f32* h, const float* B, float* C, cudaStream_t s, int bit)
@@ -94,7 +121,7 @@ static cudaError_t tf32_launch_ns(spmm_b200_f32* h, const float* B, float* C, cu
 		if (e != cudaSuccess) return e;
 		h->smem_attr |= 1u << bit;
 	}
-	kern<<<h->tf32.nslabs, TF32_THREADS, Cfg::SMEM, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, h->tf32.d_win, (int) h->m, (int) h->c);
+	kern<<<h->tf32.nslabs, TF32_THREADS, Cfg::SMEM, s>>>(h->tf32.d_ent, h->tf32.d_eptr, h->tf32.d_chunk0, B, C, h->tf32.d_win, (int) h->m, (int) h->c);
 	return cudaGetLastError();
 }
 
@@ -255,6 +282,7 @@ static int create_slice(spmm_b200_f32** out, const int32_t* ia_slice, const int3
 	if (h->variant == SPMM_B200_BCSR) {
 		int rc = tf32_build_plan(h);
 		if (rc) return rc;
+		if (!h->tf32.d_ent && h->m > 0) h->variant = SPMM_B200_ROWSPLIT;      // not a banded matrix (see tf32_build_plan)
 	}
 	CU_TRY(cudaStreamSynchronize(h->stream));
 	return SPMM_B200_OK;

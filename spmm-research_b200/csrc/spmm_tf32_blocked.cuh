@@ -34,17 +34,22 @@
 namespace sb200 {
 
 struct Tf32Plan {
-	int2* d_win = nullptr;      // [nslabs] (first, last) column of the slab; first > last: the slab has no nonzero
+	int2* d_win = nullptr;       // [nslabs] (first, last) column of the slab; first > last: the slab has no nonzero
+	int32_t* d_chunk0 = nullptr; // [nslabs + 1] exclusive prefix of the slabs' chunk counts
+	int32_t* d_eptr = nullptr;   // [total_chunks + 1] first entry of every (slab, chunk)
+	uint2* d_ent = nullptr;      // [nnz] chunk-major copy of A: x = row_in_slab * 32 + column_in_chunk, y = value as TF32 bits
 	int nslabs = 0;
-	double window_cols = 0;     // sum of the slabs' window widths (dense work = 128 * window_cols * k multiply-adds)
+	int64_t total_chunks = 0;
+	double window_cols = 0;      // sum of the slabs' window widths (dense work = 128 * window_cols * k multiply-adds)
 };
 
 constexpr int TF32_M = 128;     // rows per slab = UMMA M
 constexpr int TF32_KT = 32;     // columns of A (rows of B) per stage
 
+// per slab: first / last column, number of KT-column chunks of its window
 __global__ void __launch_bounds__(TF32_M)
 tf32_window_kernel(const int32_t* __restrict__ ia, const int32_t* __restrict__ ja, int m, int2* __restrict__ win,
-                   unsigned long long* __restrict__ total)
+                   int32_t* __restrict__ nchunks, unsigned long long* __restrict__ total)
 {
 	__shared__ int s_lo[4], s_hi[4];
 	const int r = blockIdx.x * TF32_M + threadIdx.x;
@@ -61,7 +66,34 @@ tf32_window_kernel(const int32_t* __restrict__ ia, const int32_t* __restrict__ j
 		lo = min(min(s_lo[0], s_lo[1]), min(s_lo[2], s_lo[3]));
 		hi = max(max(s_hi[0], s_hi[1]), max(s_hi[2], s_hi[3]));
 		win[blockIdx.x] = make_int2(lo, hi);
+		nchunks[blockIdx.x] = hi >= lo ? (hi - lo) / TF32_KT + 1 : 0;
+		if (blockIdx.x == gridDim.x - 1) nchunks[gridDim.x] = 0;
 		if (hi >= lo) atomicAdd(total, (unsigned long long) (hi - lo + 1));
+	}
+}
+
+// Chunk-major copy of A for the tensor-core kernel.  FILL = false: count the entries of every (slab, chunk);
+// FILL = true: place them (cursor = running copy of the entry pointers).  The order inside a chunk is whatever the
+// atomics give: every entry lands on its own element of the dense tile, so the result does not depend on it.
+template <bool FILL>
+__global__ void __launch_bounds__(TF32_M)
+tf32_bucket_kernel(const int32_t* __restrict__ ia, const int32_t* __restrict__ ja, const float* __restrict__ a, int m,
+                   const int2* __restrict__ win, const int32_t* __restrict__ chunk0, int32_t* __restrict__ counter,
+                   uint2* __restrict__ ent)
+{
+	const int r = blockIdx.x * TF32_M + threadIdx.x;
+	if (r >= m) return;
+	const int lo = win[blockIdx.x].x;
+	const int c0 = chunk0[blockIdx.x];
+	for (int j = ia[r], je = ia[r + 1]; j < je; j++) {
+		const int rel = ja[j] - lo;
+		const int chunk = c0 + rel / TF32_KT;
+		const int pos = atomicAdd(counter + chunk, 1);
+		if constexpr (FILL) {
+			uint32_t bits;
+			asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(bits) : "f"(a[j]));
+			ent[pos] = make_uint2((uint32_t) (threadIdx.x * TF32_KT + rel % TF32_KT), bits);
+		}
 	}
 }
 
@@ -163,23 +195,13 @@ __device__ __forceinline__ void tf32_load_b(const float* __restrict__ B, int kc,
 	}
 }
 
-// up to four (col, val) pairs of a row starting at nonzero j, with independent loads
-__device__ __forceinline__ void tf32_load_a(const int32_t* __restrict__ ja, const float* __restrict__ a, int j, int jend, int (&cols)[4], float (&vals)[4])
-{
-	#pragma unroll
-	for (int q = 0; q < 4; q++) {
-		const bool ok = j + q < jend;
-		cols[q] = ok ? __ldg(ja + j + q) : INT_MAX;
-		vals[q] = ok ? __ldg(a + j + q) : 0.f;
-	}
-}
-
 template <int N, int STAGES>
 __global__ void __launch_bounds__(TF32_THREADS)
-spmm_tf32_blocked_kernel(const int32_t* __restrict__ ia, const int32_t* __restrict__ ja, const float* __restrict__ a,
+spmm_tf32_blocked_kernel(const uint2* __restrict__ ent, const int32_t* __restrict__ eptr, const int32_t* __restrict__ chunk0,
                          const float* __restrict__ B, float* __restrict__ C, const int2* __restrict__ win, int m, int c)
 {
 	using Cfg = Tf32Cfg<N, STAGES>;
+	constexpr int EPT = 3;                          // entries of a chunk a row thread keeps in registers (128 * 3 per chunk)
 	constexpr int KT = TF32_KT;
 	constexpr int UNITS = (KT / 4) * (N / 4), PER_THREAD = (UNITS + TF32_BTHREADS - 1) / TF32_BTHREADS;
 	static_assert(Cfg::STAGE_BYTES % 16 == 0, "stages stay 16-byte aligned");
@@ -215,27 +237,23 @@ spmm_tf32_blocked_kernel(const int32_t* __restrict__ ia, const int32_t* __restri
 	const int nchunks = any ? (w.y - w.x) / KT + 1 : 0;
 
 	if (producer) {
-		int j = 0, jend = 0;
-		if (row_thread && row < m) {
-			j = __ldg(ia + row); jend = __ldg(ia + row + 1);
-			// the row's (col, val) range is walked four entries per chunk: pull its lines into L2 now, so that the
-			// per-chunk queue loads find them there instead of paying an HBM round trip each
-			for (int q = j; q < jend; q += 32) {
-				asm volatile("prefetch.global.L2 [%0];" ::"l"(ja + q));
-				asm volatile("prefetch.global.L2 [%0];" ::"l"(a + q));
-			}
-		}
 		int kc = w.x;
-		// operands of the chunk about to be staged are already on their way: the loads of chunk it+1 are issued before
-		// chunk it is handed over
-		// warps 0..3 stage A (one row per thread), warps 4..7 stage B: the two run side by side and meet at the stage's barrier
+		// warps 0..3 stage A, warps 4..7 stage B: the two run side by side and meet at the stage's barrier.  The operands
+		// of chunk it+1 are requested before chunk it is handed over, so their latency hides behind the hand-over.
 		float4 br[PER_THREAD][4];
-		int qc[4];
-		float qv[4];
+		uint2 er[EPT];
 		const int btid = tid - TF32_M;
+		const int cb = chunk0[slab];
+		int e0 = 0, e1 = 0, e2 = 0;                  // entry ranges: [e0, e1) = this chunk, [e1, e2) = the next one
 		if (any) {
-			if (row_thread) tf32_load_a(ja, a, j, jend, qc, qv);
-			else tf32_load_b<N, PER_THREAD>(B, kc, c, btid, br);
+			if (row_thread) {
+				e0 = __ldg(eptr + cb); e1 = __ldg(eptr + cb + 1); e2 = nchunks > 1 ? __ldg(eptr + cb + 2) : e1;
+				#pragma unroll
+				for (int q = 0; q < EPT; q++)
+					if (e0 + q * TF32_M + tid < e1) er[q] = __ldg(ent + e0 + q * TF32_M + tid);
+			} else {
+				tf32_load_b<N, PER_THREAD>(B, kc, c, btid, br);
+			}
 		}
 		for (int it = 0; it < nchunks; it++, kc += KT) {
 			const int stage = it % STAGES;
@@ -258,35 +276,30 @@ spmm_tf32_blocked_kernel(const int32_t* __restrict__ ia, const int32_t* __restri
 				}
 				if (it + 1 < nchunks) tf32_load_b<N, PER_THREAD>(B, kc + KT, c, btid, br);
 			} else {
-				// ---- A: my row of the stage: zero, then scatter this chunk's nonzeros (TF32, round to nearest).  Columns
-				// are sorted, so the ones of this chunk are a prefix of the queue; a full queue is refilled on the spot.
+				// ---- A: zero the stage (thread = row), then scatter the chunk's entries from the chunk-major copy of A
+				// (coalesced 8-byte loads, already TF32; thread != row here, hence the barrier of the four A warps)
 				unsigned char* const myrow = sA + (tid >> 3) * Cfg::SBO_A + (tid & 7) * 16;
-				const int kend = kc + KT;
-				// how much of the queue belongs to this chunk is known from registers: the refill (entries j + used ...)
-				// is issued FIRST and has the whole chunk to arrive
-				int used = (qc[0] < kend) + (qc[1] < kend) + (qc[2] < kend) + (qc[3] < kend);
-				int nqc[4];
-				float nqv[4];
-				tf32_load_a(ja, a, j + used, jend, nqc, nqv);
 				#pragma unroll
 				for (int q = 0; q < KT / 4; q++) *reinterpret_cast<uint4*>(myrow + q * Cfg::LBO) = make_uint4(0, 0, 0, 0);
-				for (;;) {
-					#pragma unroll
-					for (int q = 0; q < 4; q++) {
-						if (qc[q] < kend) {
-							const int kk = qc[q] - kc;
-							uint32_t bits;
-							asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(bits) : "f"(qv[q]));
-							*reinterpret_cast<uint32_t*>(myrow + (kk >> 2) * Cfg::LBO + (kk & 3) * 4) = bits;
-						}
+				asm volatile("bar.sync 1, 128;" ::: "memory");
+				#pragma unroll
+				for (int q = 0; q < EPT; q++) {
+					if (e0 + q * TF32_M + tid < e1) {
+						const uint32_t r = er[q].x / KT, kk = er[q].x % KT;
+						*reinterpret_cast<uint32_t*>(sA + (r >> 3) * Cfg::SBO_A + (kk >> 2) * Cfg::LBO + (r & 7) * 16 + (kk & 3) * 4) = er[q].y;
 					}
-					j += used;
-					#pragma unroll
-					for (int q = 0; q < 4; q++) { qc[q] = nqc[q]; qv[q] = nqv[q]; }
-					if (used < 4) break;                               // the usual case: the new queue is for later chunks
-					used = (qc[0] < kend) + (qc[1] < kend) + (qc[2] < kend) + (qc[3] < kend);
-					tf32_load_a(ja, a, j + used, jend, nqc, nqv);
 				}
+				for (int e = e0 + EPT * TF32_M + tid; e < e1; e += TF32_M) {        // a chunk with more than 384 entries
+					const uint2 v = __ldg(ent + e);
+					const uint32_t r = v.x / KT, kk = v.x % KT;
+					*reinterpret_cast<uint32_t*>(sA + (r >> 3) * Cfg::SBO_A + (kk >> 2) * Cfg::LBO + (r & 7) * 16 + (kk & 3) * 4) = v.y;
+				}
+				// next chunk's entries (contiguous with this chunk's) and the pointer after them
+				e0 = e1; e1 = e2;
+				if (it + 2 < nchunks) e2 = __ldg(eptr + cb + it + 3);
+				#pragma unroll
+				for (int q = 0; q < EPT; q++)
+					if (e0 + q * TF32_M + tid < e1) er[q] = __ldg(ent + e0 + q * TF32_M + tid);
 			}
 			asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // st.shared data -> visible to the tensor core
 			mbar_arrive(bar_full + 8 * stage);
