@@ -28,9 +28,10 @@ def main():
     ap.add_argument("--variant", default="rowsplit")
     ap.add_argument("--set", action="append", default=[], help="comma-separated NAME=VALUE handle options of one configuration")
     ap.add_argument("--calls", type=int, default=30)
+    ap.add_argument("--gen", default=None, help="generator arguments instead of a named workload (then --k is required)")
     args = ap.parse_args()
     pkg = g.load_package()
-    gen, k = WORKLOADS[args.workload]
+    gen, k = (args.gen, args.k) if args.gen else WORKLOADS[args.workload]
     k = args.k or k
     ia, ja, a, m, c = L.generate(gen)
     nnz = len(ja)

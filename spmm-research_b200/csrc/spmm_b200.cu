@@ -56,6 +56,7 @@ struct Options {
 	int merge_maxrow = 256;    // MERGE_MAXROW
 	int bcsr_fill_pct = 30;    // BCSR_FILL_PCT
 	int bcsr_tma = 1, bcsr_stages = 2, bcsr_brw = 0;
+	int l2_hint = 0;           // L2_HINT: 1 = static row-split launches carry L2 eviction hints (B evict-last, A / C evict-first)
 	int tf32_stages = 2;       // TF32_STAGES: shared-memory stages of the TF32 blocked kernel (2 or 3)
 };
 
@@ -72,7 +73,7 @@ static const OptionName OPTION_TABLE[] = {
 	{"PIPELINE_COLS", &Options::pipeline_cols}, {"PIPELINE_MIN_KB", &Options::pipeline_min_kb},
 	{"DIRECT_STORE", &Options::direct_store}, {"CTAS_PER_SM", &Options::ctas_per_sm},
 	{"MERGE_MAXROW", &Options::merge_maxrow}, {"BCSR_FILL_PCT", &Options::bcsr_fill_pct},
-	{"TF32_STAGES", &Options::tf32_stages}, {"BCSR_TMA", &Options::bcsr_tma}, {"BCSR_STAGES", &Options::bcsr_stages}, {"BCSR_BRW", &Options::bcsr_brw},
+	{"TF32_STAGES", &Options::tf32_stages}, {"L2_HINT", &Options::l2_hint}, {"BCSR_TMA", &Options::bcsr_tma}, {"BCSR_STAGES", &Options::bcsr_stages}, {"BCSR_BRW", &Options::bcsr_brw},
 };
 
 static Options options_from_env()
@@ -339,6 +340,8 @@ static void launch_rowsplit_gv(spmm_b200* h, const double* B, double* C, cudaStr
 		spmm_rowsplit_kernel<G, V, 2, THREADS><<<h->n_ctas, THREADS, 0, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, h->d_cta_rows, ldb, ldc);
 	else if (whole)
 		spmm_rowsplit_kernel<G, V, 4, THREADS, K><<<h->n_ctas, THREADS, 0, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, h->d_cta_rows, ldb, ldc);
+	else if (o.l2_hint && V >= 2)
+		spmm_rowsplit_kernel<G, V, 4, THREADS, 0, 1><<<h->n_ctas, THREADS, 0, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, h->d_cta_rows, ldb, ldc);
 	else
 		spmm_rowsplit_kernel<G, V, 4, THREADS><<<h->n_ctas, THREADS, 0, s>>>(h->d_ia, h->d_ja, h->d_a, B, C, h->d_cta_rows, ldb, ldc);
 }

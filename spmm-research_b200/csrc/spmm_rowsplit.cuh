@@ -33,11 +33,38 @@ namespace sb200 {
 
 template <int V> struct Frag { double v[V]; };
 
+// L2 eviction-priority hints (createpolicy + ld/st .L2::cache_hint): B rows "evict last", the single-use A stream and C
+// "evict first" -- for matrices whose gather window is about the size of L2 (HINT kernels, option L2_HINT)
+__device__ __forceinline__ uint64_t l2_policy_evict_last() { uint64_t p; asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p)); return p; }
+__device__ __forceinline__ uint64_t l2_policy_evict_first() { uint64_t p; asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p)); return p; }
+__device__ __forceinline__ double2 ldg_hint_v2(const double2* p, uint64_t pol)
+{
+	double2 v;
+	asm volatile("ld.global.nc.L2::cache_hint.v2.f64 {%0, %1}, [%2], %3;" : "=d"(v.x), "=d"(v.y) : "l"(p), "l"(pol));
+	return v;
+}
+__device__ __forceinline__ int ldg_hint_s32(const int* p, uint64_t pol)
+{
+	int v;
+	asm volatile("ld.global.nc.L2::cache_hint.s32 %0, [%1], %2;" : "=r"(v) : "l"(p), "l"(pol));
+	return v;
+}
+__device__ __forceinline__ double ldg_hint_f64(const double* p, uint64_t pol)
+{
+	double v;
+	asm volatile("ld.global.nc.L2::cache_hint.f64 %0, [%1], %2;" : "=d"(v) : "l"(p), "l"(pol));
+	return v;
+}
+__device__ __forceinline__ void stg_hint_v2(double2* p, double2 v, uint64_t pol)
+{
+	asm volatile("st.global.L2::cache_hint.v2.f64 [%0], {%1, %2}, %3;" ::"l"(p), "d"(v.x), "d"(v.y), "l"(pol) : "memory");
+}
+
 // Load this lane's V columns of B row `col`.  Columns are dealt to lanes in pairs:
 // lane l holds columns {2l, 2l+1} (+ 2G for the second pair when V == 4), so every
 // load instruction of the group covers one contiguous span.
-template <int G, int V, int LD = 0>
-__device__ __forceinline__ Frag<V> load_b(const double* __restrict__ B, int col, int lig, int ldb)
+template <int G, int V, int LD = 0, int HINT = 0>
+__device__ __forceinline__ Frag<V> load_b(const double* __restrict__ B, int col, int lig, int ldb, uint64_t pol = 0)
 {
 	Frag<V> f;
 	// LD > 0: the row stride is a compile-time constant and c*LD < 2^32 (checked by the launcher), so the element
@@ -52,15 +79,16 @@ __device__ __forceinline__ Frag<V> load_b(const double* __restrict__ B, int col,
 		static_assert(V % 2 == 0, "V must be 1 or even");
 		#pragma unroll
 		for (int i = 0; i < V / 2; i++) {
-			const double2 t = __ldg(reinterpret_cast<const double2*>(p) + i * G + lig);
+			const double2 t = HINT ? ldg_hint_v2(reinterpret_cast<const double2*>(p) + i * G + lig, pol)
+			                       : __ldg(reinterpret_cast<const double2*>(p) + i * G + lig);
 			f.v[2 * i] = t.x; f.v[2 * i + 1] = t.y;
 		}
 	}
 	return f;
 }
 
-template <int G, int V>
-__device__ __forceinline__ void store_c(double* __restrict__ C, size_t row, int lig, const double (&acc)[V], int ldc)
+template <int G, int V, int HINT = 0>
+__device__ __forceinline__ void store_c(double* __restrict__ C, size_t row, int lig, const double (&acc)[V], int ldc, uint64_t pol = 0)
 {
 	double* p = C + row * ldc;
 	if constexpr (V == 1) {
@@ -69,8 +97,10 @@ __device__ __forceinline__ void store_c(double* __restrict__ C, size_t row, int 
 		// (streaming stores / loads -- st.global.cs for C, ld.global.cs for the A stream -- were measured in round 2 to keep
 		// B in L2 on the large-window workloads: no gain on cfg5-large, 5-8 % slower on cfg2 bw 0.3 / 1; plain accesses stay)
 		#pragma unroll
-		for (int i = 0; i < V / 2; i++)
-			reinterpret_cast<double2*>(p)[i * G + lig] = make_double2(acc[2 * i], acc[2 * i + 1]);
+		for (int i = 0; i < V / 2; i++) {
+			if constexpr (HINT) stg_hint_v2(reinterpret_cast<double2*>(p) + i * G + lig, make_double2(acc[2 * i], acc[2 * i + 1]), pol);
+			else reinterpret_cast<double2*>(p)[i * G + lig] = make_double2(acc[2 * i], acc[2 * i + 1]);
+		}
 	}
 }
 
@@ -89,13 +119,15 @@ __device__ __forceinline__ double shfl_f64(double v, int src)
 // (the groups of a warp own consecutive rows, so the warp's loads are contiguous in ja / a) and hand them round
 // with shuffles; UNROLL B-row gathers are in flight per group.  All lanes of a warp run the same trip counts (the
 // shuffles need the full warp).  The per-row sum runs strictly left to right.
-template <int G, int V, int UNROLL, int LD>
+template <int G, int V, int UNROLL, int LD, int HINT = 0>
 __device__ __forceinline__ void row_sweep(const int32_t* __restrict__ ia, const int32_t* __restrict__ ja, const double* __restrict__ a,
                                           const double* __restrict__ B, double* __restrict__ C,
                                           int r0, int r1, int stride, int gid, int lig, int ldb, int ldc)
 {
 	static_assert(G % UNROLL == 0 || UNROLL % G == 0, "UNROLL and G must nest");
 	constexpr int U = UNROLL < G ? UNROLL : G;
+	uint64_t pol_b = 0, pol_s = 0;
+	if constexpr (HINT) { pol_b = l2_policy_evict_last(); pol_s = l2_policy_evict_first(); }
 	for (int base = r0; base < r1; base += stride) {
 		const int row = base + gid;
 		const bool live = row < r1;
@@ -111,7 +143,10 @@ __device__ __forceinline__ void row_sweep(const int32_t* __restrict__ ia, const 
 			if (rem_warp <= 0) break;
 			int cj = 0;
 			double ca = 0.0;
-			if (lig < rem) { cj = __ldg(ja + j + lig); ca = __ldg(a + j + lig); }
+			if (lig < rem) {
+				if constexpr (HINT) { cj = ldg_hint_s32(ja + j + lig, pol_s); ca = ldg_hint_f64(a + j + lig, pol_s); }
+				else { cj = __ldg(ja + j + lig); ca = __ldg(a + j + lig); }
+			}
 			const int cnt = min(rem_warp, G);
 			// at most G/U steps: unrolled so that the shuffle source lanes are immediates
 			#pragma unroll
@@ -127,7 +162,7 @@ __device__ __forceinline__ void row_sweep(const int32_t* __restrict__ ia, const 
 				}
 				#pragma unroll
 				for (int i = 0; i < U; i++)
-					if (u + i < rem) bb[i] = load_b<G, V, LD>(B, cc[i], lig, ldb);
+					if (u + i < rem) bb[i] = load_b<G, V, LD, HINT>(B, cc[i], lig, ldb, pol_b);
 				#pragma unroll
 				for (int i = 0; i < U; i++) {
 					if (u + i < rem) {
@@ -138,19 +173,19 @@ __device__ __forceinline__ void row_sweep(const int32_t* __restrict__ ia, const 
 			}
 			j += G;
 		}
-		if (live) store_c<G, V>(C, (size_t) row, lig, acc, ldc);
+		if (live) store_c<G, V, HINT>(C, (size_t) row, lig, acc, ldc, pol_s);
 	}
 }
 
 // ldb / ldc = row strides of B and C in doubles (G*V for a whole operand; larger when the launch
 // works on a column slice of a wider B / C, see launch_spmm's L2-aware k slicing)
-template <int G, int V, int UNROLL, int THREADS, int LD = 0>
+template <int G, int V, int UNROLL, int THREADS, int LD = 0, int HINT = 0>
 __global__ void __launch_bounds__(THREADS)
 spmm_rowsplit_kernel(const int32_t* __restrict__ ia, const int32_t* __restrict__ ja, const double* __restrict__ a,
                      const double* __restrict__ B, double* __restrict__ C,
                      const int32_t* __restrict__ cta_rows, int ldb, int ldc)
 {
-	row_sweep<G, V, UNROLL, LD>(ia, ja, a, B, C, cta_rows[blockIdx.x], cta_rows[blockIdx.x + 1], THREADS / G,
+	row_sweep<G, V, UNROLL, LD, HINT>(ia, ja, a, B, C, cta_rows[blockIdx.x], cta_rows[blockIdx.x + 1], THREADS / G,
 	                            threadIdx.x / G, threadIdx.x % G, ldb, ldc);
 }
 
