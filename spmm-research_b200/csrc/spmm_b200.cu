@@ -49,6 +49,7 @@ struct Options {
 	int const_ld = 1;          // CONST_LD: compile-time row stride when the operand is whole
 	int unroll = 4;            // UNROLL: B-row gathers in flight per lane group
 	int kslice = 0;            // KSLICE: 0 = measure, -1 = never, w = force
+	int kslice_min_mb = 64;    // KSLICE_MIN_MB: measure when the touched window of B (col_span x 8k bytes) exceeds this
 	int pipeline_cols = -1;    // PIPELINE_COLS: host pipeline slice width; 0 = off, -1 = choose
 	int pipeline_min_kb = 8 << 10;
 	int direct_store = 1;      // DIRECT_STORE
@@ -69,7 +70,7 @@ static int env_int(const char* name, int dflt)
 struct OptionName { const char* name; int Options::*field; };
 static const OptionName OPTION_TABLE[] = {
 	{"TICKET", &Options::ticket}, {"TICKET_CTAS", &Options::ticket_ctas}, {"TICKET_MIN_NNZ", &Options::ticket_min_nnz}, {"STAGE", &Options::stage},
-	{"CONST_LD", &Options::const_ld}, {"UNROLL", &Options::unroll}, {"KSLICE", &Options::kslice},
+	{"CONST_LD", &Options::const_ld}, {"UNROLL", &Options::unroll}, {"KSLICE", &Options::kslice}, {"KSLICE_MIN_MB", &Options::kslice_min_mb},
 	{"PIPELINE_COLS", &Options::pipeline_cols}, {"PIPELINE_MIN_KB", &Options::pipeline_min_kb},
 	{"DIRECT_STORE", &Options::direct_store}, {"CTAS_PER_SM", &Options::ctas_per_sm},
 	{"MERGE_MAXROW", &Options::merge_maxrow}, {"BCSR_FILL_PCT", &Options::bcsr_fill_pct},
@@ -904,8 +905,10 @@ extern "C" int spmm_b200_run_device(spmm_b200_t* h, const double* b_dev, double*
 	// this k run one candidate slice width each and are timed (they block until their kernels finish; every
 	// candidate computes the same bits), then the fastest is kept -- per k, so alternating k values do not re-tune.
 	// Never while the stream is being captured into a graph (the measurement synchronises).
-	bool tunable = h->variant == SPMM_B200_ROWSPLIT && k >= 64 && k % 16 == 0 && h->opt.kslice == 0
-	               && (double) h->col_span * 8.0 * k > 192e6 && h->nnz > 0;
+	// (k >= 32 and 64 MB since round 2: gathers read by all SMs see roughly half of the 126 MB L2 -- cfg5-large's
+	// 107 MB slice window still misses, profiles/r2_cfg5_large_sliced.md -- so a 77 MB window at k = 32 is worth a try too)
+	bool tunable = h->variant == SPMM_B200_ROWSPLIT && k >= 32 && k % 16 == 0 && h->opt.kslice == 0
+	               && (double) h->col_span * 8.0 * k > h->opt.kslice_min_mb * 1e6 && h->nnz > 0;
 	if (tunable && h->ks_k != k) {
 		h->ks_k = k; h->ks_best = 0; h->ks_try = 0;
 		for (const KsliceChoice& d : h->ks_done)
