@@ -157,7 +157,7 @@ int spmm_b200_fetch_c(spmm_b200_t *h, double *y_host, int k);
  * (bench.py / torch.distributed ranks): b_dev = row-major c x k, c_dev =
  * row-major m_local x k, both on the handle's device; `stream` is a
  * cudaStream_t (NULL = default stream).  Asynchronous -- except that, when the B rows the matrix touches
- * (column span x 8k bytes) are far beyond the 126 MB L2 and k >= 64, the first 8 calls with a given k each run and
+ * (column span x 8k bytes) exceed 64 MB and k >= 32, the first calls with a given k (two per candidate, at most 8) each run and
  * time one candidate column-slice width of the row-split kernel (same bits for every candidate) and BLOCK
  * until their kernels finish; the fastest is kept per k (spmm_b200_kslice).  The measurement is skipped while
  * `stream` is being captured into a CUDA graph; SPMM_B200_KSLICE=-1 turns it off. */
