@@ -97,6 +97,43 @@ def test_argument_validation(pkg):
     lib.spmm_b200_pipeline_destroy_f32(None)
 
 
+def test_argument_validation_round2_entry_points(pkg):
+    """Multi-GPU, option, timeline and fp32-variant entry points reject bad arguments before touching a device."""
+    lib = pkg.load_library()
+    ia, ja, a = random_csr(10, 10, 2.0, 0)
+    h = C.c_void_p()
+    rp, ci, va = ia.ctypes.data, ja.ctypes.data, a.ctypes.data
+    # single-process multi-GPU
+    assert lib.spmm_b200_create_multi(None, rp, ci, va, 10, 10, len(ja), 4, 1, None, pkg.AUTO, 0) == -1
+    assert lib.spmm_b200_create_multi(C.byref(h), None, ci, va, 10, 10, len(ja), 4, 1, None, pkg.AUTO, 0) == -1
+    assert lib.spmm_b200_create_multi(C.byref(h), rp, ci, va, 10, 10, len(ja), 4, 0, None, pkg.AUTO, 0) == -1
+    assert lib.spmm_b200_create_multi(C.byref(h), rp, ci, va, 10, 10, len(ja), 4, 1000, None, pkg.AUTO, 0) == -1
+    assert lib.spmm_b200_create_multi(C.byref(h), rp, ci, va, 10, 10, len(ja), 4, 1, None, 17, 0) == -1
+    assert lib.spmm_b200_create_multi(C.byref(h), rp, ci, va, 10, 10, len(ja), 4, 1, None, pkg.AUTO, 9) == -1
+    assert lib.spmm_b200_create_multi(C.byref(h), rp, ci, va, 10, 10, 2 ** 31, 4, 1, None, pkg.AUTO, 0) == -5
+    assert h.value is None
+    assert lib.spmm_b200_run_multi(None, None, None, 4, 1) == -1
+    assert lib.spmm_b200_set_b_multi(None, None, 4) == -1
+    assert lib.spmm_b200_run_resident_multi(None, 4) == -1
+    assert lib.spmm_b200_fetch_c_multi(None, None, 4) == -1
+    assert lib.spmm_b200_multi_ngpus(None) == -1
+    assert lib.spmm_b200_multi_shard(None, 0) is None
+    lib.spmm_b200_destroy_multi(None)
+    # per-handle options and the slice timeline
+    assert lib.spmm_b200_set_option(None, b"TICKET", 1) == -1
+    assert lib.spmm_b200_set_option_f32(None, b"TICKET", 1) == -1
+    assert lib.spmm_b200_pipeline_set_option(None, b"RESIDENT", 1) == -1
+    assert lib.spmm_b200_last_timeline(None, None, 0) == -1
+    # fp32: variant range includes the fp32-only variants, nothing beyond
+    af = a.astype(np.float32)
+    assert lib.spmm_b200_create_f32(None, rp, ci, af.ctypes.data, 10, 10, len(ja), 4, 0, pkg.AUTO, 0) == -1
+    assert lib.spmm_b200_create_f32(C.byref(h), rp, ci, af.ctypes.data, 10, 10, len(ja), 4, 0, 99, 0) == -1
+    assert lib.spmm_b200_create_f32(C.byref(h), rp, ci, af.ctypes.data, 10, 10, len(ja), 0, 0, pkg.AUTO, 0) == -1
+    assert lib.spmm_b200_variant_f32(None) == -1
+    # the nnz-carry split needs an output array like the other modes
+    assert lib.spmm_b200_partition(rp, 10, len(ja), 4, pkg.PART_NNZ_CARRY, None, 0) == -1
+
+
 def test_no_cpu_fallback(pkg):
     """Without a usable device construction raises; with one this test is vacuous."""
     lib = pkg.load_library()
