@@ -390,22 +390,49 @@ def gpu_arm(args, ia, ja, a, m, c, k, nnz, workload_desc):
 
     def e2e_step():
         # the public drop-in call with HOST buffers: upload (root) -> broadcast -> kernel -> download of the
-        # row-local C, pipelined over 16-column slices inside the library
-        if world == 1:
+        # row-local C, pipelined inside the library over row blocks (banded matrix, N = 1) or 16-column slices
+        if world == 1 or own_window:
             mf.spmm(x_host.numpy(), y_host.numpy()[: m_loc * k], k)
         else:
             mf.spmm_replicated(x_host.numpy(), y_host.numpy()[: m_loc * k], k, bcast, x_on_every_rank=True)
-    for _ in range(2):
-        e2e_step()
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(e2e_steps):
-        e2e_step()
-    barrier()
-    e2e_s = max_over_ranks((time.perf_counter() - t0) / e2e_steps)
+
+    def time_e2e(steps):
+        for _ in range(2):
+            e2e_step()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            e2e_step()
+        barrier()
+        return max_over_ranks((time.perf_counter() - t0) / steps)
+
+    # Every rank holds x (the reference's harness is one process with one x).  A shard reads only the rows of B between
+    # its first and last touched column; when that window is no larger than the 1/N share of B a rank would upload for
+    # the all-gather, every rank uploads its own window over its own PCIe link and no collective runs at all.
+    span = mf.col_window()[1]
+    own_window = world > 1 and max_over_ranks(float(span)) * world <= c
+    e2e_s = time_e2e(e2e_steps)
     clocks = sampler.stop()
     e2e_val = 2.0 * nnz * k / e2e_s / 1e9
     timeline = mf.last_timeline()            # event times of the last e2e step on this rank (ms since its first enqueue)
+    band = mf.last_rowband()
+    up_bytes, down_bytes = mf.last_transfer_bytes()       # what the library actually moved over PCIe on this rank
+    if world > 1:
+        t = torch.tensor([up_bytes, down_bytes], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        up_bytes, down_bytes = int(t[0].item()), int(t[1].item())
+    # the same call with the whole of B uploaded and the k-slice pipeline (what round 1 and the first half of round 2
+    # measured): kept on the line so that the effect of uploading only the touched rows of B is visible
+    full = None
+    if world == 1 and up_bytes < 8 * c * k:
+        y_keep = y_host.clone()
+        mf.set_option("UPLOAD_WINDOW", 0); mf.set_option("ROWBAND", 0)
+        full_s = time_e2e(3)
+        full = {"ms_per_step": full_s * 1e3, "value": 2.0 * nnz * k / full_s / 1e9, "h2d_bytes_per_step": mf.last_transfer_bytes()[0],
+                "same_result": bool(torch.equal(y_keep, y_host)),
+                "note": "UPLOAD_WINDOW=0, ROWBAND=0: all c x k of B uploaded, k-slice pipeline"}
+        mf.set_option("UPLOAD_WINDOW", 1); mf.set_option("ROWBAND", -1)
+        y_host.copy_(y_keep)
 
     # ---- checksum so that the work cannot be skipped silently -----------------------------------
     csum = float(c_dev[: m_loc * k].sum().item()) if m_loc else 0.0
@@ -433,8 +460,10 @@ def gpu_arm(args, ia, ja, a, m, c, k, nnz, workload_desc):
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic", "config": workload_desc,
-        "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": 8 * c * k, "d2h_bytes_per_step": 8 * m * k,
-                "ms_per_step": e2e_s * 1e3, "steps": e2e_steps},
+        "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": up_bytes, "d2h_bytes_per_step": down_bytes,
+                "ms_per_step": e2e_s * 1e3, "steps": e2e_steps,
+                "x_bytes": 8 * c * k, "b_rows_uploaded": "first..last column the matrix touches (%d of %d rows of B on rank 0); "
+                                                          "rows no nonzero references cannot change y" % (span, c)},
         "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": ncu_traffic(args.workload, k, world, mf.format_name), "peak_source": peak_src,
@@ -455,6 +484,15 @@ def gpu_arm(args, ia, ja, a, m, c, k, nnz, workload_desc):
         "bcsr_fill": mf.bcsr_fill(), "kslice": mf.kslice(),
     }
     line["e2e"]["timeline_ms_last_step_rank0"] = timeline
+    # which host pipeline the library took for the e2e call: row blocks of a banded matrix (B rows up, C rows down)
+    # or column slices
+    line["e2e"]["pipeline"] = (f"row-band, {band} row blocks" if band > 0 else
+                               f"k-slice, {len(timeline)} column slices" if timeline else "single upload / kernel / download")
+    if world > 1:
+        line["e2e"]["replication"] = ("none: every rank uploads its own window of B" if own_window else
+                                      "1/N of B per rank + NCCL all-gather per slice")
+    if full:
+        line["e2e"]["full_b_upload"] = full
     if rank == 0 and not args.no_parity:
         # the e2e result (host buffer) against the reference's CPU kernel on the same rows: whole matrix at N = 1,
         # rank 0's shard rows at N > 1
@@ -506,7 +544,7 @@ def main():
     desc = {"workload": f"{args.workload}: artificial-matrix-generator '{gen_args}', fp64 CSR SpMM k={k}",
             "m": m, "c": c, "nnz": nnz, "k": k, "b_layout": "oracle column-major x[n*c+j] at the boundary, row-major on device",
             "l2": "inputs larger than L2 (A stream + C = %.0f MB per step >> 126 MB); no flush" % ((12.0 * nnz + 8.0 * k * m) / 1e6),
-            "sharding": "nnz-balanced rows (lib/parallel_util.h:141-165), B by one NCCL broadcast, C row-local"}
+            "sharding": "nnz-balanced rows (lib/parallel_util.h:141-165), B replicated on device (e2e: see e2e.replication), C row-local"}
     if args.impl == "reference":
         reference_arm(args, ia, ja, a, m, c, k, nnz, desc)
     else:

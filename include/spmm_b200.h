@@ -142,9 +142,10 @@ int spmm_b200_unregister_host(spmm_b200_t *h, const void *p);
  * optional).  Unknown names: SPMM_B200_EINVAL. */
 int spmm_b200_set_option(spmm_b200_t *h, const char *name, int value);
 
-/* Event-stamped timeline of the last k-sliced host-buffer run (spmm_b200_run / _run_replicated): out[0] = number of
- * slices S, then per slice six times in ms since the first enqueue: H2D done, replication done, transpose done,
- * kernel start, kernel end, D2H done.  Returns the number of doubles written. */
+/* Event-stamped timeline of the last pipelined host-buffer run (spmm_b200_run / _run_replicated): out[0] = number of
+ * steps S (column slices, or row blocks when the run was row-banded, see spmm_b200_last_rowband), then per step six
+ * times in ms since the first enqueue: H2D done, replication done, transpose done, kernel start, kernel end, D2H
+ * done.  Returns the number of doubles written. */
 int spmm_b200_last_timeline(const spmm_b200_t *h, double *out, int max_values);
 
 /* Upload B once (x is constant across the reference's timed loop,
@@ -283,6 +284,9 @@ int64_t spmm_b200_rows(const spmm_b200_t *h);         /* rows held by this handl
 int64_t spmm_b200_nnz(const spmm_b200_t *h);
 int     spmm_b200_variant(const spmm_b200_t *h);      /* the variant AUTO resolved to         */
 int64_t spmm_b200_bcsr_blocks(const spmm_b200_t *h);  /* 8x1 blocks stored (0 unless a BCSR variant); fill = nnz / (8*blocks) */
+int     spmm_b200_last_rowband(const spmm_b200_t *h); /* row blocks of the last spmm_b200_run when it took the row-band host pipeline (banded matrix: B rows up, C rows down, block by block), else 0 */
+int     spmm_b200_col_window(const spmm_b200_t *h, int64_t *first_col, int64_t *ncols); /* first touched column and last - first + 1 over the handle's nonzeros (0 columns: no nonzero): the rows of B this handle reads */
+int     spmm_b200_last_transfer_bytes(const spmm_b200_t *h, int64_t *h2d_bytes, int64_t *d2h_bytes); /* bytes the last host-buffer call moved over PCIe: only the rows of B the matrix's nonzeros reference go up (UPLOAD_WINDOW) */
 int     spmm_b200_kslice(const spmm_b200_t *h);       /* column-slice width the row-split path settled on for its last k (0: none / still measuring; k: one launch) */
 double  spmm_b200_last_kernel_ms(const spmm_b200_t *h); /* CUDA-event time of the last run's kernels */
 int64_t spmm_b200_launch_count(const spmm_b200_t *h); /* kernels launched by this handle so far */

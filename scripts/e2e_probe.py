@@ -55,7 +55,8 @@ def main():
             y0 = y.numpy().copy()
         else:
             same = "identical" if np.array_equal(y.numpy(), y0) else "DIFFERS"
-        print(f"{conf or '(defaults)':36s} median {np.median(ts):.3f} ms  min {np.min(ts):.3f} ms  kernels {mf.last_kernel_ms():.3f} ms  {same}", flush=True)
+        band = "" if args.multi else f"rowband {mf.last_rowband()}  "
+        print(f"{conf or '(defaults)':36s} median {np.median(ts):.3f} ms  min {np.min(ts):.3f} ms  kernels {mf.last_kernel_ms():.3f} ms  {band}{same}", flush=True)
         if not args.multi:
             for s, t in enumerate(mf.last_timeline()):
                 print(f"    slice {s}: " + "  ".join(f"{kk} {v:.3f}" for kk, v in t.items()), flush=True)

@@ -38,7 +38,7 @@ EXPORTS = [
     "spmm_b200_multi_peer_access", "spmm_b200_destroy_multi",
     "spmm_b200_run_resident", "spmm_b200_fetch_c", "spmm_b200_run_device",
     "spmm_b200_transpose_b_device", "spmm_b200_partition", "spmm_b200_partition_host", "spmm_b200_coo_to_csr", "spmm_b200_rows", "spmm_b200_nnz",
-    "spmm_b200_variant", "spmm_b200_bcsr_blocks", "spmm_b200_kslice", "spmm_b200_last_kernel_ms", "spmm_b200_launch_count", "spmm_b200_stats",
+    "spmm_b200_variant", "spmm_b200_bcsr_blocks", "spmm_b200_kslice", "spmm_b200_last_rowband", "spmm_b200_last_transfer_bytes", "spmm_b200_col_window", "spmm_b200_last_kernel_ms", "spmm_b200_launch_count", "spmm_b200_stats",
     "spmm_b200_stats_labels", "spmm_b200_destroy", "spmm_b200_strerror", "spmm_b200_last_cuda_error",
     "spmm_b200_create_f32", "spmm_b200_create_shard_f32", "spmm_b200_run_f32", "spmm_b200_run_device_f32",
     "spmm_b200_fetch_c_f32", "spmm_b200_variant_f32", "spmm_b200_set_option_f32", "spmm_b200_rows_f32", "spmm_b200_nnz_f32", "spmm_b200_launch_count_f32",
@@ -115,6 +115,9 @@ def load_library():
     lib.spmm_b200_variant.argtypes = [_vp]
     lib.spmm_b200_bcsr_blocks.argtypes = [_vp]; lib.spmm_b200_bcsr_blocks.restype = _i64
     lib.spmm_b200_kslice.argtypes = [_vp]
+    lib.spmm_b200_last_rowband.argtypes = [_vp]
+    lib.spmm_b200_last_transfer_bytes.argtypes = [_vp, C.POINTER(_i64), C.POINTER(_i64)]
+    lib.spmm_b200_col_window.argtypes = [_vp, C.POINTER(_i64), C.POINTER(_i64)]
     lib.spmm_b200_last_kernel_ms.argtypes = [_vp]; lib.spmm_b200_last_kernel_ms.restype = _dbl
     lib.spmm_b200_launch_count.argtypes = [_vp]; lib.spmm_b200_launch_count.restype = _i64
     lib.spmm_b200_stats.argtypes = [_vp, C.c_char_p, C.c_long]
@@ -294,6 +297,23 @@ class MatrixFormat:
     def kslice(self):
         """Column-slice width the row-split path settled on (0: none / still measuring)."""
         return load_library().spmm_b200_kslice(self._h)
+
+    def last_rowband(self):
+        """Row blocks of the last host-buffer spmm() when it ran the row-band pipeline (banded matrix), else 0."""
+        return load_library().spmm_b200_last_rowband(self._h)
+
+    def col_window(self):
+        """(first touched column, number of columns up to the last touched one): the rows of B this handle reads."""
+        lo, n = _i64(0), _i64(0)
+        _check(load_library().spmm_b200_col_window(self._h, C.byref(lo), C.byref(n)), "col_window")
+        return int(lo.value), int(n.value)
+
+    def last_transfer_bytes(self):
+        """(host->device, device->host) bytes the last host-buffer spmm() copied: only the rows of B between the first
+        and the last column the matrix touches are uploaded."""
+        up, down = _i64(0), _i64(0)
+        _check(load_library().spmm_b200_last_transfer_bytes(self._h, C.byref(up), C.byref(down)), "last_transfer_bytes")
+        return int(up.value), int(down.value)
 
     def statistics_start(self):
         pass

@@ -53,6 +53,9 @@ struct Options {
 	int pipeline_cols = -1;    // PIPELINE_COLS: host pipeline slice width; 0 = off, -1 = choose
 	int pipeline_min_kb = 8 << 10;
 	int direct_store = 1;      // DIRECT_STORE
+	int rowband = -1;          // ROWBAND: host pipeline over row blocks of a banded matrix; -1 = by the transfer model, 0 = off, R = force R equal blocks, -2 = force the graded blocks
+	int rowband_direct = 0;    // ROWBAND_DIRECT: 1 = row-band blocks store C straight into mapped host memory (measured slower than one contiguous copy per block)
+	int upload_window = 1;     // UPLOAD_WINDOW: host-buffer calls upload only the rows of B the matrix's nonzeros reference (first..last touched column)
 	int ctas_per_sm = 0;       // CTAS_PER_SM: 0 = by k
 	int merge_maxrow = 256;    // MERGE_MAXROW
 	int bcsr_fill_pct = 30;    // BCSR_FILL_PCT
@@ -72,7 +75,7 @@ static const OptionName OPTION_TABLE[] = {
 	{"TICKET", &Options::ticket}, {"TICKET_CTAS", &Options::ticket_ctas}, {"TICKET_MIN_NNZ", &Options::ticket_min_nnz}, {"STAGE", &Options::stage},
 	{"CONST_LD", &Options::const_ld}, {"UNROLL", &Options::unroll}, {"KSLICE", &Options::kslice}, {"KSLICE_MIN_MB", &Options::kslice_min_mb},
 	{"PIPELINE_COLS", &Options::pipeline_cols}, {"PIPELINE_MIN_KB", &Options::pipeline_min_kb},
-	{"DIRECT_STORE", &Options::direct_store}, {"CTAS_PER_SM", &Options::ctas_per_sm},
+	{"DIRECT_STORE", &Options::direct_store}, {"ROWBAND", &Options::rowband}, {"ROWBAND_DIRECT", &Options::rowband_direct}, {"UPLOAD_WINDOW", &Options::upload_window}, {"CTAS_PER_SM", &Options::ctas_per_sm},
 	{"MERGE_MAXROW", &Options::merge_maxrow}, {"BCSR_FILL_PCT", &Options::bcsr_fill_pct},
 	{"TF32_STAGES", &Options::tf32_stages}, {"L2_HINT", &Options::l2_hint}, {"BCSR_TMA", &Options::bcsr_tma}, {"BCSR_STAGES", &Options::bcsr_stages}, {"BCSR_BRW", &Options::bcsr_brw},
 };
@@ -103,6 +106,12 @@ struct spmm_b200 {
 	int rank = 0, nranks = 1;             // shard identity (spmm_b200_create_shard)
 	int max_row = 0;                      // longest row of the shard
 	int64_t col_min = 0, col_span = 0;    // first touched column, max column - min column + 1 over the shard's nonzeros
+	// first / last touched column of each of BAND_FINE equal row blocks (min > max: the block has no nonzero): what the
+	// row-band host pipeline (run_rowband) needs to know which rows of B a block of C rows waits for
+	int band_min[64], band_max[64];
+	int band_blocks = 0;                  // run_rowband: row blocks of the last run (0: the last run was not row-banded)
+	int64_t last_h2d_bytes = 0, last_d2h_bytes = 0;   // bytes the last host-buffer call copied over PCIe (spmm_b200_last_transfer_bytes)
+	int64_t win_r0 = 0, win_rows = -1;    // row window of the next row-split launches (-1: all rows); set by run_rowband only
 	// L2-aware k slicing of the row-split kernel, chosen by timing the candidates on the first calls
 	int ks_k = 0;                         // k being measured (or last looked up)
 	int ks_best = 0;                      // chosen slice width (== k: one launch); 0 while still measuring
@@ -210,6 +219,27 @@ __global__ void col_span_kernel(const int32_t* __restrict__ ja, int64_t nnz, int
 	if ((threadIdx.x & 31) == 0 && hi >= 0) { atomicMin(out_min, lo); atomicMax(out_max, hi); }
 }
 
+static constexpr int BAND_FINE = 64;
+
+// Column range of each of nblk equal row blocks: block b = rows [m*b/nblk, m*(b+1)/nblk); grid (x, nblk).
+__global__ void row_block_span_kernel(const int32_t* __restrict__ ia, const int32_t* __restrict__ ja, int64_t m, int nblk,
+                                      int* __restrict__ out_min, int* __restrict__ out_max)
+{
+	const int b = blockIdx.y;
+	const int64_t r0 = m * b / nblk, r1 = m * (b + 1) / nblk;
+	const int64_t j0 = ia[r0], j1 = ia[r1];
+	int lo = INT32_MAX, hi = -1;
+	for (int64_t i = j0 + (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < j1; i += (int64_t) gridDim.x * blockDim.x) {
+		const int c = ja[i];
+		lo = min(lo, c); hi = max(hi, c);
+	}
+	for (int off = 16; off > 0; off >>= 1) {
+		lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, off));
+		hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, off));
+	}
+	if ((threadIdx.x & 31) == 0 && hi >= 0) { atomicMin(out_min + b, lo); atomicMax(out_max + b, hi); }
+}
+
 // ------------------------------------------------------------------------------------------
 // work lists
 // ------------------------------------------------------------------------------------------
@@ -289,6 +319,23 @@ static void launch_rowsplit_gv(spmm_b200* h, const double* B, double* C, cudaStr
 		// k = 32 (4 rows per warp): 4-row tickets = one row per lane group; same time on a whole matrix (cfg2 0.764 vs
 		// 0.767 ms), better on the 1/8 shards of the 8-GPU run (0.114 vs 0.120 ms, static ranges 0.124 ms)
 		tick = (avg >= 32.0 && h->nnz >= (int64_t) o.ticket_min_nnz) ? (K == 32 ? 4 : 8) : 0;
+	}
+	// a row window (run_rowband) always runs on tickets: rows [win_r0, win_r0 + win_rows) through a shifted row
+	// pointer (the offsets in it stay absolute) and a shifted C
+	const bool win = h->win_rows >= 0;
+	if (win) {
+		if (tick <= 0) tick = K == 32 ? 4 : 8;
+		tick = (tick + NGW - 1) / NGW * NGW;
+		const int64_t rows = h->win_rows;
+		const int32_t* ia = h->d_ia + h->win_r0;
+		double* Cw = C + h->win_r0 * ldc;
+		const int grid = (int) std::min<int64_t>((rows + tick * (THREADS / 32) - 1) / (tick * (THREADS / 32)) + 1,
+		                                         (int64_t) h->sm_count * std::max(1, o.ticket_ctas));
+		if (whole)
+			spmm_rowsplit_ticket_kernel<G, V, 4, THREADS, K><<<grid, THREADS, 0, s>>>(ia, h->d_ja, h->d_a, B, Cw, (int) rows, tick, h->d_ticket, ldb, ldc);
+		else
+			spmm_rowsplit_ticket_kernel<G, V, 4, THREADS><<<grid, THREADS, 0, s>>>(ia, h->d_ja, h->d_a, B, Cw, (int) rows, tick, h->d_ticket, ldb, ldc);
+		return;
 	}
 	if constexpr (V >= 2 && K >= 32) {
 		// A stream staged through shared memory by TMA bulk copies (spmm_rowsplit_staged_kernel)
@@ -701,6 +748,20 @@ static int create_from_slice(spmm_b200_t** out, const int32_t* row_ptr_slice, co
 		h->col_span = mm[1] >= mm[0] ? (int64_t) mm[1] - mm[0] + 1 : 0;
 		h->col_min = mm[1] >= mm[0] ? mm[0] : 0;
 	}
+	for (int b = 0; b < BAND_FINE; b++) { h->band_min[b] = INT32_MAX; h->band_max[b] = -1; }
+	if (nnz_local > 0 && m_local >= BAND_FINE) {
+		int* d_bb = nullptr;
+		CU_TRY(cudaMalloc(&d_bb, 2 * BAND_FINE * sizeof(int)));
+		CU_TRY(cudaMemcpyAsync(d_bb, h->band_min, BAND_FINE * sizeof(int), cudaMemcpyHostToDevice, h->stream));
+		CU_TRY(cudaMemcpyAsync(d_bb + BAND_FINE, h->band_max, BAND_FINE * sizeof(int), cudaMemcpyHostToDevice, h->stream));
+		const unsigned gx = (unsigned) std::max<int64_t>(1, std::min<int64_t>((int64_t) sm_count * 8 / BAND_FINE + 1, (nnz_local / BAND_FINE + 255) / 256));
+		row_block_span_kernel<<<dim3(gx, BAND_FINE), 256, 0, h->stream>>>(h->d_ia, h->d_ja, m_local, BAND_FINE, d_bb, d_bb + BAND_FINE);
+		h->launches++;
+		CU_TRY(cudaMemcpyAsync(h->band_min, d_bb, BAND_FINE * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+		CU_TRY(cudaMemcpyAsync(h->band_max, d_bb + BAND_FINE, BAND_FINE * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+		CU_TRY(cudaStreamSynchronize(h->stream));
+		cudaFree(d_bb);
+	}
 	if (variant == SPMM_B200_AUTO) {
 		// row-split serialises a row on one lane group: switch to merge-path when one row is far
 		// longer than the mean (SURVEY 8(d) cfg 3: 200 040 nnz against a mean of 20)
@@ -857,20 +918,58 @@ extern "C" int spmm_b200_unregister_host(spmm_b200_t* h, const void* p)
 	return SPMM_B200_OK;
 }
 
+// Rows of B the handle's nonzeros can read: [lo, lo + n) = first..last touched column (col_span_kernel at create).
+// A row of B no nonzero references cannot change C, so host-buffer calls do not move it over PCIe: the reference's
+// generator with bw = 0.05 puts every nonzero into the middle 5.2 % of the columns (cfg2: 13 of 256 MB).
+static void b_window(const spmm_b200* h, int64_t& lo, int64_t& n)
+{
+	lo = 0; n = h->c;
+	if (!h->opt.upload_window) return;
+	if (h->nnz == 0 || h->col_span <= 0) { n = 0; return; }
+	lo = h->col_min; n = std::min<int64_t>(h->col_span, h->c - lo);
+}
+
+// Upload rows [lo, lo + n) of the column block [col0, col0 + w) of the host operand (k columns in all) into the
+// row-major device block Bs (c x w, row stride w) on stream s; column-major operands pass through d_x and a transpose.
+static int upload_b_rows(spmm_b200* h, const double* x_host, int k, int col0, int w, int64_t lo, int64_t n, double* Bs, cudaStream_t s)
+{
+	if (n <= 0 || w <= 0) return SPMM_B200_OK;
+	const int64_t c = h->c;
+	if (h->b_layout == SPMM_B200_B_ROWMAJOR || k == 1) {
+		if (w == k)
+			CU_TRY(cudaMemcpyAsync(Bs + lo * k, x_host + lo * k, sizeof(double) * n * k, cudaMemcpyHostToDevice, s));
+		else
+			CU_TRY(cudaMemcpy2DAsync(Bs + lo * w, sizeof(double) * w, x_host + lo * k + col0, sizeof(double) * k, sizeof(double) * w, (size_t) n,
+			                         cudaMemcpyHostToDevice, s));
+	} else {
+		double* xs = h->d_x + (size_t) col0 * c + lo;
+		if (n == c)
+			CU_TRY(cudaMemcpyAsync(xs, x_host + (size_t) col0 * c, sizeof(double) * c * w, cudaMemcpyHostToDevice, s));
+		else
+			CU_TRY(cudaMemcpy2DAsync(xs, sizeof(double) * c, x_host + (size_t) col0 * c + lo, sizeof(double) * c, sizeof(double) * n, (size_t) w,
+			                         cudaMemcpyHostToDevice, s));
+		dim3 grid((unsigned) ((n + 31) / 32), (unsigned) ((w + 31) / 32)), block(32, 8);
+		transpose_b_rows_kernel<<<grid, block, 0, s>>>(xs, Bs + lo * w, c, n, w);
+		CU_TRY(cudaGetLastError());
+		h->launches++;
+	}
+	h->last_h2d_bytes += (int64_t) sizeof(double) * n * w;
+	return SPMM_B200_OK;
+}
+
 static int upload_b(spmm_b200* h, const double* x_host, int k)
 {
 	const size_t nb = (size_t) h->c * k;
 	int rc = ensure(&h->d_B, &h->cap_B, nb);
 	if (rc) return rc;
-	if (h->b_layout == SPMM_B200_B_ROWMAJOR || k == 1) {
-		CU_TRY(cudaMemcpyAsync(h->d_B, x_host, nb * sizeof(double), cudaMemcpyHostToDevice, h->stream));
-	} else {
+	if (h->b_layout != SPMM_B200_B_ROWMAJOR && k != 1) {
 		rc = ensure(&h->d_x, &h->cap_x, nb);
 		if (rc) return rc;
-		CU_TRY(cudaMemcpyAsync(h->d_x, x_host, nb * sizeof(double), cudaMemcpyHostToDevice, h->stream));
-		rc = spmm_b200_transpose_b_device(h, h->d_x, h->d_B, k, h->stream);
-		if (rc) return rc;
 	}
+	int64_t lo, n;
+	b_window(h, lo, n);
+	rc = upload_b_rows(h, x_host, k, 0, k, lo, n, h->d_B, h->stream);
+	if (rc) return rc;
 	h->resident_k = k;
 	return SPMM_B200_OK;
 }
@@ -1027,7 +1126,7 @@ static int slice_width(const spmm_b200* h, int k)
 enum { TL_H2D = 0, TL_BCAST, TL_TRANSPOSE, TL_K0, TL_K1, TL_D2H, TL_PER_SLICE };
 
 static int run_pipelined(spmm_b200* h, const double* x_host, double* y_host, int k, int ks,
-                         spmm_b200_bcast_fn bcast = nullptr, void* bcast_ctx = nullptr, int parts = 1)
+                         spmm_b200_bcast_fn bcast = nullptr, void* bcast_ctx = nullptr, int parts = 1, bool sync = true)
 {
 	const int S = k / ks;
 	const size_t nb = (size_t) h->c * k;
@@ -1056,19 +1155,32 @@ static int run_pipelined(spmm_b200* h, const double* x_host, double* y_host, int
 	h->resident_k = 0;                       // d_B is about to hold slices, not the c x k operand
 	const size_t bslice = (size_t) h->c * ks, cslice = (size_t) h->m * ks;
 	CU_TRY(cudaEventRecord(h->ev_tl[0], h->s_up));
+	int64_t wlo, wn;
+	b_window(h, wlo, wn);
 	for (int s = 0; s < S; s++) {
 		double* Bs = h->d_B + s * bslice;
-		if (h->b_layout == SPMM_B200_B_COLMAJOR) {
+		if (!bcast) {
+			// no replication step: this handle uploads exactly the rows of B its own nonzeros read
+			if (x_host) {
+				rc = upload_b_rows(h, x_host, k, s * ks, ks, wlo, wn, Bs, h->s_up);
+				if (rc) return rc;
+			}
+			CU_TRY(cudaEventRecord(tl[TL_PER_SLICE * s + TL_H2D], h->s_up));
+			CU_TRY(cudaEventRecord(tl[TL_PER_SLICE * s + TL_BCAST], h->s_up));
+		} else if (h->b_layout == SPMM_B200_B_COLMAJOR) {
 			// columns [s*ks, (s+1)*ks) are contiguous in x: one H2D, then transpose to row-major c x ks
 			if (x_host && parts > 1) {
 				// every rank holds x: upload only part `rank` of the slice over this GPU's own PCIe link;
 				// the replication callback then fills in the other ranks' parts over NVLink
 				const size_t per = (bslice + parts - 1) / parts;
 				const size_t lo = std::min(bslice, per * (size_t) h->rank), hi = std::min(bslice, lo + per);
-				if (hi > lo)
+				if (hi > lo) {
 					CU_TRY(cudaMemcpyAsync(h->d_x + s * bslice + lo, x_host + s * bslice + lo, (hi - lo) * sizeof(double), cudaMemcpyHostToDevice, h->s_up));
+					h->last_h2d_bytes += (int64_t) ((hi - lo) * sizeof(double));
+				}
 			} else if (x_host) {
 				CU_TRY(cudaMemcpyAsync(h->d_x + s * bslice, x_host + s * bslice, bslice * sizeof(double), cudaMemcpyHostToDevice, h->s_up));
+				h->last_h2d_bytes += (int64_t) (bslice * sizeof(double));
 			}
 			CU_TRY(cudaEventRecord(tl[TL_PER_SLICE * s + TL_H2D], h->s_up));
 			if (bcast && bslice > 0 && bcast(bcast_ctx, h->d_x + s * bslice, bslice, parts, h->s_up)) return SPMM_B200_ECOMM;
@@ -1076,9 +1188,11 @@ static int run_pipelined(spmm_b200* h, const double* x_host, double* y_host, int
 			rc = spmm_b200_transpose_b_device(h, h->d_x + s * bslice, Bs, ks, h->s_up);
 			if (rc) return rc;
 		} else {
-			if (x_host)
+			if (x_host) {
 				CU_TRY(cudaMemcpy2DAsync(Bs, sizeof(double) * ks, x_host + (size_t) s * ks, sizeof(double) * k, sizeof(double) * ks,
 				                         (size_t) h->c, cudaMemcpyHostToDevice, h->s_up));
+				h->last_h2d_bytes += (int64_t) (bslice * sizeof(double));
+			}
 			CU_TRY(cudaEventRecord(tl[TL_PER_SLICE * s + TL_H2D], h->s_up));
 			if (bcast && bslice > 0 && bcast(bcast_ctx, Bs, bslice, 1, h->s_up)) return SPMM_B200_ECOMM;
 			CU_TRY(cudaEventRecord(tl[TL_PER_SLICE * s + TL_BCAST], h->s_up));
@@ -1091,7 +1205,7 @@ static int run_pipelined(spmm_b200* h, const double* x_host, double* y_host, int
 	// download of slice s is the kernel itself and overlaps the upload of slice s+1 with no copy-engine pass and no
 	// staging in d_C (profiles/r1_pcie_probe.md: SM stores into mapped host memory run at the 2-D copy's rate).
 	double* y_map = nullptr;
-	if (y_host && h->m > 0 && h->variant == SPMM_B200_ROWSPLIT && (ks == 8 || ks == 16 || ks == 32 || ks == 64)
+	if (y_host && h->m > 0 && S > 1 && h->variant == SPMM_B200_ROWSPLIT && (ks == 8 || ks == 16 || ks == 32 || ks == 64)
 	    && h->opt.direct_store) {
 		cudaPointerAttributes at;
 		if (cudaPointerGetAttributes(&at, y_host) == cudaSuccess && at.type == cudaMemoryTypeHost && at.devicePointer)
@@ -1124,12 +1238,222 @@ static int run_pipelined(spmm_b200* h, const double* x_host, double* y_host, int
 		}
 		CU_TRY(cudaEventRecord(tl[TL_PER_SLICE * s + TL_D2H], h->s_down));
 	}
+	if (y_host) h->last_d2h_bytes += (int64_t) sizeof(double) * h->m * k;
 	h->c_slices = y_map ? 0 : S;            // 0: C went straight to the host, d_C holds nothing to fetch
 	h->timed = true;
 	h->timed_slices = S;
+	h->tl_slices = S;
+	if (!sync) return SPMM_B200_OK;          // the multi-GPU caller synchronises all devices at the end
 	CU_TRY(cudaStreamSynchronize(h->stream));
 	CU_TRY(cudaStreamSynchronize(h->s_down));
-	h->tl_slices = S;
+	return SPMM_B200_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// Row-band host pipeline.  The k-slice pipeline above leaves a whole slice of B un-overlapped at the head and a whole
+// slice of C at the tail (cfg2: 2.3 + 2.5 of 7.9 ms) and moves C in w*8-byte pieces.  When the matrix is banded -- the
+// rows of C block b only read B rows up to band_max(b) -- the call can instead walk down the rows: upload the B rows
+// block b adds to the window (all k columns), run the row-split kernel on the block's rows alone, download its C rows
+// as ONE contiguous range.  Head and tail shrink to 1/R of the transfers and both directions of the link stay busy in
+// between.  Whether a matrix is banded enough is decided by a transfer model over the per-block column ranges taken
+// at create (row_block_span_kernel); ROWBAND=0 turns it off, ROWBAND=R forces R blocks.
+// ------------------------------------------------------------------------------------------
+
+struct BandStep { int64_t r0, r1; int64_t up[2][2]; int nup; };      // rows of C; up to two row ranges of B to upload first
+
+// The steps of a row-band run whose block b covers the fine row blocks [cut[b], cut[b+1]) (cut[0] = 0, last = BAND_FINE).
+static bool rowband_steps(const spmm_b200* h, const std::vector<int>& cut, std::vector<BandStep>& steps)
+{
+	if (cut.size() < 2 || cut.front() != 0 || cut.back() != BAND_FINE || h->m < BAND_FINE) return false;
+	steps.clear();
+	int64_t u_lo = 0, u_hi = 0;
+	bool have = false;
+	for (size_t b = 0; b + 1 < cut.size(); b++) {
+		const int f0 = cut[b], f1 = cut[b + 1];
+		if (f1 <= f0) return false;
+		BandStep st;
+		st.r0 = h->m * f0 / BAND_FINE; st.r1 = h->m * f1 / BAND_FINE; st.nup = 0;
+		int64_t lo = INT64_MAX, hi = -1;
+		for (int f = f0; f < f1; f++)
+			if (h->band_max[f] >= h->band_min[f]) { lo = std::min<int64_t>(lo, h->band_min[f]); hi = std::max<int64_t>(hi, (int64_t) h->band_max[f] + 1); }
+		if (hi > lo) {
+			if (!have) { st.up[st.nup][0] = lo; st.up[st.nup][1] = hi; st.nup++; u_lo = lo; u_hi = hi; have = true; }
+			else {
+				if (hi > u_hi) { st.up[st.nup][0] = u_hi; st.up[st.nup][1] = hi; st.nup++; u_hi = hi; }
+				if (lo < u_lo) { st.up[st.nup][0] = lo; st.up[st.nup][1] = u_lo; st.nup++; u_lo = lo; }
+			}
+		}
+		steps.push_back(st);
+	}
+	return true;
+}
+
+static std::vector<int> equal_cuts(int R)
+{
+	std::vector<int> cut;
+	for (int b = 0; b <= R; b++) cut.push_back(BAND_FINE * b / R);
+	return cut;
+}
+
+// Transfer model (one PCIe Gen5 x16 link; profiles/r1_pcie_probe.md, r2_e2e_probe.md, r2_rowband_probe.md): 55 GB/s one
+// way for contiguous copies, ~42 GB/s per direction while both are busy, 48 GB/s for the w*8-byte pieces the k-slice
+// kernels store into host memory, ~10 us per pipeline step for the hand-overs.
+static double xfer_ms(double up, double down, double down_rate)
+{
+	const double one = 55e6, both = 42e6;        // bytes per ms
+	const double shared = std::min(up, down);
+	return shared / both + (up - shared) / one + (down - shared) / down_rate;
+}
+
+// Three queues (upload, kernel, download), each in block order; a block's kernel waits for its upload, its download
+// for its kernel.  Both directions share the link when the uploads are comparable to the downloads.
+static double rowband_model_ms(const spmm_b200* h, int k, const std::vector<BandStep>& steps)
+{
+	double up_all = 0.0;
+	for (const BandStep& st : steps)
+		for (int u = 0; u < st.nup; u++) up_all += (double) (st.up[u][1] - st.up[u][0]) * k * 8.0;
+	const double down_all = (double) h->m * k * 8.0;
+	const double rate = up_all > 0.25 * down_all ? 44e6 : 55e6;
+	const double kernel_all = (double) h->nnz * k * 8.0 / 12e9;          // ms: B rows gathered at ~12 TB/s
+	double t_up = 0.0, t_k = 0.0, t_d = 0.0;
+	for (const BandStep& st : steps) {
+		double up = 0.0;
+		for (int u = 0; u < st.nup; u++) up += (double) (st.up[u][1] - st.up[u][0]) * k * 8.0;
+		const double rows = (double) (st.r1 - st.r0);
+		t_up += up / rate + (up > 0.0 ? 0.004 : 0.0);
+		t_k = std::max(t_up, t_k) + kernel_all * rows / (double) h->m + 0.005;
+		t_d = std::max(t_k, t_d) + rows * k * 8.0 / rate + 0.008;
+	}
+	return t_d;
+}
+
+static double kslice_model_ms(const spmm_b200* h, int k, int ks)
+{
+	int64_t lo, n;
+	b_window(h, lo, n);
+	const double bb = (double) n * k * 8.0, cb = (double) h->m * k * 8.0;
+	if (ks <= 0) return bb / 55e6 + cb / 55e6;
+	const int S = k / ks;
+	return bb / S / 55e6 + (S - 1) * (xfer_ms(bb / S, cb / S, 48e6) + 0.012) + cb / S / 48e6;
+}
+
+// Row blocks for this call, 0 = use the k-slice pipeline.
+static int rowband_blocks(const spmm_b200* h, int k, int ks, const double* x_host, const double* y_host, std::vector<BandStep>& steps)
+{
+	const int want = h->opt.rowband;
+	if (want == 0 || !x_host || !y_host || h->m < BAND_FINE || h->nnz == 0) return 0;
+	if (h->variant != SPMM_B200_ROWSPLIT || !(k == 8 || k == 16 || k == 32 || k == 64 || k == 128)) return 0;
+	if (!h->d_ticket || h->opt.unroll != 4) return 0;
+	if (want > 0) return rowband_steps(h, equal_cuts(std::min(want, BAND_FINE)), steps) ? (int) steps.size() : 0;
+	const std::vector<int> graded = {0, 1, 3, 8, 16, 32, 48, BAND_FINE};
+	if (want == -2) return rowband_steps(h, graded, steps) ? (int) steps.size() : 0;      // probe: force the graded blocks
+	int64_t wlo, wn;
+	b_window(h, wlo, wn);
+	if ((size_t) (wn + h->m) * k * sizeof(double) < 2 * ((size_t) h->opt.pipeline_min_kb << 10)) return 0;
+	const double t_ks = kslice_model_ms(h, k, ks);
+	int best = 0;
+	double t_best = 0.93 * t_ks;
+	std::vector<BandStep> cand;
+	// equal blocks for a diagonal band (every block brings its own rows of B); a small first block and few large ones
+	// after it when the uploads are short (a column stripe): the download chain then starts early and has few seams
+	for (const std::vector<int>& cut : {equal_cuts(8), equal_cuts(16), graded}) {
+		if (!rowband_steps(h, cut, cand)) continue;
+		const double t = rowband_model_ms(h, k, cand);
+		if (t < t_best) { t_best = t; best = (int) cand.size(); steps = cand; }
+	}
+	return best;
+}
+
+struct RowWindowGuard {            // the row window never outlives run_rowband, whatever path leaves it
+	spmm_b200* h;
+	~RowWindowGuard() { h->win_r0 = 0; h->win_rows = -1; }
+};
+
+static int run_rowband(spmm_b200* h, const double* x_host, double* y_host, int k, const std::vector<BandStep>& steps, bool sync = true)
+{
+	const int R = (int) steps.size();
+	const bool colmajor = h->b_layout == SPMM_B200_B_COLMAJOR;
+	int rc = ensure(&h->d_B, &h->cap_B, (size_t) h->c * k);
+	if (rc) return rc;
+	if (colmajor) {
+		rc = ensure(&h->d_x, &h->cap_x, (size_t) h->c * k);
+		if (rc) return rc;
+	}
+	if (!h->s_up) CU_TRY(cudaStreamCreateWithFlags(&h->s_up, cudaStreamNonBlocking));
+	if (!h->s_down) CU_TRY(cudaStreamCreateWithFlags(&h->s_down, cudaStreamNonBlocking));
+	while (h->ev_slice.size() < (size_t) 3 * R) {
+		cudaEvent_t e;
+		CU_TRY(cudaEventCreate(&e));
+		h->ev_slice.push_back(e);
+	}
+	while (h->ev_tl.size() < (size_t) TL_PER_SLICE * R + 1) {
+		cudaEvent_t e;
+		CU_TRY(cudaEventCreate(&e));
+		h->ev_tl.push_back(e);
+	}
+	cudaEvent_t* tl = h->ev_tl.data() + 1;
+	h->tl_slices = 0;
+	h->band_blocks = 0;
+	h->resident_k = 0;                       // d_B holds only the rows of B this matrix reads
+	// C rows go down as ONE contiguous copy per block (cfg2, 8 blocks: 5.02 ms); ROWBAND_DIRECT=1 lets the kernel store
+	// them straight into a page-locked, mapped y_host instead (5.46 ms: SM stores reach 50, the copy engine 55 GB/s)
+	double* y_map = nullptr;
+	if (h->opt.rowband_direct) {
+		cudaPointerAttributes at;
+		if (cudaPointerGetAttributes(&at, y_host) == cudaSuccess && at.type == cudaMemoryTypeHost && at.devicePointer)
+			y_map = (double*) at.devicePointer;
+		else
+			cudaGetLastError();
+		if (((uintptr_t) y_map & 15) != 0) y_map = nullptr;
+	}
+	if (!y_map) {
+		rc = ensure(&h->d_C, &h->cap_C, (size_t) h->m * k);
+		if (rc) return rc;
+	}
+	CU_TRY(cudaEventRecord(h->ev_tl[0], h->s_up));
+	for (int b = 0; b < R; b++) {
+		const BandStep& st = steps[b];
+		for (int u = 0; u < st.nup; u++) {
+			rc = upload_b_rows(h, x_host, k, 0, k, st.up[u][0], st.up[u][1] - st.up[u][0], h->d_B, h->s_up);
+			if (rc) return rc;
+		}
+		CU_TRY(cudaEventRecord(tl[TL_PER_SLICE * b + TL_H2D], h->s_up));
+		CU_TRY(cudaEventRecord(tl[TL_PER_SLICE * b + TL_BCAST], h->s_up));
+		CU_TRY(cudaEventRecord(tl[TL_PER_SLICE * b + TL_TRANSPOSE], h->s_up));
+		CU_TRY(cudaEventRecord(h->ev_slice[3 * b], h->s_up));
+	}
+	RowWindowGuard guard{h};
+	double* const c_base = y_map ? y_map : h->d_C;
+	for (int b = 0; b < R; b++) {
+		const BandStep& st = steps[b];
+		CU_TRY(cudaStreamWaitEvent(h->stream, h->ev_slice[3 * b], 0));
+		CU_TRY(cudaEventRecord(h->ev_slice[3 * b + 1], h->stream));
+		CU_TRY(cudaEventRecord(tl[TL_PER_SLICE * b + TL_K0], h->stream));
+		h->win_r0 = st.r0; h->win_rows = st.r1 - st.r0;
+		if (h->win_rows > 0) {
+			const int n = launch_spmm(h, h->d_B, c_base, k, h->stream);
+			if (n < 0) return n;
+		}
+		CU_TRY(cudaEventRecord(h->ev_slice[3 * b + 2], h->stream));
+		CU_TRY(cudaEventRecord(tl[TL_PER_SLICE * b + TL_K1], h->stream));
+		if (y_map) {
+			CU_TRY(cudaEventRecord(tl[TL_PER_SLICE * b + TL_D2H], h->stream));
+		} else {
+			CU_TRY(cudaStreamWaitEvent(h->s_down, h->ev_slice[3 * b + 2], 0));
+			if (st.r1 > st.r0)
+				CU_TRY(cudaMemcpyAsync(y_host + st.r0 * k, h->d_C + st.r0 * k, sizeof(double) * (st.r1 - st.r0) * k, cudaMemcpyDeviceToHost, h->s_down));
+			CU_TRY(cudaEventRecord(tl[TL_PER_SLICE * b + TL_D2H], h->s_down));
+		}
+	}
+	h->last_d2h_bytes += (int64_t) sizeof(double) * h->m * k;
+	h->c_slices = y_map ? 0 : 1;
+	h->timed = true;
+	h->timed_slices = R;
+	h->tl_slices = R;
+	h->band_blocks = R;
+	if (!sync) return SPMM_B200_OK;
+	CU_TRY(cudaStreamSynchronize(h->stream));
+	CU_TRY(cudaStreamSynchronize(h->s_down));
 	return SPMM_B200_OK;
 }
 
@@ -1154,6 +1478,12 @@ extern "C" int spmm_b200_run(spmm_b200_t* h, const double* x_host, double* y_hos
 	if (!h || !x_host || k < 1 || (copy_back && !y_host)) return SPMM_B200_EINVAL;
 	CU_TRY(cudaSetDevice(h->device));
 	const int ks = slice_width(h, k);
+	h->last_h2d_bytes = h->last_d2h_bytes = 0;
+	{
+		std::vector<BandStep> steps;
+		if (copy_back && rowband_blocks(h, k, ks, x_host, y_host, steps) > 0) return run_rowband(h, x_host, y_host, k, steps);
+	}
+	h->band_blocks = 0;
 	if (ks > 0) return run_pipelined(h, x_host, copy_back ? y_host : nullptr, k, ks);
 	int rc = upload_b(h, x_host, k);
 	if (rc) return rc;
@@ -1165,6 +1495,7 @@ extern "C" int spmm_b200_run(spmm_b200_t* h, const double* x_host, double* y_hos
 	if (copy_back) {
 		rc = download_c(h, y_host, k, h->stream);
 		if (rc) return rc;
+		h->last_d2h_bytes += (int64_t) sizeof(double) * h->m * k;
 	}
 	CU_TRY(cudaStreamSynchronize(h->stream));
 	return SPMM_B200_OK;
@@ -1179,6 +1510,8 @@ extern "C" int spmm_b200_run_replicated(spmm_b200_t* h, const double* x_host, do
 	if (!h || k < 1 || (copy_back && !y_host) || (!x_host && !bcast)) return SPMM_B200_EINVAL;
 	if (x_on_every_rank && !x_host) return SPMM_B200_EINVAL;
 	CU_TRY(cudaSetDevice(h->device));
+	h->last_h2d_bytes = h->last_d2h_bytes = 0;
+	h->band_blocks = 0;
 	int ks = slice_width(h, k);
 	if (ks <= 0) ks = k;
 	// split uploads need the oracle layout (a slice of x is one contiguous range) and a communicator
@@ -1389,6 +1722,21 @@ extern "C" int64_t spmm_b200_nnz(const spmm_b200_t* h) { return h ? h->nnz : -1;
 extern "C" int spmm_b200_variant(const spmm_b200_t* h) { return h ? h->variant : SPMM_B200_EINVAL; }
 extern "C" int64_t spmm_b200_bcsr_blocks(const spmm_b200_t* h) { return h ? h->bcsr.nnzb : -1; }
 extern "C" int spmm_b200_kslice(const spmm_b200_t* h) { return h ? h->ks_best : SPMM_B200_EINVAL; }
+extern "C" int spmm_b200_last_rowband(const spmm_b200_t* h) { return h ? h->band_blocks : SPMM_B200_EINVAL; }
+extern "C" int spmm_b200_col_window(const spmm_b200_t* h, int64_t* first_col, int64_t* ncols)
+{
+	if (!h) return SPMM_B200_EINVAL;
+	if (first_col) *first_col = h->col_min;
+	if (ncols) *ncols = h->col_span;
+	return SPMM_B200_OK;
+}
+extern "C" int spmm_b200_last_transfer_bytes(const spmm_b200_t* h, int64_t* h2d_bytes, int64_t* d2h_bytes)
+{
+	if (!h) return SPMM_B200_EINVAL;
+	if (h2d_bytes) *h2d_bytes = h->last_h2d_bytes;
+	if (d2h_bytes) *d2h_bytes = h->last_d2h_bytes;
+	return SPMM_B200_OK;
+}
 extern "C" int64_t spmm_b200_launch_count(const spmm_b200_t* h) { return h ? h->launches : -1; }
 
 extern "C" double spmm_b200_last_kernel_ms(const spmm_b200_t* h)

@@ -230,6 +230,34 @@ extern "C" int spmm_b200_run_multi(spmm_b200_multi_t* mh, const double* x_host, 
 {
 	if (!mh || !x_host || k < 1 || (copy_back && !y_host)) return SPMM_B200_EINVAL;
 	int ks = slice_width(mh->sh[0], k);
+	// Own windows: a shard reads only the rows of B between its first and last touched column.  When no shard's window
+	// is larger than the 1/N share of B it would upload for the peer gather, every device uploads its own window over
+	// its own link and runs its own host pipeline (row blocks or column slices) -- no replication step at all.
+	{
+		int64_t worst = 0;
+		for (int g = 0; g < mh->n; g++) {
+			int64_t lo, n;
+			b_window(mh->sh[g], lo, n);
+			worst = std::max(worst, n);
+		}
+		if (copy_back && mh->sh[0]->opt.upload_window && worst * mh->n <= mh->c) {
+			int rc = multi_prepare(mh, k, 1);
+			if (rc) return rc;
+			std::vector<BandStep> steps;
+			for (int g = 0; g < mh->n; g++) {
+				spmm_b200* h = mh->sh[g];
+				CU_TRY(cudaSetDevice(h->device));
+				h->last_h2d_bytes = h->last_d2h_bytes = 0;
+				h->band_blocks = 0;
+				if (h->m == 0) continue;
+				double* y_rows = y_host + (size_t) h->first_row * k;
+				if (rowband_blocks(h, k, ks, x_host, y_rows, steps) > 0) rc = run_rowband(h, x_host, y_rows, k, steps, false);
+				else rc = run_pipelined(h, x_host, y_rows, k, ks > 0 ? ks : k, nullptr, nullptr, 1, false);
+				if (rc) return rc;
+			}
+			return multi_sync(mh);
+		}
+	}
 	if (ks <= 0) ks = k;
 	const int S = k / ks;
 	int rc = multi_prepare(mh, k, S);

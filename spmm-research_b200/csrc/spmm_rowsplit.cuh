@@ -587,4 +587,24 @@ __global__ void transpose_b_kernel(const double* __restrict__ x, double* __restr
 	}
 }
 
+// The same for `rows` consecutive rows of B out of a column-major operand whose columns are `pitch` elements apart:
+// x[n*pitch + j] -> B[j*k + n], j < rows (the row-band host pipeline uploads B a few rows at a time).
+__global__ void transpose_b_rows_kernel(const double* __restrict__ x, double* __restrict__ B, int64_t pitch, int64_t rows, int k)
+{
+	__shared__ double tile[32][33];
+	const int64_t j0 = (int64_t) blockIdx.x * 32;
+	const int n0 = blockIdx.y * 32;
+	for (int dy = threadIdx.y; dy < 32; dy += blockDim.y) {
+		const int n = n0 + dy;
+		const int64_t j = j0 + threadIdx.x;
+		if (n < k && j < rows) tile[dy][threadIdx.x] = x[(int64_t) n * pitch + j];
+	}
+	__syncthreads();
+	for (int dy = threadIdx.y; dy < 32; dy += blockDim.y) {
+		const int64_t j = j0 + dy;
+		const int n = n0 + threadIdx.x;
+		if (n < k && j < rows) B[j * k + n] = tile[threadIdx.x][dy];
+	}
+}
+
 } // namespace sb200
