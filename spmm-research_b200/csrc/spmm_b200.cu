@@ -1411,6 +1411,8 @@ static int run_rowband(spmm_b200* h, const double* x_host, double* y_host, int k
 		if (rc) return rc;
 	}
 	CU_TRY(cudaEventRecord(h->ev_tl[0], h->s_up));
+	RowWindowGuard guard{h};
+	double* const c_base = y_map ? y_map : h->d_C;
 	for (int b = 0; b < R; b++) {
 		const BandStep& st = steps[b];
 		for (int u = 0; u < st.nup; u++) {
@@ -1421,11 +1423,7 @@ static int run_rowband(spmm_b200* h, const double* x_host, double* y_host, int k
 		CU_TRY(cudaEventRecord(tl[TL_PER_SLICE * b + TL_BCAST], h->s_up));
 		CU_TRY(cudaEventRecord(tl[TL_PER_SLICE * b + TL_TRANSPOSE], h->s_up));
 		CU_TRY(cudaEventRecord(h->ev_slice[3 * b], h->s_up));
-	}
-	RowWindowGuard guard{h};
-	double* const c_base = y_map ? y_map : h->d_C;
-	for (int b = 0; b < R; b++) {
-		const BandStep& st = steps[b];
+		// block by block on all three streams: the first kernel is enqueued right behind the first upload
 		CU_TRY(cudaStreamWaitEvent(h->stream, h->ev_slice[3 * b], 0));
 		CU_TRY(cudaEventRecord(h->ev_slice[3 * b + 1], h->stream));
 		CU_TRY(cudaEventRecord(tl[TL_PER_SLICE * b + TL_K0], h->stream));
