@@ -407,10 +407,10 @@ def gpu_arm(args, ia, ja, a, m, c, k, nnz, workload_desc):
         return max_over_ranks((time.perf_counter() - t0) / steps)
 
     # Every rank holds x (the reference's harness is one process with one x).  A shard reads only the rows of B between
-    # its first and last touched column; when that window is no larger than the 1/N share of B a rank would upload for
+    # its first and last touched column; when that window is about the 1/N share of B a rank would upload for
     # the all-gather, every rank uploads its own window over its own PCIe link and no collective runs at all.
     span = mf.col_window()[1]
-    own_window = world > 1 and max_over_ranks(float(span)) * world <= c
+    own_window = world > 1 and max_over_ranks(float(span)) * world <= 1.25 * c      # same rule as spmm_b200_run_multi
     e2e_s = time_e2e(e2e_steps)
     clocks = sampler.stop()
     e2e_val = 2.0 * nnz * k / e2e_s / 1e9

@@ -1352,7 +1352,7 @@ static int rowband_blocks(const spmm_b200* h, int k, int ks, const double* x_hos
 	if ((size_t) (wn + h->m) * k * sizeof(double) < 2 * ((size_t) h->opt.pipeline_min_kb << 10)) return 0;
 	const double t_ks = kslice_model_ms(h, k, ks);
 	int best = 0;
-	double t_best = 0.93 * t_ks;
+	double t_best = 0.97 * t_ks;            // near a tie the contiguous copies of the row blocks have been the faster ones (cfg2 on 1 and 2 GPUs)
 	std::vector<BandStep> cand;
 	// equal blocks for a diagonal band (every block brings its own rows of B); a small first block and few large ones
 	// after it when the uploads are short (a column stripe): the download chain then starts early and has few seams

@@ -231,7 +231,7 @@ extern "C" int spmm_b200_run_multi(spmm_b200_multi_t* mh, const double* x_host, 
 	if (!mh || !x_host || k < 1 || (copy_back && !y_host)) return SPMM_B200_EINVAL;
 	int ks = slice_width(mh->sh[0], k);
 	// Own windows: a shard reads only the rows of B between its first and last touched column.  When no shard's window
-	// is larger than the 1/N share of B it would upload for the peer gather, every device uploads its own window over
+	// is larger than ~the 1/N share of B it would upload for the peer gather, every device uploads its own window over
 	// its own link and runs its own host pipeline (row blocks or column slices) -- no replication step at all.
 	{
 		int64_t worst = 0;
@@ -240,7 +240,8 @@ extern "C" int spmm_b200_run_multi(spmm_b200_multi_t* mh, const double* x_host, 
 			b_window(mh->sh[g], lo, n);
 			worst = std::max(worst, n);
 		}
-		if (copy_back && mh->sh[0]->opt.upload_window && worst * mh->n <= mh->c) {
+		// (a diagonal band gives each shard c/N rows of B plus the band: the same bytes as its share of a gather, minus the gather)
+		if (copy_back && mh->sh[0]->opt.upload_window && worst * mh->n * 4 <= mh->c * 5) {
 			int rc = multi_prepare(mh, k, 1);
 			if (rc) return rc;
 			std::vector<BandStep> steps;
