@@ -558,14 +558,25 @@ static int build_bcsr_plan(spmm_b200* h)
 	return bcsr_fill(h);
 }
 
+// The block rows a blocked launch covers: all of them, or -- inside run_rowband -- the block rows of the row window
+// (window starts are multiples of 8 rows; the block-row pointer and C are shifted, the offsets in brow stay absolute).
+struct BcsrRange { const int32_t* brow; double* C; int m, mb; };
+static BcsrRange bcsr_range(const spmm_b200* h, double* C, int K)
+{
+	const BcsrPlan& p = h->bcsr;
+	if (h->win_rows < 0) return {p.d_brow, C, (int) h->m, p.mb};
+	const int64_t b0 = h->win_r0 / 8, r1 = h->win_r0 + h->win_rows;
+	return {p.d_brow + b0, C + h->win_r0 * K, (int) h->win_rows, (int) ((r1 + 7) / 8 - b0)};
+}
+
 template <int K, int WARPS, int STAGES>
-static void launch_bcsr_tma(spmm_b200* h, const double* B, double* C, int brw, unsigned grid, cudaStream_t s)
+static void launch_bcsr_tma(spmm_b200* h, const double* B, const BcsrRange& r, int brw, unsigned grid, cudaStream_t s)
 {
 	using Cfg = BcsrTmaCfg<K, WARPS, STAGES>;
 	const BcsrPlan& p = h->bcsr;
 	auto kern = spmm_bcsr_dmma_tma_kernel<K, WARPS, STAGES>;
 	raise_smem_limit(h, ATTR_BCSR_TMA + (STAGES - 2) + 3 * (K == 128 ? 2 : K == 64 ? 1 : 0), kern, Cfg::SMEM);
-	kern<<<grid, WARPS * 32, Cfg::SMEM, s>>>(p.d_brow, p.d_bcol, p.d_bval, B, C, (int) h->m, p.mb, brw);
+	kern<<<grid, WARPS * 32, Cfg::SMEM, s>>>(r.brow, p.d_bcol, p.d_bval, B, r.C, r.m, r.mb, brw);
 }
 
 template <int K>
@@ -574,24 +585,26 @@ static void launch_bcsr_k(spmm_b200* h, const double* B, double* C, cudaStream_t
 	constexpr int WARPS = 4;
 	const BcsrPlan& p = h->bcsr;
 	const Options& o = h->opt;
-	const unsigned grid = (unsigned) ((p.mb + WARPS - 1) / WARPS);
+	const BcsrRange r = bcsr_range(h, C, K);
+	if (r.mb <= 0) return;
+	const unsigned grid = (unsigned) ((r.mb + WARPS - 1) / WARPS);
 	// bulk copies of 8K bytes per B row pay from K = 64 on (cfg4: K=32 0.57 ms fragment loads vs 0.63 ms TMA;
 	// K=128 2.55 ms vs 1.23 ms); 2 stages = most warps per SM, which is what the tensor pipe needs
 	if (h->variant == SPMM_B200_BCSR && (o.bcsr_tma == 2 || (o.bcsr_tma == 1 && K >= 64))) {
 		if constexpr (K >= 32) {
 			// block rows per warp: enough to keep the ring flowing, few enough for >= 8 CTAs per SM
-			const int brw = o.bcsr_brw > 0 ? o.bcsr_brw : (int) std::max<int64_t>(1, std::min<int64_t>(8, p.mb / ((int64_t) h->sm_count * WARPS * 8)));
-			const unsigned g2 = (unsigned) ((p.mb + (int64_t) WARPS * brw - 1) / ((int64_t) WARPS * brw));
-			if (o.bcsr_stages <= 2) launch_bcsr_tma<K, WARPS, 2>(h, B, C, brw, g2, s);
-			else if (o.bcsr_stages == 3) launch_bcsr_tma<K, WARPS, 3>(h, B, C, brw, g2, s);
-			else launch_bcsr_tma<K, WARPS, 4>(h, B, C, brw, g2, s);
+			const int brw = o.bcsr_brw > 0 ? o.bcsr_brw : (int) std::max<int64_t>(1, std::min<int64_t>(8, r.mb / ((int64_t) h->sm_count * WARPS * 8)));
+			const unsigned g2 = (unsigned) ((r.mb + (int64_t) WARPS * brw - 1) / ((int64_t) WARPS * brw));
+			if (o.bcsr_stages <= 2) launch_bcsr_tma<K, WARPS, 2>(h, B, r, brw, g2, s);
+			else if (o.bcsr_stages == 3) launch_bcsr_tma<K, WARPS, 3>(h, B, r, brw, g2, s);
+			else launch_bcsr_tma<K, WARPS, 4>(h, B, r, brw, g2, s);
 			return;
 		}
 	}
 	if (h->variant == SPMM_B200_BCSR)
-		spmm_bcsr_dmma_kernel<K, WARPS><<<grid, WARPS * 32, 0, s>>>(p.d_brow, p.d_bcol, p.d_bval, B, C, (int) h->m, p.mb);
+		spmm_bcsr_dmma_kernel<K, WARPS><<<grid, WARPS * 32, 0, s>>>(r.brow, p.d_bcol, p.d_bval, B, r.C, r.m, r.mb);
 	else if constexpr (K % 32 == 0)
-		spmm_bcsr_simt_kernel<K, WARPS><<<grid, WARPS * 32, 0, s>>>(p.d_brow, p.d_bcol, p.d_bval, p.d_bmask, B, C, (int) h->m, p.mb);
+		spmm_bcsr_simt_kernel<K, WARPS><<<grid, WARPS * 32, 0, s>>>(r.brow, p.d_bcol, p.d_bval, p.d_bmask, B, r.C, r.m, r.mb);
 }
 
 static int launch_bcsr(spmm_b200* h, const double* B, double* C, int k, cudaStream_t s)
@@ -1272,7 +1285,11 @@ static bool rowband_steps(const spmm_b200* h, const std::vector<int>& cut, std::
 		const int f0 = cut[b], f1 = cut[b + 1];
 		if (f1 <= f0) return false;
 		BandStep st;
-		st.r0 = h->m * f0 / BAND_FINE; st.r1 = h->m * f1 / BAND_FINE; st.nup = 0;
+		// block starts on multiples of 8 rows (the blocked variants work on 8-row block rows); the rows this moves across
+		// a fine-block border have their columns in the neighbouring fine block, which an earlier step uploaded
+		st.r0 = (h->m * f0 / BAND_FINE) & ~(int64_t) 7;
+		st.r1 = f1 == BAND_FINE ? h->m : (h->m * f1 / BAND_FINE) & ~(int64_t) 7;
+		st.nup = 0;
 		int64_t lo = INT64_MAX, hi = -1;
 		for (int f = f0; f < f1; f++)
 			if (h->band_max[f] >= h->band_min[f]) { lo = std::min<int64_t>(lo, h->band_min[f]); hi = std::max<int64_t>(hi, (int64_t) h->band_max[f] + 1); }
@@ -1342,8 +1359,14 @@ static int rowband_blocks(const spmm_b200* h, int k, int ks, const double* x_hos
 {
 	const int want = h->opt.rowband;
 	if (want == 0 || !x_host || !y_host || h->m < BAND_FINE || h->nnz == 0) return 0;
-	if (h->variant != SPMM_B200_ROWSPLIT || !(k == 8 || k == 16 || k == 32 || k == 64 || k == 128)) return 0;
-	if (!h->d_ticket || h->opt.unroll != 4) return 0;
+	// kernels that can run on a row window: the row-split ticket kernel and the blocked (8-row block rows) kernels
+	if (h->variant == SPMM_B200_ROWSPLIT) {
+		if (!(k == 8 || k == 16 || k == 32 || k == 64 || k == 128) || !h->d_ticket || h->opt.unroll != 4) return 0;
+	} else if (h->variant == SPMM_B200_BCSR || h->variant == SPMM_B200_BCSR_FMA) {
+		if (!bcsr_supports_k(h->variant, k)) return 0;
+	} else {
+		return 0;
+	}
 	if (want > 0) return rowband_steps(h, equal_cuts(std::min(want, BAND_FINE)), steps) ? (int) steps.size() : 0;
 	const std::vector<int> graded = {0, 1, 3, 8, 16, 32, 48, BAND_FINE};
 	if (want == -2) return rowband_steps(h, graded, steps) ? (int) steps.size() : 0;      // probe: force the graded blocks

@@ -195,6 +195,9 @@ def test_upload_window(pkg, L, layout):
     xp = xp.ravel()
     mf = pkg.csr_to_format(ia, ja, a, m, c, len(ja), k, variant=pkg.ROWSPLIT,
                            b_layout=pkg.B_ROWMAJOR if layout == "rowmajor" else pkg.B_COLMAJOR)
+    mf.set_option("UPLOAD_WINDOW", 0); mf.set_option("ROWBAND", 0)        # poison the device copies of B: NaN everywhere
+    mf.spmm(np.full(c * k, np.nan), np.empty(m * k), k)
+    mf.set_option("UPLOAD_WINDOW", 1)
     for name, opts in [("single", {"ROWBAND": 0}), ("kslice", {"ROWBAND": 0, "PIPELINE_MIN_KB": 0}),
                        ("rowband", {"ROWBAND": 8}), ("graded", {"ROWBAND": -2})]:
         for o, v in opts.items():
@@ -235,4 +238,57 @@ def test_multi_gpu_own_windows(pkg, L, ngpus):
         buf[:] = np.nan
         mf.spmm(xp if opts.get("UPLOAD_WINDOW", 1) else x, buf, k)
         assert max_rel_err(buf, y_ref) <= FP64_TOL, (ngpus, opts)
+    mf.close()
+
+
+@pytest.mark.parametrize("variant,k", [("ROWSPLIT", 1), ("ROWSPLIT", 2), ("ROWSPLIT", 4), ("ROWSPLIT", 24), ("ROWSPLIT", 128),
+                                       ("MERGE", 1), ("MERGE", 32), ("BCSR", 32), ("BCSR", 128), ("BCSR_FMA", 64)])
+def test_no_kernel_reads_b_outside_the_window(pkg, L, variant, k):
+    """With the window upload the device copy of B holds the caller's data only between the first and the last touched
+    column.  No kernel family may read outside it, not even to multiply by zero (padding slots, dead lanes): x is NaN
+    there and the device buffers are poisoned by a first call on an all-NaN operand."""
+    m, c = 3000, 8000
+    lo, hi = 3100, 3700
+    ia, ja, a = banded_csr(m, hi - lo, 14.0, 40, seed=61)
+    ja = (ja + lo).astype(np.int32)
+    x = dense_b(c, k, 6)
+    y_ref = L.spmm_oracle(ia, ja, a, m, c, x, k)
+    xp = x.reshape(k, c).copy()
+    xp[:, :int(ja.min())] = np.nan; xp[:, int(ja.max()) + 1:] = np.nan
+    mf = pkg.csr_to_format(ia, ja, a, m, c, len(ja), k, variant=getattr(pkg, variant))
+    mf.set_option("UPLOAD_WINDOW", 0)
+    junk = np.full(c * k, np.nan); y = np.empty(m * k)
+    mf.spmm(junk, y, k)                                      # d_B / d_x now hold NaN everywhere
+    mf.set_option("UPLOAD_WINDOW", 1)
+    for opts in ({}, {"PIPELINE_MIN_KB": 0}):
+        for o, v in opts.items():
+            mf.set_option(o, v)
+        y = np.full(m * k, np.nan); mf.spmm(xp.ravel(), y, k)
+        assert np.isfinite(y).all(), (variant, k, opts)
+        assert max_rel_err(y, y_ref) <= FP64_TOL, (variant, k, opts)
+        assert mf.last_transfer_bytes()[0] == (int(ja.max()) - int(ja.min()) + 1) * k * 8
+    mf.close()
+
+
+@pytest.mark.parametrize("variant,k", [("BCSR", 32), ("BCSR", 128), ("BCSR_FMA", 64)])
+def test_rowband_blocked_variants(pkg, L, variant, k):
+    """The blocked kernels run on row windows too (block-row pointer and C shifted; window starts on multiples of 8 rows):
+    same bits as the whole launch, rows not a multiple of 8, empty block rows inside."""
+    m, c = 6003, 5000
+    ia, ja, a = banded_csr(m, c, 24.0, 150, seed=70 + k, empty_rows=[(1000, 1100)])
+    x = dense_b(c, k, 3)
+    y_ref = L.spmm_oracle(ia, ja, a, m, c, x, k)
+    mf = pkg.csr_to_format(ia, ja, a, m, c, len(ja), k, variant=getattr(pkg, variant))
+    assert variant.split("_")[0] in mf.format_name
+    mf.set_option("ROWBAND", 0)
+    y0 = _run(mf, x, k, m, pinned=False)
+    assert max_rel_err(y0, y_ref) <= FP64_TOL
+    garbage = dense_b(c, k, 78) * 1e3 - 5e2
+    for blocks in (1, 4, 7, 16, 64, -2):
+        mf.set_option("ROWBAND", 0)
+        _run(mf, garbage, k, m, False)
+        mf.set_option("ROWBAND", blocks)
+        y = _run(mf, x, k, m, pinned=True)
+        assert mf.last_rowband() == (blocks if blocks > 0 else 7), (variant, k, blocks)
+        assert np.array_equal(y, y0), (variant, k, blocks)
     mf.close()
