@@ -17,6 +17,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--mbs", default="32,128")
     ap.add_argument("--reps", type=int, default=20)
+    ap.add_argument("--subsets", default="", help="comma list of rank sets (digits), e.g. 0123,4567,0246: D2H with only those ranks copying")
     args = ap.parse_args()
     rank, world, local = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
     torch.cuda.set_device(local)
@@ -58,6 +59,36 @@ def main():
             if rank == 0:
                 print(json.dumps({"ranks": world, "mb_per_copy": mb, "mode": mode, "per_rank_gbs_min": round(float(lo), 1),
                                   "aggregate_gbs": round(float(tot), 1)}), flush=True)
+    # which ranks share what: D2H with only a subset of the ranks active (the others wait at the barrier)
+    for sub in [v for v in args.subsets.split(",") if v]:
+        active = str(rank) in sub
+        mb = 32
+        n = mb * (1 << 20) // 8
+        h_dn = torch.empty(n, dtype=torch.float64, pin_memory=True)
+        d_dn = torch.ones(n, dtype=torch.float64, device=dev)
+        gbs = 0.0
+        for timed in (False, True):
+            torch.cuda.synchronize()
+            if world > 1:
+                dist.barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(s2)
+            if active:
+                for _ in range(args.reps if timed else 3):
+                    with torch.cuda.stream(s2):
+                        h_dn.copy_(d_dn, non_blocking=True)
+            e1.record(s2)
+            torch.cuda.synchronize()
+        if active:
+            gbs = mb * (1 << 20) / (e0.elapsed_time(e1) / args.reps * 1e-3) / 1e9
+        t = torch.tensor([gbs], dtype=torch.float64, device=dev)
+        lo = torch.tensor([gbs if active else 1e9], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+            dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        if rank == 0:
+            print(json.dumps({"ranks": world, "active": sub, "mode": "d2h", "mb_per_copy": mb, "per_rank_gbs_min": round(float(lo), 1),
+                              "aggregate_gbs": round(float(t), 1)}), flush=True)
     if world > 1:
         dist.destroy_process_group()
 
