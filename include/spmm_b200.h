@@ -195,6 +195,12 @@ int64_t spmm_b200_multi_first_row(const spmm_b200_multi_t *mh, int g);  /* g = n
 double  spmm_b200_multi_last_kernel_ms(const spmm_b200_multi_t *mh);    /* max over the shards */
 int64_t spmm_b200_multi_launch_count(const spmm_b200_multi_t *mh);
 int     spmm_b200_multi_peer_access(const spmm_b200_multi_t *mh);      /* 1: B is exchanged over NVLink */
+/* Download routes of spmm_b200_run_multi: out[g] = the device whose PCIe link carries device g's rows of C (g itself
+ * unless the box's links were measured to be unequal: then devices behind the slow path store C into a partner over
+ * NVLink), followed by the measured GB/s of the five candidate downloader sets {all, lower half, upper half, evens,
+ * odds} (zeros when nothing was measured).  Option MULTI_ROUTE (on shard 0): -1 measure once, 0 off, mask = forced set.
+ * Returns the number of doubles written. */
+int     spmm_b200_multi_routes(const spmm_b200_multi_t *mh, double *out, int max_values);
 void    spmm_b200_destroy_multi(spmm_b200_multi_t *mh);
 
 /* ---- partitioning, testable without an SpMM kernel (host pointers in and out,

@@ -57,6 +57,9 @@ def main():
             same = "identical" if np.array_equal(y.numpy(), y0) else "DIFFERS"
         band = "" if args.multi else f"rowband {mf.last_rowband()}  "
         print(f"{conf or '(defaults)':36s} median {np.median(ts):.3f} ms  min {np.min(ts):.3f} ms  kernels {mf.last_kernel_ms():.3f} ms  {band}{same}", flush=True)
+        if args.multi:
+            route, probe = mf.routes()
+            print(f"    download routes {route}  probe GB/s [all, lower, upper, even, odd] {[round(v, 1) for v in probe]}", flush=True)
         if not args.multi:
             for s, t in enumerate(mf.last_timeline()):
                 print(f"    slice {s}: " + "  ".join(f"{kk} {v:.3f}" for kk, v in t.items()), flush=True)

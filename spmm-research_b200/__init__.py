@@ -35,7 +35,7 @@ EXPORTS = [
     "spmm_b200_create_multi", "spmm_b200_run_multi", "spmm_b200_set_b_multi", "spmm_b200_run_resident_multi",
     "spmm_b200_fetch_c_multi", "spmm_b200_register_host_multi", "spmm_b200_multi_ngpus", "spmm_b200_multi_shard",
     "spmm_b200_multi_first_row", "spmm_b200_multi_last_kernel_ms", "spmm_b200_multi_launch_count",
-    "spmm_b200_multi_peer_access", "spmm_b200_destroy_multi",
+    "spmm_b200_multi_peer_access", "spmm_b200_multi_routes", "spmm_b200_destroy_multi",
     "spmm_b200_run_resident", "spmm_b200_fetch_c", "spmm_b200_run_device",
     "spmm_b200_transpose_b_device", "spmm_b200_partition", "spmm_b200_partition_host", "spmm_b200_coo_to_csr", "spmm_b200_rows", "spmm_b200_nnz",
     "spmm_b200_variant", "spmm_b200_bcsr_blocks", "spmm_b200_kslice", "spmm_b200_last_rowband", "spmm_b200_last_transfer_bytes", "spmm_b200_col_window", "spmm_b200_last_kernel_ms", "spmm_b200_launch_count", "spmm_b200_stats",
@@ -97,6 +97,7 @@ def load_library():
     lib.spmm_b200_fetch_c_multi.argtypes = [_vp, _vp, _int]
     lib.spmm_b200_register_host_multi.argtypes = [_vp, _vp, C.c_size_t]
     lib.spmm_b200_multi_ngpus.argtypes = [_vp]
+    lib.spmm_b200_multi_routes.argtypes = [_vp, _vp, _int]
     lib.spmm_b200_multi_shard.argtypes = [_vp, _int]; lib.spmm_b200_multi_shard.restype = _vp
     lib.spmm_b200_multi_first_row.argtypes = [_vp, _int]; lib.spmm_b200_multi_first_row.restype = _i64
     lib.spmm_b200_multi_last_kernel_ms.argtypes = [_vp]; lib.spmm_b200_multi_last_kernel_ms.restype = _dbl
@@ -615,6 +616,14 @@ class MultiGpuFormat:
         lib = load_library()
         for g in range(self.ngpus):
             _check(lib.spmm_b200_set_option(lib.spmm_b200_multi_shard(self._h, g), name.encode(), int(value)), f"set_option({name})")
+
+    def routes(self):
+        """(route, probe): route[g] = device that downloads device g's rows of C; probe = measured GB/s of the candidate
+        downloader sets {all, lower half, upper half, evens, odds} (zeros when nothing was measured)."""
+        out = np.zeros(self.ngpus + 5)
+        n = load_library().spmm_b200_multi_routes(self._h, out.ctypes.data, out.size)
+        _check(min(n, 0), "multi_routes")
+        return [int(v) for v in out[:self.ngpus]], out[self.ngpus:].tolist()
 
     def shard_variant(self, g):
         lib = load_library()

@@ -21,6 +21,7 @@
 #include <limits.h>
 #include <math.h>
 #include <vector>
+#include <chrono>
 #include <algorithm>
 
 using namespace sb200;
@@ -55,6 +56,7 @@ struct Options {
 	int direct_store = 1;      // DIRECT_STORE
 	int rowband = -1;          // ROWBAND: host pipeline over row blocks of a banded matrix; -1 = by the transfer model, 0 = off, R = force R equal blocks, -2 = force the graded blocks
 	int rowband_direct = 0;    // ROWBAND_DIRECT: 1 = row-band blocks store C straight into mapped host memory (measured slower than one contiguous copy per block)
+	int multi_route = -1;      // MULTI_ROUTE (spmm_b200_run_multi): which devices download C; -1 = measure the box once, 0 = every device its own rows, mask = bit g set: device g downloads
 	int upload_window = 1;     // UPLOAD_WINDOW: host-buffer calls upload only the rows of B the matrix's nonzeros reference (first..last touched column)
 	int ctas_per_sm = 0;       // CTAS_PER_SM: 0 = by k
 	int merge_maxrow = 256;    // MERGE_MAXROW
@@ -75,7 +77,7 @@ static const OptionName OPTION_TABLE[] = {
 	{"TICKET", &Options::ticket}, {"TICKET_CTAS", &Options::ticket_ctas}, {"TICKET_MIN_NNZ", &Options::ticket_min_nnz}, {"STAGE", &Options::stage},
 	{"CONST_LD", &Options::const_ld}, {"UNROLL", &Options::unroll}, {"KSLICE", &Options::kslice}, {"KSLICE_MIN_MB", &Options::kslice_min_mb},
 	{"PIPELINE_COLS", &Options::pipeline_cols}, {"PIPELINE_MIN_KB", &Options::pipeline_min_kb},
-	{"DIRECT_STORE", &Options::direct_store}, {"ROWBAND", &Options::rowband}, {"ROWBAND_DIRECT", &Options::rowband_direct}, {"UPLOAD_WINDOW", &Options::upload_window}, {"CTAS_PER_SM", &Options::ctas_per_sm},
+	{"DIRECT_STORE", &Options::direct_store}, {"ROWBAND", &Options::rowband}, {"ROWBAND_DIRECT", &Options::rowband_direct}, {"UPLOAD_WINDOW", &Options::upload_window}, {"MULTI_ROUTE", &Options::multi_route}, {"CTAS_PER_SM", &Options::ctas_per_sm},
 	{"MERGE_MAXROW", &Options::merge_maxrow}, {"BCSR_FILL_PCT", &Options::bcsr_fill_pct},
 	{"TF32_STAGES", &Options::tf32_stages}, {"L2_HINT", &Options::l2_hint}, {"BCSR_TMA", &Options::bcsr_tma}, {"BCSR_STAGES", &Options::bcsr_stages}, {"BCSR_BRW", &Options::bcsr_brw},
 };

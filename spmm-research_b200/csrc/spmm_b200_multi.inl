@@ -50,6 +50,12 @@ struct spmm_b200_multi {
 	std::vector<std::vector<cudaEvent_t>> ev_part;   // [device][slice]: that device's part of the slice is uploaded
 	std::vector<void*> pinned;
 	int resident_k = 0;
+	// download routing (multi_choose_routes): route[g] = the device whose PCIe link carries device g's rows of C
+	std::vector<int> route;
+	int route_mask = -2;                         // the MULTI_ROUTE value the routes were made for (-2: not yet)
+	std::vector<double*> relay;                  // relay[p]: buffer on device p that its clients' kernels store C into over NVLink
+	std::vector<size_t> relay_cap;
+	std::vector<double> route_probe;             // GB/s of the candidate downloader sets, as measured (spmm_b200_multi_routes)
 };
 
 extern "C" void spmm_b200_destroy_multi(spmm_b200_multi_t* mh)
@@ -60,6 +66,7 @@ extern "C" void spmm_b200_destroy_multi(spmm_b200_multi_t* mh)
 			cudaSetDevice(mh->dev[g]);
 			for (cudaEvent_t e : mh->ev_part[g]) cudaEventDestroy(e);
 		}
+		if (g < (int) mh->relay.size() && mh->relay[g]) { cudaSetDevice(mh->dev[g]); cudaFree(mh->relay[g]); }
 		spmm_b200_destroy(mh->sh[g]);
 	}
 	for (void* p : mh->pinned) cudaHostUnregister(p);
@@ -226,6 +233,164 @@ static int multi_sync(spmm_b200_multi* mh)
 	return SPMM_B200_OK;
 }
 
+// ------------------------------------------------------------------------------------------
+// Download routing.  The PCIe links of an 8-GPU box do not end in equal shares of the host: on the pool's boxes four
+// of the eight devices sit behind ONE ~75 GB/s path while the other four sustain 44 GB/s each, and with all eight
+// writing at once the box moves 125 GB/s -- less than the good four alone (177 GB/s; profiles/r2_multi_gpu.md, section
+// 6).  C is row-local on each device but any device can carry it to the host: a device that does not download stores
+// its rows of C straight into a relay buffer on a partner (the SpMM kernel's C pointer is peer memory: NVLink stores),
+// and the partner's copy engine moves them into the caller's y.  Which devices download is MEASURED once per handle
+// (a few 16 MB copies per candidate set: all, either half, evens, odds); a subset is used only when it beats "all" by
+// 20 %.  MULTI_ROUTE=0 turns it off, a bit mask forces the set.
+// ------------------------------------------------------------------------------------------
+
+static int multi_probe_set(spmm_b200_multi* mh, unsigned mask, double* const* dbuf, char* hbuf, size_t bytes, double* gbs)
+{
+	for (int g = 0; g < mh->n; g++) { CU_TRY(cudaSetDevice(mh->dev[g])); CU_TRY(cudaStreamSynchronize(mh->sh[g]->stream)); }
+	const auto t0 = std::chrono::steady_clock::now();
+	int active = 0;
+	for (int rep = 0; rep < 2; rep++)
+		for (int g = 0; g < mh->n; g++) {
+			if (!(mask >> g & 1u)) continue;
+			CU_TRY(cudaSetDevice(mh->dev[g]));
+			CU_TRY(cudaMemcpyAsync(hbuf + (size_t) g * bytes, dbuf[g], bytes, cudaMemcpyDeviceToHost, mh->sh[g]->stream));
+			active += rep == 0;
+		}
+	for (int g = 0; g < mh->n; g++) {
+		if (!(mask >> g & 1u)) continue;
+		CU_TRY(cudaSetDevice(mh->dev[g]));
+		CU_TRY(cudaStreamSynchronize(mh->sh[g]->stream));
+	}
+	const double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+	*gbs = 2.0 * active * (double) bytes / sec / 1e9;
+	return SPMM_B200_OK;
+}
+
+static void multi_routes_from_mask(spmm_b200_multi* mh, unsigned mask)
+{
+	std::vector<int> down;
+	for (int g = 0; g < mh->n; g++) if (mask >> g & 1u) down.push_back(g);
+	mh->route.assign(mh->n, 0);
+	int next = 0;
+	for (int g = 0; g < mh->n; g++) {
+		if (down.empty() || (mask >> g & 1u)) { mh->route[g] = g; continue; }
+		mh->route[g] = down[next++ % down.size()];
+	}
+}
+
+static int multi_choose_routes(spmm_b200_multi* mh)
+{
+	const int want = mh->sh[0]->opt.multi_route;
+	if (mh->route_mask == want && (int) mh->route.size() == mh->n) return SPMM_B200_OK;
+	const unsigned all = mh->n >= 32 ? ~0u : (1u << mh->n) - 1u;
+	mh->route_mask = want;
+	mh->route_probe.clear();
+	multi_routes_from_mask(mh, all);
+	if (want == 0 || !mh->peer) return SPMM_B200_OK;
+	if (want > 0) { if (((unsigned) want & all) != 0) multi_routes_from_mask(mh, (unsigned) want & all); return SPMM_B200_OK; }
+	if (mh->n < 4) return SPMM_B200_OK;          // two links have never been seen to hurt each other
+	// measure
+	const size_t bytes = (size_t) 16 << 20;
+	std::vector<double*> dbuf(mh->n, nullptr);
+	char* hbuf = nullptr;
+	int rc = SPMM_B200_OK;
+	if (cudaHostAlloc((void**) &hbuf, bytes * mh->n, cudaHostAllocPortable) != cudaSuccess) { cudaGetLastError(); return SPMM_B200_OK; }
+	for (int g = 0; g < mh->n && !rc; g++) {
+		if (cudaSetDevice(mh->dev[g]) != cudaSuccess || cudaMalloc((void**) &dbuf[g], bytes) != cudaSuccess) { cudaGetLastError(); rc = SPMM_B200_ENOMEM; }
+	}
+	unsigned lower = 0, upper = 0, even = 0, odd = 0;
+	for (int g = 0; g < mh->n; g++) {
+		(g < mh->n / 2 ? lower : upper) |= 1u << g;
+		(g % 2 == 0 ? even : odd) |= 1u << g;
+	}
+	const unsigned cand[5] = {all, lower, upper, even, odd};
+	double rate[5] = {0, 0, 0, 0, 0}, warm = 0;
+	if (!rc) rc = multi_probe_set(mh, all, dbuf.data(), hbuf, bytes, &warm);
+	for (int i = 0; i < 5 && !rc; i++) rc = multi_probe_set(mh, cand[i], dbuf.data(), hbuf, bytes, &rate[i]);
+	for (int g = 0; g < mh->n; g++) if (dbuf[g]) { cudaSetDevice(mh->dev[g]); cudaFree(dbuf[g]); }
+	cudaFreeHost(hbuf);
+	if (rc) return rc == SPMM_B200_ENOMEM ? SPMM_B200_OK : rc;      // no room for the probe: every device downloads its own rows
+	mh->route_probe.assign(rate, rate + 5);
+	int best = 0;
+	for (int i = 1; i < 5; i++) if (rate[i] > rate[best]) best = i;
+	if (best != 0 && rate[best] > 1.2 * rate[0]) multi_routes_from_mask(mh, cand[best]);
+	return SPMM_B200_OK;
+}
+
+// out[0..n): route[g]; then the measured GB/s of the candidate sets {all, lower half, upper half, evens, odds} (0 when
+// nothing was measured).  Returns the number of doubles written.
+extern "C" int spmm_b200_multi_routes(const spmm_b200_multi_t* mh, double* out, int max_values)
+{
+	if (!mh || !out || max_values < 1) return SPMM_B200_EINVAL;
+	int n = 0;
+	for (int g = 0; g < mh->n && n < max_values; g++) out[n++] = g < (int) mh->route.size() ? mh->route[g] : g;
+	for (size_t i = 0; i < 5 && n < max_values; i++) out[n++] = i < mh->route_probe.size() ? mh->route_probe[i] : 0.0;
+	return n;
+}
+
+// Own windows + routed downloads: per device one upload of its window of B, one kernel on its shard whose C pointer is
+// its own d_C (downloaders) or the partner's relay buffer (peer stores), then the downloaders' copy engines carry first
+// their own rows and then their clients' rows into y.
+static int run_multi_routed(spmm_b200_multi* mh, const double* x_host, double* y_host, int k)
+{
+	int rc = multi_prepare(mh, k, 1);
+	if (rc) return rc;
+	mh->relay.resize(mh->n, nullptr);
+	mh->relay_cap.resize(mh->n, 0);
+	std::vector<size_t> off(mh->n, 0);
+	for (int p = 0; p < mh->n; p++) {
+		size_t need = 0;
+		for (int g = 0; g < mh->n; g++)
+			if (mh->route[g] == p && g != p) { off[g] = need; need += (size_t) mh->sh[g]->m * k; }
+		if (need > mh->relay_cap[p]) {
+			CU_TRY(cudaSetDevice(mh->dev[p]));
+			if (mh->relay[p]) cudaFree(mh->relay[p]);
+			mh->relay[p] = nullptr; mh->relay_cap[p] = 0;
+			CU_TRY(cudaMalloc((void**) &mh->relay[p], need * sizeof(double)));
+			mh->relay_cap[p] = need;
+		}
+	}
+	for (int g = 0; g < mh->n; g++) {
+		spmm_b200* h = mh->sh[g];
+		CU_TRY(cudaSetDevice(h->device));
+		h->last_h2d_bytes = h->last_d2h_bytes = 0;
+		h->band_blocks = 0;
+		int64_t lo, n;
+		b_window(h, lo, n);
+		rc = upload_b_rows(h, x_host, k, 0, k, lo, n, h->d_B, h->s_up);
+		if (rc) return rc;
+		CU_TRY(cudaEventRecord(h->ev_slice[0], h->s_up));
+		CU_TRY(cudaStreamWaitEvent(h->stream, h->ev_slice[0], 0));
+		CU_TRY(cudaEventRecord(h->ev_slice[1], h->stream));
+		const int p = mh->route[g];
+		if (h->m > 0) {
+			const int nl = launch_spmm(h, h->d_B, p == g ? h->d_C : mh->relay[p] + off[g], k, h->stream);
+			if (nl < 0) return nl;
+		}
+		CU_TRY(cudaEventRecord(h->ev_slice[2], h->stream));
+		h->c_slices = p == g ? 1 : 0;
+		h->timed = true; h->timed_slices = 1;
+	}
+	for (int p = 0; p < mh->n; p++) {
+		if (mh->route[p] != p) continue;
+		spmm_b200* hp = mh->sh[p];
+		CU_TRY(cudaSetDevice(hp->device));
+		CU_TRY(cudaStreamWaitEvent(hp->s_down, hp->ev_slice[2], 0));
+		if (hp->m > 0) {
+			CU_TRY(cudaMemcpyAsync(y_host + (size_t) hp->first_row * k, hp->d_C, sizeof(double) * hp->m * k, cudaMemcpyDeviceToHost, hp->s_down));
+			hp->last_d2h_bytes += (int64_t) sizeof(double) * hp->m * k;
+		}
+		for (int g = 0; g < mh->n; g++) {
+			if (mh->route[g] != p || g == p || mh->sh[g]->m == 0) continue;
+			CU_TRY(cudaStreamWaitEvent(hp->s_down, mh->sh[g]->ev_slice[2], 0));
+			CU_TRY(cudaMemcpyAsync(y_host + (size_t) mh->sh[g]->first_row * k, mh->relay[p] + off[g], sizeof(double) * mh->sh[g]->m * k,
+			                       cudaMemcpyDeviceToHost, hp->s_down));
+			hp->last_d2h_bytes += (int64_t) sizeof(double) * mh->sh[g]->m * k;
+		}
+	}
+	return multi_sync(mh);
+}
+
 extern "C" int spmm_b200_run_multi(spmm_b200_multi_t* mh, const double* x_host, double* y_host, int k, int copy_back)
 {
 	if (!mh || !x_host || k < 1 || (copy_back && !y_host)) return SPMM_B200_EINVAL;
@@ -242,7 +407,12 @@ extern "C" int spmm_b200_run_multi(spmm_b200_multi_t* mh, const double* x_host, 
 		}
 		// (a diagonal band gives each shard c/N rows of B plus the band: the same bytes as its share of a gather, minus the gather)
 		if (copy_back && mh->sh[0]->opt.upload_window && worst * mh->n * 4 <= mh->c * 5) {
-			int rc = multi_prepare(mh, k, 1);
+			int rc = multi_choose_routes(mh);
+			if (rc) return rc;
+			bool routed = false;
+			for (int g = 0; g < mh->n; g++) routed = routed || mh->route[g] != g;
+			if (routed) return run_multi_routed(mh, x_host, y_host, k);
+			rc = multi_prepare(mh, k, 1);
 			if (rc) return rc;
 			std::vector<BandStep> steps;
 			for (int g = 0; g < mh->n; g++) {

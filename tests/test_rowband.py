@@ -292,3 +292,40 @@ def test_rowband_blocked_variants(pkg, L, variant, k):
         assert mf.last_rowband() == (blocks if blocks > 0 else 7), (variant, k, blocks)
         assert np.array_equal(y, y0), (variant, k, blocks)
     mf.close()
+
+
+@pytest.mark.parametrize("ngpus,variant", [(2, "ROWSPLIT"), (2, "MERGE"), (4, "ROWSPLIT"), (8, "ROWSPLIT"), (8, "BCSR")])
+def test_multi_gpu_download_routes(pkg, L, ngpus, variant):
+    """MULTI_ROUTE: devices that do not download store their rows of C into a partner's relay buffer over NVLink and the
+    partner's copy engine carries them into y.  Forced downloader sets, then the measured choice; same y every time."""
+    if pkg.load_library().spmm_b200_device_count() < ngpus:
+        pytest.skip(f"needs {ngpus} GPUs")
+    m, c, k = 6000, 16000, 32
+    ia, ja, a = banded_csr(m, 900, 20.0, 80, seed=52)
+    ja = (ja + 7000).astype(np.int32)
+    if variant == "MERGE":                        # one long row so that tiles carry into each other inside a relay buffer
+        extra = np.setdiff1d(np.arange(7000, 7900, dtype=np.int32), ja[ia[100]:ia[101]])
+        row = np.sort(np.concatenate([ja[ia[100]:ia[101]], extra]))
+        vals = np.concatenate([a[ia[100]:ia[101]], np.full(len(extra), 0.5)])[np.argsort(np.concatenate([ja[ia[100]:ia[101]], extra]), kind="stable")]
+        ja = np.concatenate([ja[:ia[100]], row, ja[ia[101]:]]).astype(np.int32)
+        a = np.concatenate([a[:ia[100]], vals, a[ia[101]:]])
+        ia = ia.copy(); ia[101:] += len(extra)
+    x = dense_b(c, k, 13)
+    y_ref = L.spmm_oracle(ia, ja, a, m, c, x, k)
+    mf = pkg.csr_to_format_multi(ia, ja, a, m, c, len(ja), k, ngpus, variant=getattr(pkg, variant))
+    buf = np.full(m * k, np.nan); mf.register_host(buf)
+    masks = [1, 1 << (ngpus - 1), sum(1 << g for g in range(0, ngpus, 2)), sum(1 << g for g in range(ngpus // 2, ngpus)), 0, -1]
+    for mask in masks:
+        mf.set_option("MULTI_ROUTE", mask)
+        buf[:] = np.nan
+        mf.spmm(x, buf, k)
+        assert max_rel_err(buf, y_ref) <= FP64_TOL, (ngpus, variant, mask)
+        route, probe = mf.routes()
+        if mask > 0:
+            assert all(mask >> r & 1 for r in route), (mask, route)
+        elif mask == 0:
+            assert route == list(range(ngpus))
+        else:
+            assert sorted(set(route)) == sorted(r for r in set(route) if route[r] == r)      # every downloader carries itself
+            assert (ngpus < 4) == (max(probe) == 0.0)
+    mf.close()
