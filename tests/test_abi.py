@@ -130,6 +130,11 @@ def test_argument_validation_round2_entry_points(pkg):
     assert lib.spmm_b200_create_f32(C.byref(h), rp, ci, af.ctypes.data, 10, 10, len(ja), 4, 0, 99, 0) == -1
     assert lib.spmm_b200_create_f32(C.byref(h), rp, ci, af.ctypes.data, 10, 10, len(ja), 0, 0, pkg.AUTO, 0) == -1
     assert lib.spmm_b200_variant_f32(None) == -1
+    # introspection added with the row-band pipeline / window upload / download routing
+    assert lib.spmm_b200_last_rowband(None) == -1
+    assert lib.spmm_b200_last_transfer_bytes(None, None, None) == -1
+    assert lib.spmm_b200_col_window(None, None, None) == -1
+    assert lib.spmm_b200_multi_routes(None, None, 0) == -1
     # the nnz-carry split needs an output array like the other modes
     assert lib.spmm_b200_partition(rp, 10, len(ja), 4, pkg.PART_NNZ_CARRY, None, 0) == -1
 
