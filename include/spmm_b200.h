@@ -75,7 +75,8 @@ enum {
 	SPMM_B200_ENOSUP  = -6,   /* variant not applicable to this matrix / k                    */
 	SPMM_B200_ECOMM   = -7,   /* the caller-supplied broadcast callback returned non-zero     */
 	SPMM_B200_EIO     = -8,   /* a matrix file could not be opened / read                     */
-	SPMM_B200_EFORMAT = -9    /* a matrix file is malformed (the reference would exit(1))     */
+	SPMM_B200_EFORMAT = -9,   /* a matrix file is malformed (the reference would exit(1))     */
+	SPMM_B200_ESCRATCH = -10  /* spmm_b200_spmm_merge_noalloc: the input needs more scratch than the fixed array holds */
 };
 
 /* ---- format construction: replaces csr_to_format() (spmv_kernel.h:29; call site spmv_bench.cpp:996).
@@ -284,6 +285,24 @@ int64_t spmm_b200_nnz_f32(const spmm_b200_f32_t *h);
 int64_t spmm_b200_launch_count_f32(const spmm_b200_f32_t *h);
 double  spmm_b200_last_kernel_ms_f32(const spmm_b200_f32_t *h);
 void    spmm_b200_destroy_f32(spmm_b200_f32_t *h);
+
+/* ---- allocation-free SpMM.  No counterpart in the reference: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * C = A * B by the merge-path kernels on the CURRENT device, everything passed as DEVICE pointers: CSR arrays as for
+ * spmm_b200_create (int32, 0-based, columns sorted per row), b_dev = row-major c x k, c_dev = row-major m x k (both
+ * 16-byte aligned when k >= 2), k in {1, 2, 4, 8, 16, 32, 64, 128}; `stream` is a cudaStream_t (NULL = default).
+ * Asynchronous.  Same arithmetic as a SPMM_B200_MERGE handle's spmm_b200_run_device (same bits).
+ * The scratch of the kernels (tile coordinates, per-tile carries) lives in ONE static device array of
+ * SPMM_B200_NOALLOC_SCRATCH_BYTES that every GPU which loads the library holds until exit; the call allocates and
+ * frees nothing.  Limit: the scratch is about (12 + 8k) bytes per tile of T merge items, m + nnz items in all (T = 4096
+ * for k <= 2, 1024 for k = 16 and k = 128, 2048 otherwise): m + nnz up to ~64 M at k = 32, ~8.3 M at k = 128, no
+ * practical bound at k = 1.  Beyond it the call returns SPMM_B200_ESCRATCH (sizes: spmm_b200_last_cuda_error) and
+ * launches nothing; such inputs take spmm_b200_create + spmm_b200_run_device.
+ * All calls on a device SHARE the array and find the previous call's contents in it (what must start at zero is cleared
+ * by the call): two calls that overlap on the GPU -- different streams, different threads -- race. */
+#define SPMM_B200_NOALLOC_SCRATCH_BYTES (8u << 20)
+int spmm_b200_spmm_merge_noalloc(const int32_t *row_ptr_dev, const int32_t *col_ind_dev, const double *values_dev,
+                                 int64_t m, int64_t c, int64_t nnz, const double *b_dev, double *c_dev, int k, void *stream);
 
 /* ---- introspection */
 int64_t spmm_b200_rows(const spmm_b200_t *h);         /* rows held by this handle (shard)     */

@@ -30,7 +30,7 @@ LIB_PATH = os.path.join(HERE, "lib", "libspmm_b200.so")
 
 # every symbol include/spmm_b200.h declares
 EXPORTS = [
-    "spmm_b200_create", "spmm_b200_create_shard", "spmm_b200_run", "spmm_b200_run_replicated", "spmm_b200_set_b",
+    "spmm_b200_create", "spmm_b200_create_shard", "spmm_b200_run", "spmm_b200_run_replicated", "spmm_b200_spmm_merge_noalloc", "spmm_b200_set_b",
     "spmm_b200_register_host", "spmm_b200_unregister_host", "spmm_b200_set_option", "spmm_b200_last_timeline",
     "spmm_b200_create_multi", "spmm_b200_run_multi", "spmm_b200_set_b_multi", "spmm_b200_run_resident_multi",
     "spmm_b200_fetch_c_multi", "spmm_b200_register_host_multi", "spmm_b200_multi_ngpus", "spmm_b200_multi_shard",
@@ -69,7 +69,7 @@ class SpmmB200Error(RuntimeError):
         lib = load_library()
         msg = lib.spmm_b200_strerror(code).decode()
         detail = lib.spmm_b200_last_cuda_error().decode()
-        super().__init__(f"{where}: {msg} (code {code})" + (f" [{detail}]" if detail and code in (-2, -3, -4) else ""))
+        super().__init__(f"{where}: {msg} (code {code})" + (f" [{detail}]" if detail and code in (-2, -3, -4, -6, -10) else ""))
         self.code = code
 
 
@@ -107,6 +107,7 @@ def load_library():
     lib.spmm_b200_run_resident.argtypes = [_vp, _int]
     lib.spmm_b200_fetch_c.argtypes = [_vp, _vp, _int]
     lib.spmm_b200_run_device.argtypes = [_vp, _vp, _vp, _int, _vp]
+    lib.spmm_b200_spmm_merge_noalloc.argtypes = [_vp, _vp, _vp, _i64, _i64, _i64, _vp, _vp, _int, _vp]
     lib.spmm_b200_transpose_b_device.argtypes = [_vp, _vp, _vp, _int, _vp]
     lib.spmm_b200_partition.argtypes = [_vp, _i64, _i64, _int, _int, _vp, _int]
     lib.spmm_b200_partition_host.argtypes = [_vp, _i64, _i64, _int, _int, _vp]
@@ -537,6 +538,18 @@ def csr_to_pipeline_format_f32(row_ptr, col_ind, values, m, nnz, n, *, device=0)
            _host(col_ind, np.int32, "col_ind") if nnz else None, _host(values, np.float32, "values") if nnz else None,
            m, nnz, n, device), "spmm_b200_pipeline_create_f32")
     return PipelineFormatF32(h, m, nnz, n, (row_ptr, col_ind, values))
+
+
+NOALLOC_SCRATCH_BYTES = 8 << 20
+ESCRATCH = -10
+
+
+def spmm_merge_noalloc(row_ptr_dev, col_ind_dev, values_dev, m, c, nnz, b_dev, c_dev, k, stream=0):
+    """Allocation-free merge-path SpMM on the current device (spmm_b200_spmm_merge_noalloc; no counterpart in the
+    reference).  Every array is a DEVICE address (int); B row-major c x k, C row-major m x k.  Asynchronous.  Raises
+    SpmmB200Error with code ESCRATCH when the input needs more than NOALLOC_SCRATCH_BYTES of scratch."""
+    _check(load_library().spmm_b200_spmm_merge_noalloc(row_ptr_dev or None, col_ind_dev or None, values_dev or None, int(m), int(c), int(nnz),
+                                                       b_dev or None, c_dev or None, int(k), stream or None), "spmm_merge_noalloc")
 
 
 def csr_to_format_f32(row_ptr, col_ind, values, m, n, nnz, k, *, device=0, variant=AUTO, b_layout=B_COLMAJOR, rank=None, nranks=None):

@@ -1812,6 +1812,7 @@ extern "C" const char* spmm_b200_strerror(int code)
 	case SPMM_B200_ECOMM:  return "the caller's broadcast callback failed";
 	case SPMM_B200_EIO:    return "cannot open or read the matrix file";
 	case SPMM_B200_EFORMAT: return "malformed matrix file";
+	case SPMM_B200_ESCRATCH: return "input needs more scratch than the fixed no-allocation array holds";
 	default:               return "unknown error";
 	}
 }
@@ -1839,3 +1840,118 @@ extern "C" int spmm_b200_device_count(void)
 // sparse-attention pipeline entry points (include/spmm_b200_pipeline.h)
 // ------------------------------------------------------------------------------------------
 #include "spmm_b200_pipeline.inl"
+
+// ------------------------------------------------------------------------------------------
+// Allocation-free entry point: spmm_b200_spmm_merge_noalloc (include/spmm_b200.h).
+// No counterpart in the reference; added for callers that cannot call cudaMalloc
+// (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  It runs the merge-path SpMM -- the one
+// kernel family here whose scratch (tile start coordinates, per-tile carries, carry rows) depends on the input -- with
+// that scratch in ONE file-scope device array of SPMM_B200_NOALLOC_SCRATCH_BYTES (8 MiB) that every GPU which loads the
+// library holds until exit.  The caller passes CSR, B and C as device pointers.  Nothing here calls cudaMalloc / cudaFree
+// or any allocating routine: three kernels and two memset nodes on the caller's stream.
+//
+// g_noalloc_scratch is, in HOST code, only a stand-in for the symbol: its device address is asked for once per device,
+// with that device current (cudaGetSymbolAddress), and that address is what the kernels receive.
+// Every call on a device shares the array and finds the previous call's contents in it: the parts a call reads before
+// writing are cleared first, and calls that overlap on the GPU (two streams, two threads) RACE on it.
+// ------------------------------------------------------------------------------------------
+#include <mutex>
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[SPMM_B200_NOALLOC_SCRATCH_BYTES];
+
+static constexpr int NOALLOC_MAX_DEVICES = 64;
+static std::mutex g_noalloc_mu;
+static unsigned char* g_noalloc_ptr[NOALLOC_MAX_DEVICES];      // device address of g_noalloc_scratch on device d (null: not asked yet)
+static uint32_t g_noalloc_attr[NOALLOC_MAX_DEVICES];           // bit i: shared-memory limit of merge instantiation i raised on device d
+
+template <int G, int V, int IPG>
+struct MergeLaunchNoAlloc {
+	using Cfg = MergeCfg<G, V, IPG, THREADS>;
+	static cudaError_t launch(int dev, int bit, const int32_t* ia, const int32_t* ja, const double* a, const double* B, double* C,
+	                          int ntiles, const int2* tile, double* carry, int32_t* carry_row, cudaStream_t s)
+	{
+		auto kern = spmm_merge_kernel<G, V, IPG, 4, THREADS>;
+		if (Cfg::SMEM > 48 * 1024) {
+			std::lock_guard<std::mutex> lock(g_noalloc_mu);
+			if (!(g_noalloc_attr[dev] >> bit & 1u)) {
+				cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) Cfg::SMEM);
+				if (e != cudaSuccess) return e;
+				g_noalloc_attr[dev] |= 1u << bit;
+			}
+		}
+		kern<<<ntiles, THREADS, Cfg::SMEM, s>>>(ia, ja, a, B, C, tile, carry, carry_row);
+		return cudaGetLastError();
+	}
+};
+
+static size_t round256(size_t v) { return (v + 255) & ~(size_t) 255; }
+
+extern "C" int spmm_b200_spmm_merge_noalloc(const int32_t* row_ptr_dev, const int32_t* col_ind_dev, const double* values_dev,
+                                            int64_t m, int64_t c, int64_t nnz, const double* b_dev, double* c_dev, int k, void* stream)
+{
+	int rc = check_sizes(row_ptr_dev, col_ind_dev, values_dev, m, c, nnz, k);
+	if (rc) return rc;
+	if ((nnz > 0 && !b_dev) || (m > 0 && !c_dev)) return SPMM_B200_EINVAL;
+	const int items = merge_items_for_k(k);
+	if (items <= 0) {
+		snprintf(g_cuda_err, sizeof(g_cuda_err), "spmm_b200_spmm_merge_noalloc: k = %d has no merge-path instantiation (1, 2, 4, 8, 16, 32, 64, 128)", k);
+		return SPMM_B200_ENOSUP;
+	}
+	// the kernels move B and C as 16-byte pieces from k = 2 on
+	if (k >= 2 && ((((uintptr_t) b_dev | (uintptr_t) c_dev) & 15) != 0)) return SPMM_B200_EINVAL;
+	// scratch layout: tile start coordinates | per-tile carries (k values each) | per-tile carry rows
+	const int64_t ntiles64 = (m + nnz + items - 1) / items;
+	const size_t off_carry = round256(sizeof(int2) * ((size_t) ntiles64 + 1));
+	const size_t off_row = off_carry + round256(sizeof(double) * (size_t) ntiles64 * k);
+	const size_t need = off_row + round256(sizeof(int32_t) * (size_t) ntiles64);
+	if (need > (size_t) SPMM_B200_NOALLOC_SCRATCH_BYTES) {
+		snprintf(g_cuda_err, sizeof(g_cuda_err),
+		         "spmm_b200_spmm_merge_noalloc: m + nnz = %lld at k = %d needs %zu bytes of scratch (%lld tiles of %d items), the fixed array holds %zu; "
+		         "use spmm_b200_create + spmm_b200_run_device for this size",
+		         (long long) (m + nnz), k, need, (long long) ntiles64, items, (size_t) SPMM_B200_NOALLOC_SCRATCH_BYTES);
+		return SPMM_B200_ESCRATCH;
+	}
+	int dev = -1;
+	if (cudaGetDevice(&dev) != cudaSuccess) { cudaGetLastError(); return SPMM_B200_ENODEV; }
+	if (dev < 0 || dev >= NOALLOC_MAX_DEVICES) return SPMM_B200_ENOSUP;
+	unsigned char* scratch = nullptr;
+	{
+		// once per device, with that device current: the DEVICE address of the array (the name itself is a host-side stand-in)
+		std::lock_guard<std::mutex> lock(g_noalloc_mu);
+		if (!g_noalloc_ptr[dev]) {
+			void* p = nullptr;
+			cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+			if (e != cudaSuccess || !p) {
+				snprintf(g_cuda_err, sizeof(g_cuda_err), "cudaGetSymbolAddress(g_noalloc_scratch) on device %d: %s", dev, cudaGetErrorString(e));
+				cudaGetLastError();
+				return SPMM_B200_ECUDA;
+			}
+			g_noalloc_ptr[dev] = (unsigned char*) p;
+		}
+		scratch = g_noalloc_ptr[dev];
+	}
+	const int ntiles = (int) ntiles64;
+	if (m == 0 || ntiles == 0) return SPMM_B200_OK;
+	cudaStream_t s = (cudaStream_t) stream;
+	int2* tile = reinterpret_cast<int2*>(scratch);
+	double* carry = reinterpret_cast<double*>(scratch + off_carry);
+	int32_t* carry_row = reinterpret_cast<int32_t*>(scratch + off_row);
+	// the array still holds the previous call's carries: every tile rewrites its own, but start from zero all the same
+	// so that no call can depend on what another left behind
+	CU_TRY(cudaMemsetAsync(scratch + off_carry, 0, sizeof(double) * (size_t) ntiles * k, s));
+	CU_TRY(cudaMemsetAsync(scratch + off_row, 0, sizeof(int32_t) * (size_t) ntiles, s));
+	tile_merge_kernel<<<(ntiles + 1 + 255) / 256, 256, 0, s>>>(row_ptr_dev, (int) m, nnz, items, ntiles, tile);
+	CU_TRY(cudaGetLastError());
+	cudaError_t e = cudaErrorInvalidValue;
+#define WHAT(G, V, IPG, BIT) e = MergeLaunchNoAlloc<G, V, IPG>::launch(dev, BIT, row_ptr_dev, col_ind_dev, values_dev, b_dev, c_dev, ntiles, tile, carry, carry_row, s)
+	MERGE_DISPATCH(k, WHAT)
+#undef WHAT
+	if (e != cudaSuccess) {
+		snprintf(g_cuda_err, sizeof(g_cuda_err), "no-alloc merge kernel launch (k=%d): %s", k, cudaGetErrorString(e));
+		return SPMM_B200_ECUDA;
+	}
+	const int64_t n = (int64_t) ntiles * k;
+	spmm_merge_fixup_kernel<THREADS><<<(unsigned) ((n + THREADS - 1) / THREADS), THREADS, 0, s>>>(carry, carry_row, ntiles, (int) m, k, c_dev);
+	CU_TRY(cudaGetLastError());
+	return SPMM_B200_OK;
+}

@@ -135,6 +135,13 @@ def test_argument_validation_round2_entry_points(pkg):
     assert lib.spmm_b200_last_transfer_bytes(None, None, None) == -1
     assert lib.spmm_b200_col_window(None, None, None) == -1
     assert lib.spmm_b200_multi_routes(None, None, 0) == -1
+    # the allocation-free entry point checks arguments and the scratch bound before it touches a device
+    fake = C.c_void_p(4096)
+    assert lib.spmm_b200_spmm_merge_noalloc(None, fake, fake, 10, 10, 10, fake, fake, 32, None) == -1
+    assert lib.spmm_b200_spmm_merge_noalloc(fake, fake, fake, 10, 10, 10, fake, fake, 3, None) == -6
+    assert lib.spmm_b200_spmm_merge_noalloc(fake, fake, fake, 10, 10, 2 ** 31, fake, fake, 32, None) == -5
+    assert lib.spmm_b200_spmm_merge_noalloc(fake, fake, fake, 20_000_000, 10, 20_000_000, fake, fake, 128, None) == -10
+    assert b"scratch" in lib.spmm_b200_strerror(-10) and b"needs" in lib.spmm_b200_last_cuda_error()
     # the nnz-carry split needs an output array like the other modes
     assert lib.spmm_b200_partition(rp, 10, len(ja), 4, pkg.PART_NNZ_CARRY, None, 0) == -1
 
