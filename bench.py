@@ -284,6 +284,43 @@ def reference_arm(args, ia, ja, a, m, c, k, nnz, workload_desc):
 # our arm
 # ---------------------------------------------------------------------------------------------
 
+def measure_download_routes(torch, dist, dev, rank, world):
+    """One process per GPU: which ranks should carry C to the host on THIS box.  Times device->host copies (16 MB, copy
+    engine) with all ranks active and with four candidate subsets; when a subset moves more than 1.2x what all ranks
+    move together, the other ranks route their rows of C through a partner in it.  Returns (route, probe):
+    route[r] = downloader of rank r (identity when nothing is gained), probe = GB/s of {all, lower, upper, even, odd}."""
+    ident = list(range(world))
+    if world < 4:
+        return ident, None
+    n = (16 << 20) // 8
+    h = torch.empty(n, dtype=torch.float64, pin_memory=True)
+    d = torch.ones(n, dtype=torch.float64, device=dev)
+    sets = [ident, ident[: world // 2], ident[world // 2:], ident[0::2], ident[1::2]]
+    rates = []
+    for si, members in enumerate([ident] + sets):          # the first pass is a warm-up
+        torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        if rank in members:
+            for _ in range(3):
+                h.copy_(d, non_blocking=True)
+            torch.cuda.synchronize()
+        el = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+        dist.all_reduce(el, op=dist.ReduceOp.MAX)
+        if si > 0:
+            rates.append(3 * len(members) * n * 8 / float(el.item()) / 1e9)
+    best = max(range(len(sets)), key=lambda i: rates[i])
+    if best == 0 or rates[best] <= 1.2 * rates[0]:
+        return ident, rates
+    down = sets[best]
+    route, nxt = [], 0
+    for r in ident:
+        if r in down:
+            route.append(r)
+        else:
+            route.append(down[nxt % len(down)]); nxt += 1
+    return route, rates
+
+
 def gpu_arm(args, ia, ja, a, m, c, k, nnz, workload_desc):
     import torch
     import torch.distributed as dist
@@ -388,10 +425,21 @@ def gpu_arm(args, ia, ja, a, m, c, k, nnz, workload_desc):
                 for w in works:
                     w.wait()
 
+    def xfer(ptr, count, peer, is_send, lib_stream):
+        # send / receive of C rows between ranks for routed downloads: NCCL point-to-point on the library's stream
+        with torch.cuda.stream(torch.cuda.ExternalStream(lib_stream, device=dev)):
+            t = torch.as_tensor(_DevArray(ptr, count), device=dev)
+            if is_send:
+                dist.send(t, dst=peer)
+            else:
+                dist.recv(t, src=peer)
+
     def e2e_step():
         # the public drop-in call with HOST buffers: upload (root) -> broadcast -> kernel -> download of the
         # row-local C, pipelined inside the library over row blocks (banded matrix, N = 1) or 16-column slices
-        if world == 1 or own_window:
+        if routed:
+            mf.spmm_routed(x_host.numpy(), y_all.numpy(), k, rank, route[rank], clients, xfer)
+        elif world == 1 or own_window:
             mf.spmm(x_host.numpy(), y_host.numpy()[: m_loc * k], k)
         else:
             mf.spmm_replicated(x_host.numpy(), y_host.numpy()[: m_loc * k], k, bcast, x_on_every_rank=True)
@@ -411,7 +459,41 @@ def gpu_arm(args, ia, ja, a, m, c, k, nnz, workload_desc):
     # the all-gather, every rank uploads its own window over its own PCIe link and no collective runs at all.
     span = mf.col_window()[1]
     own_window = world > 1 and max_over_ranks(float(span)) * world <= 1.25 * c      # same rule as spmm_b200_run_multi
+    # Download routing: the PCIe links of a box are not equal.  With own windows, N >= 4 and a result small
+    # enough for one shared-memory y, the ranks measure which of them should carry C to the host; the others send their
+    # rows to a partner over NVLink (NCCL send / recv) and the partner stores them into the shared y.
+    route, route_probe, routed, clients, y_all, shm_path = list(range(world)), None, False, [], None, None
+    shm_free = 0
+    if world > 1 and os.path.isdir("/dev/shm"):
+        st = os.statvfs("/dev/shm")
+        shm_free = -int(max_over_ranks(-float(st.f_bavail * st.f_frsize)))          # min over ranks
+    if own_window and world >= 4 and 8 * m * k + (64 << 20) <= min(2 << 30, shm_free) and not os.environ.get("SPMM_B200_BENCH_NO_ROUTE"):
+        route, route_probe = measure_download_routes(torch, dist, dev, rank, world)
+        routed = any(route[r] != r for r in range(world))
+    forced = os.environ.get("SPMM_B200_BENCH_FORCE_ROUTE")          # e.g. "1,1": rank 1 downloads for both (testing at N = 2)
+    if forced and own_window and world > 1:
+        route = [int(v) for v in forced.split(",")]
+        assert len(route) == world and all(route[route[r]] == route[r] for r in range(world)), "a downloader must carry its own rows"
+        routed = any(route[r] != r for r in range(world))
+    if routed:
+        first = torch.tensor([mf.first_row if r == rank else 0 for r in range(world)] + [m_loc if r == rank else 0 for r in range(world)],
+                             dtype=torch.int64, device=dev)
+        dist.all_reduce(first, op=dist.ReduceOp.SUM)
+        first = first.tolist()
+        clients = [(r, first[r], first[world + r]) for r in range(world) if route[r] == rank and r != rank]
+        shm_path = "/dev/shm/spmm_b200_bench_y_%s" % os.environ.get("MASTER_PORT", "0")
+        if rank == 0:
+            with open(shm_path, "wb") as f:
+                f.truncate(8 * m * k)
+        dist.barrier()
+        y_all = torch.from_file(shm_path, shared=True, size=m * k, dtype=torch.float64)      # ONE y for all ranks
+        mf.register_host(y_all.numpy())
+        dist.barrier()
+        if rank == 0:
+            os.unlink(shm_path)              # the mappings keep it alive
     e2e_s = time_e2e(e2e_steps)
+    if routed:
+        y_host = y_all[mf.first_row * k: (mf.first_row + m_loc) * k]       # this rank's rows of the shared result
     clocks = sampler.stop()
     e2e_val = 2.0 * nnz * k / e2e_s / 1e9
     timeline = mf.last_timeline()            # event times of the last e2e step on this rank (ms since its first enqueue)
@@ -491,6 +573,11 @@ def gpu_arm(args, ia, ja, a, m, c, k, nnz, workload_desc):
     if world > 1:
         line["e2e"]["replication"] = ("none: every rank uploads its own window of B" if own_window else
                                       "1/N of B per rank + NCCL all-gather per slice")
+        line["e2e"]["download_routes"] = {"route": route, "probe_gbs_all_lower_upper_even_odd": route_probe,
+                                          "note": "route[r] = rank whose PCIe link carries rank r's rows of C into the shared y "
+                                                  "(identity: every rank its own rows); measured at set-up"}
+        if routed:
+            line["e2e"]["pipeline"] = "routed: own window up, shard kernel, C rows to the downloader rank over NVLink, one contiguous copy per shard"
     if full:
         line["e2e"]["full_b_upload"] = full
     if rank == 0 and not args.no_parity:

@@ -131,6 +131,20 @@ typedef int (*spmm_b200_bcast_fn)(void *ctx, double *dev_ptr, size_t count, int 
 int spmm_b200_run_replicated(spmm_b200_t *h, const double *x_host, double *y_host, int k, int copy_back,
                              spmm_b200_bcast_fn bcast, void *bcast_ctx, int x_on_every_rank);
 
+/* One process per GPU on a box whose PCIe links are unequal ("download routing"): the ranks share ONE y
+ * (m_global x k, e.g. POSIX shared memory mapped and page-locked by every rank) and the caller has decided -- by
+ * measurement, see bench.py -- which ranks carry C to the host.  Every rank uploads its own window of B and runs its
+ * shard; a rank with downloader_rank != its own sends its rows of C to that rank and moves nothing over PCIe on the way
+ * down; a downloader stores its own rows into y_all at its first row and then, for each of its `nclients` clients,
+ * receives the client's rows into a relay buffer and stores them at the client's first row.
+ * `xfer(ctx, dev_ptr, count, peer_rank, is_send, stream)` must enqueue on `stream` the send (is_send != 0) or receive of
+ * `count` doubles at `dev_ptr` to / from `peer_rank` and return 0 (ncclSend / ncclRecv, torch.distributed.send / recv).
+ * Requires x on every rank (x_host != NULL).  Same bits as spmm_b200_run on the shard. */
+typedef int (*spmm_b200_xfer_fn)(void *ctx, double *dev_ptr, size_t count, int peer_rank, int is_send, void *stream);
+int spmm_b200_run_routed(spmm_b200_t *h, const double *x_host, double *y_all, int k, int my_rank, int downloader_rank,
+                         const int *client_ranks, const int64_t *client_first_row, const int64_t *client_rows, int nclients,
+                         spmm_b200_xfer_fn xfer, void *xfer_ctx);
+
 /* Optional: page-lock a caller-owned host range (x or y) so that spmm_b200_run copies at full
  * PCIe rate.  The caller promises the range stays mapped until spmm_b200_unregister_host /
  * spmm_b200_destroy -- true for the harness's x and y (spmv_bench.cpp:896-907).  Ranges that

@@ -30,7 +30,7 @@ LIB_PATH = os.path.join(HERE, "lib", "libspmm_b200.so")
 
 # every symbol include/spmm_b200.h declares
 EXPORTS = [
-    "spmm_b200_create", "spmm_b200_create_shard", "spmm_b200_run", "spmm_b200_run_replicated", "spmm_b200_spmm_merge_noalloc", "spmm_b200_set_b",
+    "spmm_b200_create", "spmm_b200_create_shard", "spmm_b200_run", "spmm_b200_run_replicated", "spmm_b200_run_routed", "spmm_b200_spmm_merge_noalloc", "spmm_b200_set_b",
     "spmm_b200_register_host", "spmm_b200_unregister_host", "spmm_b200_set_option", "spmm_b200_last_timeline",
     "spmm_b200_create_multi", "spmm_b200_run_multi", "spmm_b200_set_b_multi", "spmm_b200_run_resident_multi",
     "spmm_b200_fetch_c_multi", "spmm_b200_register_host_multi", "spmm_b200_multi_ngpus", "spmm_b200_multi_shard",
@@ -59,6 +59,7 @@ _vp, _i64, _int, _dbl = C.c_void_p, C.c_int64, C.c_int, C.c_double
 
 # int (*spmm_b200_bcast_fn)(void *ctx, double *dev_ptr, size_t count, int parts, void *stream)
 BCAST_FN = C.CFUNCTYPE(_int, _vp, _vp, C.c_size_t, _int, _vp)
+XFER_FN = C.CFUNCTYPE(_int, _vp, _vp, C.c_size_t, _int, _int, _vp)
 
 
 class SpmmB200Error(RuntimeError):
@@ -85,6 +86,7 @@ def load_library():
     lib.spmm_b200_create_shard.argtypes = lib.spmm_b200_create.argtypes + [_int, _int, C.POINTER(_i64), C.POINTER(_i64)]
     lib.spmm_b200_run.argtypes = [_vp, _vp, _vp, _int, _int]
     lib.spmm_b200_run_replicated.argtypes = [_vp, _vp, _vp, _int, _int, BCAST_FN, _vp, _int]
+    lib.spmm_b200_run_routed.argtypes = [_vp, _vp, _vp, _int, _int, _int, _vp, _vp, _vp, _int, XFER_FN, _vp]
     lib.spmm_b200_set_b.argtypes = [_vp, _vp, _int]
     lib.spmm_b200_register_host.argtypes = [_vp, _vp, C.c_size_t]
     lib.spmm_b200_unregister_host.argtypes = [_vp, _vp]
@@ -232,6 +234,31 @@ class MatrixFormat:
         if err:
             raise err[0]
         _check(rc, "spmm_replicated")
+
+    def spmm_routed(self, x, y_all, k, my_rank, downloader_rank, clients, xfer):
+        """One process per GPU with routed downloads (spmm_b200_run_routed): y_all is the ONE m_global x k result every
+        rank shares (shared memory, page-locked by every rank).  A rank whose downloader_rank is another rank sends its
+        rows of C there; a downloader stores its own rows and those of `clients` = [(rank, first_row, rows), ...] into
+        y_all.  `xfer(dev_ptr, count, peer_rank, is_send, stream)` enqueues the send / receive on `stream`."""
+        err = []
+
+        def _cb(_ctx, ptr, count, peer, is_send, stream):
+            try:
+                xfer(ptr, count, peer, bool(is_send), stream)
+                return 0
+            except Exception as e:      # an exception must not unwind through the C frames
+                err.append(e)
+                return 1
+        cb = XFER_FN(_cb) if xfer is not None else C.cast(None, XFER_FN)
+        ranks = np.array([c[0] for c in clients], np.int32)
+        first = np.array([c[1] for c in clients], np.int64)
+        rows = np.array([c[2] for c in clients], np.int64)
+        rc = load_library().spmm_b200_run_routed(self._h, _host(x, np.float64, "x"), _host(y_all, np.float64, "y_all"), int(k),
+                                                 int(my_rank), int(downloader_rank), ranks.ctypes.data, first.ctypes.data,
+                                                 rows.ctypes.data, len(clients), cb, None)
+        if err:
+            raise err[0]
+        _check(rc, "spmm_routed")
 
     ACCURACY_LABELS = ("max_rel_diff", "mae", "max_ae", "mse", "mape", "smape", "lnQ_error", "mlare", "gmare", "passed")
 

@@ -1543,6 +1543,79 @@ extern "C" int spmm_b200_run_replicated(spmm_b200_t* h, const double* x_host, do
 	return run_pipelined(h, x_host, copy_back ? y_host : nullptr, k, ks, bcast, bcast_ctx, parts);
 }
 
+// One process per GPU with routed downloads (include/spmm_b200.h): own window up, kernel on the shard, then either
+// send C to the downloader rank or carry own + clients' rows into the shared y.
+extern "C" int spmm_b200_run_routed(spmm_b200_t* h, const double* x_host, double* y_all, int k, int my_rank, int downloader_rank,
+                                    const int* client_ranks, const int64_t* client_first_row, const int64_t* client_rows, int nclients,
+                                    spmm_b200_xfer_fn xfer, void* xfer_ctx)
+{
+	if (!h || !x_host || !y_all || k < 1 || nclients < 0) return SPMM_B200_EINVAL;
+	const bool download = downloader_rank == my_rank;
+	if ((!download || nclients > 0) && !xfer) return SPMM_B200_EINVAL;
+	if (nclients > 0 && (!download || !client_ranks || !client_first_row || !client_rows)) return SPMM_B200_EINVAL;
+	CU_TRY(cudaSetDevice(h->device));
+	h->last_h2d_bytes = h->last_d2h_bytes = 0;
+	h->band_blocks = 0; h->tl_slices = 0;
+	int rc = ensure(&h->d_B, &h->cap_B, (size_t) h->c * k);
+	if (rc) return rc;
+	if (h->b_layout == SPMM_B200_B_COLMAJOR && k != 1) {
+		rc = ensure(&h->d_x, &h->cap_x, (size_t) h->c * k);
+		if (rc) return rc;
+	}
+	size_t relay = 0;
+	for (int i = 0; i < nclients; i++) {
+		if (client_rows[i] < 0 || client_first_row[i] < 0) return SPMM_B200_EINVAL;
+		relay += (size_t) client_rows[i] * k;
+	}
+	rc = ensure(&h->d_C, &h->cap_C, (size_t) h->m * k + relay);        // own rows, then the clients' rows behind them
+	if (rc) return rc;
+	if (!h->s_up) CU_TRY(cudaStreamCreateWithFlags(&h->s_up, cudaStreamNonBlocking));
+	if (!h->s_down) CU_TRY(cudaStreamCreateWithFlags(&h->s_down, cudaStreamNonBlocking));
+	while (h->ev_slice.size() < (size_t) 3 + nclients) {
+		cudaEvent_t e;
+		CU_TRY(cudaEventCreate(&e));
+		h->ev_slice.push_back(e);
+	}
+	h->resident_k = 0;
+	int64_t lo, n;
+	b_window(h, lo, n);
+	rc = upload_b_rows(h, x_host, k, 0, k, lo, n, h->d_B, h->s_up);
+	if (rc) return rc;
+	CU_TRY(cudaEventRecord(h->ev_slice[0], h->s_up));
+	CU_TRY(cudaStreamWaitEvent(h->stream, h->ev_slice[0], 0));
+	CU_TRY(cudaEventRecord(h->ev_slice[1], h->stream));
+	if (h->m > 0) {
+		const int nl = launch_spmm(h, h->d_B, h->d_C, k, h->stream);
+		if (nl < 0) return nl;
+	}
+	CU_TRY(cudaEventRecord(h->ev_slice[2], h->stream));
+	h->c_slices = 1; h->timed = true; h->timed_slices = 1;
+	if (!download) {
+		if (h->m > 0 && xfer(xfer_ctx, h->d_C, (size_t) h->m * k, downloader_rank, 1, h->stream)) return SPMM_B200_ECOMM;
+		CU_TRY(cudaStreamSynchronize(h->stream));
+		return SPMM_B200_OK;
+	}
+	CU_TRY(cudaStreamWaitEvent(h->s_down, h->ev_slice[2], 0));
+	if (h->m > 0) {
+		CU_TRY(cudaMemcpyAsync(y_all + (size_t) h->first_row * k, h->d_C, sizeof(double) * h->m * k, cudaMemcpyDeviceToHost, h->s_down));
+		h->last_d2h_bytes += (int64_t) sizeof(double) * h->m * k;
+	}
+	double* dst = h->d_C + (size_t) h->m * k;
+	for (int i = 0; i < nclients; i++) {
+		const size_t cnt = (size_t) client_rows[i] * k;
+		if (cnt == 0) continue;
+		if (xfer(xfer_ctx, dst, cnt, client_ranks[i], 0, h->stream)) return SPMM_B200_ECOMM;
+		CU_TRY(cudaEventRecord(h->ev_slice[3 + i], h->stream));
+		CU_TRY(cudaStreamWaitEvent(h->s_down, h->ev_slice[3 + i], 0));
+		CU_TRY(cudaMemcpyAsync(y_all + (size_t) client_first_row[i] * k, dst, sizeof(double) * cnt, cudaMemcpyDeviceToHost, h->s_down));
+		h->last_d2h_bytes += (int64_t) (sizeof(double) * cnt);
+		dst += cnt;
+	}
+	CU_TRY(cudaStreamSynchronize(h->stream));
+	CU_TRY(cudaStreamSynchronize(h->s_down));
+	return SPMM_B200_OK;
+}
+
 // ------------------------------------------------------------------------------------------
 // partitioning (device search, host pointers in and out)
 // ------------------------------------------------------------------------------------------

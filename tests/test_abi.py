@@ -135,6 +135,7 @@ def test_argument_validation_round2_entry_points(pkg):
     assert lib.spmm_b200_last_transfer_bytes(None, None, None) == -1
     assert lib.spmm_b200_col_window(None, None, None) == -1
     assert lib.spmm_b200_multi_routes(None, None, 0) == -1
+    assert lib.spmm_b200_run_routed(None, None, None, 4, 0, 0, None, None, None, 0, C.cast(None, pkg.XFER_FN), None) == -1
     # the allocation-free entry point checks arguments and the scratch bound before it touches a device
     fake = C.c_void_p(4096)
     assert lib.spmm_b200_spmm_merge_noalloc(None, fake, fake, 10, 10, 10, fake, fake, 32, None) == -1

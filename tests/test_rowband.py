@@ -329,3 +329,49 @@ def test_multi_gpu_download_routes(pkg, L, ngpus, variant):
             assert sorted(set(route)) == sorted(r for r in set(route) if route[r] == r)      # every downloader carries itself
             assert (ngpus < 4) == (max(probe) == 0.0)
     mf.close()
+
+
+def test_routed_downloads_between_shard_handles(pkg, L):
+    """spmm_b200_run_routed, the one-process-per-GPU form of download routing, exercised inside one process: three shard
+    handles on one device play ranks 0..2, rank 1 downloads for ranks 0 and 2, the transfer callback is a device copy.
+    The shared y must equal the oracle's whole result."""
+    import torch
+    m, c, k = 9000, 12000, 32
+    ia, ja, a = banded_csr(m, 1000, 16.0, 90, seed=81)
+    ja = (ja + 4000).astype(np.int32)
+    x = dense_b(c, k, 14)
+    y_ref = L.spmm_oracle(ia, ja, a, m, c, x, k)
+    shards = [pkg.csr_to_format(ia, ja, a, m, c, len(ja), k, variant=pkg.ROWSPLIT, rank=r, nranks=3) for r in range(3)]
+    y_all = torch.full((m * k,), float("nan"), dtype=torch.float64).pin_memory()
+    sent = {}                                   # rank -> tensor: what a client "sent"
+
+    class _Dev:
+        def __init__(self, ptr, count):
+            self.__cuda_array_interface__ = {"shape": (int(count),), "typestr": "<f8", "data": (int(ptr), False), "version": 3}
+
+    def make_xfer(rank):
+        def xfer(ptr, count, peer, is_send, stream):
+            with torch.cuda.stream(torch.cuda.ExternalStream(stream)):
+                if is_send:
+                    sent[rank] = torch.as_tensor(_Dev(ptr, count), device="cuda").clone()     # the message in flight
+                else:
+                    torch.cuda.current_stream().wait_stream(torch.cuda.default_stream())
+                    torch.as_tensor(_Dev(ptr, count), device="cuda").copy_(sent.pop(peer))
+        return xfer
+
+    # clients first (their sends complete into `sent`), then the downloader
+    for r in (0, 2):
+        shards[r].spmm_routed(x, y_all.numpy(), k, r, 1, [], make_xfer(r))
+    torch.cuda.synchronize()
+    clients = [(r, shards[r].first_row, shards[r].m) for r in (0, 2)]
+    shards[1].spmm_routed(x, y_all.numpy(), k, 1, 1, clients, make_xfer(1))
+    torch.cuda.synchronize()
+    assert max_rel_err(y_all.numpy(), y_ref) <= FP64_TOL
+    assert shards[0].last_transfer_bytes()[1] == 0 and shards[1].last_transfer_bytes()[1] == m * k * 8
+    # a downloader without clients is the plain call
+    y2 = torch.full((m * k,), float("nan"), dtype=torch.float64).pin_memory()
+    for r in range(3):
+        shards[r].spmm_routed(x, y2.numpy(), k, r, r, [], None)
+    assert np.array_equal(y2.numpy(), y_all.numpy())
+    for s in shards:
+        s.close()
