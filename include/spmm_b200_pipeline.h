@@ -110,6 +110,9 @@ int spmm_b200_pipeline_spmm_f32(spmm_b200_pipeline_f32_t *p, char type, int64_t 
                                 const int32_t *ia, const int32_t *ja, const float *a,
                                 const float *x_host, float *y_host);
 int spmm_b200_pipeline_sddmm_f32(spmm_b200_pipeline_f32_t *p, float *y_host, int mode);
+/* softmax of y in place, fp32 (running sums in double): rowwise != 0 = per mask row, 0 = over all nonzeros (the
+ * reference's commented-out host softmax(y)); y_host (optional) receives the nnz values */
+int spmm_b200_pipeline_softmax_f32(spmm_b200_pipeline_f32_t *p, float *y_host, int rowwise);
 int spmm_b200_pipeline_final_f32(spmm_b200_pipeline_f32_t *p, float *y_final_host);
 int64_t spmm_b200_pipeline_launch_count_f32(const spmm_b200_pipeline_f32_t *p);
 void    spmm_b200_pipeline_destroy_f32(spmm_b200_pipeline_f32_t *p);

@@ -50,7 +50,7 @@ EXPORTS = [
     "spmm_b200_pipeline_device_ptr", "spmm_b200_pipeline_last_kernel_ms", "spmm_b200_pipeline_launch_count",
     "spmm_b200_pipeline_destroy", "spmm_b200_pipeline_invalidate", "spmm_b200_pipeline_set_option",
     "spmm_b200_pipeline_create_f32", "spmm_b200_pipeline_spmm_f32", "spmm_b200_pipeline_sddmm_f32",
-    "spmm_b200_pipeline_final_f32", "spmm_b200_pipeline_launch_count_f32", "spmm_b200_pipeline_destroy_f32",
+    "spmm_b200_pipeline_softmax_f32", "spmm_b200_pipeline_final_f32", "spmm_b200_pipeline_launch_count_f32", "spmm_b200_pipeline_destroy_f32",
 ]
 
 _lib = None
@@ -164,6 +164,7 @@ def load_library():
     lib.spmm_b200_pipeline_spmm_f32.argtypes = lib.spmm_b200_pipeline_spmm.argtypes
     lib.spmm_b200_pipeline_sddmm_f32.argtypes = [_vp, _vp, _int]
     lib.spmm_b200_pipeline_final_f32.argtypes = [_vp, _vp]
+    lib.spmm_b200_pipeline_softmax_f32.argtypes = [_vp, _vp, _int]
     lib.spmm_b200_pipeline_launch_count_f32.argtypes = [_vp]; lib.spmm_b200_pipeline_launch_count_f32.restype = _i64
     lib.spmm_b200_pipeline_destroy_f32.argtypes = [_vp]; lib.spmm_b200_pipeline_destroy_f32.restype = None
     _lib = lib
@@ -537,6 +538,13 @@ class PipelineFormatF32:
             raise ValueError("y holds fewer than nnz values")
         _check(load_library().spmm_b200_pipeline_sddmm_f32(self._h, None if y is None else _host(y, np.float32, "y"), mode),
                "spmm_b200_pipeline_sddmm_f32")
+
+    def softmax(self, y=None, rowwise=True):
+        """softmax of y in place on the device (fp32, sums in double); rowwise=False: over all nonzeros at once."""
+        if y is not None and y.size < self.nnz:
+            raise ValueError("y holds fewer than nnz values")
+        _check(load_library().spmm_b200_pipeline_softmax_f32(self._h, None if y is None else _host(y, np.float32, "y"), 1 if rowwise else 0),
+               "spmm_b200_pipeline_softmax_f32")
 
     def final(self, y_final):
         if y_final.size < self.m * self.n:

@@ -514,4 +514,64 @@ softmax_rows_kernel(const int32_t* __restrict__ ia, double* __restrict__ y, int6
 	}
 }
 
+// ---- fp32 softmax (the "_f" pipeline): y in float, running sums in double so that a global sum over 10^7 entries keeps
+// its digits; exp in fp32 (expf), like an "_f" build of the reference's commented-out host softmax would compute it.
+template <int THREADS>
+__global__ void __launch_bounds__(THREADS)
+softmax_max_f32_kernel(const float* __restrict__ y, int64_t n, double* __restrict__ part)
+{
+	double v = -DBL_MAX;
+	for (int64_t i = (int64_t) blockIdx.x * THREADS + threadIdx.x; i < n; i += (int64_t) gridDim.x * THREADS) v = fmax(v, (double) y[i]);
+	v = block_reduce<THREADS, true>(v);
+	if (threadIdx.x == 0) part[blockIdx.x] = v;
+}
+
+template <int THREADS>
+__global__ void __launch_bounds__(THREADS)
+softmax_exp_f32_kernel(float* __restrict__ y, int64_t n, const double* __restrict__ maxv, double* __restrict__ part)
+{
+	const float mx = (float) *maxv;
+	double s = 0.0;
+	for (int64_t i = (int64_t) blockIdx.x * THREADS + threadIdx.x; i < n; i += (int64_t) gridDim.x * THREADS) {
+		const float e = expf(y[i] - mx);
+		y[i] = e;
+		s += (double) e;
+	}
+	s = block_reduce<THREADS, false>(s);
+	if (threadIdx.x == 0) part[blockIdx.x] = s;
+}
+
+template <int THREADS>
+__global__ void __launch_bounds__(THREADS)
+softmax_scale_f32_kernel(float* __restrict__ y, int64_t n, const double* __restrict__ sum)
+{
+	const float s = (float) *sum;
+	for (int64_t i = (int64_t) blockIdx.x * THREADS + threadIdx.x; i < n; i += (int64_t) gridDim.x * THREADS) y[i] = y[i] / s;
+}
+
+template <int THREADS>
+__global__ void __launch_bounds__(THREADS)
+softmax_rows_f32_kernel(const int32_t* __restrict__ ia, float* __restrict__ y, int64_t m)
+{
+	constexpr int NW = THREADS / 32;
+	const int lane = threadIdx.x & 31;
+	for (int64_t row = (int64_t) blockIdx.x * NW + (threadIdx.x >> 5); row < m; row += (int64_t) gridDim.x * NW) {
+		const int js = ia[row], je = ia[row + 1];
+		if (js == je) continue;
+		float mx = -FLT_MAX;
+		for (int p = js + lane; p < je; p += 32) mx = fmaxf(mx, y[p]);
+		#pragma unroll
+		for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+		float s = 0.f;
+		for (int p = js + lane; p < je; p += 32) {
+			const float e = expf(y[p] - mx);
+			y[p] = e;
+			s += e;
+		}
+		#pragma unroll
+		for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+		for (int p = js + lane; p < je; p += 32) y[p] = y[p] / s;
+	}
+}
+
 } // namespace sb200

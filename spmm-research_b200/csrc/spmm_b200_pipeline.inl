@@ -505,6 +505,7 @@ struct spmm_b200_pipeline_f32 {
 	float* d_x = nullptr; size_t cap_x = 0;
 	float* d_tmp = nullptr; size_t cap_tmp = 0;
 	float* d_final = nullptr;
+	double* d_part = nullptr;                // partials of the global softmax (allocated on first use)
 	bool have_y = false;
 	cudaStream_t stream = nullptr;
 	int64_t own_launches = 0;
@@ -515,6 +516,7 @@ extern "C" void spmm_b200_pipeline_destroy_f32(spmm_b200_pipeline_f32_t* p)
 	if (!p) return;
 	cudaSetDevice(p->device);
 	if (p->stream) cudaStreamSynchronize(p->stream);
+	if (p->d_part) cudaFree(p->d_part);
 	if (p->mask) spmm_b200_destroy_f32(p->mask);
 	for (auto& w : p->w) {
 		if (w.h) spmm_b200_destroy_f32(w.h);
@@ -633,6 +635,36 @@ extern "C" int spmm_b200_pipeline_sddmm_f32(spmm_b200_pipeline_f32_t* p, float* 
 	}
 	p->have_y = true;
 	if (y_host && p->nnz > 0) CU_TRY(cudaMemcpyAsync(y_host, p->mask->d_a, sizeof(float) * p->nnz, cudaMemcpyDeviceToHost, p->stream));
+	CU_TRY(cudaStreamSynchronize(p->stream));
+	return SPMM_B200_OK;
+}
+
+// softmax over the mask's nonzeros in place (y lives in the mask handle's value array): rowwise != 0 = per mask row (what
+// attention uses), 0 = over all nonzeros at once (the reference's commented-out host softmax(y), sddmm_bench.cpp)
+extern "C" int spmm_b200_pipeline_softmax_f32(spmm_b200_pipeline_f32_t* p, float* y_host, int rowwise)
+{
+	if (!p || !p->have_y) return SPMM_B200_EINVAL;
+	CU_TRY(cudaSetDevice(p->device));
+	if (p->nnz > 0) {
+		float* y = p->mask->d_a;
+		if (rowwise) {
+			const int grid = (int) std::min<int64_t>((p->m + THREADS / 32 - 1) / (THREADS / 32), (int64_t) p->mask->sm_count * 64);
+			sb200::softmax_rows_f32_kernel<THREADS><<<grid, THREADS, 0, p->stream>>>(p->mask->d_ia, y, p->m);
+			p->own_launches += 1;
+		} else {
+			if (!p->d_part) CU_TRY(cudaMalloc(&p->d_part, sizeof(double) * (PIPE_PARTS + 2)));
+			const int grid = (int) std::min<int64_t>((p->nnz + THREADS - 1) / THREADS, PIPE_PARTS);
+			sb200::softmax_max_f32_kernel<THREADS><<<grid, THREADS, 0, p->stream>>>(y, p->nnz, p->d_part);
+			sb200::softmax_combine_kernel<THREADS, true><<<1, THREADS, 0, p->stream>>>(p->d_part, grid);
+			CU_TRY(cudaMemcpyAsync(p->d_part + PIPE_PARTS + 1, p->d_part + grid, sizeof(double), cudaMemcpyDeviceToDevice, p->stream));
+			sb200::softmax_exp_f32_kernel<THREADS><<<grid, THREADS, 0, p->stream>>>(y, p->nnz, p->d_part + PIPE_PARTS + 1, p->d_part);
+			sb200::softmax_combine_kernel<THREADS, false><<<1, THREADS, 0, p->stream>>>(p->d_part, grid);
+			sb200::softmax_scale_f32_kernel<THREADS><<<grid, THREADS, 0, p->stream>>>(y, p->nnz, p->d_part + grid);
+			p->own_launches += 5;
+		}
+		CU_TRY(cudaGetLastError());
+		if (y_host) CU_TRY(cudaMemcpyAsync(y_host, y, sizeof(float) * p->nnz, cudaMemcpyDeviceToHost, p->stream));
+	}
 	CU_TRY(cudaStreamSynchronize(p->stream));
 	return SPMM_B200_OK;
 }

@@ -93,6 +93,7 @@ def test_argument_validation(pkg):
     assert lib.spmm_b200_pipeline_create_f32(C.byref(h), rp, ci, af.ctypes.data, 10, 2 ** 31, 8, 0) == -5
     assert lib.spmm_b200_pipeline_sddmm_f32(None, None, 0) == -1
     assert lib.spmm_b200_pipeline_final_f32(None, None) == -1
+    assert lib.spmm_b200_pipeline_softmax_f32(None, None, 1) == -1
     assert lib.spmm_b200_pipeline_launch_count_f32(None) == 0
     lib.spmm_b200_pipeline_destroy_f32(None)
 

@@ -114,6 +114,47 @@ def test_gpu_pipeline_f32_errors(pkg):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("rowwise", [True, False])
+def test_gpu_pipeline_f32_softmax(pkg, L, rowwise):
+    """fp32 softmax of y on the device (row-wise = what attention uses; global = the reference's commented-out host
+    softmax(y)), against a float64 softmax of the GPU's own y, then the final product on the normalised y."""
+    n, kdim = 32, 220
+    mask, W, x = f32_case(77, 600, kdim, n, 9, 0.08, "random")
+    mia, mja, ma, m = mask
+    MF = pkg.csr_to_pipeline_format_f32(mia, mja, ma, m, len(mja), n)
+    with pytest.raises(pkg.SpmmB200Error):
+        MF.softmax()                                         # no y yet
+    V = np.full(m * n, np.nan, np.float32)
+    for t, out in (("K", None), ("Q", None), ("V", V)):
+        MF.spmm(t, m, kdim, n, *W[t], x, out)
+    y = np.full(len(mja), np.nan, np.float32)
+    MF.sddmm(y, 1)
+    y = (y * np.float32(0.05)).astype(np.float32)            # keep exp() away from a one-hot result
+    MF.spmm("final", m, m, n, mia, mja, y, V, np.empty(m * n, np.float32))      # puts the scaled y on the device
+    p = np.full(len(mja), np.nan, np.float32)
+    MF.softmax(p, rowwise=rowwise)
+    y64 = y.astype(np.float64)
+    ref = np.empty_like(y64)
+    if rowwise:
+        for i in range(m):
+            seg = y64[mia[i]:mia[i + 1]]
+            if seg.size:
+                e = np.exp(seg - seg.max()); ref[mia[i]:mia[i + 1]] = e / e.sum()
+        sums = np.add.reduceat(p.astype(np.float64), mia[:-1][np.diff(mia) > 0])
+        assert np.allclose(sums, 1.0, atol=1e-5)
+    else:
+        e = np.exp(y64 - y64.max()); ref = e / e.sum()
+        assert abs(float(p.astype(np.float64).sum()) - 1.0) <= 1e-5
+    assert float(np.abs(p - ref).max()) <= 4e-6 * float(ref.max())
+    yf = np.full(m * n, np.nan, np.float32)
+    MF.final(yf)
+    import scipy.sparse as sp
+    want = sp.csr_matrix((p.astype(np.float64), mja, mia), shape=(m, m)) @ V.astype(np.float64).reshape(m, n)
+    close32(yf.reshape(m, n), want, "final after softmax")
+    MF.close()
+
+
+@pytest.mark.gpu
 def test_gpu_reference_pipeline_harness_f_build(tmp_path):
     """The unchanged pipeline harness compiled with the reference's float defines + our plug-in TU."""
     from test_pipeline import run_pipeline_harness, harness_mask_nnz
