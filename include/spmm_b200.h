@@ -294,6 +294,7 @@ int spmm_b200_run_device_f32(spmm_b200_f32_t *h, const float *b_dev, float *c_de
 int spmm_b200_fetch_c_f32(spmm_b200_f32_t *h, float *y_host, int k);
 int     spmm_b200_variant_f32(const spmm_b200_f32_t *h);      /* the variant the handle resolved to */
 int     spmm_b200_set_option_f32(spmm_b200_f32_t *h, const char *name, int value);
+int64_t spmm_b200_last_h2d_bytes_f32(const spmm_b200_f32_t *h); /* bytes of B the last spmm_b200_run_f32 uploaded: the rows between the first and the last touched column (all of B for the TF32 variant or with UPLOAD_WINDOW=0) */
 int64_t spmm_b200_rows_f32(const spmm_b200_f32_t *h);
 int64_t spmm_b200_nnz_f32(const spmm_b200_f32_t *h);
 int64_t spmm_b200_launch_count_f32(const spmm_b200_f32_t *h);

@@ -41,7 +41,7 @@ EXPORTS = [
     "spmm_b200_variant", "spmm_b200_bcsr_blocks", "spmm_b200_kslice", "spmm_b200_last_rowband", "spmm_b200_last_transfer_bytes", "spmm_b200_col_window", "spmm_b200_last_kernel_ms", "spmm_b200_launch_count", "spmm_b200_stats",
     "spmm_b200_stats_labels", "spmm_b200_destroy", "spmm_b200_strerror", "spmm_b200_last_cuda_error",
     "spmm_b200_create_f32", "spmm_b200_create_shard_f32", "spmm_b200_run_f32", "spmm_b200_run_device_f32",
-    "spmm_b200_fetch_c_f32", "spmm_b200_variant_f32", "spmm_b200_set_option_f32", "spmm_b200_rows_f32", "spmm_b200_nnz_f32", "spmm_b200_launch_count_f32",
+    "spmm_b200_fetch_c_f32", "spmm_b200_variant_f32", "spmm_b200_set_option_f32", "spmm_b200_last_h2d_bytes_f32", "spmm_b200_rows_f32", "spmm_b200_nnz_f32", "spmm_b200_launch_count_f32",
     "spmm_b200_last_kernel_ms_f32", "spmm_b200_destroy_f32",
     "spmm_b200_device_count", "spmm_b200_read_mtx", "spmm_b200_read_smtx", "spmm_b200_free", "spmm_b200_check_accuracy",
     # include/spmm_b200_pipeline.h
@@ -164,6 +164,7 @@ def load_library():
     lib.spmm_b200_pipeline_spmm_f32.argtypes = lib.spmm_b200_pipeline_spmm.argtypes
     lib.spmm_b200_pipeline_sddmm_f32.argtypes = [_vp, _vp, _int]
     lib.spmm_b200_pipeline_final_f32.argtypes = [_vp, _vp]
+    lib.spmm_b200_last_h2d_bytes_f32.argtypes = [_vp]; lib.spmm_b200_last_h2d_bytes_f32.restype = _i64
     lib.spmm_b200_pipeline_softmax_f32.argtypes = [_vp, _vp, _int]
     lib.spmm_b200_pipeline_launch_count_f32.argtypes = [_vp]; lib.spmm_b200_pipeline_launch_count_f32.restype = _i64
     lib.spmm_b200_pipeline_destroy_f32.argtypes = [_vp]; lib.spmm_b200_pipeline_destroy_f32.restype = None
@@ -384,6 +385,10 @@ class MatrixFormatF32:
             raise ValueError(f"y holds {y.size} values, expected m*k = {self.m * k}")
         _check(load_library().spmm_b200_run_f32(self._h, _host(x, np.float32, "x"), _host(y, np.float32, "y") if copy_back else None,
                                                 k, 1 if copy_back else 0), "spmm(f32)")
+
+    def last_h2d_bytes(self):
+        """Bytes of B the last host-buffer spmm() uploaded (rows between the first and the last touched column)."""
+        return int(load_library().spmm_b200_last_h2d_bytes_f32(self._h))
 
     def spmm_device(self, b_ptr, c_ptr, k, stream=0):
         _check(load_library().spmm_b200_run_device_f32(self._h, b_ptr, c_ptr, int(k), stream or None), "spmm_device(f32)")

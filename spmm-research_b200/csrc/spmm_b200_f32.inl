@@ -21,6 +21,8 @@ struct spmm_b200_f32 {
 	Tf32Plan tf32;
 	uint32_t smem_attr = 0;
 	int64_t m = 0, c = 0, nnz = 0, first_row = 0;
+	int64_t col_min = 0, col_span = 0;       // first touched column, last - first + 1 (window upload of spmm_b200_run_f32)
+	int64_t last_h2d_bytes = 0;
 	int32_t* d_ia = nullptr;
 	int32_t* d_ja = nullptr;
 	float* d_a = nullptr;
@@ -267,6 +269,20 @@ static int create_slice(spmm_b200_f32** out, const int32_t* ia_slice, const int3
 		CU_TRY(cudaStreamSynchronize(h->stream));
 		cudaFree(d_max);
 	}
+	if (nnz > 0) {
+		// touched window of B, as in the fp64 handle (create_from_slice)
+		int* d_mm = nullptr;
+		int mm[2] = {INT32_MAX, -1};
+		CU_TRY(cudaMalloc(&d_mm, 2 * sizeof(int)));
+		CU_TRY(cudaMemcpyAsync(d_mm, mm, sizeof(mm), cudaMemcpyHostToDevice, h->stream));
+		col_span_kernel<<<(unsigned) std::min<int64_t>((int64_t) h->sm_count * 8, (nnz + 255) / 256), 256, 0, h->stream>>>(h->d_ja, nnz, d_mm, d_mm + 1);
+		h->launches++;
+		CU_TRY(cudaMemcpyAsync(mm, d_mm, sizeof(mm), cudaMemcpyDeviceToHost, h->stream));
+		CU_TRY(cudaStreamSynchronize(h->stream));
+		cudaFree(d_mm);
+		h->col_span = mm[1] >= mm[0] ? (int64_t) mm[1] - mm[0] + 1 : 0;
+		h->col_min = mm[1] >= mm[0] ? mm[0] : 0;
+	}
 	if (variant == SPMM_B200_AUTO) {
 		// the fp64 rule (create_from_slice): merge-path when one row is far longer than the mean.  AUTO never picks the
 		// TF32 blocked kernel: it rounds A and B to 10 mantissa bits, which the caller has to ask for.
@@ -426,17 +442,32 @@ extern "C" int spmm_b200_run_f32(spmm_b200_f32_t* h, const float* x_host, float*
 	if (rc) return rc;
 	rc = ensure32(&h->d_C, &h->cap_C, (size_t) h->m * k);
 	if (rc) return rc;
-	if (h->b_layout == SPMM_B200_B_ROWMAJOR || k == 1) {
-		CU_TRY(cudaMemcpyAsync(h->d_B, x_host, nb * sizeof(float), cudaMemcpyHostToDevice, h->stream));
-	} else {
-		rc = ensure32(&h->d_x, &h->cap_x, nb);
-		if (rc) return rc;
-		CU_TRY(cudaMemcpyAsync(h->d_x, x_host, nb * sizeof(float), cudaMemcpyHostToDevice, h->stream));
-		if (h->c > 0) {
-			dim3 grid((unsigned) ((h->c + 31) / 32), (unsigned) ((k + 31) / 32)), block(32, 8);
-			transpose_b_f32_kernel<<<grid, block, 0, h->stream>>>(h->d_x, h->d_B, h->c, k);
+	// Only the rows of B between the first and the last touched column travel (a row no nonzero references cannot change
+	// C; the fp64 twin is upload_b_rows).  The TF32 blocked kernel reads whole 32-row chunks of B, zeros
+	// of A included, so it keeps the full upload.
+	int64_t lo = 0, n = h->c;
+	if (h->opt.upload_window && h->variant != SPMM_B200_BCSR) {
+		if (h->nnz == 0 || h->col_span <= 0) n = 0;
+		else { lo = h->col_min; n = std::min<int64_t>(h->col_span, h->c - lo); }
+	}
+	h->last_h2d_bytes = 0;
+	if (n > 0) {
+		if (h->b_layout == SPMM_B200_B_ROWMAJOR || k == 1) {
+			CU_TRY(cudaMemcpyAsync(h->d_B + lo * k, x_host + lo * k, sizeof(float) * n * k, cudaMemcpyHostToDevice, h->stream));
+		} else {
+			rc = ensure32(&h->d_x, &h->cap_x, nb);
+			if (rc) return rc;
+			if (n == h->c)
+				CU_TRY(cudaMemcpyAsync(h->d_x, x_host, nb * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+			else
+				CU_TRY(cudaMemcpy2DAsync(h->d_x + lo, sizeof(float) * h->c, x_host + lo, sizeof(float) * h->c, sizeof(float) * n, (size_t) k,
+				                         cudaMemcpyHostToDevice, h->stream));
+			dim3 grid((unsigned) ((n + 31) / 32), (unsigned) ((k + 31) / 32)), block(32, 8);
+			transpose_b_rows_f32_kernel<<<grid, block, 0, h->stream>>>(h->d_x + lo, h->d_B + lo * k, h->c, n, k);
+			CU_TRY(cudaGetLastError());
 			h->launches++;
 		}
+		h->last_h2d_bytes = (int64_t) sizeof(float) * n * k;
 	}
 	rc = spmm_b200_run_device_f32(h, h->d_B, h->d_C, k, h->stream);
 	if (rc) return rc;
@@ -457,6 +488,7 @@ extern "C" int spmm_b200_fetch_c_f32(spmm_b200_f32_t* h, float* y_host, int k)
 
 extern "C" int64_t spmm_b200_rows_f32(const spmm_b200_f32_t* h) { return h ? h->m : -1; }
 extern "C" int spmm_b200_variant_f32(const spmm_b200_f32_t* h) { return h ? h->variant : SPMM_B200_EINVAL; }
+extern "C" int64_t spmm_b200_last_h2d_bytes_f32(const spmm_b200_f32_t* h) { return h ? h->last_h2d_bytes : -1; }
 
 extern "C" int spmm_b200_set_option_f32(spmm_b200_f32_t* h, const char* name, int value)
 {

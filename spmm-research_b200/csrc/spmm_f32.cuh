@@ -144,4 +144,24 @@ __global__ void transpose_b_f32_kernel(const float* __restrict__ x, float* __res
 	}
 }
 
+// The same for `rows` consecutive rows of B out of a column-major operand whose columns are `pitch` elements apart
+// (window upload of spmm_b200_run_f32): x[n*pitch + j] -> B[j*k + n], j < rows.
+__global__ void transpose_b_rows_f32_kernel(const float* __restrict__ x, float* __restrict__ B, int64_t pitch, int64_t rows, int k)
+{
+	__shared__ float tile[32][33];
+	const int64_t j0 = (int64_t) blockIdx.x * 32;
+	const int n0 = blockIdx.y * 32;
+	for (int dy = threadIdx.y; dy < 32; dy += blockDim.y) {
+		const int n = n0 + dy;
+		const int64_t j = j0 + threadIdx.x;
+		if (n < k && j < rows) tile[dy][threadIdx.x] = x[(int64_t) n * pitch + j];
+	}
+	__syncthreads();
+	for (int dy = threadIdx.y; dy < 32; dy += blockDim.y) {
+		const int64_t j = j0 + dy;
+		const int n = n0 + threadIdx.x;
+		if (n < k && j < rows) B[j * k + n] = tile[threadIdx.x][dy];
+	}
+}
+
 } // namespace sb200

@@ -194,3 +194,36 @@ def test_gpu_tf32_blocked_kernel(pkg, L, k):
     y = np.full(300 * 16, np.nan, np.float32); mf.spmm(x, y, 16); mf.close()
     assert rel_err(y, L.spmm_oracle_f32(ia, ja, a, 300, 300, x, 16).astype(np.float64)) <= F32_TOL
     assert pkg.csr_to_format_f32(ia, ja, a, 300, 300, len(ja), 32).format_name == "B200_CSR_ROWSPLIT_F32"
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("variant,k,layout", [("ROWSPLIT", 32, "col"), ("ROWSPLIT", 20, "col"), ("ROWSPLIT", 1, "col"), ("ROWSPLIT", 64, "row"),
+                                              ("MERGE", 32, "col"), ("MERGE", 8, "row"), ("BCSR", 32, "col")])
+def test_gpu_f32_upload_window(pkg, L, variant, k, layout):
+    """The fp32 host call uploads only rows [first, last touched column] of B (the fp64 rule): what lies
+    outside may be NaN; the device copy is poisoned with an all-NaN operand first so that a read outside the window
+    shows.  The TF32 blocked kernel reads whole chunks of B and keeps the full upload."""
+    m, c = 3000, 9000
+    lo = 4100
+    ia, ja, a, _ = case(m, 700, 11.0, 300 + k, k, long_row=600 if variant == "MERGE" else 0)
+    ja = (ja + lo).astype(np.int32)
+    x = np.random.default_rng(5).random(c * k, dtype=np.float32)
+    y_ref = L.spmm_oracle_f32(ia, ja, a, m, c, x, k).astype(np.float64)
+    span = int(ja.max()) - int(ja.min()) + 1
+    full = variant == "BCSR"
+    xp = x.reshape(k, c).copy()
+    if not full:
+        xp[:, :int(ja.min())] = np.nan; xp[:, int(ja.max()) + 1:] = np.nan
+    xp = (np.ascontiguousarray(xp.T) if layout == "row" else xp).ravel()
+    mf = pkg.csr_to_format_f32(ia, ja, a, m, c, len(ja), k, variant=getattr(pkg, variant),
+                               b_layout=pkg.B_ROWMAJOR if layout == "row" else pkg.B_COLMAJOR)
+    mf.set_option("UPLOAD_WINDOW", 0)
+    mf.spmm(np.full(c * k, np.nan, np.float32), np.empty(m * k, np.float32), k)       # poison d_B / d_x
+    assert mf.last_h2d_bytes() == c * k * 4
+    mf.set_option("UPLOAD_WINDOW", 1)
+    for _ in range(2):
+        y = np.full(m * k, np.nan, np.float32); mf.spmm(xp, y, k)
+        assert np.isfinite(y).all(), (variant, k)
+        assert rel_err(y, y_ref) <= (2e-3 if full else F32_TOL), (variant, k)
+        assert mf.last_h2d_bytes() == (c if full else span) * k * 4
+    mf.close()
